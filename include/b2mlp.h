@@ -1,0 +1,141 @@
+/*
+ * b2mlp.h -- C ABI of the B200-native training-step library (libb2mlp.so).
+ *
+ * This is the drop-in boundary for the ONE hot path of manigoswami/tensorflow-examples:
+ * the `sess.run(train_op, feed_dict)` call inside the Python training loops of
+ *   simple/simple.py:34-35,37          (scalar linear regression, sum-of-squares loss)
+ *   distributed/distributed.py:145-150 (784-100-10 sigmoid MLP, softmax cross-entropy)
+ * and, for the distributed form, the parameter-server pull/push that
+ * `replica_device_setter` (distributed/distributed.py:63-65) implies, which is
+ * replaced here by a synchronous gradient all-reduce before the SGD apply.
+ *
+ * The reference has no FFI of its own (it is pure Python on top of TensorFlow 1.x);
+ * each entry point below cites the reference lines whose work it takes over.
+ * Plain pointers and sizes only: no torch, no C++ types.  Every function that can
+ * fail returns an int: 0 = ok, non-zero = error class (B2_ERR_*); the message is
+ * available from b2_last_error() on the calling thread.  No C++ exception crosses
+ * this boundary.  There is NO CPU fallback: without a CUDA device every compute
+ * entry point fails with B2_ERR_CUDA.
+ *
+ * Memory layouts (all row-major, all float32 unless stated):
+ *   x pool   [pool_rows, dims[0]]        distributed.py:77  placeholder x  [None,784]
+ *   y pool   [pool_rows, dims[n_layers]] distributed.py:80  placeholder y_ [None,10] (one-hot or soft)
+ *   W[l]     [dims[l], dims[l+1]]        distributed.py:85-86 ([in,out], as tf.matmul(x, W) wants)
+ *   b[l]     [dims[l+1]]                 distributed.py:90-91
+ * Threading: one context per GPU, used from one host thread at a time.
+ */
+#ifndef B2MLP_H_
+#define B2MLP_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b2_ctx b2_ctx;          /* opaque */
+typedef void* b2_stream_t;             /* a cudaStream_t (0 = legacy default stream) */
+
+enum {
+  B2_OK = 0,
+  B2_ERR_ARG = 1,        /* bad argument / unsupported configuration */
+  B2_ERR_CUDA = 2,       /* CUDA runtime error (no device, launch failure, OOM ...) */
+  B2_ERR_NCCL = 3,       /* NCCL error or NCCL library not found */
+  B2_ERR_STATE = 4       /* call not valid in the context's current state */
+};
+
+enum { B2_ACT_IDENTITY = 0, B2_ACT_SIGMOID = 1 };          /* simple.py:16 / distributed.py:97 */
+enum { B2_LOSS_SSE_SUM = 0, B2_LOSS_SOFTMAX_CE_MEAN = 1 }; /* simple.py:20 / distributed.py:99-102 */
+enum { B2_PREC_FP32 = 0, B2_PREC_BF16_FP32ACC = 1 };       /* BASELINE.json configs[4] uses 1 */
+
+/* Engine selection knobs for b2_set_option (tests cross-check the paths against each other). */
+enum {
+  B2_OPT_FORCE_LAYERED = 1   /* value 1: never use the single-kernel fused step, even when the shape allows it */
+};
+
+#define B2_UNIQUE_ID_BYTES 128
+
+/* Library / build information: "b2mlp <version> sm_100a ..." (static string). */
+const char* b2_version(void);
+
+/* Message of the last failing call made by this thread (static thread-local buffer). */
+const char* b2_last_error(void);
+
+/*
+ * Builds the model + optimizer state on one GPU: parameters, gradient buffer, activations and
+ * scratch are allocated here, once.  Replaces graph construction + variable creation
+ * (simple.py:11-23; distributed.py:68-108) and tf.Session()/Supervisor set-up
+ * (simple.py:28-32; distributed.py:129-135).  Parameters start at zero; load them with
+ * b2_params_set().  n_layers = number of dense layers, dims has n_layers+1 entries.
+ * `act` applies to every layer but the last.  max_local_batch bounds the rows per step on this GPU.
+ */
+int b2_create(b2_ctx** out, int device, int n_layers, const int* dims, int act, int loss,
+              int precision, int max_local_batch);
+void b2_destroy(b2_ctx* ctx);
+
+int b2_set_option(b2_ctx* ctx, int option, int value);
+
+/* Total number of trainable scalars (sum over layers of dims[l]*dims[l+1] + dims[l+1]). */
+long b2_param_count(const b2_ctx* ctx);
+
+/*
+ * Copy one layer's weights/bias from/to DEVICE buffers owned by the caller (stream-ordered).
+ * Replaces the init_op run by the chief (distributed.py:126,129-135; simple.py:28,32) and the
+ * fetch of W, b (simple.py:37).  Either pointer may be NULL to skip it.
+ */
+int b2_params_set(b2_ctx* ctx, int layer, const float* W_dev, const float* b_dev, b2_stream_t stream);
+int b2_params_get(b2_ctx* ctx, int layer, float* W_dev, float* b_dev, b2_stream_t stream);
+
+/*
+ * Data-parallel set-up, replacing tf.train.ClusterSpec / tf.train.Server / replica_device_setter
+ * (distributed.py:37-43,63-65): rank = worker task_index, nranks = number of worker hosts.
+ * b2_get_unique_id fills a 128-byte NCCL unique id on one rank; every rank then passes the same
+ * bytes to b2_comm_init.  With nranks == 1 no communicator is created.
+ */
+int b2_get_unique_id(void* out128);
+int b2_comm_init(b2_ctx* ctx, int rank, int nranks, const void* unique_id128);
+
+/*
+ * n_steps consecutive training steps on device-resident data; nothing is copied to or from the
+ * host and the call returns as soon as the work is enqueued on `stream`.
+ * Replaces n_steps iterations of the hot loops (simple.py:34-35; distributed.py:145-150):
+ * forward, loss, accuracy, backward, [all-reduce], SGD apply, global_step += 1.
+ *   step s uses global rows  start_s = (first_row + s*global_batch) mod (floor(pool_rows/global_batch)*global_batch)
+ *   this rank takes rows     start_s + rank*local_batch ... + local_batch   (local_batch*nranks == global_batch)
+ *   the loss head's mean divides by global_batch (distributed.py:102 reduce_mean over the whole batch).
+ * loss_trace_dev[s]    <- the PRE-update loss of step s over the global batch (what the reference fetches)
+ * correct_trace_dev[s] <- number of rows of the global batch whose argmax matches the label's (distributed.py:117)
+ * Either trace pointer may be NULL.
+ */
+int b2_train_steps(b2_ctx* ctx, const void* x_pool_dev, const void* y_pool_dev, long pool_rows,
+                   int local_batch, long global_batch, int n_steps, long first_row, float lr,
+                   float* loss_trace_dev, int* correct_trace_dev, b2_stream_t stream);
+
+/*
+ * Loss and correct-row count over `rows` device-resident rows without touching the parameters
+ * (distributed.py:164 final accuracy; simple.py:37 final loss).  Rows are processed in chunks of
+ * at most max_local_batch.  Results are written to device memory (stream-ordered).
+ */
+int b2_eval(b2_ctx* ctx, const void* x_dev, const void* y_dev, long rows, float* loss_dev,
+            long* correct_dev, b2_stream_t stream);
+
+/*
+ * The reference's call shape: sess.run([train_op, cross_entropy, accuracy], feed_dict={x:..., y_:...})
+ * (distributed.py:148-150; simple.py:35).  x_host / y_host are HOST buffers holding this rank's
+ * `rows` rows; they are copied to the device, one step runs, and the pre-update loss and
+ * correct-row count come back to the host.  Synchronous.  This is the end-to-end path bench.py
+ * reports as `e2e`.  global_batch = rows * nranks.
+ */
+int b2_session_run_train(b2_ctx* ctx, const float* x_host, const float* y_host, int rows, float lr,
+                         float* loss_out, int* correct_out);
+
+/* The float32 `global_step` variable (distributed.py:68-70,108) as of the last enqueued step. */
+float b2_global_step(const b2_ctx* ctx);
+
+/* How many of this library's kernels the context has launched so far (bench.py's gpu_launches). */
+long b2_launch_count(const b2_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2MLP_H_ */

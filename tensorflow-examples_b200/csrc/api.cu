@@ -1,0 +1,498 @@
+// C ABI of libb2mlp (see include/b2mlp.h): context life cycle, parameter I/O, the training step
+// orchestration (which kernels run, in which order, on which stream) and the NCCL plumbing.
+#include <dlfcn.h>
+#include <stdarg.h>
+#include <stdlib.h>
+
+#include "common.cuh"
+
+// ---------------------------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------------------------
+static thread_local char g_err[1024] = "";
+
+void b2_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+extern "C" const char* b2_last_error(void) { return g_err; }
+extern "C" const char* b2_version(void) {
+  return "b2mlp 0.1 sm_100a (fp32 CUDA-core layer kernels, fused 784->10 step, NCCL data parallel)";
+}
+
+// ---------------------------------------------------------------------------------------------
+// NCCL, resolved at run time so the library loads (and its symbols can be checked) on a box
+// without a GPU or without NCCL on the loader path.
+// ---------------------------------------------------------------------------------------------
+namespace {
+struct nccl_uid { char internal[128]; };
+typedef int (*pfn_ncclGetUniqueId)(nccl_uid*);
+typedef int (*pfn_ncclCommInitRank)(void**, int, nccl_uid, int);
+typedef int (*pfn_ncclCommDestroy)(void*);
+typedef int (*pfn_ncclAllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef const char* (*pfn_ncclGetErrorString)(int);
+struct nccl_api {
+  void* handle;
+  pfn_ncclGetUniqueId GetUniqueId;
+  pfn_ncclCommInitRank CommInitRank;
+  pfn_ncclCommDestroy CommDestroy;
+  pfn_ncclAllReduce AllReduce;
+  pfn_ncclGetErrorString GetErrorString;
+};
+nccl_api g_nccl = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+constexpr int kNcclFloat = 7;  // ncclFloat32
+constexpr int kNcclSum = 0;    // ncclSum
+
+int load_nccl() {
+  if (g_nccl.handle) return B2_OK;
+  void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);  // already mapped by torch?
+  if (!h) {
+    const char* env = getenv("B2_NCCL_LIB");
+    if (env && *env) h = dlopen(env, RTLD_NOW | RTLD_GLOBAL);
+  }
+  if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) {
+    b2_set_error("NCCL not found (set B2_NCCL_LIB to libnccl.so.2): %s", dlerror());
+    return B2_ERR_NCCL;
+  }
+  g_nccl.GetUniqueId = (pfn_ncclGetUniqueId)dlsym(h, "ncclGetUniqueId");
+  g_nccl.CommInitRank = (pfn_ncclCommInitRank)dlsym(h, "ncclCommInitRank");
+  g_nccl.CommDestroy = (pfn_ncclCommDestroy)dlsym(h, "ncclCommDestroy");
+  g_nccl.AllReduce = (pfn_ncclAllReduce)dlsym(h, "ncclAllReduce");
+  g_nccl.GetErrorString = (pfn_ncclGetErrorString)dlsym(h, "ncclGetErrorString");
+  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.CommDestroy || !g_nccl.AllReduce ||
+      !g_nccl.GetErrorString) {
+    b2_set_error("NCCL library lacks a required symbol");
+    return B2_ERR_NCCL;
+  }
+  g_nccl.handle = h;
+  return B2_OK;
+}
+
+#define B2_NCCL(expr)                                                                \
+  do {                                                                               \
+    int _r = (expr);                                                                 \
+    if (_r != 0) {                                                                   \
+      b2_set_error("%s failed: %s", #expr, g_nccl.GetErrorString(_r));               \
+      return B2_ERR_NCCL;                                                            \
+    }                                                                                \
+  } while (0)
+
+inline long round4(long v) { return (v + 3) & ~3L; }
+inline long w_size(const b2_ctx* c, int l) { return (long)c->dims[l] * c->dims[l + 1]; }
+inline long b_size(const b2_ctx* c, int l) { return c->dims[l + 1]; }
+inline long part_stride(const b2_ctx* c, int l) { return round4(w_size(c, l)) + round4(b_size(c, l)); }
+
+bool use_fused_linear(const b2_ctx* c) {
+  return !c->opt_force_layered && c->precision == B2_PREC_FP32 && c->n_layers == 1 &&
+         b2_fused_linear_supported(c->dims[0], c->dims[1], c->loss);
+}
+
+// Enqueue forward + loss head (+ backward partials) for `rows` rows.  train == 0: forward and head only.
+int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float inv_B, int train,
+                    int* splits_used, cudaStream_t s) {
+  const int n = c->n_layers;
+  const float* a_in = x;
+  for (int l = 0; l < n; ++l) {
+    float* out = (l == n - 1) ? c->z_last : c->act_buf[l];
+    int rc = b2_launch_dense_fwd(a_in, c->params + c->w_off[l], c->params + c->b_off[l], out, rows,
+                                 c->dims[l + 1], c->dims[l], (l == n - 1) ? B2_ACT_IDENTITY : c->act, s);
+    if (rc) return rc;
+    c->launches++;
+    a_in = out;
+  }
+  float* head = c->scratch + c->head_part_off;
+  int rc = b2_launch_loss_head(c->z_last, y, c->dz[0], head, head + c->head_blocks, rows, c->dims[n],
+                               c->loss, inv_B, c->head_blocks, s);
+  if (rc) return rc;
+  c->launches++;
+  if (!train) return B2_OK;
+  int cur = 0;
+  for (int l = n - 1; l >= 0; --l) {
+    const float* a_prev = (l == 0) ? x : c->act_buf[l - 1];
+    int sp = c->splits[l];
+    const int max_sp = (rows + 63) / 64;
+    if (sp > max_sp) sp = max_sp;
+    if (sp < 1) sp = 1;
+    splits_used[l] = sp;
+    float* pw = c->scratch + c->part_off[l];
+    float* pb = pw + round4(w_size(c, l));
+    rc = b2_launch_wgrad(a_prev, c->dz[cur], pw, pb, part_stride(c, l), rows, c->dims[l],
+                         c->dims[l + 1], sp, s);
+    if (rc) return rc;
+    c->launches++;
+    if (l > 0) {
+      rc = b2_launch_dgrad(c->dz[cur], c->params + c->w_off[l], c->act_buf[l - 1], c->dz[cur ^ 1], rows,
+                           c->dims[l], c->dims[l + 1], c->act, s);
+      if (rc) return rc;
+      c->launches++;
+      cur ^= 1;
+    }
+  }
+  return B2_OK;
+}
+
+// One full training step on `rows` local rows starting at x / y.
+int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long global_batch, float lr,
+                 float* loss_trace, int* correct_trace, cudaStream_t s) {
+  const float inv_B = 1.0f / (float)global_batch;
+  const int apply = (c->nranks == 1) ? 1 : 0;
+  int rc;
+  if (use_fused_linear(c)) {
+    int grid = (rows + 31) / 32;
+    if (grid > c->fused_grid) grid = c->fused_grid;
+    rc = b2_launch_fused_linear_step(x, y, rows, c->params + c->w_off[0], c->params + c->b_off[0],
+                                     c->fused_scratch, grid, inv_B, s);
+    if (rc) return rc;
+    rc = b2_launch_fused_linear_reduce(c->fused_scratch, grid, c->grads, c->params, apply, lr,
+                                       loss_trace, correct_trace, c->global_step_dev, c->P, s);
+    if (rc) return rc;
+    c->launches += 2;
+  } else {
+    b2_reduce_args a;
+    memset(&a, 0, sizeof(a));
+    rc = enqueue_layered(c, x, y, rows, inv_B, 1, a.splits, s);
+    if (rc) return rc;
+    a.n_layers = c->n_layers;
+    for (int l = 0; l < c->n_layers; ++l) {
+      a.w_off[l] = c->w_off[l];
+      a.b_off[l] = c->b_off[l];
+      a.w_size[l] = w_size(c, l);
+      a.b_size[l] = b_size(c, l);
+      a.part_off[l] = c->part_off[l];
+    }
+    a.P = c->P;
+    a.head_part_off = c->head_part_off;
+    a.head_blocks = c->head_blocks;
+    rc = b2_launch_reduce(a, c->scratch, c->grads, c->params, apply, lr, loss_trace, correct_trace,
+                          c->global_step_dev, c->sm_count, s);
+    if (rc) return rc;
+    c->launches++;
+  }
+  if (!apply) {
+    // the parameter-server push/pull of the reference (distributed.py:63-65) becomes one
+    // all-reduce of [gradients..., loss, correct]; every rank then applies the same update.
+    B2_NCCL(g_nccl.AllReduce(c->grads, c->grads, (size_t)(c->P + 4), kNcclFloat, kNcclSum, c->nccl_comm, s));
+    rc = b2_launch_sgd_apply(c->params, c->grads, c->P, lr, loss_trace, correct_trace,
+                             c->global_step_dev, c->sm_count, s);
+    if (rc) return rc;
+    c->launches++;
+  }
+  c->global_step_host += 1.0f;
+  return B2_OK;
+}
+
+void free_ctx(b2_ctx* c) {
+  if (!c) return;
+  if (c->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
+  cudaFree(c->params);
+  cudaFree(c->grads);
+  for (int l = 0; l < B2_MAX_LAYERS; ++l) cudaFree(c->act_buf[l]);
+  cudaFree(c->z_last);
+  cudaFree(c->dz[0]);
+  cudaFree(c->dz[1]);
+  cudaFree(c->scratch);
+  cudaFree(c->fused_scratch);
+  cudaFree(c->global_step_dev);
+  cudaFree(c->eval_acc_dev);
+  cudaFree(c->feed_x);
+  cudaFree(c->feed_y);
+  cudaFree(c->fetch_dev);
+  if (c->fetch_host) cudaFreeHost(c->fetch_host);
+  if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  free(c);
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// life cycle
+// ---------------------------------------------------------------------------------------------
+extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims, int act, int loss,
+                         int precision, int max_local_batch) {
+  B2_CHECK_ARG(out != nullptr, "b2_create: out is NULL");
+  *out = nullptr;
+  B2_CHECK_ARG(n_layers >= 1 && n_layers <= B2_MAX_LAYERS, "b2_create: n_layers must be in [1,%d], got %d",
+               B2_MAX_LAYERS, n_layers);
+  B2_CHECK_ARG(dims != nullptr, "b2_create: dims is NULL");
+  for (int i = 0; i <= n_layers; ++i)
+    B2_CHECK_ARG(dims[i] >= 1, "b2_create: dims[%d] = %d must be >= 1", i, dims[i]);
+  B2_CHECK_ARG(act == B2_ACT_IDENTITY || act == B2_ACT_SIGMOID, "b2_create: unknown activation %d", act);
+  B2_CHECK_ARG(loss == B2_LOSS_SSE_SUM || loss == B2_LOSS_SOFTMAX_CE_MEAN, "b2_create: unknown loss %d", loss);
+  B2_CHECK_ARG(precision == B2_PREC_FP32,
+               "b2_create: precision %d not available in this build (fp32 only)", precision);
+  B2_CHECK_ARG(max_local_batch >= 1, "b2_create: max_local_batch must be >= 1");
+
+  int ndev = 0;
+  B2_CUDA(cudaGetDeviceCount(&ndev));
+  B2_CHECK_ARG(device >= 0 && device < ndev, "b2_create: device %d out of range (%d visible)", device, ndev);
+  B2_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  B2_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {
+    b2_set_error("b2_create: device %d is sm_%d%d; this library is built for sm_100a (B200) only", device,
+                 prop.major, prop.minor);
+    return B2_ERR_CUDA;
+  }
+
+  b2_ctx* c = (b2_ctx*)calloc(1, sizeof(b2_ctx));
+  if (!c) { b2_set_error("b2_create: out of host memory"); return B2_ERR_CUDA; }
+  c->device = device;
+  c->n_layers = n_layers;
+  for (int i = 0; i <= n_layers; ++i) c->dims[i] = dims[i];
+  c->act = act; c->loss = loss; c->precision = precision;
+  c->max_local_batch = max_local_batch;
+  c->sm_count = prop.multiProcessorCount;
+  c->rank = 0; c->nranks = 1;
+
+  long off = 0, maxw = 0;
+  for (int l = 0; l < n_layers; ++l) {
+    c->w_off[l] = off; off += round4(w_size(c, l));
+    c->b_off[l] = off; off += round4(b_size(c, l));
+    if (dims[l + 1] > maxw) maxw = dims[l + 1];
+  }
+  c->P = off;
+
+  // scratch: per-layer split partials, then the loss-head partials
+  long soff = 0;
+  for (int l = 0; l < n_layers; ++l) {
+    const long tiles = (long)((dims[l] + 63) / 64) * ((dims[l + 1] + 63) / 64);
+    long sp = (4L * c->sm_count + tiles - 1) / tiles;
+    const long cap = (max_local_batch + 63) / 64;
+    if (sp > cap) sp = cap;
+    if (sp > 256) sp = 256;
+    if (sp < 1) sp = 1;
+    c->splits[l] = (int)sp;
+    c->part_off[l] = soff;
+    soff += sp * part_stride(c, l);
+  }
+  c->head_blocks = 2 * c->sm_count;
+  {
+    const int cap = (max_local_batch + 7) / 8;
+    if (c->head_blocks > cap) c->head_blocks = cap;
+  }
+  c->head_part_off = soff;
+  soff += 2L * c->head_blocks;
+  c->scratch_floats = soff;
+
+#define B2_ALLOC(ptr, nfloats)                                                         \
+  do {                                                                                 \
+    cudaError_t _e = cudaMalloc((void**)&(ptr), (size_t)(nfloats) * sizeof(float));    \
+    if (_e != cudaSuccess) {                                                           \
+      b2_set_error("b2_create: cudaMalloc of %ld bytes failed: %s",                    \
+                   (long)((size_t)(nfloats) * sizeof(float)), cudaGetErrorString(_e)); \
+      free_ctx(c);                                                                     \
+      return B2_ERR_CUDA;                                                              \
+    }                                                                                  \
+  } while (0)
+
+  B2_ALLOC(c->params, c->P);
+  B2_ALLOC(c->grads, c->P + 4);
+  for (int l = 0; l < n_layers - 1; ++l) B2_ALLOC(c->act_buf[l], (long)max_local_batch * dims[l + 1]);
+  B2_ALLOC(c->z_last, (long)max_local_batch * dims[n_layers]);
+  B2_ALLOC(c->dz[0], (long)max_local_batch * maxw);
+  if (n_layers > 1) B2_ALLOC(c->dz[1], (long)max_local_batch * maxw);
+  B2_ALLOC(c->scratch, c->scratch_floats);
+  B2_ALLOC(c->global_step_dev, 1);
+  B2_ALLOC(c->eval_acc_dev, 2);
+  B2_ALLOC(c->fetch_dev, 2);
+  if (b2_fused_linear_supported(dims[0], dims[1], loss) && n_layers == 1) {
+    c->fused_grid = b2_fused_linear_grid(c->sm_count);
+    c->fused_stride = b2_fused_linear_stride();
+    B2_ALLOC(c->fused_scratch, (long)c->fused_grid * c->fused_stride);
+    if (b2_fused_linear_prepare() != B2_OK) { free_ctx(c); return B2_ERR_CUDA; }
+  }
+#undef B2_ALLOC
+  cudaError_t e = cudaMemset(c->params, 0, (size_t)c->P * sizeof(float));
+  if (e == cudaSuccess) e = cudaMemset(c->grads, 0, (size_t)(c->P + 4) * sizeof(float));
+  if (e == cudaSuccess) e = cudaMemset(c->global_step_dev, 0, sizeof(float));
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaMallocHost((void**)&c->fetch_host, 2 * sizeof(float));
+  if (e != cudaSuccess) {
+    b2_set_error("b2_create: initialisation failed: %s", cudaGetErrorString(e));
+    free_ctx(c);
+    return B2_ERR_CUDA;
+  }
+  *out = c;
+  return B2_OK;
+}
+
+extern "C" void b2_destroy(b2_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  free_ctx(ctx);
+}
+
+extern "C" int b2_set_option(b2_ctx* ctx, int option, int value) {
+  B2_CHECK_ARG(ctx != nullptr, "b2_set_option: ctx is NULL");
+  switch (option) {
+    case B2_OPT_FORCE_LAYERED: ctx->opt_force_layered = value ? 1 : 0; return B2_OK;
+    default: b2_set_error("b2_set_option: unknown option %d", option); return B2_ERR_ARG;
+  }
+}
+
+extern "C" long b2_param_count(const b2_ctx* ctx) {
+  if (!ctx) return 0;
+  long p = 0;
+  for (int l = 0; l < ctx->n_layers; ++l) p += w_size(ctx, l) + b_size(ctx, l);
+  return p;
+}
+
+extern "C" float b2_global_step(const b2_ctx* ctx) { return ctx ? ctx->global_step_host : 0.f; }
+extern "C" long b2_launch_count(const b2_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+// ---------------------------------------------------------------------------------------------
+// parameters
+// ---------------------------------------------------------------------------------------------
+extern "C" int b2_params_set(b2_ctx* ctx, int layer, const float* W_dev, const float* b_dev,
+                             b2_stream_t stream) {
+  B2_CHECK_ARG(ctx != nullptr, "b2_params_set: ctx is NULL");
+  B2_CHECK_ARG(layer >= 0 && layer < ctx->n_layers, "b2_params_set: layer %d out of range", layer);
+  B2_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  if (W_dev)
+    B2_CUDA(cudaMemcpyAsync(ctx->params + ctx->w_off[layer], W_dev, (size_t)w_size(ctx, layer) * sizeof(float),
+                            cudaMemcpyDefault, s));
+  if (b_dev)
+    B2_CUDA(cudaMemcpyAsync(ctx->params + ctx->b_off[layer], b_dev, (size_t)b_size(ctx, layer) * sizeof(float),
+                            cudaMemcpyDefault, s));
+  return B2_OK;
+}
+
+extern "C" int b2_params_get(b2_ctx* ctx, int layer, float* W_dev, float* b_dev, b2_stream_t stream) {
+  B2_CHECK_ARG(ctx != nullptr, "b2_params_get: ctx is NULL");
+  B2_CHECK_ARG(layer >= 0 && layer < ctx->n_layers, "b2_params_get: layer %d out of range", layer);
+  B2_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  if (W_dev)
+    B2_CUDA(cudaMemcpyAsync(W_dev, ctx->params + ctx->w_off[layer], (size_t)w_size(ctx, layer) * sizeof(float),
+                            cudaMemcpyDefault, s));
+  if (b_dev)
+    B2_CUDA(cudaMemcpyAsync(b_dev, ctx->params + ctx->b_off[layer], (size_t)b_size(ctx, layer) * sizeof(float),
+                            cudaMemcpyDefault, s));
+  return B2_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// data parallel
+// ---------------------------------------------------------------------------------------------
+extern "C" int b2_get_unique_id(void* out128) {
+  B2_CHECK_ARG(out128 != nullptr, "b2_get_unique_id: out is NULL");
+  int rc = load_nccl();
+  if (rc) return rc;
+  nccl_uid id;
+  B2_NCCL(g_nccl.GetUniqueId(&id));
+  memcpy(out128, &id, sizeof(id));
+  return B2_OK;
+}
+
+extern "C" int b2_comm_init(b2_ctx* ctx, int rank, int nranks, const void* unique_id128) {
+  B2_CHECK_ARG(ctx != nullptr, "b2_comm_init: ctx is NULL");
+  B2_CHECK_ARG(nranks >= 1 && rank >= 0 && rank < nranks, "b2_comm_init: bad rank %d / nranks %d", rank, nranks);
+  if (ctx->nccl_comm) { b2_set_error("b2_comm_init: communicator already initialised"); return B2_ERR_STATE; }
+  ctx->rank = rank;
+  ctx->nranks = nranks;
+  if (nranks == 1) return B2_OK;
+  B2_CHECK_ARG(unique_id128 != nullptr, "b2_comm_init: unique id is NULL");
+  int rc = load_nccl();
+  if (rc) { ctx->rank = 0; ctx->nranks = 1; return rc; }
+  B2_CUDA(cudaSetDevice(ctx->device));
+  nccl_uid id;
+  memcpy(&id, unique_id128, sizeof(id));
+  int r = g_nccl.CommInitRank(&ctx->nccl_comm, nranks, id, rank);
+  if (r != 0) {
+    b2_set_error("ncclCommInitRank failed: %s", g_nccl.GetErrorString(r));
+    ctx->nccl_comm = nullptr; ctx->rank = 0; ctx->nranks = 1;
+    return B2_ERR_NCCL;
+  }
+  return B2_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// the hot path
+// ---------------------------------------------------------------------------------------------
+extern "C" int b2_train_steps(b2_ctx* ctx, const void* x_pool_dev, const void* y_pool_dev, long pool_rows,
+                              int local_batch, long global_batch, int n_steps, long first_row, float lr,
+                              float* loss_trace_dev, int* correct_trace_dev, b2_stream_t stream) {
+  B2_CHECK_ARG(ctx != nullptr, "b2_train_steps: ctx is NULL");
+  B2_CHECK_ARG(x_pool_dev && y_pool_dev, "b2_train_steps: NULL data pool");
+  B2_CHECK_ARG(local_batch >= 1 && local_batch <= ctx->max_local_batch,
+               "b2_train_steps: local_batch %d outside [1, max_local_batch=%d]", local_batch, ctx->max_local_batch);
+  B2_CHECK_ARG(global_batch == (long)local_batch * ctx->nranks,
+               "b2_train_steps: global_batch %ld != local_batch %d * nranks %d", global_batch, local_batch, ctx->nranks);
+  B2_CHECK_ARG(pool_rows >= global_batch, "b2_train_steps: pool_rows %ld < global_batch %ld", pool_rows, global_batch);
+  B2_CHECK_ARG(n_steps >= 0, "b2_train_steps: n_steps must be >= 0");
+  const long span = (pool_rows / global_batch) * global_batch;
+  B2_CHECK_ARG(first_row >= 0 && first_row % global_batch == 0 && first_row < span,
+               "b2_train_steps: first_row %ld must be a multiple of global_batch inside the pool", first_row);
+  B2_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const float* xp = (const float*)x_pool_dev;
+  const float* yp = (const float*)y_pool_dev;
+  const int in = ctx->dims[0], outd = ctx->dims[ctx->n_layers];
+  for (int i = 0; i < n_steps; ++i) {
+    const long start = (first_row + (long)i * global_batch) % span + (long)ctx->rank * local_batch;
+    int rc = enqueue_step(ctx, xp + start * in, yp + start * outd, local_batch, global_batch, lr,
+                          loss_trace_dev ? loss_trace_dev + i : nullptr,
+                          correct_trace_dev ? correct_trace_dev + i : nullptr, s);
+    if (rc) return rc;
+  }
+  return B2_OK;
+}
+
+extern "C" int b2_eval(b2_ctx* ctx, const void* x_dev, const void* y_dev, long rows, float* loss_dev,
+                       long* correct_dev, b2_stream_t stream) {
+  B2_CHECK_ARG(ctx != nullptr, "b2_eval: ctx is NULL");
+  B2_CHECK_ARG(x_dev && y_dev && rows >= 1, "b2_eval: bad arguments");
+  B2_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const float* xp = (const float*)x_dev;
+  const float* yp = (const float*)y_dev;
+  const int in = ctx->dims[0], outd = ctx->dims[ctx->n_layers];
+  const float inv_B = 1.0f / (float)rows;
+  B2_CUDA(cudaMemsetAsync(ctx->eval_acc_dev, 0, 2 * sizeof(float), s));
+  int dummy[B2_MAX_LAYERS];
+  for (long r0 = 0; r0 < rows; r0 += ctx->max_local_batch) {
+    const int n = (int)((rows - r0 < ctx->max_local_batch) ? rows - r0 : ctx->max_local_batch);
+    int rc = enqueue_layered(ctx, xp + r0 * in, yp + r0 * outd, n, inv_B, 0, dummy, s);
+    if (rc) return rc;
+    float* head = ctx->scratch + ctx->head_part_off;
+    rc = b2_launch_eval_accumulate(head, head + ctx->head_blocks, ctx->head_blocks, ctx->eval_acc_dev, s);
+    if (rc) return rc;
+    ctx->launches++;
+  }
+  int rc = b2_launch_eval_finish(ctx->eval_acc_dev, loss_dev, correct_dev, s);
+  if (rc) return rc;
+  ctx->launches++;
+  return B2_OK;
+}
+
+extern "C" int b2_session_run_train(b2_ctx* ctx, const float* x_host, const float* y_host, int rows, float lr,
+                                    float* loss_out, int* correct_out) {
+  B2_CHECK_ARG(ctx != nullptr, "b2_session_run_train: ctx is NULL");
+  B2_CHECK_ARG(x_host && y_host, "b2_session_run_train: NULL feed");
+  B2_CHECK_ARG(rows >= 1 && rows <= ctx->max_local_batch,
+               "b2_session_run_train: rows %d outside [1, max_local_batch=%d]", rows, ctx->max_local_batch);
+  B2_CUDA(cudaSetDevice(ctx->device));
+  const int in = ctx->dims[0], outd = ctx->dims[ctx->n_layers];
+  if (!ctx->feed_x) {
+    B2_CUDA(cudaMalloc((void**)&ctx->feed_x, (size_t)ctx->max_local_batch * in * sizeof(float)));
+    B2_CUDA(cudaMalloc((void**)&ctx->feed_y, (size_t)ctx->max_local_batch * outd * sizeof(float)));
+  }
+  cudaStream_t s = ctx->own_stream;
+  B2_CUDA(cudaMemcpyAsync(ctx->feed_x, x_host, (size_t)rows * in * sizeof(float), cudaMemcpyHostToDevice, s));
+  B2_CUDA(cudaMemcpyAsync(ctx->feed_y, y_host, (size_t)rows * outd * sizeof(float), cudaMemcpyHostToDevice, s));
+  int rc = enqueue_step(ctx, ctx->feed_x, ctx->feed_y, rows, (long)rows * ctx->nranks, lr, ctx->fetch_dev,
+                        (int*)(ctx->fetch_dev + 1), s);
+  if (rc) return rc;
+  B2_CUDA(cudaMemcpyAsync(ctx->fetch_host, ctx->fetch_dev, 2 * sizeof(float), cudaMemcpyDeviceToHost, s));
+  B2_CUDA(cudaStreamSynchronize(s));
+  if (loss_out) *loss_out = ctx->fetch_host[0];
+  if (correct_out) memcpy(correct_out, &ctx->fetch_host[1], sizeof(int));
+  return B2_OK;
+}

@@ -1,0 +1,126 @@
+// Shared declarations of libb2mlp: error plumbing, the context, and the launchers each
+// translation unit exports to api.cu.  Not part of the public ABI (see include/b2mlp.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/b2mlp.h"
+
+#define B2_MAX_LAYERS 8
+
+// ---- error plumbing --------------------------------------------------------------------------
+void b2_set_error(const char* fmt, ...);
+
+#define B2_CUDA(expr)                                                                      \
+  do {                                                                                     \
+    cudaError_t _e = (expr);                                                               \
+    if (_e != cudaSuccess) {                                                               \
+      b2_set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return B2_ERR_CUDA;                                                                  \
+    }                                                                                      \
+  } while (0)
+
+#define B2_CHECK_ARG(cond, ...)      \
+  do {                               \
+    if (!(cond)) {                   \
+      b2_set_error(__VA_ARGS__);     \
+      return B2_ERR_ARG;             \
+    }                                \
+  } while (0)
+
+// ---- context ---------------------------------------------------------------------------------
+struct b2_ctx {
+  int device;
+  int n_layers;
+  int dims[B2_MAX_LAYERS + 1];
+  int act, loss, precision;
+  int max_local_batch;
+  int sm_count;
+  int opt_force_layered;
+
+  long P;                          // trainable scalars
+  long w_off[B2_MAX_LAYERS];       // offset of W[l] in the flat parameter / gradient layout
+  long b_off[B2_MAX_LAYERS];       // offset of b[l]
+
+  float* params;                   // [P]                      fp32 master parameters
+  float* grads;                    // [P + 2]                  reduced gradients, then loss, then correct count
+  float* act_buf[B2_MAX_LAYERS];   // act_buf[l] = output of layer l (l < n_layers-1), [max_local_batch, dims[l+1]]
+  float* z_last;                   // [max_local_batch, dims[n_layers]] logits / predictions
+  float* dz[2];                    // ping-pong [max_local_batch, max width]
+  float* scratch;                  // split-batch partial gradients + per-block loss partials
+  long scratch_floats;
+  long part_off[B2_MAX_LAYERS];    // offset of layer l's partials inside scratch
+  int splits[B2_MAX_LAYERS];       // number of batch splits of layer l's weight-gradient reduction
+  long head_part_off;              // offset of the loss-head partials [2][head_blocks]
+  int head_blocks;
+  float* fused_scratch;            // fused single-layer path: [fused_grid][fused_stride]
+  int fused_grid;
+  long fused_stride;
+  float* global_step_dev;          // float32 scalar, distributed.py:68-70
+  float* eval_acc_dev;             // [2] accumulators for b2_eval
+  float global_step_host;          // mirror advanced at enqueue time
+  long launches;
+
+  // staging for b2_session_run_train
+  float* feed_x;                   // [max_local_batch, dims[0]]
+  float* feed_y;                   // [max_local_batch, dims[n]]
+  float* fetch_dev;                // [2] loss, correct (as int bits)
+  float* fetch_host;               // pinned [2]
+  cudaStream_t own_stream;
+
+  // data parallel
+  int rank, nranks;
+  void* nccl_comm;
+};
+
+// ---- launchers (kernels_layered.cu) --------------------------------------------------------------
+// C[M,N] = act(A[M,K] @ W[K,N] + bias[N])
+int b2_launch_dense_fwd(const float* A, const float* W, const float* bias, float* C, int M, int N,
+                        int K, int act, cudaStream_t s);
+// partial[z][K*N] = A[rows of split z]^T @ dZ ; bias partial[z][N] = column sums of dZ
+int b2_launch_wgrad(const float* A, const float* dZ, float* partW, float* partB, long part_stride,
+                    int M, int Kin, int N, int splits, cudaStream_t s);
+// dA[M,Kin] = (dZ[M,N] @ W[Kin,N]^T) * act'(Aout)
+int b2_launch_dgrad(const float* dZ, const float* W, const float* Aout, float* dA, int M, int Kin,
+                    int N, int act, cudaStream_t s);
+// loss head: z -> dz, per-block loss / correct partials
+int b2_launch_loss_head(const float* z, const float* y, float* dz, float* loss_part,
+                        float* correct_part, int rows, int C, int loss, float inv_global_batch,
+                        int blocks, cudaStream_t s);
+// sums the split partials in fixed order into grads (+loss, +correct); when apply != 0 also does
+// the SGD update, the trace writes and global_step += 1.
+struct b2_reduce_args {
+  int n_layers;
+  long w_off[B2_MAX_LAYERS], b_off[B2_MAX_LAYERS];
+  long w_size[B2_MAX_LAYERS], b_size[B2_MAX_LAYERS];
+  long part_off[B2_MAX_LAYERS];
+  int splits[B2_MAX_LAYERS];
+  long P;
+  long head_part_off;
+  int head_blocks;
+};
+int b2_launch_reduce(const b2_reduce_args& a, const float* scratch, float* grads, float* params,
+                     int apply, float lr, float* loss_trace, int* correct_trace,
+                     float* global_step, int sm_count, cudaStream_t s);
+// params -= lr * grads after the all-reduce; trace writes; global_step += 1
+int b2_launch_sgd_apply(float* params, const float* grads, long P, float lr, float* loss_trace,
+                        int* correct_trace, float* global_step, int sm_count, cudaStream_t s);
+// eval accumulation: acc[0] += loss partials, acc[1] += correct partials (fixed order)
+int b2_launch_eval_accumulate(const float* loss_part, const float* correct_part, int blocks,
+                              float* acc, cudaStream_t s);
+int b2_launch_eval_finish(const float* acc, float* loss_out, long* correct_out, cudaStream_t s);
+
+// ---- launchers (fused_linear.cu): single dense layer 784 -> 10 + softmax-CE head, one kernel --------
+bool b2_fused_linear_supported(int in_dim, int out_dim, int loss);
+int b2_fused_linear_grid(int sm_count);
+long b2_fused_linear_stride(void);
+int b2_fused_linear_smem_bytes(void);
+int b2_launch_fused_linear_step(const float* x, const float* y, int rows, const float* W,
+                                const float* b, float* scratch, int grid, float inv_global_batch,
+                                cudaStream_t s);
+int b2_launch_fused_linear_reduce(const float* scratch, int grid, float* grads, float* params,
+                                  int apply, float lr, float* loss_trace, int* correct_trace,
+                                  float* global_step, long P, cudaStream_t s);
+int b2_fused_linear_prepare(void);

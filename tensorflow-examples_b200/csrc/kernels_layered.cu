@@ -1,0 +1,568 @@
+// Generic fp32 layer kernels (CUDA cores) for any [in, hidden..., out] stack:
+//   K1 dense forward          matmul + bias + activation       distributed.py:96-98, simple.py:16
+//   K2 loss head              softmax-CE / SSE forward+backward  distributed.py:99-102,117-118, simple.py:20
+//   K3 gradient reductions    dW = A^T dZ, db = colsum(dZ), dA   TF1 MatMul/BiasAdd/Sigmoid gradients
+//   K4 reduce + SGD apply     var -= lr * grad, global_step += 1  distributed.py:107-108, simple.py:22-23
+// All batch-dimension reductions are split into fixed slices and summed in a fixed order: no float
+// atomics, so a step is bit-reproducible.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int BM = 64, BN = 64, BK = 16;
+constexpr int PADT = 4;  // smem row padding (floats)
+
+__device__ __forceinline__ float act_fwd(float z, int act) {
+  // distributed.py:97 tf.nn.sigmoid
+  return act == B2_ACT_SIGMOID ? 1.0f / (1.0f + expf(-z)) : z;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1: C[M,N] = act(A[M,K] @ W[K,N] + bias[N]).  64x64 tile, 256 threads, 4x4 micro-tile.
+// ---------------------------------------------------------------------------------------------
+template <bool VEC_A, bool VEC_W>
+__global__ void __launch_bounds__(256)
+dense_fwd_kernel(const float* __restrict__ A, const float* __restrict__ W,
+                 const float* __restrict__ bias, float* __restrict__ C, int M, int N, int K, int act) {
+  __shared__ __align__(16) float As[BK][BM + PADT];  // As[k][m]
+  __shared__ __align__(16) float Bs[BK][BN + PADT];  // Bs[k][n]
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  const int a_row = tid >> 2, a_kq = (tid & 3) * 4;   // A tile: 64 rows x 16 k
+  const int w_k = tid >> 4, w_nq = (tid & 15) * 4;    // W tile: 16 k x 64 n
+
+  for (int k0 = 0; k0 < K; k0 += BK) {
+    {
+      const int m = m0 + a_row, k = k0 + a_kq;
+      float v[4] = {0.f, 0.f, 0.f, 0.f};
+      if (m < M) {
+        if (VEC_A) {
+          if (k < K) {
+            const float4 t = *reinterpret_cast<const float4*>(A + (size_t)m * K + k);
+            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (k + j < K) v[j] = A[(size_t)m * K + k + j];
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) As[a_kq + j][a_row] = v[j];
+    }
+    {
+      const int k = k0 + w_k, n = n0 + w_nq;
+      float v[4] = {0.f, 0.f, 0.f, 0.f};
+      if (k < K) {
+        if (VEC_W) {
+          if (n < N) {
+            const float4 t = *reinterpret_cast<const float4*>(W + (size_t)k * N + n);
+            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (n + j < N) v[j] = W[(size_t)k * N + n + j];
+        }
+      }
+      *reinterpret_cast<float4*>(&Bs[w_k][w_nq]) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < BK; ++kk) {
+      const float4 a = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
+      const float4 b = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
+      const float av[4] = {a.x, a.y, a.z, a.w};
+      const float bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int m = m0 + ty * 4 + i;
+    if (m >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n0 + tx * 4 + j;
+      if (n < N) C[(size_t)m * N + n] = act_fwd(acc[i][j] + bias[n], act);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K3a: weight / bias gradient of one layer over one batch slice.
+//   partW[z][k][n] = sum_{m in slice z} A[m][k] * dZ[m][n]      (MatMul grad, transpose_a)
+//   partB[z][n]    = sum_{m in slice z} dZ[m][n]                (BiasAdd grad)
+// grid = (ceil(N/64), ceil(Kin/64), splits)
+// ---------------------------------------------------------------------------------------------
+template <bool VEC_A, bool VEC_Z>
+__global__ void __launch_bounds__(256)
+wgrad_kernel(const float* __restrict__ A, const float* __restrict__ dZ, float* __restrict__ partW,
+             float* __restrict__ partB, long part_stride, int M, int Kin, int N, int chunk) {
+  __shared__ __align__(16) float As[BK][BM + PADT];  // As[m][k]
+  __shared__ __align__(16) float Zs[BK][BN + PADT];  // Zs[m][n]
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int n0 = blockIdx.x * BN, k0 = blockIdx.y * BM;
+  const int z = blockIdx.z;
+  const int m_begin = z * chunk;
+  const int m_end = min(M, m_begin + chunk);
+
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  float bacc[4] = {0.f, 0.f, 0.f, 0.f};
+
+  const int l_m = tid >> 4, l_q = (tid & 15) * 4;  // both tiles: 16 rows x 64 cols
+
+  for (int mb = m_begin; mb < m_end; mb += BK) {
+    const int m = mb + l_m;
+    {
+      const int k = k0 + l_q;
+      float v[4] = {0.f, 0.f, 0.f, 0.f};
+      if (m < m_end) {
+        if (VEC_A) {
+          if (k < Kin) {
+            const float4 t = *reinterpret_cast<const float4*>(A + (size_t)m * Kin + k);
+            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (k + j < Kin) v[j] = A[(size_t)m * Kin + k + j];
+        }
+      }
+      *reinterpret_cast<float4*>(&As[l_m][l_q]) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+    {
+      const int n = n0 + l_q;
+      float v[4] = {0.f, 0.f, 0.f, 0.f};
+      if (m < m_end) {
+        if (VEC_Z) {
+          if (n < N) {
+            const float4 t = *reinterpret_cast<const float4*>(dZ + (size_t)m * N + n);
+            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (n + j < N) v[j] = dZ[(size_t)m * N + n + j];
+        }
+      }
+      *reinterpret_cast<float4*>(&Zs[l_m][l_q]) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int mm = 0; mm < BK; ++mm) {
+      const float4 a = *reinterpret_cast<const float4*>(&As[mm][ty * 4]);
+      const float4 b = *reinterpret_cast<const float4*>(&Zs[mm][tx * 4]);
+      const float av[4] = {a.x, a.y, a.z, a.w};
+      const float bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+      if (ty == 0) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) bacc[j] += bv[j];
+      }
+    }
+    __syncthreads();
+  }
+  float* pw = partW + (size_t)z * part_stride;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int k = k0 + ty * 4 + i;
+    if (k >= Kin) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n0 + tx * 4 + j;
+      if (n < N) pw[(size_t)k * N + n] = acc[i][j];
+    }
+  }
+  if (blockIdx.y == 0 && ty == 0) {
+    float* pb = partB + (size_t)z * part_stride;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n0 + tx * 4 + j;
+      if (n < N) pb[n] = bacc[j];
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K3b: dA[M,Kin] = (dZ[M,N] @ W[Kin,N]^T) * act'(Aout)       (MatMul grad transpose_b + SigmoidGrad)
+// grid = (ceil(Kin/64), ceil(M/64))
+// ---------------------------------------------------------------------------------------------
+template <bool VEC_N>
+__global__ void __launch_bounds__(256)
+dgrad_kernel(const float* __restrict__ dZ, const float* __restrict__ W,
+             const float* __restrict__ Aout, float* __restrict__ dA, int M, int Kin, int N, int act) {
+  __shared__ __align__(16) float Zs[BK][BM + PADT];  // Zs[n][m]
+  __shared__ __align__(16) float Ws[BK][BN + PADT];  // Ws[n][k]
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int m0 = blockIdx.y * BM, k0 = blockIdx.x * BN;
+
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  const int l_r = tid >> 2, l_nq = (tid & 3) * 4;  // 64 rows x 16 n
+
+  for (int nb = 0; nb < N; nb += BK) {
+    const int n = nb + l_nq;
+    {
+      const int m = m0 + l_r;
+      float v[4] = {0.f, 0.f, 0.f, 0.f};
+      if (m < M) {
+        if (VEC_N) {
+          if (n < N) {
+            const float4 t = *reinterpret_cast<const float4*>(dZ + (size_t)m * N + n);
+            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (n + j < N) v[j] = dZ[(size_t)m * N + n + j];
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) Zs[l_nq + j][l_r] = v[j];
+    }
+    {
+      const int k = k0 + l_r;
+      float v[4] = {0.f, 0.f, 0.f, 0.f};
+      if (k < Kin) {
+        if (VEC_N) {
+          if (n < N) {
+            const float4 t = *reinterpret_cast<const float4*>(W + (size_t)k * N + n);
+            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (n + j < N) v[j] = W[(size_t)k * N + n + j];
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) Ws[l_nq + j][l_r] = v[j];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int nn = 0; nn < BK; ++nn) {
+      const float4 a = *reinterpret_cast<const float4*>(&Zs[nn][ty * 4]);
+      const float4 b = *reinterpret_cast<const float4*>(&Ws[nn][tx * 4]);
+      const float av[4] = {a.x, a.y, a.z, a.w};
+      const float bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int m = m0 + ty * 4 + i;
+    if (m >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int k = k0 + tx * 4 + j;
+      if (k >= Kin) continue;
+      float g = acc[i][j];
+      if (act == B2_ACT_SIGMOID) {
+        const float a = Aout[(size_t)m * Kin + k];
+        g = g * a * (1.0f - a);  // SigmoidGrad: dy * y * (1 - y)
+      }
+      dA[(size_t)m * Kin + k] = g;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2: loss head.  One warp per row, rows strided over a fixed grid, warp-shuffle row reductions.
+//   softmax-CE (distributed.py:99-102): y = exp(z-max) * (1/sum); loss_row = -sum(y_*log(y));
+//       dz = (y * sum(y_) - y_) * (1/B)   [= TF1's (g - sum(g*y))*y with g = -y_/(B*y)]
+//       correct = argmax(y) == argmax(y_), first index wins ties (distributed.py:117)
+//   SSE (simple.py:20): loss = sum((z-y_)^2), dz = 2*(z-y_)
+// Per-block partial sums (fixed order) go to loss_part / correct_part.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+// argmax with first-index tie-break: larger value wins; equal values -> smaller index wins.
+__device__ __forceinline__ void warp_argmax(float& v, int& idx) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, v, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+    if (ov > v || (ov == v && oi < idx)) { v = ov; idx = oi; }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+loss_head_kernel(const float* __restrict__ z, const float* __restrict__ y_, float* __restrict__ dz,
+                 float* __restrict__ loss_part, float* __restrict__ correct_part, int rows, int C,
+                 int loss_kind, float inv_B) {
+  __shared__ float s_loss[8], s_corr[8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float loss_acc = 0.f, corr_acc = 0.f;
+  for (long row = (long)blockIdx.x * 8 + warp; row < rows; row += (long)gridDim.x * 8) {
+    const float* zr = z + row * C;
+    const float* yr = y_ + row * C;
+    float* dr = dz + row * C;
+    if (loss_kind == B2_LOSS_SSE_SUM) {
+      float l = 0.f;
+      for (int c = lane; c < C; c += 32) {
+        const float d = zr[c] - yr[c];
+        l = fmaf(d, d, l);
+        dr[c] = 2.0f * d;
+      }
+      loss_acc += warp_sum(l);
+    } else {
+      float m = -INFINITY;
+      for (int c = lane; c < C; c += 32) m = fmaxf(m, zr[c]);
+      m = warp_max(m);
+      float s = 0.f;
+      for (int c = lane; c < C; c += 32) s += expf(zr[c] - m);
+      s = warp_sum(s);
+      const float inv = 1.0f / s;
+      float l = 0.f, sy = 0.f;
+      float bv = -INFINITY, lv = -INFINITY;
+      int bi = 0x7fffffff, li = 0x7fffffff;
+      for (int c = lane; c < C; c += 32) {
+        const float y = expf(zr[c] - m) * inv;
+        const float t = yr[c];
+        l -= t * logf(y);  // un-fused log(softmax), as the reference writes it
+        sy += t;
+        if (y > bv) { bv = y; bi = c; }
+        if (t > lv) { lv = t; li = c; }
+      }
+      l = warp_sum(l);
+      sy = warp_sum(sy);
+      warp_argmax(bv, bi);
+      warp_argmax(lv, li);
+      for (int c = lane; c < C; c += 32) {
+        const float y = expf(zr[c] - m) * inv;
+        dr[c] = (y * sy - yr[c]) * inv_B;
+      }
+      loss_acc += l;
+      corr_acc += (bi == li) ? 1.0f : 0.0f;
+    }
+  }
+  if (lane == 0) { s_loss[warp] = loss_acc; s_corr[warp] = corr_acc; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float l = 0.f, c = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { l += s_loss[w]; c += s_corr[w]; }
+    loss_part[blockIdx.x] = (loss_kind == B2_LOSS_SSE_SUM) ? l : l * inv_B;
+    correct_part[blockIdx.x] = c;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K4: fixed-order reduction of the split partials, optionally fused with the SGD apply
+// (ApplyGradientDescent: var -= lr*grad; then global_step += 1 -- distributed.py:107-108).
+// ---------------------------------------------------------------------------------------------
+__device__ float block0_head_sum(const float* __restrict__ part, int n) {
+  // warp 0 of the block: lane-strided partial sums, then a shuffle tree.  Fixed order.
+  float v = 0.f;
+  for (int i = threadIdx.x; i < n; i += 32) v += part[i];
+  return warp_sum(v);
+}
+
+__global__ void __launch_bounds__(256)
+reduce_kernel(b2_reduce_args a, const float* __restrict__ scratch, float* __restrict__ grads,
+              float* __restrict__ params, int apply, float lr, float* __restrict__ loss_trace,
+              int* __restrict__ correct_trace, float* __restrict__ global_step, long total) {
+  for (long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+       e += (long)gridDim.x * blockDim.x) {
+    // locate (layer, segment) of logical element e
+    long r = e;
+    int l = 0;
+    for (; l < a.n_layers; ++l) {
+      const long sz = a.w_size[l] + a.b_size[l];
+      if (r < sz) break;
+      r -= sz;
+    }
+    const long pstride = ((a.w_size[l] + 3) & ~3L) + ((a.b_size[l] + 3) & ~3L);
+    long src, dst;
+    if (r < a.w_size[l]) { src = r; dst = a.w_off[l] + r; }
+    else { src = ((a.w_size[l] + 3) & ~3L) + (r - a.w_size[l]); dst = a.b_off[l] + (r - a.w_size[l]); }
+    const float* p = scratch + a.part_off[l] + src;
+    float g = 0.f;
+    const int S = a.splits[l];
+    for (int s = 0; s < S; ++s) g += p[(size_t)s * pstride];
+    grads[dst] = g;
+    if (apply) params[dst] -= lr * g;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < 32) {
+    const float loss = block0_head_sum(scratch + a.head_part_off, a.head_blocks);
+    const float corr = block0_head_sum(scratch + a.head_part_off + a.head_blocks, a.head_blocks);
+    if (threadIdx.x == 0) {
+      grads[a.P] = loss;
+      grads[a.P + 1] = corr;
+      if (apply) {
+        if (loss_trace) *loss_trace = loss;
+        if (correct_trace) *correct_trace = (int)(corr + 0.5f);
+        *global_step += 1.0f;
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+sgd_apply_kernel(float* __restrict__ params, const float* __restrict__ grads, long P, float lr,
+                 float* __restrict__ loss_trace, int* __restrict__ correct_trace,
+                 float* __restrict__ global_step) {
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < P;
+       i += (long)gridDim.x * blockDim.x)
+    params[i] -= lr * grads[i];
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    if (loss_trace) *loss_trace = grads[P];
+    if (correct_trace) *correct_trace = (int)(grads[P + 1] + 0.5f);
+    *global_step += 1.0f;
+  }
+}
+
+__global__ void eval_accumulate_kernel(const float* __restrict__ loss_part,
+                                       const float* __restrict__ correct_part, int blocks,
+                                       float* __restrict__ acc) {
+  const float l = block0_head_sum(loss_part, blocks);
+  const float c = block0_head_sum(correct_part, blocks);
+  if (threadIdx.x == 0) { acc[0] += l; acc[1] += c; }
+}
+
+__global__ void eval_finish_kernel(const float* __restrict__ acc, float* loss_out, long* correct_out) {
+  if (threadIdx.x == 0) {
+    if (loss_out) *loss_out = acc[0];
+    if (correct_out) *correct_out = (long)(acc[1] + 0.5f);
+  }
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+}  // namespace
+
+#define B2_LAUNCH_CHECK()                                                               \
+  do {                                                                                  \
+    cudaError_t _e = cudaGetLastError();                                                \
+    if (_e != cudaSuccess) {                                                            \
+      b2_set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return B2_ERR_CUDA;                                                               \
+    }                                                                                   \
+  } while (0)
+
+int b2_launch_dense_fwd(const float* A, const float* W, const float* bias, float* C, int M, int N,
+                        int K, int act, cudaStream_t s) {
+  dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM);
+  const bool va = (K % 4 == 0) && aligned16(A);
+  const bool vw = (N % 4 == 0) && aligned16(W);
+  if (va && vw) dense_fwd_kernel<true, true><<<grid, 256, 0, s>>>(A, W, bias, C, M, N, K, act);
+  else if (va) dense_fwd_kernel<true, false><<<grid, 256, 0, s>>>(A, W, bias, C, M, N, K, act);
+  else if (vw) dense_fwd_kernel<false, true><<<grid, 256, 0, s>>>(A, W, bias, C, M, N, K, act);
+  else dense_fwd_kernel<false, false><<<grid, 256, 0, s>>>(A, W, bias, C, M, N, K, act);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_launch_wgrad(const float* A, const float* dZ, float* partW, float* partB, long part_stride,
+                    int M, int Kin, int N, int splits, cudaStream_t s) {
+  int chunk = (M + splits - 1) / splits;
+  chunk = ((chunk + BK - 1) / BK) * BK;
+  dim3 grid((N + BN - 1) / BN, (Kin + BM - 1) / BM, splits);
+  const bool va = (Kin % 4 == 0) && aligned16(A);
+  const bool vz = (N % 4 == 0) && aligned16(dZ);
+  if (va && vz) wgrad_kernel<true, true><<<grid, 256, 0, s>>>(A, dZ, partW, partB, part_stride, M, Kin, N, chunk);
+  else if (va) wgrad_kernel<true, false><<<grid, 256, 0, s>>>(A, dZ, partW, partB, part_stride, M, Kin, N, chunk);
+  else if (vz) wgrad_kernel<false, true><<<grid, 256, 0, s>>>(A, dZ, partW, partB, part_stride, M, Kin, N, chunk);
+  else wgrad_kernel<false, false><<<grid, 256, 0, s>>>(A, dZ, partW, partB, part_stride, M, Kin, N, chunk);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_launch_dgrad(const float* dZ, const float* W, const float* Aout, float* dA, int M, int Kin,
+                    int N, int act, cudaStream_t s) {
+  dim3 grid((Kin + BN - 1) / BN, (M + BM - 1) / BM);
+  const bool vn = (N % 4 == 0) && aligned16(dZ) && aligned16(W);
+  if (vn) dgrad_kernel<true><<<grid, 256, 0, s>>>(dZ, W, Aout, dA, M, Kin, N, act);
+  else dgrad_kernel<false><<<grid, 256, 0, s>>>(dZ, W, Aout, dA, M, Kin, N, act);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_launch_loss_head(const float* z, const float* y, float* dz, float* loss_part,
+                        float* correct_part, int rows, int C, int loss, float inv_global_batch,
+                        int blocks, cudaStream_t s) {
+  loss_head_kernel<<<blocks, 256, 0, s>>>(z, y, dz, loss_part, correct_part, rows, C, loss,
+                                          inv_global_batch);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_launch_reduce(const b2_reduce_args& a, const float* scratch, float* grads, float* params,
+                     int apply, float lr, float* loss_trace, int* correct_trace,
+                     float* global_step, int sm_count, cudaStream_t s) {
+  long total = 0;
+  for (int l = 0; l < a.n_layers; ++l) total += a.w_size[l] + a.b_size[l];
+  long blocks = (total + 255) / 256;
+  const long cap = (long)sm_count * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  reduce_kernel<<<(int)blocks, 256, 0, s>>>(a, scratch, grads, params, apply, lr, loss_trace,
+                                            correct_trace, global_step, total);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_launch_sgd_apply(float* params, const float* grads, long P, float lr, float* loss_trace,
+                        int* correct_trace, float* global_step, int sm_count, cudaStream_t s) {
+  long blocks = (P + 255) / 256;
+  const long cap = (long)sm_count * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  sgd_apply_kernel<<<(int)blocks, 256, 0, s>>>(params, grads, P, lr, loss_trace, correct_trace,
+                                               global_step);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_launch_eval_accumulate(const float* loss_part, const float* correct_part, int blocks,
+                              float* acc, cudaStream_t s) {
+  eval_accumulate_kernel<<<1, 32, 0, s>>>(loss_part, correct_part, blocks, acc);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_launch_eval_finish(const float* acc, float* loss_out, long* correct_out, cudaStream_t s) {
+  eval_finish_kernel<<<1, 32, 0, s>>>(acc, loss_out, correct_out);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}

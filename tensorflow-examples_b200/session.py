@@ -1,0 +1,199 @@
+"""Host-side mirror of the reference's training interface.
+
+The reference drives its model through `sess.run(fetches, feed_dict)` (simple/simple.py:35,37;
+distributed/distributed.py:148-150,164).  `DenseTrainer` offers the same three operations --
+a training step that returns the pre-update cost, an evaluation that returns cost/accuracy, and a
+fetch of the variables -- on top of the C ABI (include/b2mlp.h).  torch is used for device memory
+and the current stream handle only.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+from . import _ffi
+
+ACT_IDENTITY, ACT_SIGMOID = 0, 1
+LOSS_SSE, LOSS_SOFTMAX_CE = 0, 1
+_PREC = {"fp32": 0, "bf16": 1}
+
+
+def _torch():
+    import torch
+    return torch
+
+
+class DenseTrainer:
+    """Model + plain gradient-descent optimizer state on one GPU.
+
+    dims : [in, hidden..., out]; act: activation of the hidden layers; loss: LOSS_SSE (simple.py:20)
+    or LOSS_SOFTMAX_CE (distributed.py:99-102).  Weights use the reference's [in, out] layout.
+    """
+
+    def __init__(self, dims, act, loss, max_local_batch, device=0, precision="fp32"):
+        torch = _torch()
+        if not torch.cuda.is_available():
+            raise RuntimeError("DenseTrainer needs a CUDA device (B200); there is no CPU fallback")
+        self._lib = _ffi.load_library()
+        self.dims = [int(d) for d in dims]
+        self.n_layers = len(self.dims) - 1
+        self.act, self.loss = int(act), int(loss)
+        self.device = int(device)
+        self.torch_device = torch.device("cuda", self.device)
+        self.max_local_batch = int(max_local_batch)
+        self.rank, self.nranks = 0, 1
+        arr = (ctypes.c_int * len(self.dims))(*self.dims)
+        h = ctypes.c_void_p()
+        _ffi.check(self._lib, self._lib.b2_create(ctypes.byref(h), self.device, self.n_layers, arr, self.act,
+                                                  self.loss, _PREC[precision], self.max_local_batch))
+        self._h = h
+
+    # -- life cycle --------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.b2_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _stream(self):
+        torch = _torch()
+        return ctypes.c_void_p(torch.cuda.current_stream(self.torch_device).cuda_stream)
+
+    def set_option(self, option, value):
+        _ffi.check(self._lib, self._lib.b2_set_option(self._h, int(option), int(value)))
+
+    def force_layered(self, on=True):
+        """Use the per-layer kernels even where a fused single-kernel step exists (for cross-checks)."""
+        self.set_option(_ffi.OPT_FORCE_LAYERED, 1 if on else 0)
+
+    @property
+    def param_count(self):
+        return int(self._lib.b2_param_count(self._h))
+
+    @property
+    def global_step(self):
+        """distributed.py:68-70: a float32 counter of applied updates."""
+        return np.float32(self._lib.b2_global_step(self._h))
+
+    @property
+    def launch_count(self):
+        return int(self._lib.b2_launch_count(self._h))
+
+    # -- variables ----------------------------------------------------------------------------
+    def set_params(self, Ws, bs):
+        """Load initial values (replaces sess.run(init_op), distributed.py:126,135; simple.py:32)."""
+        torch = _torch()
+        keep = []
+        for l in range(self.n_layers):
+            W = torch.as_tensor(np.asarray(Ws[l], dtype=np.float32).reshape(self.dims[l], self.dims[l + 1])
+                                if not isinstance(Ws[l], torch.Tensor) else Ws[l], dtype=torch.float32)
+            b = torch.as_tensor(np.asarray(bs[l], dtype=np.float32).reshape(self.dims[l + 1])
+                                if not isinstance(bs[l], torch.Tensor) else bs[l], dtype=torch.float32)
+            W = W.to(self.torch_device).contiguous()
+            b = b.to(self.torch_device).contiguous()
+            keep += [W, b]
+            _ffi.check(self._lib, self._lib.b2_params_set(self._h, l, W.data_ptr(), b.data_ptr(), self._stream()))
+        torch.cuda.synchronize(self.torch_device)
+
+    def get_params(self):
+        """Fetch the variables (simple.py:37 sess.run([W, b, ...])).  Returns numpy float32 arrays."""
+        torch = _torch()
+        Ws, bs = [], []
+        for l in range(self.n_layers):
+            W = torch.empty(self.dims[l], self.dims[l + 1], dtype=torch.float32, device=self.torch_device)
+            b = torch.empty(self.dims[l + 1], dtype=torch.float32, device=self.torch_device)
+            _ffi.check(self._lib, self._lib.b2_params_get(self._h, l, W.data_ptr(), b.data_ptr(), self._stream()))
+            Ws.append(W)
+            bs.append(b)
+        torch.cuda.synchronize(self.torch_device)
+        return [w.cpu().numpy() for w in Ws], [b.cpu().numpy() for b in bs]
+
+    # -- data parallel ------------------------------------------------------------------------
+    @staticmethod
+    def new_unique_id():
+        lib = _ffi.load_library()
+        hint = _ffi.nccl_library_hint()
+        if hint and not os.environ.get("B2_NCCL_LIB"):
+            os.environ["B2_NCCL_LIB"] = hint
+        buf = ctypes.create_string_buffer(_ffi.UNIQUE_ID_BYTES)
+        _ffi.check(lib, lib.b2_get_unique_id(buf))
+        return buf.raw
+
+    def init_comm(self, rank, nranks, unique_id):
+        """rank = worker task_index, nranks = number of workers (distributed.py:37-43)."""
+        hint = _ffi.nccl_library_hint()
+        if hint and not os.environ.get("B2_NCCL_LIB"):
+            os.environ["B2_NCCL_LIB"] = hint
+        buf = ctypes.create_string_buffer(bytes(unique_id), _ffi.UNIQUE_ID_BYTES) if unique_id else None
+        _ffi.check(self._lib, self._lib.b2_comm_init(self._h, int(rank), int(nranks), buf))
+        self.rank, self.nranks = int(rank), int(nranks)
+
+    # -- the hot path ---------------------------------------------------------------------------
+    def train_steps(self, x_pool, y_pool, local_batch, n_steps, first_row=0, lr=0.001,
+                    loss_trace=None, correct_trace=None):
+        """n_steps training steps over device-resident pools (torch CUDA tensors, float32, row-major).
+
+        Asynchronous: returns (loss_trace, correct_trace) device tensors that are valid once the
+        current stream has drained.  loss_trace[s] is the PRE-update cost of step s.
+        """
+        torch = _torch()
+        assert x_pool.is_cuda and y_pool.is_cuda and x_pool.dtype == torch.float32 and y_pool.dtype == torch.float32
+        assert x_pool.is_contiguous() and y_pool.is_contiguous()
+        pool_rows = x_pool.shape[0]
+        if loss_trace is None:
+            loss_trace = torch.empty(max(n_steps, 1), dtype=torch.float32, device=self.torch_device)
+        if correct_trace is None:
+            correct_trace = torch.empty(max(n_steps, 1), dtype=torch.int32, device=self.torch_device)
+        _ffi.check(self._lib, self._lib.b2_train_steps(
+            self._h, x_pool.data_ptr(), y_pool.data_ptr(), pool_rows, int(local_batch),
+            int(local_batch) * self.nranks, int(n_steps), int(first_row), float(lr),
+            loss_trace.data_ptr(), correct_trace.data_ptr(), self._stream()))
+        return loss_trace, correct_trace
+
+    def run_train(self, x_host, y_host, lr):
+        """sess.run([train_op, cross_entropy, accuracy-count], feed_dict={x: x_host, y_: y_host}).
+
+        x_host / y_host: host float32 arrays (numpy, or pinned torch CPU tensors).  Synchronous.
+        Returns (pre-update cost as np.float32, number of correct rows).
+        """
+        xp, rows_x = _host_ptr(x_host, self.dims[0])
+        yp, rows_y = _host_ptr(y_host, self.dims[-1])
+        assert rows_x == rows_y, "x and y_ feeds disagree on the number of rows"
+        loss = ctypes.c_float()
+        correct = ctypes.c_int()
+        _ffi.check(self._lib, self._lib.b2_session_run_train(self._h, xp, yp, rows_x, float(lr),
+                                                             ctypes.byref(loss), ctypes.byref(correct)))
+        return np.float32(loss.value), int(correct.value)
+
+    def evaluate(self, x_dev, y_dev):
+        """sess.run([cost, accuracy]) without a train op (distributed.py:164; simple.py:37)."""
+        torch = _torch()
+        assert x_dev.is_cuda and y_dev.is_cuda
+        rows = x_dev.shape[0] if x_dev.dim() > 1 else x_dev.numel() // self.dims[0]
+        loss = torch.empty(1, dtype=torch.float32, device=self.torch_device)
+        correct = torch.empty(1, dtype=torch.int64, device=self.torch_device)
+        _ffi.check(self._lib, self._lib.b2_eval(self._h, x_dev.data_ptr(), y_dev.data_ptr(), int(rows),
+                                                loss.data_ptr(), correct.data_ptr(), self._stream()))
+        torch.cuda.synchronize(self.torch_device)
+        return np.float32(loss.item()), int(correct.item())
+
+
+def _host_ptr(a, width):
+    """(pointer, rows) of a host float32 buffer given as numpy array or torch CPU tensor."""
+    if isinstance(a, np.ndarray):
+        if a.dtype != np.float32 or not a.flags["C_CONTIGUOUS"]:
+            a = np.ascontiguousarray(a, dtype=np.float32)
+        _host_ptr.keep = a
+        return ctypes.c_void_p(a.ctypes.data), a.size // width
+    torch = _torch()
+    if isinstance(a, torch.Tensor):
+        assert not a.is_cuda and a.dtype == torch.float32 and a.is_contiguous()
+        return ctypes.c_void_p(a.data_ptr()), a.numel() // width
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    _host_ptr.keep = a
+    return ctypes.c_void_p(a.ctypes.data), a.size // width
