@@ -1,0 +1,311 @@
+#!/usr/bin/env python
+"""Headline benchmark: training samples/sec of the hot path (BASELINE.json `metric`).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c3|c2] [--batch B]
+  python bench.py --impl reference ...      # the reference's CPU implementation of the same step
+
+One JSON line on stdout (rank 0).  A "step" is one pass of the training step (forward, loss,
+accuracy, backward, [all-reduce], SGD apply) over one batch of synthetic MNIST-shaped rows.
+  value   whole-job samples/s with the data pool resident in HBM (CUDA events, max over ranks)
+  e2e     the same through the sess.run-shaped C-ABI call with HOST feeds (H2D + D2H inside the timing)
+  roofline / cpu_baseline / clocks / gpu_launches   see DESIGN.md "Measurement"
+Multi-GPU: launched by torchrun, one rank per GPU; weak scaling (per-GPU batch fixed).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name: (dims, act, loss, scaled_init, default local batch, description)
+    "c3": ([784, 10], 0, 1, True, 65536,
+           "784->10 dense + softmax-CE (simple.py-style single layer on MNIST-shaped rows), fp32"),
+    "c2": ([784, 100, 10], 1, 1, False, 65536,
+           "784-100-10 sigmoid MLP + softmax-CE (distributed.py model), fp32"),
+}
+BYTES_PER_SAMPLE = 784 * 4 + 10 * 4   # x row + one-hot y row, each read once
+LR = 0.001
+HOST_POOL_ROWS = 1 << 17               # generated on the host with the fixed seed, tiled on the device
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            d = json.load(open(p))
+            return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def _traffic_bytes(workload):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture, if any."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get(workload)
+        except Exception:
+            return None
+    return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.lines, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [t.strip() for t in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for nme, val in zip(names, f[2:6]):
+                if val.lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference_run(dims, act, loss, scaled, batch, steps, warmup, budget_s=None):
+    """The reference's CPU implementation of the step (oracle/torch_cpu.py, all host threads)."""
+    import torch
+    from oracle.torch_cpu import TorchCPUGraph
+    from tensorflow_examples_b200 import synthetic
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    rows = min(HOST_POOL_ROWS, max(batch, 2 * batch))
+    rows = max(rows, batch)
+    x, y = synthetic.make_pool(rows)
+    Ws, bs = synthetic.make_weights(dims, scaled)
+    g = TorchCPUGraph(dims, act, loss, Ws, bs, threads=threads)
+    xt, yt = torch.from_numpy(x), torch.from_numpy(y)
+    nb = rows // batch
+    losses = []
+    for s in range(warmup):
+        sl = slice((s % nb) * batch, (s % nb) * batch + batch)
+        losses.append(g.train_step(xt[sl], yt[sl], LR)[0])
+    t0 = time.perf_counter()
+    done = 0
+    for s in range(warmup, warmup + steps):
+        sl = slice((s % nb) * batch, (s % nb) * batch + batch)
+        losses.append(g.train_step(xt[sl], yt[sl], LR)[0])
+        done += 1
+        if budget_s and time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    return {"value": batch * done / dt, "steps": done, "seconds": dt, "threads": threads,
+            "first_loss": losses[0], "ms_per_step": 1e3 * dt / done}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=None, help="rows per GPU per step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    dims, act, loss, scaled, dbatch, desc = WORKLOADS[args.workload]
+    batch = args.batch or dbatch
+    global_batch = batch * world
+    warmup = max(3, args.warmup)
+    cfg = {"workload": "%s: %s" % (args.workload, desc), "dims": dims, "local_batch": batch,
+           "global_batch": global_batch, "lr": LR, "parallelism": "dp%d" % world}
+
+    # ------------------------------------------------------------------ reference arm (CPU)
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        r = cpu_reference_run(dims, act, loss, scaled, batch, args.steps, min(warmup, 5))
+        line = {"impl": "reference", "metric": "training samples/sec", "value": r["value"], "unit": "samples/s",
+                "n_gpus": args.gpus, "steps": r["steps"], "warmup": min(warmup, 5), "ms_per_step": r["ms_per_step"],
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic", "config": cfg,
+                "cpu_baseline": {"value": r["value"], "unit": "samples/s", "cores": r["threads"], "kind": "port",
+                                 "sample": "%d steps of %d rows each (one GPU's batch), torch-CPU restatement "
+                                           "of the TF1 graph (TensorFlow 1.x is not installable here)" % (r["steps"], batch)},
+                "e2e": {"value": r["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return 0
+
+    # ------------------------------------------------------------------ B200 arm
+    import torch
+    import tensorflow_examples_b200 as pkg
+    from tensorflow_examples_b200 import synthetic
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    def max_over_ranks(v):
+        if dist is None:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # data: fixed-seed host pool, tiled on the device to >= 2 global batches and >= 1.6 GB (>> 126 MB L2)
+    hx, hy = synthetic.make_pool(HOST_POOL_ROWS)
+    pool_rows = max(2 * global_batch, 1 << 19)
+    pool_rows = ((pool_rows + global_batch - 1) // global_batch) * global_batch
+    reps = (pool_rows + HOST_POOL_ROWS - 1) // HOST_POOL_ROWS
+    x_pool = torch.from_numpy(hx).to(dev).repeat(reps, 1)[:pool_rows].contiguous()
+    y_pool = torch.from_numpy(hy).to(dev).repeat(reps, 1)[:pool_rows].contiguous()
+    cfg["pool_rows"] = pool_rows
+    cfg["l2"] = "inputs larger than L2: %.2f GB pool, consecutive batches" % (pool_rows * BYTES_PER_SAMPLE / 1e9)
+
+    tr = pkg.DenseTrainer(dims, act, loss, max_local_batch=batch, device=local_rank)
+    Ws, bs = synthetic.make_weights(dims, scaled)
+    tr.set_params(Ws, bs)
+    if world > 1:
+        uid = [pkg.DenseTrainer.new_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        tr.init_comm(rank, world, uid[0])
+
+    # ---- value: device-resident pool -----------------------------------------------------
+    lt, ct = tr.train_steps(x_pool, y_pool, batch, warmup, first_row=0, lr=LR)
+    torch.cuda.synchronize(dev)
+    first_loss = float(lt[0].item())
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    barrier()
+    torch.cuda.synchronize(dev)
+    l0 = tr.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    lt, ct = tr.train_steps(x_pool, y_pool, batch, args.steps, first_row=(warmup * global_batch) % pool_rows, lr=LR)
+    ev1.record()
+    torch.cuda.synchronize(dev)
+    barrier()
+    ms = max_over_ranks(ev0.elapsed_time(ev1))
+    launches = tr.launch_count - l0
+    clocks = sampler.stop() if rank == 0 else None
+    last_loss = float(lt[args.steps - 1].item())
+    value = global_batch * args.steps / (ms / 1e3)
+
+    # ---- roofline: per-kernel device times over the same steps (events on the launch stream) ----
+    tr.kernel_timing(True)
+    tsteps = min(args.steps, 200)
+    tr.train_steps(x_pool, y_pool, batch, tsteps, first_row=0, lr=LR)
+    kt = tr.kernel_times()
+    tr.kernel_timing(False)
+    dom = max(kt.items(), key=lambda kv: kv[1][0])
+    dom_ms = dom[1][0] / dom[1][1]
+    total_ms = sum(v[0] for v in kt.values())
+    peak, peak_src = _peaks()
+    achieved = batch * BYTES_PER_SAMPLE / (dom_ms / 1e3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": _traffic_bytes(args.workload), "kernel": dom[0], "kernel_ms": dom_ms,
+                "kernel_share_of_step": dom[1][0] / total_ms, "peak_source": "of " + peak_src,
+                "algorithmic_bytes_per_launch": batch * BYTES_PER_SAMPLE,
+                "kernel_ms_by_class": {k: v[0] / v[1] for k, v in kt.items()}}
+
+    # ---- e2e: host feeds through the sess.run-shaped call ------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        in_b, out_b = batch * dims[0] * 4, batch * dims[-1] * 4
+        feeds = []
+        for i in range(2):
+            fx = torch.empty(batch, dims[0], dtype=torch.float32).pin_memory()
+            fy = torch.empty(batch, dims[-1], dtype=torch.float32).pin_memory()
+            src = slice((i * batch) % HOST_POOL_ROWS, (i * batch) % HOST_POOL_ROWS + batch)
+            n = min(batch, HOST_POOL_ROWS)
+            fx[:n].copy_(torch.from_numpy(hx[src][:n]) if batch <= HOST_POOL_ROWS else torch.from_numpy(hx[:n]))
+            fy[:n].copy_(torch.from_numpy(hy[src][:n]) if batch <= HOST_POOL_ROWS else torch.from_numpy(hy[:n]))
+            feeds.append((fx, fy))
+        esteps = max(5, min(args.steps, 50))
+        for i in range(3):
+            tr.run_train(feeds[i % 2][0], feeds[i % 2][1], LR)
+        barrier()
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        for i in range(esteps):
+            tr.run_train(feeds[i % 2][0], feeds[i % 2][1], LR)
+        torch.cuda.synchronize(dev)
+        dt = max_over_ranks(time.perf_counter() - t0)
+        e2e = {"value": global_batch * esteps / dt, "unit": "samples/s", "h2d_bytes_per_step": in_b + out_b,
+               "d2h_bytes_per_step": 8, "steps": esteps, "ms_per_step": 1e3 * dt / esteps,
+               "api": "DenseTrainer.run_train -> b2_session_run_train (pinned host feeds, synchronous)"}
+
+    # ---- cpu_baseline: rank 0, N=1 only, bounded sample -----------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        r = cpu_reference_run(dims, act, loss, scaled, batch, 400, 2, budget_s=12.0)
+        cpu = {"value": r["value"], "unit": "samples/s", "cores": r["threads"], "kind": "port",
+               "sample": "%d steps of %d rows in %.1f s, torch-CPU restatement of the TF1 graph, all host threads"
+                         % (r["steps"], batch, r["seconds"]),
+               "first_loss_cpu": r["first_loss"], "first_loss_gpu": first_loss}
+
+    if rank == 0:
+        line = {"metric": "training samples/sec", "value": value, "unit": "samples/s", "n_gpus": world,
+                "steps": args.steps, "warmup": warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
+                "gpu_launches": launches, "loss_first": first_loss, "loss_last": last_loss}
+        print(json.dumps(line))
+    tr.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -50,7 +50,21 @@ enum { B2_PREC_FP32 = 0, B2_PREC_BF16_FP32ACC = 1 };       /* BASELINE.json conf
 
 /* Engine selection knobs for b2_set_option (tests cross-check the paths against each other). */
 enum {
-  B2_OPT_FORCE_LAYERED = 1   /* value 1: never use the single-kernel fused step, even when the shape allows it */
+  B2_OPT_FORCE_LAYERED = 1,  /* value 1: never use the single-kernel fused step, even when the shape allows it */
+  B2_OPT_KERNEL_TIMING = 2   /* value 1: bracket every kernel launch with CUDA events (see b2_kernel_times) */
+};
+
+/* Kernel classes reported by b2_kernel_times. */
+enum {
+  B2_K_DENSE_FWD = 0,     /* matmul + bias + activation            distributed.py:96-98 */
+  B2_K_LOSS_HEAD = 1,     /* softmax-CE / SSE forward + backward   distributed.py:99-102,117-118; simple.py:20 */
+  B2_K_WGRAD = 2,         /* dW = A^T dZ, db = colsum(dZ)          TF1 MatMul / BiasAdd gradients */
+  B2_K_DGRAD = 3,         /* dA = dZ W^T * act'                    TF1 MatMul / Sigmoid gradients */
+  B2_K_REDUCE_APPLY = 4,  /* fixed-order partial sums (+ SGD)      distributed.py:107-108 */
+  B2_K_FUSED_STEP = 5,    /* single-kernel 784->10 step */
+  B2_K_FUSED_REDUCE = 6,  /* its partial reduction (+ SGD) */
+  B2_K_ALLREDUCE_APPLY = 7, /* gradient all-reduce + SGD apply (data parallel only) */
+  B2_KERNEL_CLASSES = 8
 };
 
 #define B2_UNIQUE_ID_BYTES 128
@@ -131,6 +145,15 @@ int b2_session_run_train(b2_ctx* ctx, const float* x_host, const float* y_host, 
 
 /* The float32 `global_step` variable (distributed.py:68-70,108) as of the last enqueued step. */
 float b2_global_step(const b2_ctx* ctx);
+
+/*
+ * Device time per kernel class since the last call, measured with CUDA events on the stream the
+ * kernels were launched on, while B2_OPT_KERNEL_TIMING is on.  Synchronises.  Replaces the
+ * wall-clock deltas the reference prints (distributed.py:155-161 "Time spent (delta)") with
+ * per-kernel figures for the roofline report.  ms_total and launches have B2_KERNEL_CLASSES entries.
+ */
+int b2_kernel_times(b2_ctx* ctx, float* ms_total, long* launches);
+const char* b2_kernel_class_name(int kernel_class);
 
 /* How many of this library's kernels the context has launched so far (bench.py's gpu_launches). */
 long b2_launch_count(const b2_ctx* ctx);

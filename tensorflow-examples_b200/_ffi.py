@@ -10,11 +10,13 @@ _LIB = None
 EXPORTS = [
     "b2_version", "b2_last_error", "b2_create", "b2_destroy", "b2_set_option", "b2_param_count",
     "b2_params_set", "b2_params_get", "b2_get_unique_id", "b2_comm_init", "b2_train_steps", "b2_eval",
-    "b2_session_run_train", "b2_global_step", "b2_launch_count",
+    "b2_session_run_train", "b2_global_step", "b2_launch_count", "b2_kernel_times", "b2_kernel_class_name",
 ]
 
 UNIQUE_ID_BYTES = 128
 OPT_FORCE_LAYERED = 1
+OPT_KERNEL_TIMING = 2
+KERNEL_CLASSES = 8
 
 
 class B2Error(RuntimeError):
@@ -71,6 +73,10 @@ def load_library():
     lib.b2_global_step.restype = c_float
     lib.b2_launch_count.argtypes = [c_void_p]
     lib.b2_launch_count.restype = c_long
+    lib.b2_kernel_times.argtypes = [c_void_p, ctypes.POINTER(c_float), ctypes.POINTER(c_long)]
+    lib.b2_kernel_times.restype = c_int
+    lib.b2_kernel_class_name.argtypes = [c_int]
+    lib.b2_kernel_class_name.restype = ctypes.c_char_p
     _LIB = lib
     return lib
 

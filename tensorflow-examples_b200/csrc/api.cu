@@ -87,6 +87,29 @@ inline long w_size(const b2_ctx* c, int l) { return (long)c->dims[l] * c->dims[l
 inline long b_size(const b2_ctx* c, int l) { return c->dims[l + 1]; }
 inline long part_stride(const b2_ctx* c, int l) { return round4(w_size(c, l)) + round4(b_size(c, l)); }
 
+constexpr int kMaxTimed = 16384;
+
+// Records an event pair around one launch when timing is on.  Past kMaxTimed launches it stops recording.
+struct timed_scope {
+  b2_ctx* c; cudaStream_t s; int idx;
+  timed_scope(b2_ctx* c_, int cls, cudaStream_t s_) : c(c_), s(s_), idx(-1) {
+    if (!c->opt_timing || c->n_timed >= kMaxTimed) return;
+    if (!c->timed) {
+      c->timed = (b2_timed*)calloc(kMaxTimed, sizeof(b2_timed));
+      if (!c->timed) return;
+    }
+    if (c->n_timed >= c->cap_timed) {
+      b2_timed& t = c->timed[c->cap_timed];
+      if (cudaEventCreate(&t.a) != cudaSuccess || cudaEventCreate(&t.b) != cudaSuccess) return;
+      c->cap_timed++;
+    }
+    idx = c->n_timed++;
+    c->timed[idx].cls = cls;
+    cudaEventRecord(c->timed[idx].a, s);
+  }
+  ~timed_scope() { if (idx >= 0) cudaEventRecord(c->timed[idx].b, s); }
+};
+
 bool use_fused_linear(const b2_ctx* c) {
   return !c->opt_force_layered && c->precision == B2_PREC_FP32 && c->n_layers == 1 &&
          b2_fused_linear_supported(c->dims[0], c->dims[1], c->loss);
@@ -99,15 +122,23 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
   const float* a_in = x;
   for (int l = 0; l < n; ++l) {
     float* out = (l == n - 1) ? c->z_last : c->act_buf[l];
-    int rc = b2_launch_dense_fwd(a_in, c->params + c->w_off[l], c->params + c->b_off[l], out, rows,
-                                 c->dims[l + 1], c->dims[l], (l == n - 1) ? B2_ACT_IDENTITY : c->act, s);
+    int rc;
+    {
+      timed_scope t(c, B2_K_DENSE_FWD, s);
+      rc = b2_launch_dense_fwd(a_in, c->params + c->w_off[l], c->params + c->b_off[l], out, rows,
+                               c->dims[l + 1], c->dims[l], (l == n - 1) ? B2_ACT_IDENTITY : c->act, s);
+    }
     if (rc) return rc;
     c->launches++;
     a_in = out;
   }
   float* head = c->scratch + c->head_part_off;
-  int rc = b2_launch_loss_head(c->z_last, y, c->dz[0], head, head + c->head_blocks, rows, c->dims[n],
-                               c->loss, inv_B, c->head_blocks, s);
+  int rc;
+  {
+    timed_scope t(c, B2_K_LOSS_HEAD, s);
+    rc = b2_launch_loss_head(c->z_last, y, c->dz[0], head, head + c->head_blocks, rows, c->dims[n],
+                             c->loss, inv_B, c->head_blocks, s);
+  }
   if (rc) return rc;
   c->launches++;
   if (!train) return B2_OK;
@@ -121,13 +152,19 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
     splits_used[l] = sp;
     float* pw = c->scratch + c->part_off[l];
     float* pb = pw + round4(w_size(c, l));
-    rc = b2_launch_wgrad(a_prev, c->dz[cur], pw, pb, part_stride(c, l), rows, c->dims[l],
-                         c->dims[l + 1], sp, s);
+    {
+      timed_scope t(c, B2_K_WGRAD, s);
+      rc = b2_launch_wgrad(a_prev, c->dz[cur], pw, pb, part_stride(c, l), rows, c->dims[l],
+                           c->dims[l + 1], sp, s);
+    }
     if (rc) return rc;
     c->launches++;
     if (l > 0) {
-      rc = b2_launch_dgrad(c->dz[cur], c->params + c->w_off[l], c->act_buf[l - 1], c->dz[cur ^ 1], rows,
-                           c->dims[l], c->dims[l + 1], c->act, s);
+      {
+        timed_scope t(c, B2_K_DGRAD, s);
+        rc = b2_launch_dgrad(c->dz[cur], c->params + c->w_off[l], c->act_buf[l - 1], c->dz[cur ^ 1], rows,
+                             c->dims[l], c->dims[l + 1], c->act, s);
+      }
       if (rc) return rc;
       c->launches++;
       cur ^= 1;
@@ -145,11 +182,17 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
   if (use_fused_linear(c)) {
     int grid = (rows + 31) / 32;
     if (grid > c->fused_grid) grid = c->fused_grid;
-    rc = b2_launch_fused_linear_step(x, y, rows, c->params + c->w_off[0], c->params + c->b_off[0],
-                                     c->fused_scratch, grid, inv_B, s);
+    {
+      timed_scope t(c, B2_K_FUSED_STEP, s);
+      rc = b2_launch_fused_linear_step(x, y, rows, c->params + c->w_off[0], c->params + c->b_off[0],
+                                       c->fused_scratch, grid, inv_B, s);
+    }
     if (rc) return rc;
-    rc = b2_launch_fused_linear_reduce(c->fused_scratch, grid, c->grads, c->params, apply, lr,
-                                       loss_trace, correct_trace, c->global_step_dev, c->P, s);
+    {
+      timed_scope t(c, B2_K_FUSED_REDUCE, s);
+      rc = b2_launch_fused_linear_reduce(c->fused_scratch, grid, c->grads, c->params, apply, lr,
+                                         loss_trace, correct_trace, c->global_step_dev, c->P, s);
+    }
     if (rc) return rc;
     c->launches += 2;
   } else {
@@ -168,14 +211,18 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
     a.P = c->P;
     a.head_part_off = c->head_part_off;
     a.head_blocks = c->head_blocks;
-    rc = b2_launch_reduce(a, c->scratch, c->grads, c->params, apply, lr, loss_trace, correct_trace,
-                          c->global_step_dev, c->sm_count, s);
+    {
+      timed_scope t(c, B2_K_REDUCE_APPLY, s);
+      rc = b2_launch_reduce(a, c->scratch, c->grads, c->params, apply, lr, loss_trace, correct_trace,
+                            c->global_step_dev, c->sm_count, s);
+    }
     if (rc) return rc;
     c->launches++;
   }
   if (!apply) {
     // the parameter-server push/pull of the reference (distributed.py:63-65) becomes one
     // all-reduce of [gradients..., loss, correct]; every rank then applies the same update.
+    timed_scope t(c, B2_K_ALLREDUCE_APPLY, s);
     B2_NCCL(g_nccl.AllReduce(c->grads, c->grads, (size_t)(c->P + 4), kNcclFloat, kNcclSum, c->nccl_comm, s));
     rc = b2_launch_sgd_apply(c->params, c->grads, c->P, lr, loss_trace, correct_trace,
                              c->global_step_dev, c->sm_count, s);
@@ -204,6 +251,10 @@ void free_ctx(b2_ctx* c) {
   cudaFree(c->fetch_dev);
   if (c->fetch_host) cudaFreeHost(c->fetch_host);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  if (c->timed) {
+    for (int i = 0; i < c->cap_timed; ++i) { cudaEventDestroy(c->timed[i].a); cudaEventDestroy(c->timed[i].b); }
+    free(c->timed);
+  }
   free(c);
 }
 
@@ -332,6 +383,7 @@ extern "C" int b2_set_option(b2_ctx* ctx, int option, int value) {
   B2_CHECK_ARG(ctx != nullptr, "b2_set_option: ctx is NULL");
   switch (option) {
     case B2_OPT_FORCE_LAYERED: ctx->opt_force_layered = value ? 1 : 0; return B2_OK;
+    case B2_OPT_KERNEL_TIMING: ctx->opt_timing = value ? 1 : 0; return B2_OK;
     default: b2_set_error("b2_set_option: unknown option %d", option); return B2_ERR_ARG;
   }
 }
@@ -345,6 +397,27 @@ extern "C" long b2_param_count(const b2_ctx* ctx) {
 
 extern "C" float b2_global_step(const b2_ctx* ctx) { return ctx ? ctx->global_step_host : 0.f; }
 extern "C" long b2_launch_count(const b2_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" const char* b2_kernel_class_name(int k) {
+  static const char* names[B2_KERNEL_CLASSES] = {"dense_fwd", "loss_head", "wgrad", "dgrad", "reduce_apply",
+                                                 "fused_linear_step", "fused_linear_reduce", "allreduce_apply"};
+  return (k >= 0 && k < B2_KERNEL_CLASSES) ? names[k] : "?";
+}
+
+extern "C" int b2_kernel_times(b2_ctx* ctx, float* ms_total, long* launches) {
+  B2_CHECK_ARG(ctx && ms_total && launches, "b2_kernel_times: NULL argument");
+  for (int k = 0; k < B2_KERNEL_CLASSES; ++k) { ms_total[k] = 0.f; launches[k] = 0; }
+  B2_CUDA(cudaSetDevice(ctx->device));
+  for (int i = 0; i < ctx->n_timed; ++i) {
+    float ms = 0.f;
+    B2_CUDA(cudaEventSynchronize(ctx->timed[i].b));
+    B2_CUDA(cudaEventElapsedTime(&ms, ctx->timed[i].a, ctx->timed[i].b));
+    ms_total[ctx->timed[i].cls] += ms;
+    launches[ctx->timed[i].cls] += 1;
+  }
+  ctx->n_timed = 0;
+  return B2_OK;
+}
 
 // ---------------------------------------------------------------------------------------------
 // parameters

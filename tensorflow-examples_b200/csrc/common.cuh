@@ -73,7 +73,13 @@ struct b2_ctx {
   // data parallel
   int rank, nranks;
   void* nccl_comm;
+
+  // optional per-kernel event timing (B2_OPT_KERNEL_TIMING)
+  int opt_timing;
+  struct b2_timed* timed;
+  int n_timed, cap_timed;
 };
+struct b2_timed { cudaEvent_t a, b; int cls; };
 
 // ---- launchers (kernels_layered.cu) --------------------------------------------------------------
 // C[M,N] = act(A[M,K] @ W[K,N] + bias[N])

@@ -71,6 +71,18 @@ class DenseTrainer:
         """Use the per-layer kernels even where a fused single-kernel step exists (for cross-checks)."""
         self.set_option(_ffi.OPT_FORCE_LAYERED, 1 if on else 0)
 
+    def kernel_timing(self, on=True):
+        """Bracket every kernel launch with CUDA events (read them back with kernel_times())."""
+        self.set_option(_ffi.OPT_KERNEL_TIMING, 1 if on else 0)
+
+    def kernel_times(self):
+        """{kernel class: (total ms, launches)} since the last call.  Synchronises."""
+        ms = (ctypes.c_float * _ffi.KERNEL_CLASSES)()
+        n = (ctypes.c_long * _ffi.KERNEL_CLASSES)()
+        _ffi.check(self._lib, self._lib.b2_kernel_times(self._h, ms, n))
+        return {self._lib.b2_kernel_class_name(k).decode(): (float(ms[k]), int(n[k]))
+                for k in range(_ffi.KERNEL_CLASSES) if n[k]}
+
     @property
     def param_count(self):
         return int(self._lib.b2_param_count(self._h))

@@ -148,3 +148,19 @@ def test_unfused_log_softmax_nan_is_reproduced():
     g = oracle.TF1Graph([1, 2], oracle.ACT_IDENTITY, oracle.LOSS_SOFTMAX_CE, [[[0.0, 200.0]]], [[0.0, 0.0]])
     loss, _ = g.evaluate(np.array([[1.0]], np.float32), np.array([[0.0, 1.0]], np.float32))
     assert np.isnan(loss)
+
+
+def test_torch_cpu_baseline_matches_numpy_oracle():
+    from oracle.torch_cpu import TorchCPUGraph
+    dims, batch, steps = [784, 100, 10], 100, 5
+    x, y = synthetic.make_pool(batch * steps)
+    Ws, bs = synthetic.make_weights(dims, False)
+    a = oracle.TF1Graph(dims, oracle.ACT_SIGMOID, oracle.LOSS_SOFTMAX_CE, Ws, bs)
+    b = TorchCPUGraph(dims, oracle.ACT_SIGMOID, oracle.LOSS_SOFTMAX_CE, Ws, bs)
+    xt, yt = torch.from_numpy(x), torch.from_numpy(y)
+    for s in range(steps):
+        sl = slice(s * batch, (s + 1) * batch)
+        la, ca = a.train_step(x[sl], y[sl], 0.001)
+        lb, cb = b.train_step(xt[sl], yt[sl], 0.001)
+        assert abs(float(la) - lb) <= 1e-5 * abs(float(la)) and ca == cb
+    np.testing.assert_allclose(a.W[0], b.W[0].numpy(), rtol=1e-4, atol=1e-5)
