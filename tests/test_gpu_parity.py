@@ -93,10 +93,15 @@ def test_c2_784_100_10_b100_trace(cuda_device):
     Ws, bs = synthetic.make_weights(dims, scaled=False)
     got = _run_case(cuda_device, dims, pkg.ACT_SIGMOID, pkg.LOSS_SOFTMAX_CE, Ws, bs, x, y, batch, steps, lr)
     _check_against_oracle(dims, oracle.ACT_SIGMOID, oracle.LOSS_SOFTMAX_CE, Ws, bs, x, y, batch, steps, lr, got)
+    # the committed fixture (20 steps over a 20-batch pool: the label stream depends on the pool size)
     f = np.load(os.path.join(GOLDEN, "c2_784_100_10_b100.npz"))
     n = len(f["loss32"])
-    np.testing.assert_allclose(got[0][:n], f["loss32"], rtol=LOSS_RTOL)
-    np.testing.assert_array_equal(got[1][:n], f["correct32"])
+    x, y = synthetic.make_pool(batch * n)
+    got = _run_case(cuda_device, dims, pkg.ACT_SIGMOID, pkg.LOSS_SOFTMAX_CE, Ws, bs, x, y, batch, n, lr)
+    np.testing.assert_allclose(got[0], f["loss32"], rtol=LOSS_RTOL)
+    np.testing.assert_array_equal(got[1], f["correct32"])
+    np.testing.assert_allclose(got[3][0], f["b0"], rtol=1e-4, atol=1e-7)
+    np.testing.assert_allclose(got[2][0][::16], f["W0_rows16"], rtol=1e-4, atol=1e-6)
 
 
 # ---- config 3: 784 -> 10, fused single-kernel step ----------------------------------------------------
@@ -111,8 +116,11 @@ def test_c3_784_10_b256_trace_fused_and_layered(cuda_device):
     _check_against_oracle(dims, oracle.ACT_IDENTITY, oracle.LOSS_SOFTMAX_CE, Ws, bs, x, y, batch, steps, lr, layered)
     f = np.load(os.path.join(GOLDEN, "c3_784_10_b256.npz"))
     n = len(f["loss32"])
-    np.testing.assert_allclose(fused[0][:n], f["loss32"], rtol=LOSS_RTOL)
-    np.testing.assert_array_equal(fused[1][:n], f["correct32"])
+    x, y = synthetic.make_pool(batch * n)
+    fused = _run_case(cuda_device, dims, pkg.ACT_IDENTITY, pkg.LOSS_SOFTMAX_CE, Ws, bs, x, y, batch, n, lr)
+    np.testing.assert_allclose(fused[0], f["loss32"], rtol=LOSS_RTOL)
+    np.testing.assert_array_equal(fused[1], f["correct32"])
+    np.testing.assert_allclose(fused[2][0][::16], f["W0_rows16"], rtol=1e-4, atol=1e-6)
 
 
 @pytest.mark.parametrize("batch", [1, 7, 8, 31, 32, 33, 100, 255, 1000, 4736 + 5])
