@@ -143,6 +143,33 @@ int b2_eval(b2_ctx* ctx, const void* x_dev, const void* y_dev, long rows, float*
 int b2_session_run_train(b2_ctx* ctx, const float* x_host, const float* y_host, int rows, float lr,
                          float* loss_out, int* correct_out);
 
+/*
+ * One training step of the 784 -> 10 softmax cross-entropy model that allocates nothing.
+ * NO COUNTERPART IN THE REFERENCE: this exists for callers that cannot call cudaMalloc -- a plugin
+ * running inside another framework's execution callback (that framework owns the allocator), a
+ * latency-critical loop that cannot take the device-wide synchronisation an allocation implies, or
+ * a host whose own memory pool already holds all of the device memory.  b2_create() allocates, so
+ * those callers use this instead and pass every input and output themselves:
+ *   x_dev [rows,784], y_dev [rows,10]   this call's batch (device, float32, row-major)
+ *   W_dev [784,10], b_dev [10]          parameters, updated IN PLACE: var -= lr * grad
+ *   loss_dev [1], correct_dev [1]       pre-update mean loss and correct-row count (either may be NULL)
+ *   global_batch                        the divisor of the loss mean (= rows on a single GPU)
+ * The step kernel's scratch (per-CTA partial sums) is a fixed array inside the library image:
+ * 160 slots x 7856 floats = 5,027,840 bytes, which every GPU that loads the library holds until the
+ * process exits.  LIMITS: at most 160 CTAs are used (the kernel loops over tiles, so more SMs are not
+ * an error) and rows must be <= 1,048,576 per call; a larger rows is rejected with B2_ERR_ARG.
+ * The first call on each device looks up the array's device address and opts the kernel into its
+ * shared-memory size; make that first call with the device current and BEFORE starting any stream
+ * capture.  Later calls only launch two kernels on `stream`; no cudaMalloc/cudaFree, no library
+ * allocation.  All calls on a device share the array and it keeps the last call's contents (nothing
+ * needs clearing: each call overwrites every entry it later reads).  Calls whose kernels can overlap
+ * on the GPU -- different streams, or different host threads -- race on it; serialise them on one
+ * stream.  Not thread-safe.
+ */
+int b2_linear_step_noalloc(const float* x_dev, const float* y_dev, int rows, long global_batch, float lr,
+                           float* W_dev, float* b_dev, float* loss_dev, int* correct_dev,
+                           b2_stream_t stream);
+
 /* The float32 `global_step` variable (distributed.py:68-70,108) as of the last enqueued step. */
 float b2_global_step(const b2_ctx* ctx);
 

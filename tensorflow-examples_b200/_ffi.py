@@ -11,6 +11,7 @@ EXPORTS = [
     "b2_version", "b2_last_error", "b2_create", "b2_destroy", "b2_set_option", "b2_param_count",
     "b2_params_set", "b2_params_get", "b2_get_unique_id", "b2_comm_init", "b2_train_steps", "b2_eval",
     "b2_session_run_train", "b2_global_step", "b2_launch_count", "b2_kernel_times", "b2_kernel_class_name",
+    "b2_linear_step_noalloc",
 ]
 
 UNIQUE_ID_BYTES = 128
@@ -77,6 +78,9 @@ def load_library():
     lib.b2_kernel_times.restype = c_int
     lib.b2_kernel_class_name.argtypes = [c_int]
     lib.b2_kernel_class_name.restype = ctypes.c_char_p
+    lib.b2_linear_step_noalloc.argtypes = [c_void_p, c_void_p, c_int, c_long, c_float, c_void_p, c_void_p,
+                                           c_void_p, c_void_p, c_void_p]
+    lib.b2_linear_step_noalloc.restype = c_int
     _LIB = lib
     return lib
 

@@ -380,3 +380,108 @@ int b2_launch_fused_linear_reduce(const float* scratch, int grid, float* grads, 
   }
   return B2_OK;
 }
+
+// =============================================================================================
+// b2_linear_step_noalloc: the same 784 -> 10 training step for callers that must not allocate.
+//
+// Who needs this: code that runs where device allocation is off limits -- a plugin called from
+// inside another framework's execution callback (which owns the allocator and forbids re-entrant
+// cudaMalloc), a latency-critical loop that cannot afford the implicit device synchronisation
+// cudaMalloc/cudaFree cause, or a host that has handed the whole device memory to its own pool
+// and leaves nothing for cudaMalloc to find.  Those callers cannot use b2_create(), which
+// allocates parameters, gradients and scratch.  Here the caller passes every input and output,
+// and the one piece of scratch the step kernel needs -- the per-CTA partial sums -- lives in the
+// file-scope device array below, which is part of the loaded library image.
+//
+// Consequences of that choice, all documented in include/b2mlp.h:
+//   * the array has a fixed size (B2_NOALLOC_MAX_CTAS slots); every GPU that loads the library
+//     holds these bytes until the process exits, used or not;
+//   * every call on a device shares it, so two calls whose kernels overlap on the GPU (different
+//     streams, or different host threads) race on it; calls on one stream are safe;
+//   * it keeps the previous call's contents.  Nothing has to be cleared: the step kernel writes
+//     every slot entry that the reduction of the same call reads (7852 floats x grid CTAs).
+// =============================================================================================
+#define B2_NOALLOC_MAX_CTAS 160
+#define B2_NOALLOC_MAX_ROWS (1 << 20)
+#define B2_NOALLOC_MAX_DEVICES 64
+
+// 160 x 7856 floats = 5,027,840 bytes per GPU.
+static __device__ __align__(256) float g_noalloc_scratch[B2_NOALLOC_MAX_CTAS * fl::SCRATCH_STRIDE];
+
+namespace fl {
+
+// Sums the per-CTA partials (read straight from the static array, which device code may name
+// directly) in CTA order and applies plain gradient descent to the caller's W and b.
+__global__ void __launch_bounds__(128)
+noalloc_reduce_apply_kernel(int grid, float* __restrict__ W, float* __restrict__ b, float lr,
+                            float* __restrict__ loss_out, int* __restrict__ correct_out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 7852) return;
+  const float* p = g_noalloc_scratch + i;
+  float g = 0.f;
+  int c = 0;
+  for (; c + 8 <= grid; c += 8) {
+    float v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = p[(size_t)(c + u) * SCRATCH_STRIDE];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) g += v[u];
+  }
+  for (; c < grid; ++c) g += p[(size_t)c * SCRATCH_STRIDE];
+  if (i < K * NC) W[i] -= lr * g;
+  else if (i < K * NC + NC) b[i - K * NC] -= lr * g;
+  else if (i == LOSS_IDX) { if (loss_out) *loss_out = g; }
+  else { if (correct_out) *correct_out = (int)(g + 0.5f); }
+}
+
+struct noalloc_device_state {
+  float* scratch;  // DEVICE address of g_noalloc_scratch on this device (0 = set-up not done yet)
+  int sm_count;
+};
+static noalloc_device_state g_noalloc_dev[B2_NOALLOC_MAX_DEVICES];
+
+}  // namespace fl
+
+extern "C" int b2_linear_step_noalloc(const float* x_dev, const float* y_dev, int rows, long global_batch,
+                                      float lr, float* W_dev, float* b_dev, float* loss_dev,
+                                      int* correct_dev, b2_stream_t stream) {
+  B2_CHECK_ARG(x_dev && y_dev && W_dev && b_dev, "b2_linear_step_noalloc: NULL x, y, W or b");
+  B2_CHECK_ARG(rows >= 1, "b2_linear_step_noalloc: rows must be >= 1, got %d", rows);
+  B2_CHECK_ARG(rows <= B2_NOALLOC_MAX_ROWS,
+               "b2_linear_step_noalloc: rows %d exceeds the fixed-scratch limit of %d rows per call; "
+               "split the batch or use b2_create()/b2_train_steps()", rows, B2_NOALLOC_MAX_ROWS);
+  B2_CHECK_ARG(global_batch >= rows, "b2_linear_step_noalloc: global_batch %ld < rows %d", global_batch, rows);
+  int dev = -1;
+  B2_CUDA(cudaGetDevice(&dev));
+  B2_CHECK_ARG(dev >= 0 && dev < B2_NOALLOC_MAX_DEVICES, "b2_linear_step_noalloc: device index %d not supported", dev);
+  fl::noalloc_device_state& st = fl::g_noalloc_dev[dev];
+  if (!st.scratch) {
+    // One-time set-up for the CURRENT device.  In host code `g_noalloc_scratch` is only a stand-in
+    // for the symbol, not an address the GPU can use, so ask the runtime where the array lives on
+    // this device and hand that pointer to the kernel.
+    int major = 0, sms = 0;
+    B2_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+    B2_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    if (major != 10) {
+      b2_set_error("b2_linear_step_noalloc: device %d is not sm_100 (B200)", dev);
+      return B2_ERR_CUDA;
+    }
+    float* ptr = nullptr;
+    B2_CUDA(cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch));
+    B2_CUDA(cudaFuncSetAttribute(fl::fused_linear_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)sizeof(fl::Smem)));
+    st.sm_count = sms;
+    st.scratch = ptr;
+  }
+  int grid = (rows + fl::TILE_ROWS - 1) / fl::TILE_ROWS;
+  if (grid > st.sm_count) grid = st.sm_count;
+  if (grid > B2_NOALLOC_MAX_CTAS) grid = B2_NOALLOC_MAX_CTAS;  // the persistent kernel loops over tiles
+  cudaStream_t s = (cudaStream_t)stream;
+  const float inv_B = 1.0f / (float)global_batch;
+  fl::fused_linear_step_kernel<<<grid, fl::THREADS, (int)sizeof(fl::Smem), s>>>(x_dev, y_dev, rows, W_dev, b_dev,
+                                                                              st.scratch, inv_B);
+  B2_CUDA(cudaGetLastError());
+  fl::noalloc_reduce_apply_kernel<<<(7852 + 127) / 128, 128, 0, s>>>(grid, W_dev, b_dev, lr, loss_dev, correct_dev);
+  B2_CUDA(cudaGetLastError());
+  return B2_OK;
+}
