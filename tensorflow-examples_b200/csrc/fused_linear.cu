@@ -4,13 +4,17 @@
 // cp.async.bulk into shared memory and used twice from there -- for the logits
 // (distributed.py:98 z = x@W + b) and for the weight gradient (TF1 MatMul grad, dW = x^T dz).
 //
-//   persistent grid, one CTA per SM, 15 warps:
-//     warp 14        producer: bulk-copies rows (8-row stages, 6-stage ring) + stages the labels
-//     warps 0..13    forward:  lane = row of a 32-row tile, warp = 56-wide slice of the 784 inputs,
-//                              W ([784][12] fp32, zero padded) broadcast from shared memory
-//                    head:     softmax / loss / accuracy / dz with half-warp shuffle reductions
-//                    backward: thread = (4 inputs, 5 classes), 20 register accumulators kept for
-//                              the whole kernel; rows stream from shared memory
+//   persistent grid, one CTA per SM, 15 warps, 32-row tiles:
+//     warp 14        producer: bulk-copies rows and labels (8-row stages, 7-stage ring, mbarrier tx counts);
+//                    it starts streaming before the weight tile is staged
+//     warps 0..13    forward:  warp = (16-row half of the tile) x (112-wide slice of the 784 inputs);
+//                              lane = (4 input sub-slices) x (8 row pairs): 2 rows x 10 classes per thread,
+//                              packed fp32x2 FMAs (FFMA2) over input pairs, W staged in shared memory as
+//                              [input pair][class][2] so both FFMA2 operands are natural 64-bit pairs
+//                    head:     7 partial sums per logit, then softmax / loss / accuracy / dz with
+//                              10-lane shuffle reductions (three rows per warp, one pass)
+//                    backward: thread = (4 inputs, 5 classes), 10 packed accumulators kept for the whole
+//                              kernel; rows stream from shared memory, dz pre-duplicated as (d,d) pairs
 //   each CTA ends by writing its partial dW / db / loss / correct to scratch[cta][7856];
 //   fused_linear_reduce_kernel sums the partials in CTA order (no float atomics) and applies SGD.
 #include <math.h>
@@ -19,29 +23,35 @@
 
 namespace fl {
 
-constexpr int K = 784, NC = 10, NCP = 12;
-constexpr int TILE_ROWS = 32, STAGE_ROWS = 8, STAGES_PER_TILE = 4, NSTAGES = 6;
+constexpr int K = 784, NC = 10;
+constexpr int TILE_ROWS = 32, STAGE_ROWS = 8, STAGES_PER_TILE = 4, NSTAGES = 7;
 constexpr int XSTRIDE = 788;  // floats per staged row: 3152 B, keeps 16 B alignment, conflict-free LDS.128
 constexpr int COMPUTE_WARPS = 14, COMPUTE_THREADS = COMPUTE_WARPS * 32, THREADS = COMPUTE_THREADS + 32;
-constexpr int KW = K / COMPUTE_WARPS;  // 56 inputs per warp in the forward pass
-constexpr int KGROUPS = K / 4;         // 196 groups of 4 inputs in the backward pass
-constexpr int ROW_BYTES = K * 4;       // 3136
-constexpr long SCRATCH_STRIDE = 7856;  // 7840 dW + 10 db + loss + correct, padded to 16 B
+constexpr int KSLICES = 7, KW = K / KSLICES;  // forward: 7 slices of 112 inputs (28 quads, 7 per lane sub-slice)
+constexpr int KGROUPS = K / 4;                // backward: 196 groups of 4 inputs
+constexpr int ROW_BYTES = K * 4;              // 3136
+constexpr int PART_ROW = 11;                  // floats per row of a partial-logit set (odd: conflict-free)
+constexpr int PART_SET = TILE_ROWS * PART_ROW;
+constexpr int DZ_ROW = 24;                    // floats per row of duplicated dz: class c at (c/5)*12 + (c%5)*2
+constexpr long SCRATCH_STRIDE = 7856;         // 7840 dW + 10 db + loss + correct, padded to 16 B
 constexpr int LOSS_IDX = 7850, CORRECT_IDX = 7851;
 
 struct __align__(16) Smem {
-  float W[K * NCP];                            // 37632 B
-  float x[NSTAGES * STAGE_ROWS * XSTRIDE];     // 151296 B
-  float part[COMPUTE_WARPS * NC * TILE_ROWS];  // 17920 B   part[warp][class][row]
-  float ys[NSTAGES * STAGE_ROWS * NC];         // 1920 B
-  float dz[TILE_ROWS * 16];                    // class c of row r at r*16 + (c/5)*8 + c%5
+  float Wp[K * NC];                            // 31360 B   [k/2][class][k&1]
+  float x[NSTAGES * STAGE_ROWS * XSTRIDE];     // 176512 B
+  float part[KSLICES * PART_SET];              // 9856 B    part[slice][row][class]
+  float ys[NSTAGES * STAGE_ROWS * NC];         // 2240 B
+  float dz2[TILE_ROWS * DZ_ROW];               // 3072 B
   float bias[16];
-  float red_db[COMPUTE_WARPS * 2 * 16];
-  float red_loss[COMPUTE_WARPS * 2];
-  float red_corr[COMPUTE_WARPS * 2];
+  float red_db[COMPUTE_WARPS * 32];
+  float red_loss[COMPUTE_WARPS * 4];
+  float red_corr[COMPUTE_WARPS * 4];
   unsigned long long full[NSTAGES];
   unsigned long long empty[NSTAGES];
 };
+static_assert(sizeof(Smem) <= 232448, "shared memory budget");
+
+typedef unsigned long long u64;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
@@ -85,24 +95,49 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 __device__ __forceinline__ void compute_bar() {
   asm volatile("bar.sync 1, %0;" ::"n"(COMPUTE_THREADS) : "memory");
 }
+// packed fp32x2 FMA (SASS FFMA2): d.lo = a.lo*b.lo + c.lo, d.hi = a.hi*b.hi + c.hi
+__device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c) {
+  u64 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ u64 pack2(float lo, float hi) {
+  u64 d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi));
+  return d;
+}
+__device__ __forceinline__ void unpack2(u64 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
 
-__device__ __forceinline__ float half_sum(float v) {
-#pragma unroll
-  for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
+// reductions over a group of 10 consecutive lanes (idx = position in the group, base = first lane)
+__device__ __forceinline__ float g10_sum(float v, int idx, int base) {
+  float o;
+  o = __shfl_down_sync(0xffffffffu, v, 8); v += (idx < 2) ? o : 0.f;
+  o = __shfl_down_sync(0xffffffffu, v, 4); v += (idx < 4) ? o : 0.f;
+  o = __shfl_down_sync(0xffffffffu, v, 2); v += (idx < 2) ? o : 0.f;
+  o = __shfl_down_sync(0xffffffffu, v, 1); v += (idx < 1) ? o : 0.f;
+  return __shfl_sync(0xffffffffu, v, base);
 }
-__device__ __forceinline__ float half_max(float v) {
-#pragma unroll
-  for (int o = 8; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
-  return v;
+__device__ __forceinline__ float g10_max(float v, int idx, int base) {
+  float o;
+  o = __shfl_down_sync(0xffffffffu, v, 8); v = (idx < 2) ? fmaxf(v, o) : v;
+  o = __shfl_down_sync(0xffffffffu, v, 4); v = (idx < 4) ? fmaxf(v, o) : v;
+  o = __shfl_down_sync(0xffffffffu, v, 2); v = (idx < 2) ? fmaxf(v, o) : v;
+  o = __shfl_down_sync(0xffffffffu, v, 1); v = (idx < 1) ? fmaxf(v, o) : v;
+  return __shfl_sync(0xffffffffu, v, base);
 }
-__device__ __forceinline__ void half_argmax(float& v, int& idx) {
+// index of the largest value in the group, the smallest index among equals (tf.argmax)
+__device__ __forceinline__ int g10_argmax(float v, int idx, int base) {
+  int i = idx;
 #pragma unroll
-  for (int o = 8; o > 0; o >>= 1) {
-    const float ov = __shfl_xor_sync(0xffffffffu, v, o);
-    const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
-    if (ov > v || (ov == v && oi < idx)) { v = ov; idx = oi; }
+  for (int d = 8; d >= 1; d >>= 1) {
+    const float ov = __shfl_down_sync(0xffffffffu, v, d);
+    const int oi = __shfl_down_sync(0xffffffffu, i, d);
+    const bool in = (d == 8) ? (idx < 2) : (idx < d);
+    if (in && (ov > v || (ov == v && oi < i))) { v = ov; i = oi; }
   }
+  return __shfl_sync(0xffffffffu, i, base);
 }
 
 __global__ void __launch_bounds__(THREADS, 1)
@@ -114,23 +149,18 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int ntiles = (rows + TILE_ROWS - 1) / TILE_ROWS;
 
-  if (tid == 0) {
-    for (int s = 0; s < NSTAGES; ++s) {
-      mbar_init(&sm.full[s], 1);
-      mbar_init(&sm.empty[s], COMPUTE_WARPS);
-    }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  // stage W as [784][12] (zero padded) and the bias
-  for (int i = tid; i < K * NCP; i += THREADS) {
-    const int k = i / NCP, c = i - k * NCP;
-    sm.W[i] = (c < NC) ? Wg[k * NC + c] : 0.f;
-  }
-  if (tid < 16) sm.bias[tid] = (tid < NC) ? bg[tid] : 0.f;
-  __syncthreads();
-
   if (warp == COMPUTE_WARPS) {
     // ------------------------------ producer ------------------------------
+    if (lane == 0) {
+      for (int s = 0; s < NSTAGES; ++s) {
+        mbar_init(&sm.full[s], 1);
+        mbar_init(&sm.empty[s], COMPUTE_WARPS);
+      }
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    asm volatile("bar.arrive 2, %0;" ::"n"(THREADS) : "memory");  // barriers are live; consumers join after staging W
+    const bool y_aligned = (reinterpret_cast<uintptr_t>(y_) & 15u) == 0;
     int n = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       for (int q = 0; q < STAGES_PER_TILE; ++q, ++n) {
@@ -140,100 +170,153 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
         const long row0 = (long)tile * TILE_ROWS + q * STAGE_ROWS;
         long left = rows - row0;
         const int nrows = left <= 0 ? 0 : (left < STAGE_ROWS ? (int)left : STAGE_ROWS);
+        const bool y_bulk = y_aligned && ((nrows & 1) == 0) && nrows > 0;   // 40*nrows bytes must be a 16 B multiple
         if (lane == 0) {
           for (int rr = 0; rr < nrows; ++rr)
             bulk_g2s(sm.x + (slot * STAGE_ROWS + rr) * XSTRIDE, x + (row0 + rr) * K, ROW_BYTES,
                      &sm.full[slot]);
+          if (y_bulk)
+            bulk_g2s(sm.ys + slot * STAGE_ROWS * NC, y_ + row0 * NC, (uint32_t)(nrows * NC * 4), &sm.full[slot]);
         }
-        for (int i = lane; i < STAGE_ROWS * NC; i += 32) {
-          const int rr = i / NC;
-          sm.ys[slot * STAGE_ROWS * NC + i] = (rr < nrows) ? y_[row0 * NC + i] : 0.f;
+        if (!y_bulk) {
+          for (int i = lane; i < STAGE_ROWS * NC; i += 32) {
+            const int rr = i / NC;
+            sm.ys[slot * STAGE_ROWS * NC + i] = (rr < nrows) ? y_[row0 * NC + i] : 0.f;
+          }
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive_expect_tx(&sm.full[slot], (uint32_t)(nrows * ROW_BYTES));
+        if (lane == 0)
+          mbar_arrive_expect_tx(&sm.full[slot], (uint32_t)(nrows * ROW_BYTES + (y_bulk ? nrows * NC * 4 : 0)));
       }
     }
   } else {
     // ------------------------------ consumers ------------------------------
-    const int j = tid >> 1, h = tid & 1;  // backward ownership: inputs 4j..4j+3, classes 5h..5h+4
+    // stage W as [input pair][class][2] and the bias; all loads are issued before the stores
+    {
+      constexpr int NF2 = K * NC / 2;                        // 3920 float2
+      constexpr int ITER = (NF2 + COMPUTE_THREADS - 1) / COMPUTE_THREADS;  // 9
+      float2 v[ITER];
+      const float2* Wg2 = reinterpret_cast<const float2*>(Wg);
+#pragma unroll
+      for (int u = 0; u < ITER; ++u) {
+        const int i = tid + u * COMPUTE_THREADS;
+        v[u] = (i < NF2) ? Wg2[i] : make_float2(0.f, 0.f);
+      }
+#pragma unroll
+      for (int u = 0; u < ITER; ++u) {
+        const int i = tid + u * COMPUTE_THREADS;
+        if (i < NF2) {
+          const int k = i / 5, cp = i - k * 5;
+          float* dst = sm.Wp + (k >> 1) * (2 * NC) + (2 * cp) * 2 + (k & 1);
+          dst[0] = v[u].x;
+          dst[2] = v[u].y;
+        }
+      }
+      if (tid < 16) sm.bias[tid] = (tid < NC) ? bg[tid] : 0.f;
+    }
+    asm volatile("bar.sync 2, %0;" ::"n"(THREADS) : "memory");
+
+    // forward ownership
+    const int team = warp / KSLICES, slice = warp - team * KSLICES;   // rows 16*team.., inputs 112*slice..
+    const int ksub = lane >> 3, rp = lane & 7;
+    // backward ownership: inputs 4j..4j+3, classes 5h..5h+4
+    const int j = tid >> 1, h = tid & 1;
     const bool bwd_active = j < KGROUPS;
-    float gacc[4][5];
+    u64 gacc[2][5];
 #pragma unroll
-    for (int a = 0; a < 4; ++a)
+    for (int a = 0; a < 2; ++a)
 #pragma unroll
-      for (int c = 0; c < 5; ++c) gacc[a][c] = 0.f;
+      for (int c = 0; c < 5; ++c) gacc[a][c] = 0ull;
     float db_acc = 0.f, loss_acc = 0.f, corr_acc = 0.f;
 
     int n0 = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, n0 += STAGES_PER_TILE) {
       const int valid = min(TILE_ROWS, rows - tile * TILE_ROWS);
-      // ---- wait for the tile's four stages ----
-#pragma unroll
-      for (int q = 0; q < STAGES_PER_TILE; ++q) {
-        const int n = n0 + q;
-        mbar_wait(&sm.full[n % NSTAGES], (uint32_t)(n / NSTAGES) & 1u);
-      }
-      // ---- forward: partial logits of row `lane` over inputs [56*warp, 56*warp+56) ----
+      // ---- forward: rows (16*team + rp) and (+8), inputs 112*slice + 4*(4i+ksub) ----
       {
-        const int n = n0 + (lane >> 3);
-        const float* xrow = sm.x + ((n % NSTAGES) * STAGE_ROWS + (lane & 7)) * XSTRIDE + warp * KW;
-        const float* wbase = sm.W + warp * KW * NCP;
-        float acc[NC];
+        const int na = n0 + 2 * team, nb = na + 1;
+        mbar_wait(&sm.full[na % NSTAGES], (uint32_t)(na / NSTAGES) & 1u);
+        mbar_wait(&sm.full[nb % NSTAGES], (uint32_t)(nb / NSTAGES) & 1u);
+        const float* xa = sm.x + ((na % NSTAGES) * STAGE_ROWS + rp) * XSTRIDE + slice * KW + 4 * ksub;
+        const float* xb = sm.x + ((nb % NSTAGES) * STAGE_ROWS + rp) * XSTRIDE + slice * KW + 4 * ksub;
+        const float* wp = sm.Wp + (slice * (KW / 2) + 2 * ksub) * (2 * NC);
+        u64 acc_a[NC], acc_b[NC];
 #pragma unroll
-        for (int c = 0; c < NC; ++c) acc[c] = 0.f;
-#pragma unroll 2
-        for (int q4 = 0; q4 < KW / 4; ++q4) {
-          const float4 xv = *reinterpret_cast<const float4*>(xrow + 4 * q4);
-          const float xs[4] = {xv.x, xv.y, xv.z, xv.w};
+        for (int c = 0; c < NC; ++c) { acc_a[c] = 0ull; acc_b[c] = 0ull; }
 #pragma unroll
-          for (int kk = 0; kk < 4; ++kk) {
-            const float4* wp = reinterpret_cast<const float4*>(wbase + (4 * q4 + kk) * NCP);
-            const float4 wa = wp[0], wb = wp[1], wc = wp[2];
-            acc[0] = fmaf(xs[kk], wa.x, acc[0]);
-            acc[1] = fmaf(xs[kk], wa.y, acc[1]);
-            acc[2] = fmaf(xs[kk], wa.z, acc[2]);
-            acc[3] = fmaf(xs[kk], wa.w, acc[3]);
-            acc[4] = fmaf(xs[kk], wb.x, acc[4]);
-            acc[5] = fmaf(xs[kk], wb.y, acc[5]);
-            acc[6] = fmaf(xs[kk], wb.z, acc[6]);
-            acc[7] = fmaf(xs[kk], wb.w, acc[7]);
-            acc[8] = fmaf(xs[kk], wc.x, acc[8]);
-            acc[9] = fmaf(xs[kk], wc.y, acc[9]);
+        for (int i = 0; i < 7; ++i) {
+          const ulonglong2 va = *reinterpret_cast<const ulonglong2*>(xa + 16 * i);
+          const ulonglong2 vb = *reinterpret_cast<const ulonglong2*>(xb + 16 * i);
+          const ulonglong2* w0 = reinterpret_cast<const ulonglong2*>(wp + i * 8 * (2 * NC));
+#pragma unroll
+          for (int m = 0; m < 5; ++m) {          // input pair 0 of the quad: classes 2m, 2m+1
+            const ulonglong2 w = w0[m];
+            acc_a[2 * m] = ffma2(va.x, w.x, acc_a[2 * m]);
+            acc_a[2 * m + 1] = ffma2(va.x, w.y, acc_a[2 * m + 1]);
+            acc_b[2 * m] = ffma2(vb.x, w.x, acc_b[2 * m]);
+            acc_b[2 * m + 1] = ffma2(vb.x, w.y, acc_b[2 * m + 1]);
+          }
+#pragma unroll
+          for (int m = 0; m < 5; ++m) {          // input pair 1 of the quad
+            const ulonglong2 w = w0[5 + m];
+            acc_a[2 * m] = ffma2(va.y, w.x, acc_a[2 * m]);
+            acc_a[2 * m + 1] = ffma2(va.y, w.y, acc_a[2 * m + 1]);
+            acc_b[2 * m] = ffma2(vb.y, w.x, acc_b[2 * m]);
+            acc_b[2 * m + 1] = ffma2(vb.y, w.y, acc_b[2 * m + 1]);
           }
         }
+        // even + odd inputs, then the four input sub-slices (lanes xor 8, 16)
+        float fa[NC], fb[NC];
 #pragma unroll
-        for (int c = 0; c < NC; ++c) sm.part[(warp * NC + c) * TILE_ROWS + lane] = acc[c];
+        for (int c = 0; c < NC; ++c) {
+          float lo, hi;
+          unpack2(acc_a[c], lo, hi); fa[c] = lo + hi;
+          unpack2(acc_b[c], lo, hi); fb[c] = lo + hi;
+        }
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+          fa[c] += __shfl_xor_sync(0xffffffffu, fa[c], 8);
+          fb[c] += __shfl_xor_sync(0xffffffffu, fb[c], 8);
+          fa[c] += __shfl_xor_sync(0xffffffffu, fa[c], 16);
+          fb[c] += __shfl_xor_sync(0xffffffffu, fb[c], 16);
+        }
+        if (ksub == 0) {
+          float* pa = sm.part + slice * PART_SET + (16 * team + rp) * PART_ROW;
+          float* pb = pa + 8 * PART_ROW;
+#pragma unroll
+          for (int c = 0; c < NC; ++c) { pa[c] = fa[c]; pb[c] = fb[c]; }
+        }
       }
       compute_bar();
-      // ---- head: two rows per warp pass (one per half-warp), lane&15 = class ----
-      for (int p = warp; p < TILE_ROWS / 2; p += COMPUTE_WARPS) {
-        const int half = lane >> 4, c = lane & 15;
-        const int row = 2 * p + half;
-        const bool cact = c < NC;
-        const bool ract = row < valid;
+      // ---- head: three rows per warp (lanes 0-9, 10-19, 20-29), lane%10 = class ----
+      {
+        const int grp = lane / 10, c = lane - grp * 10;
+        const int row = 3 * warp + grp;
+        const bool act = (lane < 30) && (row < TILE_ROWS);
+        const bool ract = act && (row < valid);
+        const int base = grp * 10;
+        const int rsafe = act ? row : 0;
         float z = 0.f;
-        if (cact) {
 #pragma unroll
-          for (int w = 0; w < COMPUTE_WARPS; ++w) z += sm.part[(w * NC + c) * TILE_ROWS + row];
-          z += sm.bias[c];
-        }
-        const float m = half_max(cact ? z : -INFINITY);
-        const float e = cact ? expf(z - m) : 0.f;
-        const float s = half_sum(e);
-        const float inv = 1.0f / s;
+        for (int s = 0; s < KSLICES; ++s) z += sm.part[s * PART_SET + rsafe * PART_ROW + c];
+        z += sm.bias[c];
+        const float m = g10_max(z, c, base);
+        const float e = expf(z - m);
+        const float ssum = g10_sum(e, c, base);
+        const float inv = 1.0f / ssum;
         const float y = e * inv;
-        const int n = n0 + (row >> 3);
-        const float t = cact ? sm.ys[((n % NSTAGES) * STAGE_ROWS + (row & 7)) * NC + c] : 0.f;
-        const float lterm = cact ? -(t * logf(y)) : 0.f;  // un-fused log(softmax) as in the reference
-        const float rowloss = half_sum(lterm);
-        const float sy = half_sum(t);
-        float bv = cact ? y : -INFINITY, lv = cact ? t : -INFINITY;
-        int bi = c, li = c;
-        half_argmax(bv, bi);
-        half_argmax(lv, li);
+        const int n = n0 + (rsafe >> 3);
+        const float t = sm.ys[((n % NSTAGES) * STAGE_ROWS + (rsafe & 7)) * NC + c];
+        const float rowloss = g10_sum(-(t * logf(y)), c, base);   // un-fused log(softmax) as in the reference
+        const float sy = g10_sum(t, c, base);
+        const int bi = g10_argmax(y, c, base);
+        const int li = g10_argmax(t, c, base);
         float dzv = (y * sy - t) * inv_B;
-        if (!(cact && ract)) dzv = 0.f;
-        if (cact) sm.dz[row * 16 + (c / 5) * 8 + (c % 5)] = dzv;
+        if (!ract) dzv = 0.f;
+        if (act) {
+          float2* d = reinterpret_cast<float2*>(sm.dz2 + row * DZ_ROW + (c / 5) * 12 + (c % 5) * 2);
+          *d = make_float2(dzv, dzv);
+        }
         db_acc += dzv;
         if (c == 0 && ract) {
           loss_acc += rowloss;
@@ -241,7 +324,7 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
         }
       }
       compute_bar();
-      // ---- backward: gacc[a][c] += x[r][4j+a] * dz[r][5h+c], rows in order; free stages as we go ----
+      // ---- backward: gacc[pair][c] += (x[r][4j+2p], x[r][4j+2p+1]) * dz[r][5h+c], rows in order ----
 #pragma unroll 1
       for (int q = 0; q < STAGES_PER_TILE; ++q) {
         const int slot = (n0 + q) % NSTAGES;
@@ -249,21 +332,23 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
         nrows = nrows < 0 ? 0 : (nrows > STAGE_ROWS ? STAGE_ROWS : nrows);
         if (bwd_active) {
           const float* xp = sm.x + (slot * STAGE_ROWS) * XSTRIDE + 4 * j;
-          const float* dp = sm.dz + (q * STAGE_ROWS) * 16 + 8 * h;
+          const float* dp = sm.dz2 + (q * STAGE_ROWS) * DZ_ROW + 12 * h;
 #pragma unroll 4
           for (int rr = 0; rr < nrows; ++rr) {
-            const float4 xv = *reinterpret_cast<const float4*>(xp + rr * XSTRIDE);
-            const float4 d4 = *reinterpret_cast<const float4*>(dp + rr * 16);
-            const float d5 = dp[rr * 16 + 4];
-            const float xs[4] = {xv.x, xv.y, xv.z, xv.w};
-#pragma unroll
-            for (int a = 0; a < 4; ++a) {
-              gacc[a][0] = fmaf(xs[a], d4.x, gacc[a][0]);
-              gacc[a][1] = fmaf(xs[a], d4.y, gacc[a][1]);
-              gacc[a][2] = fmaf(xs[a], d4.z, gacc[a][2]);
-              gacc[a][3] = fmaf(xs[a], d4.w, gacc[a][3]);
-              gacc[a][4] = fmaf(xs[a], d5, gacc[a][4]);
-            }
+            const ulonglong2 xv = *reinterpret_cast<const ulonglong2*>(xp + rr * XSTRIDE);
+            const ulonglong2 d01 = *reinterpret_cast<const ulonglong2*>(dp + rr * DZ_ROW);
+            const ulonglong2 d23 = *reinterpret_cast<const ulonglong2*>(dp + rr * DZ_ROW + 4);
+            const u64 d4 = *reinterpret_cast<const u64*>(dp + rr * DZ_ROW + 8);
+            gacc[0][0] = ffma2(xv.x, d01.x, gacc[0][0]);
+            gacc[0][1] = ffma2(xv.x, d01.y, gacc[0][1]);
+            gacc[0][2] = ffma2(xv.x, d23.x, gacc[0][2]);
+            gacc[0][3] = ffma2(xv.x, d23.y, gacc[0][3]);
+            gacc[0][4] = ffma2(xv.x, d4, gacc[0][4]);
+            gacc[1][0] = ffma2(xv.y, d01.x, gacc[1][0]);
+            gacc[1][1] = ffma2(xv.y, d01.y, gacc[1][1]);
+            gacc[1][2] = ffma2(xv.y, d23.x, gacc[1][2]);
+            gacc[1][3] = ffma2(xv.y, d23.y, gacc[1][3]);
+            gacc[1][4] = ffma2(xv.y, d4, gacc[1][4]);
           }
         }
         __syncwarp();
@@ -274,31 +359,39 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
     float* out = scratch + (size_t)blockIdx.x * SCRATCH_STRIDE;
     if (bwd_active) {
 #pragma unroll
-      for (int a = 0; a < 4; ++a)
+      for (int a = 0; a < 2; ++a)
 #pragma unroll
-        for (int c = 0; c < 5; ++c) out[(4 * j + a) * NC + 5 * h + c] = gacc[a][c];
+        for (int c = 0; c < 5; ++c) {
+          float lo, hi;
+          unpack2(gacc[a][c], lo, hi);
+          out[(4 * j + 2 * a) * NC + 5 * h + c] = lo;
+          out[(4 * j + 2 * a + 1) * NC + 5 * h + c] = hi;
+        }
     }
+    sm.red_db[warp * 32 + lane] = db_acc;
     {
-      const int half = lane >> 4, c = lane & 15;
-      sm.red_db[(warp * 2 + half) * 16 + c] = db_acc;
-      if (c == 0) {
-        sm.red_loss[warp * 2 + half] = loss_acc;
-        sm.red_corr[warp * 2 + half] = corr_acc;
+      const int grp = lane / 10;
+      if (lane < 30 && lane == grp * 10) {
+        sm.red_loss[warp * 4 + grp] = loss_acc;
+        sm.red_corr[warp * 4 + grp] = corr_acc;
       }
     }
   }
   __syncthreads();
   if (tid < NC) {
     float v = 0.f;
-    for (int i = 0; i < COMPUTE_WARPS * 2; ++i) v += sm.red_db[i * 16 + tid];
+    for (int w = 0; w < COMPUTE_WARPS; ++w)
+      for (int g = 0; g < 3; ++g) v += sm.red_db[w * 32 + g * 10 + tid];
     scratch[(size_t)blockIdx.x * SCRATCH_STRIDE + K * NC + tid] = v;
   } else if (tid == 32) {
     float v = 0.f;
-    for (int i = 0; i < COMPUTE_WARPS * 2; ++i) v += sm.red_loss[i];
+    for (int w = 0; w < COMPUTE_WARPS; ++w)
+      for (int g = 0; g < 3; ++g) v += sm.red_loss[w * 4 + g];
     scratch[(size_t)blockIdx.x * SCRATCH_STRIDE + LOSS_IDX] = v * inv_B;
   } else if (tid == 64) {
     float v = 0.f;
-    for (int i = 0; i < COMPUTE_WARPS * 2; ++i) v += sm.red_corr[i];
+    for (int w = 0; w < COMPUTE_WARPS; ++w)
+      for (int g = 0; g < 3; ++g) v += sm.red_corr[w * 4 + g];
     scratch[(size_t)blockIdx.x * SCRATCH_STRIDE + CORRECT_IDX] = v;
   }
 }
