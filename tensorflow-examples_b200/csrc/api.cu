@@ -180,7 +180,8 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
   const int apply = (c->nranks == 1) ? 1 : 0;
   int rc;
   if (use_fused_linear(c)) {
-    int grid = (rows + 31) / 32;
+    const int tr = b2_fused_linear_tile_rows();
+    int grid = (rows + tr - 1) / tr;
     if (grid > c->fused_grid) grid = c->fused_grid;
     {
       timed_scope t(c, B2_K_FUSED_STEP, s);

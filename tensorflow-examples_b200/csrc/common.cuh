@@ -123,6 +123,7 @@ bool b2_fused_linear_supported(int in_dim, int out_dim, int loss);
 int b2_fused_linear_grid(int sm_count);
 long b2_fused_linear_stride(void);
 int b2_fused_linear_smem_bytes(void);
+int b2_fused_linear_tile_rows(void);
 int b2_launch_fused_linear_step(const float* x, const float* y, int rows, const float* W,
                                 const float* b, float* scratch, int grid, float inv_global_batch,
                                 cudaStream_t s);

@@ -4,19 +4,19 @@
 // cp.async.bulk into shared memory and used twice from there -- for the logits
 // (distributed.py:98 z = x@W + b) and for the weight gradient (TF1 MatMul grad, dW = x^T dz).
 //
-//   persistent grid, one CTA per SM, 15 warps, 32-row tiles:
-//     warp 14        producer: bulk-copies rows and labels (8-row stages, 7-stage ring, mbarrier tx counts);
-//                    it starts streaming before the weight tile is staged
-//     warps 0..13    forward:  warp = (16-row half of the tile) x (112-wide slice of the 784 inputs);
-//                              lane = (4 input sub-slices) x (8 row pairs): 2 rows x 10 classes per thread,
-//                              packed fp32x2 FMAs (FFMA2) over input pairs, W staged in shared memory as
-//                              [input pair][class][2] so both FFMA2 operands are natural 64-bit pairs
-//                    head:     7 partial sums per logit, then softmax / loss / accuracy / dz with
-//                              10-lane shuffle reductions (three rows per warp, one pass)
-//                    backward: thread = (4 inputs, 5 classes), 10 packed accumulators kept for the whole
-//                              kernel; rows stream from shared memory, dz pre-duplicated as (d,d) pairs
-//   each CTA ends by writing its partial dW / db / loss / correct to scratch[cta][7856];
-//   fused_linear_reduce_kernel sums the partials in CTA order (no float atomics) and applies SGD.
+// Persistent grid, one CTA per SM, 16 warps working as a pipeline over 16-row tiles; the stages
+// hand tiles to each other through mbarriers, so nobody waits on a CTA-wide barrier:
+//   warp 14     P  producer: cp.async.bulk of rows + labels into a 7-stage ring of 8-row stages
+//   warps 0-6   F  forward of tile t+1: warp = 112-wide slice of the 784 inputs, lane = (4 input
+//                  sub-slices) x (8 row pairs): 2 rows x 10 classes per thread, packed fp32x2 FMAs
+//                  (FFMA2) over input pairs; W staged in shared memory as [input pair][class][2] so
+//                  both FFMA2 operands are natural 64-bit pairs
+//   warp 15     H  head of tile t+1: sums the 7 partial logits, softmax / loss / accuracy / dz
+//                  (lane = row x class-half, one shuffle per reduction), dz stored as (d,d) pairs
+//   warps 7-13  G  backward of tile t: thread = 4 inputs x 10 classes, 20 packed accumulators kept
+//                  for the whole kernel; rows stream from shared memory; frees ring stages as it goes
+// Each CTA ends by writing its partial dW / db / loss / correct to scratch[cta][7856];
+// fused_linear_reduce_kernel sums the partials in CTA order (no float atomics) and applies SGD.
 #include <math.h>
 
 #include "common.cuh"
@@ -24,30 +24,39 @@
 namespace fl {
 
 constexpr int K = 784, NC = 10;
-constexpr int TILE_ROWS = 32, STAGE_ROWS = 8, STAGES_PER_TILE = 4, NSTAGES = 7;
+constexpr int TILE_ROWS = 16, STAGE_ROWS = 8, STAGES_PER_TILE = 2, NSTAGES = 7;
 constexpr int XSTRIDE = 788;  // floats per staged row: 3152 B, keeps 16 B alignment, conflict-free LDS.128
-constexpr int COMPUTE_WARPS = 14, COMPUTE_THREADS = COMPUTE_WARPS * 32, THREADS = COMPUTE_THREADS + 32;
-constexpr int KSLICES = 7, KW = K / KSLICES;  // forward: 7 slices of 112 inputs (28 quads, 7 per lane sub-slice)
-constexpr int KGROUPS = K / 4;                // backward: 196 groups of 4 inputs
-constexpr int ROW_BYTES = K * 4;              // 3136
-constexpr int PART_ROW = 11;                  // floats per row of a partial-logit set (odd: conflict-free)
-constexpr int PART_SET = TILE_ROWS * PART_ROW;
-constexpr int DZ_ROW = 24;                    // floats per row of duplicated dz: class c at (c/5)*12 + (c%5)*2
-constexpr long SCRATCH_STRIDE = 7856;         // 7840 dW + 10 db + loss + correct, padded to 16 B
+constexpr int F_WARPS = 7, G_WARPS = 7;
+constexpr int P_WARP = 14, H_WARP = 15;
+constexpr int THREADS = 16 * 32;
+constexpr int STAGING_THREADS = THREADS - 32;   // everyone but the producer stages W
+constexpr int KSLICES = 7, KW = K / KSLICES;    // forward: 7 slices of 112 inputs (28 quads, 7 per lane sub-slice)
+constexpr int KGROUPS = K / 4;                  // backward: 196 groups of 4 inputs
+constexpr int ROW_BYTES = K * 4;                // 3136
+constexpr int PART_ROW = 11;                    // floats per row of a partial-logit set (odd: conflict-free)
+constexpr int PART_SET = TILE_ROWS * PART_ROW;  // 176
+constexpr int PART_BUF = KSLICES * PART_SET;    // 1232
+constexpr int DZ_ROW = 20;                      // duplicated dz: class c at 2c, 2c+1
+constexpr int DZ_BUF = TILE_ROWS * DZ_ROW;
+constexpr long SCRATCH_STRIDE = 7856;           // 7840 dW + 10 db + loss + correct, padded to 16 B
 constexpr int LOSS_IDX = 7850, CORRECT_IDX = 7851;
 
 struct __align__(16) Smem {
   float Wp[K * NC];                            // 31360 B   [k/2][class][k&1]
   float x[NSTAGES * STAGE_ROWS * XSTRIDE];     // 176512 B
-  float part[KSLICES * PART_SET];              // 9856 B    part[slice][row][class]
+  float part[2 * PART_BUF];                    // 9856 B    part[buf][slice][row][class]
   float ys[NSTAGES * STAGE_ROWS * NC];         // 2240 B
-  float dz2[TILE_ROWS * DZ_ROW];               // 3072 B
+  float dz2[2 * DZ_BUF];                       // 2560 B
   float bias[16];
-  float red_db[COMPUTE_WARPS * 32];
-  float red_loss[COMPUTE_WARPS * 4];
-  float red_corr[COMPUTE_WARPS * 4];
-  unsigned long long full[NSTAGES];
-  unsigned long long empty[NSTAGES];
+  float red_db[32 * 5];
+  float red_loss[16];
+  float red_corr[16];
+  unsigned long long full[NSTAGES];            // producer -> F, H, G   (tx bytes)
+  unsigned long long empty[NSTAGES];           // G -> producer
+  unsigned long long part_full[2];             // F -> H
+  unsigned long long part_empty[2];            // H -> F
+  unsigned long long dz_full[2];               // H -> G
+  unsigned long long dz_empty[2];              // G -> H
 };
 static_assert(sizeof(Smem) <= 232448, "shared memory budget");
 
@@ -92,52 +101,14 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
       "l"(src), "r"(bytes), "r"(smem_u32(bar))
       : "memory");
 }
-__device__ __forceinline__ void compute_bar() {
-  asm volatile("bar.sync 1, %0;" ::"n"(COMPUTE_THREADS) : "memory");
-}
 // packed fp32x2 FMA (SASS FFMA2): d.lo = a.lo*b.lo + c.lo, d.hi = a.hi*b.hi + c.hi
 __device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c) {
   u64 d;
   asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
   return d;
 }
-__device__ __forceinline__ u64 pack2(float lo, float hi) {
-  u64 d;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi));
-  return d;
-}
 __device__ __forceinline__ void unpack2(u64 v, float& lo, float& hi) {
   asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
-}
-
-// reductions over a group of 10 consecutive lanes (idx = position in the group, base = first lane)
-__device__ __forceinline__ float g10_sum(float v, int idx, int base) {
-  float o;
-  o = __shfl_down_sync(0xffffffffu, v, 8); v += (idx < 2) ? o : 0.f;
-  o = __shfl_down_sync(0xffffffffu, v, 4); v += (idx < 4) ? o : 0.f;
-  o = __shfl_down_sync(0xffffffffu, v, 2); v += (idx < 2) ? o : 0.f;
-  o = __shfl_down_sync(0xffffffffu, v, 1); v += (idx < 1) ? o : 0.f;
-  return __shfl_sync(0xffffffffu, v, base);
-}
-__device__ __forceinline__ float g10_max(float v, int idx, int base) {
-  float o;
-  o = __shfl_down_sync(0xffffffffu, v, 8); v = (idx < 2) ? fmaxf(v, o) : v;
-  o = __shfl_down_sync(0xffffffffu, v, 4); v = (idx < 4) ? fmaxf(v, o) : v;
-  o = __shfl_down_sync(0xffffffffu, v, 2); v = (idx < 2) ? fmaxf(v, o) : v;
-  o = __shfl_down_sync(0xffffffffu, v, 1); v = (idx < 1) ? fmaxf(v, o) : v;
-  return __shfl_sync(0xffffffffu, v, base);
-}
-// index of the largest value in the group, the smallest index among equals (tf.argmax)
-__device__ __forceinline__ int g10_argmax(float v, int idx, int base) {
-  int i = idx;
-#pragma unroll
-  for (int d = 8; d >= 1; d >>= 1) {
-    const float ov = __shfl_down_sync(0xffffffffu, v, d);
-    const int oi = __shfl_down_sync(0xffffffffu, i, d);
-    const bool in = (d == 8) ? (idx < 2) : (idx < d);
-    if (in && (ov > v || (ov == v && oi < i))) { v = ov; i = oi; }
-  }
-  return __shfl_sync(0xffffffffu, i, base);
 }
 
 __global__ void __launch_bounds__(THREADS, 1)
@@ -149,17 +120,23 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int ntiles = (rows + TILE_ROWS - 1) / TILE_ROWS;
 
-  if (warp == COMPUTE_WARPS) {
-    // ------------------------------ producer ------------------------------
+  if (warp == P_WARP) {
+    // =============================== P: producer ===============================
     if (lane == 0) {
       for (int s = 0; s < NSTAGES; ++s) {
         mbar_init(&sm.full[s], 1);
-        mbar_init(&sm.empty[s], COMPUTE_WARPS);
+        mbar_init(&sm.empty[s], G_WARPS);
+      }
+      for (int b = 0; b < 2; ++b) {
+        mbar_init(&sm.part_full[b], F_WARPS);
+        mbar_init(&sm.part_empty[b], 1);
+        mbar_init(&sm.dz_full[b], 1);
+        mbar_init(&sm.dz_empty[b], G_WARPS);
       }
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
-    asm volatile("bar.arrive 2, %0;" ::"n"(THREADS) : "memory");  // barriers are live; consumers join after staging W
+    asm volatile("bar.arrive 2, %0;" ::"n"(THREADS) : "memory");  // barriers are live; the others join after staging W
     const bool y_aligned = (reinterpret_cast<uintptr_t>(y_) & 15u) == 0;
     int n = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -190,21 +167,21 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
       }
     }
   } else {
-    // ------------------------------ consumers ------------------------------
     // stage W as [input pair][class][2] and the bias; all loads are issued before the stores
     {
+      const int st = tid < P_WARP * 32 ? tid : tid - 32;     // 0..479 over the 15 non-producer warps
       constexpr int NF2 = K * NC / 2;                        // 3920 float2
-      constexpr int ITER = (NF2 + COMPUTE_THREADS - 1) / COMPUTE_THREADS;  // 9
+      constexpr int ITER = (NF2 + STAGING_THREADS - 1) / STAGING_THREADS;  // 9
       float2 v[ITER];
       const float2* Wg2 = reinterpret_cast<const float2*>(Wg);
 #pragma unroll
       for (int u = 0; u < ITER; ++u) {
-        const int i = tid + u * COMPUTE_THREADS;
+        const int i = st + u * STAGING_THREADS;
         v[u] = (i < NF2) ? Wg2[i] : make_float2(0.f, 0.f);
       }
 #pragma unroll
       for (int u = 0; u < ITER; ++u) {
-        const int i = tid + u * COMPUTE_THREADS;
+        const int i = st + u * STAGING_THREADS;
         if (i < NF2) {
           const int k = i / 5, cp = i - k * 5;
           float* dst = sm.Wp + (k >> 1) * (2 * NC) + (2 * cp) * 2 + (k & 1);
@@ -212,29 +189,17 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
           dst[2] = v[u].y;
         }
       }
-      if (tid < 16) sm.bias[tid] = (tid < NC) ? bg[tid] : 0.f;
+      if (st < 16) sm.bias[st] = (st < NC) ? bg[st] : 0.f;
     }
     asm volatile("bar.sync 2, %0;" ::"n"(THREADS) : "memory");
 
-    // forward ownership
-    const int team = warp / KSLICES, slice = warp - team * KSLICES;   // rows 16*team.., inputs 112*slice..
-    const int ksub = lane >> 3, rp = lane & 7;
-    // backward ownership: inputs 4j..4j+3, classes 5h..5h+4
-    const int j = tid >> 1, h = tid & 1;
-    const bool bwd_active = j < KGROUPS;
-    u64 gacc[2][5];
-#pragma unroll
-    for (int a = 0; a < 2; ++a)
-#pragma unroll
-      for (int c = 0; c < 5; ++c) gacc[a][c] = 0ull;
-    float db_acc = 0.f, loss_acc = 0.f, corr_acc = 0.f;
-
-    int n0 = 0;
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, n0 += STAGES_PER_TILE) {
-      const int valid = min(TILE_ROWS, rows - tile * TILE_ROWS);
-      // ---- forward: rows (16*team + rp) and (+8), inputs 112*slice + 4*(4i+ksub) ----
-      {
-        const int na = n0 + 2 * team, nb = na + 1;
+    if (warp < F_WARPS) {
+      // =============================== F: forward ===============================
+      const int slice = warp;                       // inputs 112*slice ..
+      const int ksub = lane >> 3, rp = lane & 7;    // quads 4i+ksub; rows rp and rp+8
+      int i_t = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++i_t) {
+        const int na = 2 * i_t, nb = na + 1, buf = i_t & 1;
         mbar_wait(&sm.full[na % NSTAGES], (uint32_t)(na / NSTAGES) & 1u);
         mbar_wait(&sm.full[nb % NSTAGES], (uint32_t)(nb / NSTAGES) & 1u);
         const float* xa = sm.x + ((na % NSTAGES) * STAGE_ROWS + rp) * XSTRIDE + slice * KW + 4 * ksub;
@@ -280,118 +245,171 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
           fa[c] += __shfl_xor_sync(0xffffffffu, fa[c], 16);
           fb[c] += __shfl_xor_sync(0xffffffffu, fb[c], 16);
         }
+        mbar_wait(&sm.part_empty[buf], ((uint32_t)(i_t >> 1) & 1u) ^ 1u);   // H is done with this buffer
         if (ksub == 0) {
-          float* pa = sm.part + slice * PART_SET + (16 * team + rp) * PART_ROW;
+          float* pa = sm.part + buf * PART_BUF + slice * PART_SET + rp * PART_ROW;
           float* pb = pa + 8 * PART_ROW;
 #pragma unroll
           for (int c = 0; c < NC; ++c) { pa[c] = fa[c]; pb[c] = fb[c]; }
         }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.part_full[buf]);
       }
-      compute_bar();
-      // ---- head: three rows per warp (lanes 0-9, 10-19, 20-29), lane%10 = class ----
-      {
-        const int grp = lane / 10, c = lane - grp * 10;
-        const int row = 3 * warp + grp;
-        const bool act = (lane < 30) && (row < TILE_ROWS);
-        const bool ract = act && (row < valid);
-        const int base = grp * 10;
-        const int rsafe = act ? row : 0;
-        float z = 0.f;
+    } else if (warp == H_WARP) {
+      // =============================== H: loss head ===============================
+      const int row = lane & 15, half = lane >> 4;          // classes 5*half .. 5*half+4
+      float db[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+      float loss_acc = 0.f, corr_acc = 0.f;
+      float bias5[5];
 #pragma unroll
-        for (int s = 0; s < KSLICES; ++s) z += sm.part[s * PART_SET + rsafe * PART_ROW + c];
-        z += sm.bias[c];
-        const float m = g10_max(z, c, base);
-        const float e = expf(z - m);
-        const float ssum = g10_sum(e, c, base);
-        const float inv = 1.0f / ssum;
-        const float y = e * inv;
-        const int n = n0 + (rsafe >> 3);
-        const float t = sm.ys[((n % NSTAGES) * STAGE_ROWS + (rsafe & 7)) * NC + c];
-        const float rowloss = g10_sum(-(t * logf(y)), c, base);   // un-fused log(softmax) as in the reference
-        const float sy = g10_sum(t, c, base);
-        const int bi = g10_argmax(y, c, base);
-        const int li = g10_argmax(t, c, base);
-        float dzv = (y * sy - t) * inv_B;
-        if (!ract) dzv = 0.f;
-        if (act) {
-          float2* d = reinterpret_cast<float2*>(sm.dz2 + row * DZ_ROW + (c / 5) * 12 + (c % 5) * 2);
-          *d = make_float2(dzv, dzv);
+      for (int cc = 0; cc < 5; ++cc) bias5[cc] = sm.bias[5 * half + cc];
+      int i_t = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++i_t) {
+        const int buf = i_t & 1;
+        const uint32_t par = (uint32_t)(i_t >> 1) & 1u;
+        const int valid = min(TILE_ROWS, rows - tile * TILE_ROWS);
+        const int n = 2 * i_t + (row >> 3);
+        mbar_wait(&sm.full[n % NSTAGES], (uint32_t)(n / NSTAGES) & 1u);     // labels of my row have landed
+        mbar_wait(&sm.part_full[buf], par);
+        const float* pp = sm.part + buf * PART_BUF + row * PART_ROW + 5 * half;
+        float z[5];
+#pragma unroll
+        for (int cc = 0; cc < 5; ++cc) {
+          float a = 0.f;
+#pragma unroll
+          for (int s = 0; s < KSLICES; ++s) a += pp[s * PART_SET + cc];
+          z[cc] = a + bias5[cc];
         }
-        db_acc += dzv;
-        if (c == 0 && ract) {
+        const float* tp = sm.ys + ((n % NSTAGES) * STAGE_ROWS + (row & 7)) * NC + 5 * half;
+        float t[5];
+#pragma unroll
+        for (int cc = 0; cc < 5; ++cc) t[cc] = tp[cc];
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.part_empty[buf]);                    // F may overwrite the partials
+        float m = fmaxf(fmaxf(fmaxf(z[0], z[1]), fmaxf(z[2], z[3])), z[4]);
+        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 16));
+        float e[5], ssum = 0.f;
+#pragma unroll
+        for (int cc = 0; cc < 5; ++cc) { e[cc] = expf(z[cc] - m); ssum += e[cc]; }
+        ssum += __shfl_xor_sync(0xffffffffu, ssum, 16);
+        const float inv = 1.0f / ssum;
+        float y[5], l = 0.f, sy = 0.f;
+        float bv = -INFINITY, lv = -INFINITY;
+        int bi = 0, li = 0;
+#pragma unroll
+        for (int cc = 0; cc < 5; ++cc) {
+          y[cc] = e[cc] * inv;
+          l -= t[cc] * logf(y[cc]);            // un-fused log(softmax) as in the reference
+          sy += t[cc];
+          if (y[cc] > bv) { bv = y[cc]; bi = 5 * half + cc; }
+          if (t[cc] > lv) { lv = t[cc]; li = 5 * half + cc; }
+        }
+        // combine the two class halves (lane ^ 16); the l sum is formed low half first on both lanes
+        const float l_o = __shfl_xor_sync(0xffffffffu, l, 16);
+        const float sy_o = __shfl_xor_sync(0xffffffffu, sy, 16);
+        const float rowloss = half ? (l_o + l) : (l + l_o);
+        sy = half ? (sy_o + sy) : (sy + sy_o);
+        {
+          const float ov = __shfl_xor_sync(0xffffffffu, bv, 16);
+          const int oi = __shfl_xor_sync(0xffffffffu, bi, 16);
+          if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+          const float ov2 = __shfl_xor_sync(0xffffffffu, lv, 16);
+          const int oi2 = __shfl_xor_sync(0xffffffffu, li, 16);
+          if (ov2 > lv || (ov2 == lv && oi2 < li)) { lv = ov2; li = oi2; }
+        }
+        const bool ract = row < valid;
+        mbar_wait(&sm.dz_empty[buf], par ^ 1u);                            // G is done with this dz buffer
+        float2* dp = reinterpret_cast<float2*>(sm.dz2 + buf * DZ_BUF + row * DZ_ROW + 10 * half);
+#pragma unroll
+        for (int cc = 0; cc < 5; ++cc) {
+          float d = (y[cc] * sy - t[cc]) * inv_B;
+          if (!ract) d = 0.f;
+          dp[cc] = make_float2(d, d);
+          db[cc] += d;
+        }
+        if (half == 0 && ract) {
           loss_acc += rowloss;
           corr_acc += (bi == li) ? 1.0f : 0.0f;
         }
-      }
-      compute_bar();
-      // ---- backward: gacc[pair][c] += (x[r][4j+2p], x[r][4j+2p+1]) * dz[r][5h+c], rows in order ----
-#pragma unroll 1
-      for (int q = 0; q < STAGES_PER_TILE; ++q) {
-        const int slot = (n0 + q) % NSTAGES;
-        int nrows = valid - q * STAGE_ROWS;
-        nrows = nrows < 0 ? 0 : (nrows > STAGE_ROWS ? STAGE_ROWS : nrows);
-        if (bwd_active) {
-          const float* xp = sm.x + (slot * STAGE_ROWS) * XSTRIDE + 4 * j;
-          const float* dp = sm.dz2 + (q * STAGE_ROWS) * DZ_ROW + 12 * h;
-#pragma unroll 4
-          for (int rr = 0; rr < nrows; ++rr) {
-            const ulonglong2 xv = *reinterpret_cast<const ulonglong2*>(xp + rr * XSTRIDE);
-            const ulonglong2 d01 = *reinterpret_cast<const ulonglong2*>(dp + rr * DZ_ROW);
-            const ulonglong2 d23 = *reinterpret_cast<const ulonglong2*>(dp + rr * DZ_ROW + 4);
-            const u64 d4 = *reinterpret_cast<const u64*>(dp + rr * DZ_ROW + 8);
-            gacc[0][0] = ffma2(xv.x, d01.x, gacc[0][0]);
-            gacc[0][1] = ffma2(xv.x, d01.y, gacc[0][1]);
-            gacc[0][2] = ffma2(xv.x, d23.x, gacc[0][2]);
-            gacc[0][3] = ffma2(xv.x, d23.y, gacc[0][3]);
-            gacc[0][4] = ffma2(xv.x, d4, gacc[0][4]);
-            gacc[1][0] = ffma2(xv.y, d01.x, gacc[1][0]);
-            gacc[1][1] = ffma2(xv.y, d01.y, gacc[1][1]);
-            gacc[1][2] = ffma2(xv.y, d23.x, gacc[1][2]);
-            gacc[1][3] = ffma2(xv.y, d23.y, gacc[1][3]);
-            gacc[1][4] = ffma2(xv.y, d4, gacc[1][4]);
-          }
-        }
         __syncwarp();
-        if (lane == 0) mbar_arrive(&sm.empty[slot]);
+        if (lane == 0) mbar_arrive(&sm.dz_full[buf]);
       }
-    }
-    // ---- per-CTA partials out ----
-    float* out = scratch + (size_t)blockIdx.x * SCRATCH_STRIDE;
-    if (bwd_active) {
+#pragma unroll
+      for (int cc = 0; cc < 5; ++cc) sm.red_db[lane * 5 + cc] = db[cc];
+      if (half == 0) { sm.red_loss[row] = loss_acc; sm.red_corr[row] = corr_acc; }
+    } else {
+      // =============================== G: backward ===============================
+      const int j = tid - F_WARPS * 32;             // inputs 4j..4j+3, all 10 classes
+      const bool active = j < KGROUPS;
+      u64 gacc[2][NC];
 #pragma unroll
       for (int a = 0; a < 2; ++a)
 #pragma unroll
-        for (int c = 0; c < 5; ++c) {
-          float lo, hi;
-          unpack2(gacc[a][c], lo, hi);
-          out[(4 * j + 2 * a) * NC + 5 * h + c] = lo;
-          out[(4 * j + 2 * a + 1) * NC + 5 * h + c] = hi;
+        for (int c = 0; c < NC; ++c) gacc[a][c] = 0ull;
+      int i_t = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++i_t) {
+        const int buf = i_t & 1;
+        const int valid = min(TILE_ROWS, rows - tile * TILE_ROWS);
+        mbar_wait(&sm.dz_full[buf], (uint32_t)(i_t >> 1) & 1u);
+#pragma unroll 1
+        for (int q = 0; q < STAGES_PER_TILE; ++q) {
+          const int n = 2 * i_t + q, slot = n % NSTAGES;
+          mbar_wait(&sm.full[slot], (uint32_t)(n / NSTAGES) & 1u);          // acquire the bulk-copied rows
+          int nrows = valid - q * STAGE_ROWS;
+          nrows = nrows < 0 ? 0 : (nrows > STAGE_ROWS ? STAGE_ROWS : nrows);
+          if (active) {
+            const float* xp = sm.x + (slot * STAGE_ROWS) * XSTRIDE + 4 * j;
+            const float* dp = sm.dz2 + buf * DZ_BUF + (q * STAGE_ROWS) * DZ_ROW;
+#pragma unroll 2
+            for (int rr = 0; rr < nrows; ++rr) {
+              const ulonglong2 xv = *reinterpret_cast<const ulonglong2*>(xp + rr * XSTRIDE);
+              const ulonglong2* d = reinterpret_cast<const ulonglong2*>(dp + rr * DZ_ROW);
+#pragma unroll
+              for (int m = 0; m < 5; ++m) {
+                const ulonglong2 dd = d[m];
+                gacc[0][2 * m] = ffma2(xv.x, dd.x, gacc[0][2 * m]);
+                gacc[0][2 * m + 1] = ffma2(xv.x, dd.y, gacc[0][2 * m + 1]);
+                gacc[1][2 * m] = ffma2(xv.y, dd.x, gacc[1][2 * m]);
+                gacc[1][2 * m + 1] = ffma2(xv.y, dd.y, gacc[1][2 * m + 1]);
+              }
+            }
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&sm.empty[slot]);
         }
-    }
-    sm.red_db[warp * 32 + lane] = db_acc;
-    {
-      const int grp = lane / 10;
-      if (lane < 30 && lane == grp * 10) {
-        sm.red_loss[warp * 4 + grp] = loss_acc;
-        sm.red_corr[warp * 4 + grp] = corr_acc;
+        if (lane == 0) mbar_arrive(&sm.dz_empty[buf]);
+      }
+      // per-CTA weight-gradient partial: rows 4j..4j+3 of dW[784][10]
+      if (active) {
+        float* out = scratch + (size_t)blockIdx.x * SCRATCH_STRIDE + (size_t)(4 * j) * NC;
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+          float lo[NC], hi[NC];
+#pragma unroll
+          for (int c = 0; c < NC; ++c) unpack2(gacc[a][c], lo[c], hi[c]);
+#pragma unroll
+          for (int c = 0; c < NC; c += 2) {
+            *reinterpret_cast<float2*>(out + (2 * a) * NC + c) = make_float2(lo[c], lo[c + 1]);
+            *reinterpret_cast<float2*>(out + (2 * a + 1) * NC + c) = make_float2(hi[c], hi[c + 1]);
+          }
+        }
       }
     }
   }
   __syncthreads();
+  // bias gradient, loss, correct count: fixed-order sums over the head warp's lanes
   if (tid < NC) {
+    const int half = tid / 5, cc = tid - 5 * half;
     float v = 0.f;
-    for (int w = 0; w < COMPUTE_WARPS; ++w)
-      for (int g = 0; g < 3; ++g) v += sm.red_db[w * 32 + g * 10 + tid];
+    for (int r = 0; r < 16; ++r) v += sm.red_db[(half * 16 + r) * 5 + cc];
     scratch[(size_t)blockIdx.x * SCRATCH_STRIDE + K * NC + tid] = v;
   } else if (tid == 32) {
     float v = 0.f;
-    for (int w = 0; w < COMPUTE_WARPS; ++w)
-      for (int g = 0; g < 3; ++g) v += sm.red_loss[w * 4 + g];
+    for (int r = 0; r < 16; ++r) v += sm.red_loss[r];
     scratch[(size_t)blockIdx.x * SCRATCH_STRIDE + LOSS_IDX] = v * inv_B;
   } else if (tid == 64) {
     float v = 0.f;
-    for (int w = 0; w < COMPUTE_WARPS; ++w)
-      for (int g = 0; g < 3; ++g) v += sm.red_corr[w * 4 + g];
+    for (int r = 0; r < 16; ++r) v += sm.red_corr[r];
     scratch[(size_t)blockIdx.x * SCRATCH_STRIDE + CORRECT_IDX] = v;
   }
 }
@@ -439,6 +457,7 @@ bool b2_fused_linear_supported(int in_dim, int out_dim, int loss) {
 int b2_fused_linear_grid(int sm_count) { return sm_count; }
 long b2_fused_linear_stride(void) { return fl::SCRATCH_STRIDE; }
 int b2_fused_linear_smem_bytes(void) { return (int)sizeof(fl::Smem); }
+int b2_fused_linear_tile_rows(void) { return fl::TILE_ROWS; }
 
 int b2_fused_linear_prepare(void) {
   // opt in to the large dynamic shared memory carve-out on the current device (done once per context)
