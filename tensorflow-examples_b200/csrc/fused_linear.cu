@@ -9,12 +9,13 @@
 //   warp 14     P  producer: cp.async.bulk of rows + labels into a 7-stage ring of 8-row stages
 //   warps 0-6   F  forward of tile t+1: warp = 112-wide slice of the 784 inputs, lane = (4 input
 //                  sub-slices) x (8 row pairs): 2 rows x 10 classes per thread, packed fp32x2 FMAs
-//                  (FFMA2) over input pairs; W staged in shared memory as [input pair][class][2] so
-//                  both FFMA2 operands are natural 64-bit pairs
+//                  (FFMA2) over class pairs: the W pair comes straight from the [784][10] tile in
+//                  shared memory (one bulk copy), the x value is the scalar-broadcast operand
 //   warp 15     H  head of tile t+1: sums the 7 partial logits, softmax / loss / accuracy / dz
 //                  (lane = row x class-half, one shuffle per reduction), dz stored as (d,d) pairs
-//   warps 7-13  G  backward of tile t: thread = 4 inputs x 10 classes, 20 packed accumulators kept
-//                  for the whole kernel; rows stream from shared memory; frees ring stages as it goes
+//   warps 7-13  G  backward of tile t: thread = 8 inputs x 5 classes, 20 packed accumulators (input
+//                  pairs) kept for the whole kernel; rows stream from shared memory, dz is the
+//                  scalar-broadcast operand; frees ring stages as it goes
 // Each CTA ends by writing its partial dW / db / loss / correct to scratch[cta][7856];
 // fused_linear_reduce_kernel sums the partials in CTA order (no float atomics) and applies SGD.
 #include <math.h>
@@ -29,34 +30,34 @@ constexpr int XSTRIDE = 788;  // floats per staged row: 3152 B, keeps 16 B align
 constexpr int F_WARPS = 7, G_WARPS = 7;
 constexpr int P_WARP = 14, H_WARP = 15;
 constexpr int THREADS = 16 * 32;
-constexpr int STAGING_THREADS = THREADS - 32;   // everyone but the producer stages W
 constexpr int KSLICES = 7, KW = K / KSLICES;    // forward: 7 slices of 112 inputs (28 quads, 7 per lane sub-slice)
-constexpr int KGROUPS = K / 4;                  // backward: 196 groups of 4 inputs
+constexpr int KGROUPS = K / 8;                  // backward: 98 groups of 8 inputs (quads kg and kg+98)
 constexpr int ROW_BYTES = K * 4;                // 3136
 constexpr int PART_ROW = 11;                    // floats per row of a partial-logit set (odd: conflict-free)
 constexpr int PART_SET = TILE_ROWS * PART_ROW;  // 176
 constexpr int PART_BUF = KSLICES * PART_SET;    // 1232
-constexpr int DZ_ROW = 20;                      // duplicated dz: class c at 2c, 2c+1
+constexpr int DZ_ROW = 16;                      // dz of class c at (c/5)*8 + c%5
 constexpr int DZ_BUF = TILE_ROWS * DZ_ROW;
+constexpr int NBUF = 3;                        // partial-logit / dz buffers between the pipeline stages
 constexpr long SCRATCH_STRIDE = 7856;           // 7840 dW + 10 db + loss + correct, padded to 16 B
 constexpr int LOSS_IDX = 7850, CORRECT_IDX = 7851;
 
 struct __align__(16) Smem {
-  float Wp[K * NC];                            // 31360 B   [k/2][class][k&1]
+  float W[K * NC];                             // 31360 B   [784][10], as in global memory
   float x[NSTAGES * STAGE_ROWS * XSTRIDE];     // 176512 B
-  float part[2 * PART_BUF];                    // 9856 B    part[buf][slice][row][class]
+  float part[NBUF * PART_BUF];                 // 14784 B   part[buf][slice][row][class]
   float ys[NSTAGES * STAGE_ROWS * NC];         // 2240 B
-  float dz2[2 * DZ_BUF];                       // 2560 B
-  float bias[16];
+  float dz[NBUF * DZ_BUF];                     // 3072 B
   float red_db[32 * 5];
   float red_loss[16];
   float red_corr[16];
+  unsigned long long w_full;                   // producer -> F: weight tile landed
   unsigned long long full[NSTAGES];            // producer -> F, H, G   (tx bytes)
   unsigned long long empty[NSTAGES];           // G -> producer
-  unsigned long long part_full[2];             // F -> H
-  unsigned long long part_empty[2];            // H -> F
-  unsigned long long dz_full[2];               // H -> G
-  unsigned long long dz_empty[2];              // G -> H
+  unsigned long long part_full[NBUF];             // F -> H
+  unsigned long long part_empty[NBUF];            // H -> F
+  unsigned long long dz_full[NBUF];               // H -> G
+  unsigned long long dz_empty[NBUF];              // G -> H
 };
 static_assert(sizeof(Smem) <= 232448, "shared memory budget");
 
@@ -78,8 +79,9 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, u
 __device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
   const uint32_t addr = smem_u32(bar);
   uint32_t ok = 0;
-  long long t0 = 0;
-  for (;;) {
+  // try_wait suspends the warp in hardware for a bounded time; the loop around it is kept to three
+  // instructions so that waiting stages do not take issue slots from the working ones.
+  for (uint32_t spins = 0;; ++spins) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
@@ -88,9 +90,7 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t pari
         : "r"(addr), "r"(parity)
         : "memory");
     if (ok) break;
-    // watchdog: a protocol bug must not hang the GPU
-    if (t0 == 0) t0 = clock64();
-    else if (clock64() - t0 > 4000000000LL) __trap();
+    if (spins > (1u << 22)) __trap();  // watchdog: a protocol bug must not hang the GPU
   }
 }
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes,
@@ -105,6 +105,11 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 __device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c) {
   u64 d;
   asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ u64 pack2(float lo, float hi) {
+  u64 d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi));
   return d;
 }
 __device__ __forceinline__ void unpack2(u64 v, float& lo, float& hi) {
@@ -127,16 +132,28 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
         mbar_init(&sm.full[s], 1);
         mbar_init(&sm.empty[s], G_WARPS);
       }
-      for (int b = 0; b < 2; ++b) {
+      for (int b = 0; b < NBUF; ++b) {
         mbar_init(&sm.part_full[b], F_WARPS);
         mbar_init(&sm.part_empty[b], 1);
         mbar_init(&sm.dz_full[b], 1);
         mbar_init(&sm.dz_empty[b], G_WARPS);
       }
+      mbar_init(&sm.w_full, 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
-    asm volatile("bar.arrive 2, %0;" ::"n"(THREADS) : "memory");  // barriers are live; the others join after staging W
+    asm volatile("bar.arrive 2, %0;" ::"n"(THREADS) : "memory");  // barriers are live
+    const bool w_bulk = (reinterpret_cast<uintptr_t>(Wg) & 15u) == 0;
+    if (w_bulk) {
+      if (lane == 0) {
+        bulk_g2s(sm.W, Wg, K * NC * 4, &sm.w_full);
+        mbar_arrive_expect_tx(&sm.w_full, K * NC * 4);
+      }
+    } else {
+      for (int i = lane; i < K * NC; i += 32) sm.W[i] = Wg[i];
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.w_full);
+    }
     const bool y_aligned = (reinterpret_cast<uintptr_t>(y_) & 15u) == 0;
     int n = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -167,76 +184,57 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
       }
     }
   } else {
-    // stage W as [input pair][class][2] and the bias; all loads are issued before the stores
-    {
-      const int st = tid < P_WARP * 32 ? tid : tid - 32;     // 0..479 over the 15 non-producer warps
-      constexpr int NF2 = K * NC / 2;                        // 3920 float2
-      constexpr int ITER = (NF2 + STAGING_THREADS - 1) / STAGING_THREADS;  // 9
-      float2 v[ITER];
-      const float2* Wg2 = reinterpret_cast<const float2*>(Wg);
-#pragma unroll
-      for (int u = 0; u < ITER; ++u) {
-        const int i = st + u * STAGING_THREADS;
-        v[u] = (i < NF2) ? Wg2[i] : make_float2(0.f, 0.f);
-      }
-#pragma unroll
-      for (int u = 0; u < ITER; ++u) {
-        const int i = st + u * STAGING_THREADS;
-        if (i < NF2) {
-          const int k = i / 5, cp = i - k * 5;
-          float* dst = sm.Wp + (k >> 1) * (2 * NC) + (2 * cp) * 2 + (k & 1);
-          dst[0] = v[u].x;
-          dst[2] = v[u].y;
-        }
-      }
-      if (st < 16) sm.bias[st] = (st < NC) ? bg[st] : 0.f;
-    }
     asm volatile("bar.sync 2, %0;" ::"n"(THREADS) : "memory");
 
     if (warp < F_WARPS) {
       // =============================== F: forward ===============================
       const int slice = warp;                       // inputs 112*slice ..
       const int ksub = lane >> 3, rp = lane & 7;    // quads 4i+ksub; rows rp and rp+8
+      mbar_wait(&sm.w_full, 0u);
       int i_t = 0;
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++i_t) {
-        const int na = 2 * i_t, nb = na + 1, buf = i_t & 1;
+        const int na = 2 * i_t, nb = na + 1, buf = i_t % NBUF;
         mbar_wait(&sm.full[na % NSTAGES], (uint32_t)(na / NSTAGES) & 1u);
         mbar_wait(&sm.full[nb % NSTAGES], (uint32_t)(nb / NSTAGES) & 1u);
         const float* xa = sm.x + ((na % NSTAGES) * STAGE_ROWS + rp) * XSTRIDE + slice * KW + 4 * ksub;
         const float* xb = sm.x + ((nb % NSTAGES) * STAGE_ROWS + rp) * XSTRIDE + slice * KW + 4 * ksub;
-        const float* wp = sm.Wp + (slice * (KW / 2) + 2 * ksub) * (2 * NC);
-        u64 acc_a[NC], acc_b[NC];
+        const float* wp = sm.W + (slice * KW + 4 * ksub) * NC;
+        u64 acc_a[5], acc_b[5];                       // class pairs (2p, 2p+1) of rows a and b
 #pragma unroll
-        for (int c = 0; c < NC; ++c) { acc_a[c] = 0ull; acc_b[c] = 0ull; }
+        for (int p = 0; p < 5; ++p) { acc_a[p] = 0ull; acc_b[p] = 0ull; }
 #pragma unroll
         for (int i = 0; i < 7; ++i) {
-          const ulonglong2 va = *reinterpret_cast<const ulonglong2*>(xa + 16 * i);
-          const ulonglong2 vb = *reinterpret_cast<const ulonglong2*>(xb + 16 * i);
-          const ulonglong2* w0 = reinterpret_cast<const ulonglong2*>(wp + i * 8 * (2 * NC));
+          const float4 va = *reinterpret_cast<const float4*>(xa + 16 * i);
+          const float4 vb = *reinterpret_cast<const float4*>(xb + 16 * i);
+          const ulonglong2* w0 = reinterpret_cast<const ulonglong2*>(wp + i * 16 * NC);   // 4 inputs x 10 classes = 10 x 16 B
+          const float xsa[4] = {va.x, va.y, va.z, va.w};
+          const float xsb[4] = {vb.x, vb.y, vb.z, vb.w};
 #pragma unroll
-          for (int m = 0; m < 5; ++m) {          // input pair 0 of the quad: classes 2m, 2m+1
-            const ulonglong2 w = w0[m];
-            acc_a[2 * m] = ffma2(va.x, w.x, acc_a[2 * m]);
-            acc_a[2 * m + 1] = ffma2(va.x, w.y, acc_a[2 * m + 1]);
-            acc_b[2 * m] = ffma2(vb.x, w.x, acc_b[2 * m]);
-            acc_b[2 * m + 1] = ffma2(vb.x, w.y, acc_b[2 * m + 1]);
-          }
-#pragma unroll
-          for (int m = 0; m < 5; ++m) {          // input pair 1 of the quad
-            const ulonglong2 w = w0[5 + m];
-            acc_a[2 * m] = ffma2(va.y, w.x, acc_a[2 * m]);
-            acc_a[2 * m + 1] = ffma2(va.y, w.y, acc_a[2 * m + 1]);
-            acc_b[2 * m] = ffma2(vb.y, w.x, acc_b[2 * m]);
-            acc_b[2 * m + 1] = ffma2(vb.y, w.y, acc_b[2 * m + 1]);
+          for (int kp = 0; kp < 2; ++kp) {            // inputs 2kp and 2kp+1 of the quad: 20 floats = 5 x 16 B
+            const ulonglong2 w01 = w0[5 * kp + 0], w23 = w0[5 * kp + 1], w45 = w0[5 * kp + 2],
+                             w67 = w0[5 * kp + 3], w89 = w0[5 * kp + 4];
+            // first input: class pairs (0,1)(2,3)(4,5)(6,7)(8,9) = w01.x w01.y w23.x w23.y w45.x
+            const u64 xa0 = pack2(xsa[2 * kp], xsa[2 * kp]), xb0 = pack2(xsb[2 * kp], xsb[2 * kp]);
+            acc_a[0] = ffma2(xa0, w01.x, acc_a[0]); acc_b[0] = ffma2(xb0, w01.x, acc_b[0]);
+            acc_a[1] = ffma2(xa0, w01.y, acc_a[1]); acc_b[1] = ffma2(xb0, w01.y, acc_b[1]);
+            acc_a[2] = ffma2(xa0, w23.x, acc_a[2]); acc_b[2] = ffma2(xb0, w23.x, acc_b[2]);
+            acc_a[3] = ffma2(xa0, w23.y, acc_a[3]); acc_b[3] = ffma2(xb0, w23.y, acc_b[3]);
+            acc_a[4] = ffma2(xa0, w45.x, acc_a[4]); acc_b[4] = ffma2(xb0, w45.x, acc_b[4]);
+            // second input: w45.y w67.x w67.y w89.x w89.y
+            const u64 xa1 = pack2(xsa[2 * kp + 1], xsa[2 * kp + 1]), xb1 = pack2(xsb[2 * kp + 1], xsb[2 * kp + 1]);
+            acc_a[0] = ffma2(xa1, w45.y, acc_a[0]); acc_b[0] = ffma2(xb1, w45.y, acc_b[0]);
+            acc_a[1] = ffma2(xa1, w67.x, acc_a[1]); acc_b[1] = ffma2(xb1, w67.x, acc_b[1]);
+            acc_a[2] = ffma2(xa1, w67.y, acc_a[2]); acc_b[2] = ffma2(xb1, w67.y, acc_b[2]);
+            acc_a[3] = ffma2(xa1, w89.x, acc_a[3]); acc_b[3] = ffma2(xb1, w89.x, acc_b[3]);
+            acc_a[4] = ffma2(xa1, w89.y, acc_a[4]); acc_b[4] = ffma2(xb1, w89.y, acc_b[4]);
           }
         }
-        // even + odd inputs, then the four input sub-slices (lanes xor 8, 16)
+        // the four input sub-slices (lanes xor 8, 16)
         float fa[NC], fb[NC];
 #pragma unroll
-        for (int c = 0; c < NC; ++c) {
-          float lo, hi;
-          unpack2(acc_a[c], lo, hi); fa[c] = lo + hi;
-          unpack2(acc_b[c], lo, hi); fb[c] = lo + hi;
+        for (int p = 0; p < 5; ++p) {
+          unpack2(acc_a[p], fa[2 * p], fa[2 * p + 1]);
+          unpack2(acc_b[p], fb[2 * p], fb[2 * p + 1]);
         }
 #pragma unroll
         for (int c = 0; c < NC; ++c) {
@@ -245,7 +243,7 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
           fa[c] += __shfl_xor_sync(0xffffffffu, fa[c], 16);
           fb[c] += __shfl_xor_sync(0xffffffffu, fb[c], 16);
         }
-        mbar_wait(&sm.part_empty[buf], ((uint32_t)(i_t >> 1) & 1u) ^ 1u);   // H is done with this buffer
+        mbar_wait(&sm.part_empty[buf], ((uint32_t)(i_t / NBUF) & 1u) ^ 1u);   // H is done with this buffer
         if (ksub == 0) {
           float* pa = sm.part + buf * PART_BUF + slice * PART_SET + rp * PART_ROW;
           float* pb = pa + 8 * PART_ROW;
@@ -262,11 +260,11 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
       float loss_acc = 0.f, corr_acc = 0.f;
       float bias5[5];
 #pragma unroll
-      for (int cc = 0; cc < 5; ++cc) bias5[cc] = sm.bias[5 * half + cc];
+      for (int cc = 0; cc < 5; ++cc) bias5[cc] = bg[5 * half + cc];
       int i_t = 0;
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++i_t) {
-        const int buf = i_t & 1;
-        const uint32_t par = (uint32_t)(i_t >> 1) & 1u;
+        const int buf = i_t % NBUF;
+        const uint32_t par = (uint32_t)(i_t / NBUF) & 1u;
         const int valid = min(TILE_ROWS, rows - tile * TILE_ROWS);
         const int n = 2 * i_t + (row >> 3);
         mbar_wait(&sm.full[n % NSTAGES], (uint32_t)(n / NSTAGES) & 1u);     // labels of my row have landed
@@ -319,12 +317,12 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
         }
         const bool ract = row < valid;
         mbar_wait(&sm.dz_empty[buf], par ^ 1u);                            // G is done with this dz buffer
-        float2* dp = reinterpret_cast<float2*>(sm.dz2 + buf * DZ_BUF + row * DZ_ROW + 10 * half);
+        float* dp = sm.dz + buf * DZ_BUF + row * DZ_ROW + 8 * half;
 #pragma unroll
         for (int cc = 0; cc < 5; ++cc) {
           float d = (y[cc] * sy - t[cc]) * inv_B;
           if (!ract) d = 0.f;
-          dp[cc] = make_float2(d, d);
+          dp[cc] = d;
           db[cc] += d;
         }
         if (half == 0 && ract) {
@@ -339,18 +337,19 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
       if (half == 0) { sm.red_loss[row] = loss_acc; sm.red_corr[row] = corr_acc; }
     } else {
       // =============================== G: backward ===============================
-      const int j = tid - F_WARPS * 32;             // inputs 4j..4j+3, all 10 classes
-      const bool active = j < KGROUPS;
-      u64 gacc[2][NC];
+      const int gt = tid - F_WARPS * 32;            // 0..223
+      const int kg = gt >> 1, h = gt & 1;           // inputs 4kg..4kg+3 and 392+4kg..392+4kg+3, classes 5h..5h+4
+      const bool active = kg < KGROUPS;
+      u64 gacc[4][5];                               // [input pair][class]
 #pragma unroll
-      for (int a = 0; a < 2; ++a)
+      for (int a = 0; a < 4; ++a)
 #pragma unroll
-        for (int c = 0; c < NC; ++c) gacc[a][c] = 0ull;
+        for (int c = 0; c < 5; ++c) gacc[a][c] = 0ull;
       int i_t = 0;
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++i_t) {
-        const int buf = i_t & 1;
+        const int buf = i_t % NBUF;
         const int valid = min(TILE_ROWS, rows - tile * TILE_ROWS);
-        mbar_wait(&sm.dz_full[buf], (uint32_t)(i_t >> 1) & 1u);
+        mbar_wait(&sm.dz_full[buf], (uint32_t)(i_t / NBUF) & 1u);
 #pragma unroll 1
         for (int q = 0; q < STAGES_PER_TILE; ++q) {
           const int n = 2 * i_t + q, slot = n % NSTAGES;
@@ -358,19 +357,22 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
           int nrows = valid - q * STAGE_ROWS;
           nrows = nrows < 0 ? 0 : (nrows > STAGE_ROWS ? STAGE_ROWS : nrows);
           if (active) {
-            const float* xp = sm.x + (slot * STAGE_ROWS) * XSTRIDE + 4 * j;
-            const float* dp = sm.dz2 + buf * DZ_BUF + (q * STAGE_ROWS) * DZ_ROW;
+            const float* xp = sm.x + (slot * STAGE_ROWS) * XSTRIDE + 4 * kg;
+            const float* dp = sm.dz + buf * DZ_BUF + (q * STAGE_ROWS) * DZ_ROW + 8 * h;
 #pragma unroll 2
             for (int rr = 0; rr < nrows; ++rr) {
-              const ulonglong2 xv = *reinterpret_cast<const ulonglong2*>(xp + rr * XSTRIDE);
-              const ulonglong2* d = reinterpret_cast<const ulonglong2*>(dp + rr * DZ_ROW);
+              const ulonglong2 x0 = *reinterpret_cast<const ulonglong2*>(xp + rr * XSTRIDE);
+              const ulonglong2 x1 = *reinterpret_cast<const ulonglong2*>(xp + rr * XSTRIDE + K / 2);
+              const float4 d03 = *reinterpret_cast<const float4*>(dp + rr * DZ_ROW);
+              const float d4 = dp[rr * DZ_ROW + 4];
+              const float ds[5] = {d03.x, d03.y, d03.z, d03.w, d4};
 #pragma unroll
-              for (int m = 0; m < 5; ++m) {
-                const ulonglong2 dd = d[m];
-                gacc[0][2 * m] = ffma2(xv.x, dd.x, gacc[0][2 * m]);
-                gacc[0][2 * m + 1] = ffma2(xv.x, dd.y, gacc[0][2 * m + 1]);
-                gacc[1][2 * m] = ffma2(xv.y, dd.x, gacc[1][2 * m]);
-                gacc[1][2 * m + 1] = ffma2(xv.y, dd.y, gacc[1][2 * m + 1]);
+              for (int c = 0; c < 5; ++c) {
+                const u64 dd = pack2(ds[c], ds[c]);
+                gacc[0][c] = ffma2(x0.x, dd, gacc[0][c]);
+                gacc[1][c] = ffma2(x0.y, dd, gacc[1][c]);
+                gacc[2][c] = ffma2(x1.x, dd, gacc[2][c]);
+                gacc[3][c] = ffma2(x1.y, dd, gacc[3][c]);
               }
             }
           }
@@ -379,18 +381,18 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
         }
         if (lane == 0) mbar_arrive(&sm.dz_empty[buf]);
       }
-      // per-CTA weight-gradient partial: rows 4j..4j+3 of dW[784][10]
+      // per-CTA weight-gradient partial: rows 4kg..4kg+3 and 392+4kg.. of dW[784][10], classes 5h..5h+4
       if (active) {
-        float* out = scratch + (size_t)blockIdx.x * SCRATCH_STRIDE + (size_t)(4 * j) * NC;
+        float* out = scratch + (size_t)blockIdx.x * SCRATCH_STRIDE + 5 * h;
 #pragma unroll
-        for (int a = 0; a < 2; ++a) {
-          float lo[NC], hi[NC];
+        for (int a = 0; a < 4; ++a) {
+          const int k0 = (a < 2 ? 4 * kg : K / 2 + 4 * kg) + 2 * (a & 1);
 #pragma unroll
-          for (int c = 0; c < NC; ++c) unpack2(gacc[a][c], lo[c], hi[c]);
-#pragma unroll
-          for (int c = 0; c < NC; c += 2) {
-            *reinterpret_cast<float2*>(out + (2 * a) * NC + c) = make_float2(lo[c], lo[c + 1]);
-            *reinterpret_cast<float2*>(out + (2 * a + 1) * NC + c) = make_float2(hi[c], hi[c + 1]);
+          for (int c = 0; c < 5; ++c) {
+            float lo, hi;
+            unpack2(gacc[a][c], lo, hi);
+            out[(size_t)k0 * NC + c] = lo;
+            out[(size_t)(k0 + 1) * NC + c] = hi;
           }
         }
       }
@@ -414,26 +416,38 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
   }
 }
 
-// Sums the per-CTA partials in CTA order; with apply != 0 also does var -= lr*grad, writes the
+// Sums the per-CTA partials in a fixed order; with apply != 0 also does var -= lr*grad, writes the
 // step's loss / correct count and bumps global_step (distributed.py:107-108).
-__global__ void __launch_bounds__(128)
+// Block = 32 outputs x 4 quarter-sums: thread (o, q) adds CTAs q*ceil(grid/4) .. in order, the four
+// quarters are then combined in order 0,1,2,3 -- the same association on every run.
+constexpr int RED_OUT = 32, RED_Q = 4, RED_N = 7852;
+__global__ void __launch_bounds__(RED_OUT * RED_Q)
 fused_linear_reduce_kernel(const float* __restrict__ scratch, int grid, float* __restrict__ grads,
                            float* __restrict__ params, int apply, float lr,
                            float* __restrict__ loss_trace, int* __restrict__ correct_trace,
                            float* __restrict__ global_step, long P) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= 7852) return;
-  const float* p = scratch + i;
+  __shared__ float sh[RED_Q][RED_OUT];
+  const int o = threadIdx.x & (RED_OUT - 1), q = threadIdx.x / RED_OUT;
+  const int i = blockIdx.x * RED_OUT + o;
+  const int per = (grid + RED_Q - 1) / RED_Q;
+  const int c0 = q * per, c1 = min(grid, c0 + per);
   float g = 0.f;
-  int c = 0;
-  for (; c + 8 <= grid; c += 8) {
-    float v[8];
+  if (i < RED_N) {
+    const float* p = scratch + i;
+    int c = c0;
+    for (; c + 8 <= c1; c += 8) {
+      float v[8];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) v[u] = p[(size_t)(c + u) * SCRATCH_STRIDE];
+      for (int u = 0; u < 8; ++u) v[u] = p[(size_t)(c + u) * SCRATCH_STRIDE];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) g += v[u];
+      for (int u = 0; u < 8; ++u) g += v[u];
+    }
+    for (; c < c1; ++c) g += p[(size_t)c * SCRATCH_STRIDE];
   }
-  for (; c < grid; ++c) g += p[(size_t)c * SCRATCH_STRIDE];
+  sh[q][o] = g;
+  __syncthreads();
+  if (q != 0 || i >= RED_N) return;
+  g = ((sh[0][o] + sh[1][o]) + sh[2][o]) + sh[3][o];
   if (i < K * NC + NC) {
     grads[i] = g;
     if (apply) params[i] -= lr * g;
@@ -483,7 +497,7 @@ int b2_launch_fused_linear_step(const float* x, const float* y, int rows, const 
 int b2_launch_fused_linear_reduce(const float* scratch, int grid, float* grads, float* params,
                                   int apply, float lr, float* loss_trace, int* correct_trace,
                                   float* global_step, long P, cudaStream_t s) {
-  fl::fused_linear_reduce_kernel<<<(7852 + 127) / 128, 128, 0, s>>>(
+  fl::fused_linear_reduce_kernel<<<(fl::RED_N + fl::RED_OUT - 1) / fl::RED_OUT, fl::RED_OUT * fl::RED_Q, 0, s>>>(
       scratch, grid, grads, params, apply, lr, loss_trace, correct_trace, global_step, P);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
