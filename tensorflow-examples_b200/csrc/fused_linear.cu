@@ -90,6 +90,7 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t pari
         : "r"(addr), "r"(parity)
         : "memory");
     if (ok) break;
+    __nanosleep(128);                   // back off: the issue slots belong to the stages that have work
     if (spins > (1u << 22)) __trap();  // watchdog: a protocol bug must not hang the GPU
   }
 }
