@@ -1,0 +1,78 @@
+"""GPU tests of the drop-in scripts: same command lines, same printed lines as the reference,
+numbers checked against the CPU oracle."""
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from oracle import tf1_graph as oracle
+from tensorflow_examples_b200 import synthetic
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_simple_py_prints_the_reference_line(cuda_device):
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "simple", "simple.py")], capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = r.stdout.strip().splitlines()[-1]
+    m = re.fullmatch(r"W: \[(-?[0-9.e+-]+)\] b: \[(-?[0-9.e+-]+)\] loss ([0-9.e+-]+)", line)   # simple.py:39
+    assert m, line
+    W, b, loss = (float(g) for g in m.groups())
+    Wo, bo, lo, _ = oracle.simple_py()
+    assert abs(W - float(Wo[0])) <= 2e-6 and abs(b - float(bo[0])) <= 2e-6 and loss < 1e-9
+    assert abs(W + 1) < 1e-5 and abs(b - 1) < 1e-5
+
+
+def _run_worker(args, timeout=900):
+    script = os.path.join(ROOT, "distributed", "distributed.py")
+    return subprocess.run([sys.executable, script] + args, capture_output=True, text=True, timeout=timeout)
+
+
+def test_distributed_py_single_worker_matches_oracle(cuda_device):
+    rows, test_rows, bs, epochs = 5500, 1000, 100, 2
+    r = _run_worker(["--ps_hosts=127.0.0.1:2222", "--worker_hosts=127.0.0.1:2223", "--job_name=worker", "--task_index=0",
+                     "--train_rows=%d" % rows, "--test_rows=%d" % test_rows, "--training_epochs=%d" % epochs,
+                     "--noshuffle", "--data_dir=/nonexistent"])
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = r.stdout.strip().splitlines()
+    assert out[0] == "Variables initialized ..."                                   # distributed.py:127
+    assert out[-1] == "done with training"                                         # distributed.py:169
+    prog = [l for l in out if l.startswith("Step so far")]
+    pat = re.compile(r"Step so far: (\d+),  Epoch so far: +(\d+),  Batch used: +(\d+) of +(\d+),  Cost now: ([0-9.]+),"
+                     r"  Time spent \(delta\): +[0-9.]+ms")
+    # the oracle on the same synthetic pool and initial weights
+    x, y = synthetic.make_pool(rows + test_rows)
+    Ws, bsz = synthetic.make_weights([784, 100, 10], False)
+    g = oracle.TF1Graph([784, 100, 10], oracle.ACT_SIGMOID, oracle.LOSS_SOFTMAX_CE, Ws, bsz)
+    per_epoch = rows // bs
+    costs = {}
+    step = 0
+    for e in range(epochs):
+        for i in range(per_epoch):
+            lo, _ = g.train_step(x[i * bs:(i + 1) * bs], y[i * bs:(i + 1) * bs], 0.001)
+            step += 1
+            costs[step] = float(lo)
+    assert len(prog) == epochs * 1                                                 # 55 batches: one line per epoch
+    for l in prog:
+        m = pat.fullmatch(l)
+        assert m, l
+        st, ep, ba, bc, cost = int(m[1]), int(m[2]), int(m[3]), int(m[4]), float(m[5])
+        assert bc == per_epoch and ba == per_epoch and st == ep * per_epoch
+        assert abs(cost - costs[st]) <= 1e-4 + 1e-5 * costs[st], (l, costs[st])
+    acc_line = [l for l in out if l.startswith("Acc: ")][0]
+    _, correct = g.evaluate(x[rows:], y[rows:])
+    assert acc_line == "Acc: %2.2f" % (correct / float(test_rows))                 # distributed.py:164
+    assert any(re.fullmatch(r"Time Taken: [0-9.]+s", l) for l in out)
+    assert [l for l in out if l.startswith("Final Computed Cost: ")][0] == "Final Computed Cost: %.2f" % costs[step]
+
+
+def test_distributed_py_strict_bug_mode_raises_like_the_reference(cuda_device):
+    r = _run_worker(["--ps_hosts=a:1", "--worker_hosts=127.0.0.1:2223", "--job_name=worker", "--train_rows=1000",
+                     "--test_rows=200", "--training_epochs=1", "--strict_reference_bugs", "--data_dir=/nonexistent"])
+    assert r.returncode != 0 and "TypeError: not all arguments converted during string formatting" in r.stderr
+    assert "Acc: " in r.stdout                                                      # distributed.py:164 ran first
