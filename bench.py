@@ -148,6 +148,7 @@ def main():
     ap.add_argument("--batch", type=int, default=None, help="rows per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-peer", action="store_true", help="multi-GPU: use the NCCL all-reduce instead of the peer-memory kernel")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -217,6 +218,12 @@ def main():
         uid = [pkg.DenseTrainer.new_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         tr.init_comm(rank, world, uid[0])
+        if not args.no_peer:
+            # map every rank's gradient buffer over NVLink: the exchange + SGD apply become one kernel
+            hs = [None] * world
+            dist.all_gather_object(hs, tr.peer_export())
+            tr.peer_import(hs)
+        cfg["gradient_exchange"] = "nccl all-reduce + apply" if args.no_peer else "one-shot peer-memory all-reduce fused with SGD apply"
 
     # ---- value: device-resident pool -----------------------------------------------------
     lt, ct = tr.train_steps(x_pool, y_pool, batch, warmup, first_row=0, lr=LR)

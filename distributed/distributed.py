@@ -43,6 +43,7 @@ flags.DEFINE_integer("train_rows", 55000, "synthetic pool: training rows (mnist.
 flags.DEFINE_integer("test_rows", 10000, "synthetic pool: test rows (mnist.test)")
 flags.DEFINE_boolean("shuffle", True, "reshuffle the training pool every epoch, as next_batch does (distributed.py:146)")
 flags.DEFINE_integer("shuffle_seed", 0, "seed of the per-epoch permutation (the reference's is unseeded)")
+flags.DEFINE_boolean("peer_exchange", True, "workers on one NVLink box sum gradients through peer memory instead of NCCL")
 flags.DEFINE_boolean("strict_reference_bugs", False,
                      "reproduce distributed.py:165 literally: the 'Time Taken' line raises TypeError")
 FLAGS = flags.FLAGS
@@ -105,6 +106,11 @@ def main(argv):
     # sv = tf.train.Supervisor(is_chief=(task_index == 0), ...); prepare_or_wait_for_session   distributed.py:129-135
     uid, store = cl.exchange_unique_id(role, b2.DenseTrainer.new_unique_id)
     model.init_comm(role.rank, role.world, uid)
+    if role.world > 1 and FLAGS.peer_exchange:
+        # replica_device_setter's ps round trip (distributed.py:63-65) -> gradients summed straight out of
+        # the other workers' GPU memory over NVLink, fused with the SGD apply
+        store.set("b2_peer_%d" % role.rank, model.peer_export())
+        model.peer_import([bytes(store.get("b2_peer_%d" % r)) for r in range(role.world)])
     cl.store_barrier(store, role, "b2_comm_ready")
 
     begin_time = time.time()

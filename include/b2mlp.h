@@ -51,7 +51,8 @@ enum { B2_PREC_FP32 = 0, B2_PREC_BF16_FP32ACC = 1 };       /* BASELINE.json conf
 /* Engine selection knobs for b2_set_option (tests cross-check the paths against each other). */
 enum {
   B2_OPT_FORCE_LAYERED = 1,  /* value 1: never use the single-kernel fused step, even when the shape allows it */
-  B2_OPT_KERNEL_TIMING = 2   /* value 1: bracket every kernel launch with CUDA events (see b2_kernel_times) */
+  B2_OPT_KERNEL_TIMING = 2,  /* value 1: bracket every kernel launch with CUDA events (see b2_kernel_times) */
+  B2_OPT_NO_PEER_EXCHANGE = 3 /* value 1: use the NCCL all-reduce even when peer memory is mapped (b2_peer_import) */
 };
 
 /* Kernel classes reported by b2_kernel_times. */
@@ -68,6 +69,7 @@ enum {
 };
 
 #define B2_UNIQUE_ID_BYTES 128
+#define B2_PEER_HANDLE_BYTES 64
 
 /* Library / build information: "b2mlp <version> sm_100a ..." (static string). */
 const char* b2_version(void);
@@ -108,6 +110,20 @@ int b2_params_get(b2_ctx* ctx, int layer, float* W_dev, float* b_dev, b2_stream_
  */
 int b2_get_unique_id(void* out128);
 int b2_comm_init(b2_ctx* ctx, int rank, int nranks, const void* unique_id128);
+
+/*
+ * Optional fast path of the gradient exchange for models whose parameter vector is small (<= 1 Mi
+ * floats): instead of calling NCCL, each rank leaves its gradient vector in a buffer that the other
+ * ranks of the box have mapped over NVLink, and one kernel per rank adds all vectors in rank order and
+ * applies the SGD update in the same pass.  This is what replaces the reference's per-step variable
+ * pull + gradient push through the parameter server (distributed.py:63-65) on an NVSwitch box.
+ * Call after b2_comm_init: b2_peer_export writes a 64-byte CUDA IPC handle; gather the handles of all
+ * ranks (rank order) and pass the nranks*64 bytes to b2_peer_import on every rank.  All ranks must be
+ * processes on one node with peer access between their GPUs; otherwise b2_peer_import fails and the
+ * NCCL path stays in use.
+ */
+int b2_peer_export(b2_ctx* ctx, void* handle_out64);
+int b2_peer_import(b2_ctx* ctx, const void* handles);
 
 /*
  * n_steps consecutive training steps on device-resident data; nothing is copied to or from the

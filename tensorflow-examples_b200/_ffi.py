@@ -11,13 +11,15 @@ EXPORTS = [
     "b2_version", "b2_last_error", "b2_create", "b2_destroy", "b2_set_option", "b2_param_count",
     "b2_params_set", "b2_params_get", "b2_get_unique_id", "b2_comm_init", "b2_train_steps", "b2_eval",
     "b2_session_run_train", "b2_global_step", "b2_launch_count", "b2_kernel_times", "b2_kernel_class_name",
-    "b2_linear_step_noalloc",
+    "b2_linear_step_noalloc", "b2_peer_export", "b2_peer_import",
 ]
 
 UNIQUE_ID_BYTES = 128
 OPT_FORCE_LAYERED = 1
 OPT_KERNEL_TIMING = 2
 KERNEL_CLASSES = 8
+OPT_NO_PEER_EXCHANGE = 3
+PEER_HANDLE_BYTES = 64
 
 
 class B2Error(RuntimeError):
@@ -81,6 +83,10 @@ def load_library():
     lib.b2_linear_step_noalloc.argtypes = [c_void_p, c_void_p, c_int, c_long, c_float, c_void_p, c_void_p,
                                            c_void_p, c_void_p, c_void_p]
     lib.b2_linear_step_noalloc.restype = c_int
+    lib.b2_peer_export.argtypes = [c_void_p, c_void_p]
+    lib.b2_peer_export.restype = c_int
+    lib.b2_peer_import.argtypes = [c_void_p, c_void_p]
+    lib.b2_peer_import.restype = c_int
     _LIB = lib
     return lib
 

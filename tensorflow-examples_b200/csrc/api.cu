@@ -20,7 +20,7 @@ void b2_set_error(const char* fmt, ...) {
 
 extern "C" const char* b2_last_error(void) { return g_err; }
 extern "C" const char* b2_version(void) {
-  return "b2mlp 0.1 sm_100a (fp32 CUDA-core layer kernels, fused 784->10 step, NCCL data parallel)";
+  return "b2mlp 0.2 sm_100a (fp32 layer kernels, fused 784->10 step, NCCL + NVLink peer-memory data parallel)";
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -178,6 +178,10 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
                  float* loss_trace, int* correct_trace, cudaStream_t s) {
   const float inv_B = 1.0f / (float)global_batch;
   const int apply = (c->nranks == 1) ? 1 : 0;
+  const bool use_peer = !apply && c->peer_ready && !c->opt_no_peer;
+  const int peer_buf = (int)(c->peer_step & 1u);
+  // where this rank's reduced vector goes: the exported peer buffer (parity of the step) or the private one
+  float* gvec = use_peer ? c->peer_local + (long)peer_buf * c->peer_stride : c->grads;
   int rc;
   if (use_fused_linear(c)) {
     const int tr = b2_fused_linear_tile_rows();
@@ -191,7 +195,7 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
     if (rc) return rc;
     {
       timed_scope t(c, B2_K_FUSED_REDUCE, s);
-      rc = b2_launch_fused_linear_reduce(c->fused_scratch, grid, c->grads, c->params, apply, lr,
+      rc = b2_launch_fused_linear_reduce(c->fused_scratch, grid, gvec, c->params, apply, lr,
                                          loss_trace, correct_trace, c->global_step_dev, c->P, s);
     }
     if (rc) return rc;
@@ -214,13 +218,28 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
     a.head_blocks = c->head_blocks;
     {
       timed_scope t(c, B2_K_REDUCE_APPLY, s);
-      rc = b2_launch_reduce(a, c->scratch, c->grads, c->params, apply, lr, loss_trace, correct_trace,
+      rc = b2_launch_reduce(a, c->scratch, gvec, c->params, apply, lr, loss_trace, correct_trace,
                             c->global_step_dev, c->sm_count, s);
     }
     if (rc) return rc;
     c->launches++;
   }
-  if (!apply) {
+  if (!apply && use_peer) {
+    // one kernel: wait for the peers' vectors, add them in rank order over NVLink, apply SGD
+    b2_peer_args a;
+    memset(&a, 0, sizeof(a));
+    a.rank = c->rank; a.nranks = c->nranks; a.stride = c->peer_stride;
+    for (int p = 0; p < c->nranks; ++p) {
+      a.vec[p] = (const float*)c->peer_base[p];
+      a.flag[p] = (unsigned*)((float*)c->peer_base[p] + 2 * c->peer_stride);
+    }
+    timed_scope t(c, B2_K_ALLREDUCE_APPLY, s);
+    rc = b2_launch_peer_allreduce_apply(a, c->params, c->grads, c->P, c->peer_step + 1, peer_buf, lr, loss_trace,
+                                        correct_trace, c->global_step_dev, c->sm_count, s);
+    if (rc) return rc;
+    c->peer_step++;
+    c->launches++;
+  } else if (!apply) {
     // the parameter-server push/pull of the reference (distributed.py:63-65) becomes one
     // all-reduce of [gradients..., loss, correct]; every rank then applies the same update.
     timed_scope t(c, B2_K_ALLREDUCE_APPLY, s);
@@ -237,6 +256,9 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
 void free_ctx(b2_ctx* c) {
   if (!c) return;
   if (c->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
+  for (int p = 0; p < B2_MAX_PEERS; ++p)
+    if (c->peer_base[p] && c->peer_base[p] != (void*)c->peer_local) cudaIpcCloseMemHandle(c->peer_base[p]);
+  cudaFree(c->peer_local);
   cudaFree(c->params);
   cudaFree(c->grads);
   for (int l = 0; l < B2_MAX_LAYERS; ++l) cudaFree(c->act_buf[l]);
@@ -385,6 +407,7 @@ extern "C" int b2_set_option(b2_ctx* ctx, int option, int value) {
   switch (option) {
     case B2_OPT_FORCE_LAYERED: ctx->opt_force_layered = value ? 1 : 0; return B2_OK;
     case B2_OPT_KERNEL_TIMING: ctx->opt_timing = value ? 1 : 0; return B2_OK;
+    case B2_OPT_NO_PEER_EXCHANGE: ctx->opt_no_peer = value ? 1 : 0; return B2_OK;
     default: b2_set_error("b2_set_option: unknown option %d", option); return B2_ERR_ARG;
   }
 }
@@ -484,6 +507,47 @@ extern "C" int b2_comm_init(b2_ctx* ctx, int rank, int nranks, const void* uniqu
     ctx->nccl_comm = nullptr; ctx->rank = 0; ctx->nranks = 1;
     return B2_ERR_NCCL;
   }
+  return B2_OK;
+}
+
+extern "C" int b2_peer_export(b2_ctx* ctx, void* handle_out64) {
+  B2_CHECK_ARG(ctx && handle_out64, "b2_peer_export: NULL argument");
+  B2_CHECK_ARG(ctx->nranks > 1, "b2_peer_export: call b2_comm_init with nranks > 1 first");
+  B2_CHECK_ARG(ctx->nranks <= B2_MAX_PEERS, "b2_peer_export: at most %d ranks", B2_MAX_PEERS);
+  B2_CHECK_ARG(ctx->P + 4 <= (1L << 20), "b2_peer_export: parameter vector too large for the one-shot exchange "
+               "(%ld floats); the NCCL path is used", ctx->P + 4);
+  B2_CUDA(cudaSetDevice(ctx->device));
+  if (!ctx->peer_local) {
+    ctx->peer_stride = ctx->P + 4;
+    const size_t bytes = (size_t)(2 * ctx->peer_stride) * sizeof(float) + 256;   // two vectors + the step flag
+    B2_CUDA(cudaMalloc((void**)&ctx->peer_local, bytes));
+    B2_CUDA(cudaMemset(ctx->peer_local, 0, bytes));
+  }
+  cudaIpcMemHandle_t h;
+  B2_CUDA(cudaIpcGetMemHandle(&h, ctx->peer_local));
+  static_assert(sizeof(h) == B2_PEER_HANDLE_BYTES, "IPC handle size");
+  memcpy(handle_out64, &h, sizeof(h));
+  return B2_OK;
+}
+
+extern "C" int b2_peer_import(b2_ctx* ctx, const void* handles) {
+  B2_CHECK_ARG(ctx && handles, "b2_peer_import: NULL argument");
+  if (!ctx->peer_local) { b2_set_error("b2_peer_import: call b2_peer_export first"); return B2_ERR_STATE; }
+  B2_CUDA(cudaSetDevice(ctx->device));
+  for (int p = 0; p < ctx->nranks; ++p) {
+    if (p == ctx->rank) { ctx->peer_base[p] = ctx->peer_local; continue; }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, (const char*)handles + (size_t)p * B2_PEER_HANDLE_BYTES, sizeof(h));
+    void* ptr = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      b2_set_error("b2_peer_import: cannot map rank %d's buffer: %s", p, cudaGetErrorString(e));
+      (void)cudaGetLastError();
+      return B2_ERR_CUDA;
+    }
+    ctx->peer_base[p] = ptr;
+  }
+  ctx->peer_ready = 1;
   return B2_OK;
 }
 

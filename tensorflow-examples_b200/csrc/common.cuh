@@ -9,6 +9,7 @@
 #include "../../include/b2mlp.h"
 
 #define B2_MAX_LAYERS 8
+#define B2_MAX_PEERS 16
 
 // ---- error plumbing --------------------------------------------------------------------------
 void b2_set_error(const char* fmt, ...);
@@ -73,6 +74,13 @@ struct b2_ctx {
   // data parallel
   int rank, nranks;
   void* nccl_comm;
+  // peer-memory exchange (optional, small models): my vectors [2][peer_stride] + step flag, and the peers' mappings
+  float* peer_local;               // cudaMalloc'ed, exported with cudaIpcGetMemHandle
+  long peer_stride;                // floats per vector (P + 4)
+  void* peer_base[B2_MAX_PEERS];   // mapped base of every rank's buffer (own entry = peer_local)
+  int peer_ready;
+  int opt_no_peer;                 // B2_OPT_NO_PEER_EXCHANGE
+  unsigned peer_step;              // exchanges enqueued so far
 
   // optional per-kernel event timing (B2_OPT_KERNEL_TIMING)
   int opt_timing;
@@ -131,3 +139,14 @@ int b2_launch_fused_linear_reduce(const float* scratch, int grid, float* grads, 
                                   int apply, float lr, float* loss_trace, int* correct_trace,
                                   float* global_step, long P, cudaStream_t s);
 int b2_fused_linear_prepare(void);
+
+// ---- launcher (peer_allreduce.cu): one-shot all-reduce over NVLink peer memory fused with the SGD apply ----
+struct b2_peer_args {
+  int rank, nranks;
+  long stride;                          // floats between the two step-parity vectors
+  const float* vec[B2_MAX_PEERS];       // every rank's vector buffer (peer mappings)
+  unsigned* flag[B2_MAX_PEERS];         // every rank's step flag
+};
+int b2_launch_peer_allreduce_apply(const b2_peer_args& a, float* params, float* grads_out, long P, unsigned step1,
+                                   int buf, float lr, float* loss_trace, int* correct_trace, float* global_step,
+                                   int sm_count, cudaStream_t s);

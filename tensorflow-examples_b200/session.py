@@ -145,6 +145,21 @@ class DenseTrainer:
         _ffi.check(self._lib, self._lib.b2_comm_init(self._h, int(rank), int(nranks), buf))
         self.rank, self.nranks = int(rank), int(nranks)
 
+    def peer_export(self):
+        """64-byte CUDA IPC handle of this rank's gradient-exchange buffer (see include/b2mlp.h)."""
+        buf = ctypes.create_string_buffer(_ffi.PEER_HANDLE_BYTES)
+        _ffi.check(self._lib, self._lib.b2_peer_export(self._h, buf))
+        return buf.raw
+
+    def peer_import(self, handles):
+        """handles: the exported handles of all ranks, in rank order (list of bytes or one bytes object)."""
+        blob = b"".join(handles) if isinstance(handles, (list, tuple)) else bytes(handles)
+        assert len(blob) == self.nranks * _ffi.PEER_HANDLE_BYTES
+        _ffi.check(self._lib, self._lib.b2_peer_import(self._h, ctypes.create_string_buffer(blob, len(blob))))
+
+    def use_peer_exchange(self, on=True):
+        self.set_option(_ffi.OPT_NO_PEER_EXCHANGE, 0 if on else 1)
+
     # -- the hot path ---------------------------------------------------------------------------
     def train_steps(self, x_pool, y_pool, local_batch, n_steps, first_row=0, lr=0.001,
                     loss_trace=None, correct_trace=None):

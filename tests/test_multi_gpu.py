@@ -35,6 +35,10 @@ tr.set_params(Ws, bs)
 uid = [b2.DenseTrainer.new_unique_id() if rank == 0 else None]
 dist.broadcast_object_list(uid, src=0)
 tr.init_comm(rank, world, uid[0])
+if %(peer)d:
+    hs = [None] * world
+    dist.all_gather_object(hs, tr.peer_export())
+    tr.peer_import(hs)
 dev = torch.device("cuda", rank)
 lt, ct = tr.train_steps(torch.from_numpy(x).to(dev), torch.from_numpy(y).to(dev), lb, steps, lr=0.001)
 torch.cuda.synchronize()
@@ -46,14 +50,15 @@ dist.destroy_process_group()
 '''
 
 
+@pytest.mark.parametrize("peer", [1, 0], ids=["peer-memory", "nccl"])
 @pytest.mark.parametrize("dims,act,scaled", [([784, 10], 0, True), ([784, 100, 10], 1, False)])
-def test_n_rank_trace_equals_single_process_oracle(cuda_device, tmp_path, dims, act, scaled):
+def test_n_rank_trace_equals_single_process_oracle(cuda_device, tmp_path, dims, act, scaled, peer):
     world = min(torch.cuda.device_count(), 4)
     if world < 2:
         pytest.skip("needs at least 2 GPUs")
-    lb, steps = 96, 5
+    lb, steps = 96, 12
     script = tmp_path / "worker.py"
-    script.write_text(WORKER % dict(root=ROOT, dims=dims, act=act, scaled=scaled, lb=lb, steps=steps, out=str(tmp_path)))
+    script.write_text(WORKER % dict(root=ROOT, dims=dims, act=act, scaled=scaled, lb=lb, steps=steps, out=str(tmp_path), peer=peer))
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % world,
                         "--master-addr", "127.0.0.1", "--master-port", "29611", str(script)],
                        capture_output=True, text=True, timeout=900)
