@@ -186,6 +186,21 @@ int b2_linear_step_noalloc(const float* x_dev, const float* y_dev, int rows, lon
                            float* W_dev, float* b_dev, float* loss_dev, int* correct_dev,
                            b2_stream_t stream);
 
+/*
+ * The layer matrix product on the tensor cores (tcgen05.mma, bf16 operands, fp32 accumulate), exposed
+ * on its own: what tf.matmul does at distributed.py:96,98 and what its TF1 gradient builds
+ * (transpose_a / transpose_b products), with the element-wise op that follows fused into the epilogue.
+ *   a_mn = 0: A is [M,K] row-major        a_mn = 1: A is [K,M] row-major (i.e. A^T is given)
+ *   b_mn = 0: B is [N,K] row-major        b_mn = 1: B is [K,N] row-major
+ *   epi  = 0: out(bf16) = sigmoid(acc + bias[N])     forward of a hidden layer (distributed.py:96-97)
+ *          1: out(bf16) = acc * act * (1 - act)      input gradient through the sigmoid (act: bf16 [M,N])
+ *          2: out(fp32) = acc                        weight gradient
+ *          3: out(fp32) = acc + bias[N]              forward of a linear layer
+ * All matrices are device pointers, 16-byte aligned, leading dimensions multiples of 8.
+ */
+int b2_matmul_bf16(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
+                   const float* bias, const void* act, void* out, b2_stream_t stream);
+
 /* The float32 `global_step` variable (distributed.py:68-70,108) as of the last enqueued step. */
 float b2_global_step(const b2_ctx* ctx);
 

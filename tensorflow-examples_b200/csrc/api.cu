@@ -510,6 +510,19 @@ extern "C" int b2_comm_init(b2_ctx* ctx, int rank, int nranks, const void* uniqu
   return B2_OK;
 }
 
+extern "C" int b2_matmul_bf16(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
+                              const float* bias, const void* act, void* out, b2_stream_t stream) {
+  B2_CHECK_ARG(A && B && out, "b2_matmul_bf16: NULL matrix");
+  B2_CHECK_ARG(M >= 1 && N >= 1 && K >= 1, "b2_matmul_bf16: bad shape %d x %d x %d", M, N, K);
+  B2_CHECK_ARG(epi >= 0 && epi <= 3, "b2_matmul_bf16: unknown epilogue %d", epi);
+  B2_CHECK_ARG((epi != 0 && epi != 3) || bias, "b2_matmul_bf16: this epilogue needs a bias vector");
+  B2_CHECK_ARG(epi != 1 || act, "b2_matmul_bf16: this epilogue needs the activations");
+  int dev = 0, sms = 0;
+  B2_CUDA(cudaGetDevice(&dev));
+  B2_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  return b2_launch_gemm_bf16(A, a_mn, B, b_mn, M, N, K, epi, bias, act, out, sms, (cudaStream_t)stream);
+}
+
 extern "C" int b2_peer_export(b2_ctx* ctx, void* handle_out64) {
   B2_CHECK_ARG(ctx && handle_out64, "b2_peer_export: NULL argument");
   B2_CHECK_ARG(ctx->nranks > 1, "b2_peer_export: call b2_comm_init with nranks > 1 first");

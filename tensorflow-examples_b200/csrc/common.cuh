@@ -150,3 +150,7 @@ struct b2_peer_args {
 int b2_launch_peer_allreduce_apply(const b2_peer_args& a, float* params, float* grads_out, long P, unsigned step1,
                                    int buf, float lr, float* loss_trace, int* correct_trace, float* global_step,
                                    int sm_count, cudaStream_t s);
+
+// ---- launcher (gemm_tcgen05.cu): bf16 tensor-core GEMM with fused epilogues ------------------------------
+int b2_launch_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
+                        const float* bias, const void* act, void* out, int sm_count, cudaStream_t s);

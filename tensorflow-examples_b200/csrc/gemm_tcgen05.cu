@@ -1,0 +1,389 @@
+// bf16 x bf16 -> fp32 GEMM on the 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM),
+// operands staged by TMA into 128B-swizzled shared memory.  This is the layer GEMM of the scaled-up
+// MLP (BASELINE.json configs[4], 784-4096-4096-10 at batch 65536), where the contractions are real
+// dense ones; the small models stay on the CUDA-core kernels.
+//
+// One kernel covers the three products of a dense layer (distributed.py:96,98 and their TF1 gradients):
+//   forward   C[M,N]  = A[M,K] . W[K,N]          A K-major,  B = W  MN-major   + bias, sigmoid  -> bf16
+//   dgrad     dA[M,K] = dZ[M,N] . W[K,N]^T       A K-major,  B = W  K-major    * a(1-a)         -> bf16
+//   wgrad     dW[K,N] = A[M,K]^T . dZ[M,N]       A MN-major, B = dZ MN-major                    -> fp32
+// so no transposed copy of any operand is ever made: the UMMA descriptors describe the transposition.
+//
+// Persistent grid (one CTA per SM), 128 x 256 output tiles, BLOCK_K = 64, 4-stage TMA ring.
+//   warp 0      TMA producer (one elected lane)
+//   warp 1      allocates TMEM (2 x 256 columns: two accumulator buffers) and issues tcgen05.mma
+//   warps 2-5   epilogue: tcgen05.ld accumulators -> registers -> fused epilogue -> global, while the
+//               next tile's MMAs already fill the other accumulator buffer
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace tg {
+
+constexpr int BLOCK_M = 128, BLOCK_K = 64, UMMA_K = 16;
+constexpr int STAGES = 4;
+constexpr int THREADS = 192;
+constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;   // 16 KB
+
+template <int BLOCK_N>
+struct Cfg {
+  static constexpr int B_STAGE_BYTES = BLOCK_N * BLOCK_K * 2;
+  static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int TMEM_COLS = 2 * BLOCK_N;          // 512 for N = 256, 256 for N = 128 (power of two)
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  uint32_t ok = 0;
+  for (uint32_t spins = 0;; ++spins) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    if (ok) break;
+    if (spins > (1u << 26)) __trap();   // watchdog: a protocol bug must not hang the GPU
+  }
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory matrix descriptor, 128B swizzle (cute::UMMA::SmemDescriptor bit layout):
+//   [0,14) start>>4   [16,30) LBO>>4   [32,46) SBO>>4   [46,48) version=1   [61,64) layout=2 (SWIZZLE_128B)
+// K-major tile  (rows of 64 bf16 = 128 B): 8-row groups 1024 B apart -> SBO = 1024, LBO unused (1)
+// MN-major tile (64 MN elements = 128 B per k row): 8-k-row atoms 1024 B apart -> SBO = 1024,
+//                                                   next 64 MN elements LBO = 64 k rows * 128 B = 8192 B apart
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, bool mn_major) {
+  const uint64_t lbo = mn_major ? (uint64_t)((BLOCK_K * 128) >> 4) : 1ull;
+  const uint64_t sbo = 1024 >> 4;
+  return (uint64_t)((saddr & 0x3FFFF) >> 4) | (lbo << 16) | (sbo << 32) | (1ull << 46) | (2ull << 61);
+}
+
+enum { EPI_BIAS_SIGMOID_BF16 = 0, EPI_DSIGMOID_BF16 = 1, EPI_STORE_F32 = 2, EPI_BIAS_F32 = 3 };
+
+struct Params {
+  int M, N, K;
+  int a_mn, b_mn;          // 1 = MN-major operand (global [K, M] / [K, N] row-major), 0 = K-major ([M, K] / [N, K])
+  int epi;
+  const float* bias;       // EPI_BIAS_*: [N]
+  const __nv_bfloat16* act;  // EPI_DSIGMOID: [M, N] activations a; out = acc * a * (1 - a)
+  void* out;               // bf16 or fp32 [M, N] row-major
+};
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(THREADS, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Params p) {
+  using C = Cfg<BLOCK_N>;
+  extern __shared__ unsigned char smem_raw[];
+  // 1024-byte alignment: required by the 128B swizzle atoms (descriptor base_offset = 0)
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  unsigned char* smA = smem;
+  unsigned char* smB = smem + STAGES * A_STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * C::STAGE_BYTES);
+  uint64_t* full = bars;                 // [STAGES]  TMA -> MMA
+  uint64_t* empty = bars + STAGES;       // [STAGES]  MMA -> TMA
+  uint64_t* tfull = bars + 2 * STAGES;   // [2]       MMA -> epilogue
+  uint64_t* tempty = tfull + 2;          // [2]       epilogue -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tiles_m = (p.M + BLOCK_M - 1) / BLOCK_M, tiles_n = (p.N + BLOCK_N - 1) / BLOCK_N;
+  const int ntiles = tiles_m * tiles_n;
+  const int num_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"((uint32_t)C::TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------ TMA producer ------------------------------------
+    if (lane == 0) {
+      int it = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int m0 = (tile / tiles_n) * BLOCK_M, n0 = (tile % tiles_n) * BLOCK_N;
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const int s = it % STAGES;
+          mbar_wait(&empty[s], ((it / STAGES) & 1) ^ 1);
+          mbar_expect_tx(&full[s], C::STAGE_BYTES);
+          const int k0 = kb * BLOCK_K;
+          unsigned char* a_dst = smA + s * A_STAGE_BYTES;
+          unsigned char* b_dst = smB + s * C::B_STAGE_BYTES;
+          if (p.a_mn) {
+#pragma unroll
+            for (int a = 0; a < BLOCK_M / 64; ++a) tma_load_2d(a_dst + a * (BLOCK_K * 128), &tmA, m0 + 64 * a, k0, &full[s]);
+          } else {
+            tma_load_2d(a_dst, &tmA, k0, m0, &full[s]);
+          }
+          if (p.b_mn) {
+#pragma unroll
+            for (int b = 0; b < BLOCK_N / 64; ++b) tma_load_2d(b_dst + b * (BLOCK_K * 128), &tmB, n0 + 64 * b, k0, &full[s]);
+          } else {
+            tma_load_2d(b_dst, &tmB, k0, n0, &full[s]);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------ MMA issuer ------------------------------------
+    if (lane == 0) {
+      // instruction descriptor (cute::UMMA::InstrDescriptor): D = F32, A = B = BF16, majors, N >> 3, M >> 4
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16) |
+                             ((uint32_t)(BLOCK_N >> 3) << 17) | ((uint32_t)(BLOCK_M >> 4) << 24);
+      const uint32_t a_step = p.a_mn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;   // descriptor units of 16 B
+      const uint32_t b_step = p.b_mn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+      int it = 0, t = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t) {
+        const int acc = t & 1;
+        mbar_wait(&tempty[acc], ((t >> 1) & 1) ^ 1);       // epilogue has drained this accumulator buffer
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const int s = it % STAGES;
+          mbar_wait(&full[s], (it / STAGES) & 1);
+          tc_fence_after();
+          const uint64_t da = make_desc(smem_u32(smA + s * A_STAGE_BYTES), p.a_mn);
+          const uint64_t db = make_desc(smem_u32(smB + s * C::B_STAGE_BYTES), p.b_mn);
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+            tc_mma(d_tmem, da + (uint64_t)(k * a_step), db + (uint64_t)(k * b_step), idesc, (kb | k) != 0);
+          tc_commit(&empty[s]);                             // frees the smem stage when these MMAs retire
+        }
+        tc_commit(&tfull[acc]);                             // accumulator complete
+      }
+    }
+  } else {
+    // ------------------------------------ epilogue ------------------------------------
+    const int quarter = warp & 3;                           // TMEM lanes 32*quarter .. +31 belong to this warp
+    int t = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t) {
+      const int acc = t & 1;
+      const int m0 = (tile / tiles_n) * BLOCK_M, n0 = (tile % tiles_n) * BLOCK_N;
+      mbar_wait(&tfull[acc], (t >> 1) & 1);
+      tc_fence_after();
+      const int row = m0 + quarter * 32 + lane;
+      const bool row_ok = row < p.M;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+        uint32_t r[32];
+        tc_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BLOCK_N + c0), r);
+        const int n = n0 + c0;
+        if (!row_ok || n >= p.N) continue;
+        const size_t off = (size_t)row * p.N + n;
+        if (p.epi == EPI_STORE_F32 || p.epi == EPI_BIAS_F32) {
+          float* o = reinterpret_cast<float*>(p.out) + off;
+          if (n + 32 <= p.N) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
+                                     __uint_as_float(r[j + 3]));
+              if (p.epi == EPI_BIAS_F32) {
+                const float4 b = *reinterpret_cast<const float4*>(p.bias + n + j);
+                v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
+              }
+              *reinterpret_cast<float4*>(o + j) = v;
+            }
+          } else {
+            for (int j = 0; j < 32 && n + j < p.N; ++j)
+              o[j] = __uint_as_float(r[j]) + (p.epi == EPI_BIAS_F32 ? p.bias[n + j] : 0.f);
+          }
+        } else if (n + 32 > p.N) {
+          // ragged last column chunk: element-wise
+          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + off;
+          for (int j = 0; j < 32 && n + j < p.N; ++j) {
+            float v = __uint_as_float(r[j]);
+            if (p.epi == EPI_BIAS_SIGMOID_BF16) {
+              v = 1.0f / (1.0f + __expf(-(v + p.bias[n + j])));
+            } else {
+              const float a = __bfloat162float(p.act[off + j]);
+              v = v * a * (1.0f - a);
+            }
+            o[j] = __float2bfloat16_rn(v);
+          }
+        } else {
+          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + off;
+          float v[32];
+          if (p.epi == EPI_BIAS_SIGMOID_BF16) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 b = *reinterpret_cast<const float4*>(p.bias + n + j);
+              const float bb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+              for (int u = 0; u < 4; ++u) {
+                const float z = __uint_as_float(r[j + u]) + bb[u];
+                v[j + u] = 1.0f / (1.0f + __expf(-z));     // distributed.py:97 (bf16 output absorbs the intrinsic's error)
+              }
+            }
+          } else {
+            const uint4* ap = reinterpret_cast<const uint4*>(p.act + off);
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              const uint4 q = ap[j / 8];
+              const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+              for (int u = 0; u < 4; ++u) {
+                const float a0 = __uint_as_float(w[u] << 16), a1 = __uint_as_float(w[u] & 0xFFFF0000u);
+                v[j + 2 * u] = __uint_as_float(r[j + 2 * u]) * a0 * (1.0f - a0);         // SigmoidGrad
+                v[j + 2 * u + 1] = __uint_as_float(r[j + 2 * u + 1]) * a1 * (1.0f - a1);
+              }
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            uint32_t w[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const __nv_bfloat162 h = __floats2bfloat162_rn(v[j + 2 * u], v[j + 2 * u + 1]);
+              w[u] = *reinterpret_cast<const uint32_t*>(&h);
+            }
+            *reinterpret_cast<uint4*>(o + j) = make_uint4(w[0], w[1], w[2], w[3]);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[acc]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::TMEM_COLS)
+                 : "memory");
+  }
+}
+
+// ---- host side: tensor maps -----------------------------------------------------------------
+typedef CUresult (*pfn_encode)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static pfn_encode g_encode = nullptr;
+
+static int get_encode() {
+  if (g_encode) return B2_OK;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+  if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || !fn) {
+    b2_set_error("cuTensorMapEncodeTiled is not available from this driver");
+    return B2_ERR_CUDA;
+  }
+  g_encode = (pfn_encode)fn;
+  return B2_OK;
+}
+
+// 2-D bf16 row-major [rows, cols]; box = {64 (inner, 128 B), box_rows}; 128B swizzle; out-of-bounds reads give 0
+static int make_map(CUtensorMap* m, const void* base, long rows, long cols, int box_rows) {
+  const cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t gstr[1] = {(cuuint64_t)cols * 2};
+  const cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1u, 1u};
+  CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    b2_set_error("cuTensorMapEncodeTiled failed (%d) for a [%ld, %ld] bf16 matrix", (int)r, rows, cols);
+    return B2_ERR_CUDA;
+  }
+  return B2_OK;
+}
+
+}  // namespace tg
+
+// A: K-major -> global [M, K]; MN-major -> global [K, M].   B: K-major -> [N, K]; MN-major -> [K, N].
+int b2_launch_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
+                        const float* bias, const void* act, void* out, int sm_count, cudaStream_t s) {
+  using namespace tg;
+  if ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B) | reinterpret_cast<uintptr_t>(out)) & 15) {
+    b2_set_error("gemm_bf16: operands must be 16-byte aligned");
+    return B2_ERR_ARG;
+  }
+  if ((a_mn ? M : K) % 8 || (b_mn ? N : K) % 8 || N % 8) {
+    b2_set_error("gemm_bf16: leading dimensions must be multiples of 8 elements (M=%d N=%d K=%d)", M, N, K);
+    return B2_ERR_ARG;
+  }
+  int rc = get_encode();
+  if (rc) return rc;
+  constexpr int BN = 256;
+  CUtensorMap ta, tb;
+  rc = a_mn ? make_map(&ta, A, K, M, BLOCK_K) : make_map(&ta, A, M, K, BLOCK_M);
+  if (rc) return rc;
+  rc = b_mn ? make_map(&tb, B, K, N, BLOCK_K) : make_map(&tb, B, N, K, BN);
+  if (rc) return rc;
+  Params p;
+  p.M = M; p.N = N; p.K = K; p.a_mn = a_mn; p.b_mn = b_mn; p.epi = epi;
+  p.bias = bias; p.act = reinterpret_cast<const __nv_bfloat16*>(act); p.out = out;
+  static bool attr = false;
+  if (!attr) {
+    B2_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
+    attr = true;
+  }
+  const int tiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + BN - 1) / BN);
+  const int grid = tiles < sm_count ? tiles : sm_count;
+  gemm_bf16_kernel<BN><<<grid, THREADS, Cfg<BN>::SMEM_BYTES, s>>>(ta, tb, p);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    b2_set_error("gemm_bf16 launch failed: %s", cudaGetErrorString(e));
+    return B2_ERR_CUDA;
+  }
+  return B2_OK;
+}
