@@ -65,7 +65,11 @@ enum {
   B2_K_FUSED_STEP = 5,    /* single-kernel 784->10 step */
   B2_K_FUSED_REDUCE = 6,  /* its partial reduction (+ SGD) */
   B2_K_ALLREDUCE_APPLY = 7, /* gradient all-reduce + SGD apply (data parallel only) */
-  B2_KERNEL_CLASSES = 8
+  B2_K_GEMM_FWD = 8,      /* tcgen05 GEMM: act(A W + b)            bf16 path, hidden layers */
+  B2_K_GEMM_DGRAD = 9,    /* tcgen05 GEMM: dZ W^T * act'           bf16 path */
+  B2_K_GEMM_WGRAD = 10,   /* tcgen05 GEMM: A^T dZ                  bf16 path */
+  B2_K_MIXED_AUX = 11,    /* casts, narrow output layer, bias column sums, SGD apply of the bf16 path */
+  B2_KERNEL_CLASSES = 12
 };
 
 #define B2_UNIQUE_ID_BYTES 128

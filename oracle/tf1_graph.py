@@ -34,7 +34,9 @@ SigmoidGrad g*a*(1-a).  dx of the first layer is pruned, as in TF1.
 `precision="bf16"` restates the scaled-up configuration (BASELINE.json configs[4]):
 every GEMM operand (inputs, activations, weights, output-side gradients) is
 rounded to bfloat16 (round-to-nearest-even) before the product, accumulation and
-everything else stay float32, master weights stay float32.
+everything else stay float32, master weights stay float32.  Hidden activations and the
+gradients w.r.t. hidden pre-activations are STORED in bf16 (so their bias gradients sum the
+rounded values); the output layer's dz stays float32 for its bias gradient.
 """
 from __future__ import annotations
 
@@ -167,6 +169,8 @@ class TF1Graph:
                     dz = da * a_in * (self.dtype.type(1) - a_in)            # SigmoidGrad
                 else:
                     dz = da
+                if self.precision == "bf16":
+                    dz = bf16_round(dz)   # hidden-layer gradients are stored in bf16, like the activations
         return loss, correct, dWs, dbs
 
     def apply(self, dWs, dbs, lr):

@@ -17,7 +17,7 @@ EXPORTS = [
 UNIQUE_ID_BYTES = 128
 OPT_FORCE_LAYERED = 1
 OPT_KERNEL_TIMING = 2
-KERNEL_CLASSES = 8
+KERNEL_CLASSES = 12
 OPT_NO_PEER_EXCHANGE = 3
 PEER_HANDLE_BYTES = 64
 

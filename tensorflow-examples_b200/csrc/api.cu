@@ -173,9 +173,145 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
   return B2_OK;
 }
 
+// ---- bf16-operand path: tensor-core GEMMs for the hidden layers, CUDA cores for the narrow output layer ----
+inline bool is_mixed(const b2_ctx* c) { return c->precision == B2_PREC_BF16_FP32ACC; }
+
+int refresh_bf16_weights(b2_ctx* c, cudaStream_t s) {
+  for (int l = 0; l < c->n_layers - 1; ++l) {
+    timed_scope t(c, B2_K_MIXED_AUX, s);
+    int rc = b2_launch_cast_bf16(c->params + c->w_off[l], c->wb[l], w_size(c, l), c->sm_count, s);
+    if (rc) return rc;
+    c->launches++;
+  }
+  c->wb_stale = 0;
+  return B2_OK;
+}
+
+// forward + loss head; leaves logits in z_last, dz of the output layer (fp32) in dz[0], head partials in scratch
+int enqueue_forward_mixed(b2_ctx* c, const float* x, const float* y, int rows, float inv_B, cudaStream_t s) {
+  const int n = c->n_layers;
+  int rc;
+  if (c->wb_stale && (rc = refresh_bf16_weights(c, s))) return rc;
+  {
+    timed_scope t(c, B2_K_MIXED_AUX, s);
+    rc = b2_launch_cast_bf16(x, c->xb, (long)rows * c->dims[0], c->sm_count, s);
+  }
+  if (rc) return rc;
+  c->launches++;
+  const void* a_in = c->xb;
+  for (int l = 0; l < n - 1; ++l) {
+    // a_out = sigmoid(a_in . W + b)   distributed.py:96-97   A K-major [rows, in], B = W [in, out] MN-major
+    timed_scope t(c, B2_K_GEMM_FWD, s);
+    rc = b2_launch_gemm_bf16(a_in, 0, c->wb[l], 1, rows, c->dims[l + 1], c->dims[l], 0, c->params + c->b_off[l],
+                             nullptr, c->ab[l], c->sm_count, s);
+    if (rc) return rc;
+    c->launches++;
+    a_in = c->ab[l];
+  }
+  {
+    timed_scope t(c, B2_K_MIXED_AUX, s);
+    rc = b2_launch_skinny_fwd(a_in, c->params + c->w_off[n - 1], c->params + c->b_off[n - 1], c->z_last, rows,
+                              c->dims[n - 1], c->dims[n], c->sm_count, s);
+  }
+  if (rc) return rc;
+  c->launches++;
+  float* head = c->scratch + c->head_part_off;
+  {
+    timed_scope t(c, B2_K_LOSS_HEAD, s);
+    rc = b2_launch_loss_head(c->z_last, y, c->dz[0], head, head + c->head_blocks, rows, c->dims[n], c->loss, inv_B,
+                             c->head_blocks, s);
+  }
+  if (rc) return rc;
+  c->launches++;
+  return B2_OK;
+}
+
+int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long global_batch, float lr,
+                       float* loss_trace, int* correct_trace, cudaStream_t s) {
+  const int n = c->n_layers;
+  const float inv_B = 1.0f / (float)global_batch;
+  int rc = enqueue_forward_mixed(c, x, y, rows, inv_B, s);
+  if (rc) return rc;
+  // ---- output layer: dz_prev, dW partials, db partials in one pass over the last hidden activations ----
+  const int L = n - 1;
+  const int slices = b2_skinny_bwd_slices(rows, c->dims[L], c->sm_count);
+  float* pw = c->scratch + c->part_off[L];
+  float* pb = pw + round4(w_size(c, L));
+  {
+    timed_scope t(c, B2_K_MIXED_AUX, s);
+    rc = b2_launch_skinny_bwd(c->ab[L - 1], c->dz[0], c->params + c->w_off[L], c->dzb[0], pw, pb, part_stride(c, L),
+                              rows, c->dims[L], c->dims[n], slices, s);
+  }
+  if (rc) return rc;
+  c->launches++;
+  int cur = 0;
+  for (int l = L - 1; l >= 0; --l) {
+    // dz of layer l (bf16 [rows, dims[l+1]]) is in dzb[cur]
+    const void* a_prev = (l == 0) ? c->xb : c->ab[l - 1];
+    {
+      timed_scope t(c, B2_K_MIXED_AUX, s);
+      rc = b2_launch_colsum_bf16(c->dzb[cur], c->colsum_part, c->grads + c->b_off[l], rows, c->dims[l + 1],
+                                 b2_colsum_slices(rows, c->dims[l + 1], c->sm_count), s);
+    }
+    if (rc) return rc;
+    c->launches += 2;
+    {
+      // dW = a_prev^T . dz     both operands MN-major (global [rows, in] and [rows, out]); fp32 straight into grads
+      timed_scope t(c, B2_K_GEMM_WGRAD, s);
+      rc = b2_launch_gemm_bf16(a_prev, 1, c->dzb[cur], 1, c->dims[l], c->dims[l + 1], rows, 2, nullptr, nullptr,
+                               c->grads + c->w_off[l], c->sm_count, s);
+    }
+    if (rc) return rc;
+    c->launches++;
+    if (l > 0) {
+      // dz_prev = (dz . W^T) * a(1-a)   A = dz K-major [rows, out], B = W [in, out] K-major
+      timed_scope t(c, B2_K_GEMM_DGRAD, s);
+      rc = b2_launch_gemm_bf16(c->dzb[cur], 0, c->wb[l], 0, rows, c->dims[l], c->dims[l + 1], 1, nullptr, c->ab[l - 1],
+                               c->dzb[cur ^ 1], c->sm_count, s);
+      if (rc) return rc;
+      c->launches++;
+      cur ^= 1;
+    }
+  }
+  // ---- output-layer partials + loss / correct -> grads ----
+  b2_reduce_args a;
+  memset(&a, 0, sizeof(a));
+  a.n_layers = 1;
+  a.w_off[0] = c->w_off[L]; a.b_off[0] = c->b_off[L];
+  a.w_size[0] = w_size(c, L); a.b_size[0] = b_size(c, L);
+  a.part_off[0] = c->part_off[L];
+  a.splits[0] = slices;
+  a.P = c->P;
+  a.head_part_off = c->head_part_off;
+  a.head_blocks = c->head_blocks;
+  {
+    timed_scope t(c, B2_K_REDUCE_APPLY, s);
+    rc = b2_launch_reduce(a, c->scratch, c->grads, c->params, 0, lr, nullptr, nullptr, c->global_step_dev,
+                          c->sm_count, s);
+  }
+  if (rc) return rc;
+  c->launches++;
+  if (c->nranks > 1) {
+    timed_scope t(c, B2_K_ALLREDUCE_APPLY, s);
+    B2_NCCL(g_nccl.AllReduce(c->grads, c->grads, (size_t)(c->P + 4), kNcclFloat, kNcclSum, c->nccl_comm, s));
+  }
+  long off[B2_MAX_LAYERS], size[B2_MAX_LAYERS];
+  for (int l = 0; l < L; ++l) { off[l] = c->w_off[l]; size[l] = w_size(c, l); }
+  {
+    timed_scope t(c, B2_K_MIXED_AUX, s);
+    rc = b2_launch_sgd_apply_mixed(c->params, c->grads, c->P, lr, L, off, size, c->wb, loss_trace, correct_trace,
+                                   c->global_step_dev, c->sm_count, s);
+  }
+  if (rc) return rc;
+  c->launches++;
+  c->global_step_host += 1.0f;
+  return B2_OK;
+}
+
 // One full training step on `rows` local rows starting at x / y.
 int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long global_batch, float lr,
                  float* loss_trace, int* correct_trace, cudaStream_t s) {
+  if (is_mixed(c)) return enqueue_step_mixed(c, x, y, rows, global_batch, lr, loss_trace, correct_trace, s);
   const float inv_B = 1.0f / (float)global_batch;
   const int apply = (c->nranks == 1) ? 1 : 0;
   const bool use_peer = !apply && c->peer_ready && !c->opt_no_peer;
@@ -259,6 +395,11 @@ void free_ctx(b2_ctx* c) {
   for (int p = 0; p < B2_MAX_PEERS; ++p)
     if (c->peer_base[p] && c->peer_base[p] != (void*)c->peer_local) cudaIpcCloseMemHandle(c->peer_base[p]);
   cudaFree(c->peer_local);
+  cudaFree(c->xb);
+  for (int l = 0; l < B2_MAX_LAYERS; ++l) { cudaFree(c->ab[l]); cudaFree(c->wb[l]); }
+  cudaFree(c->dzb[0]);
+  cudaFree(c->dzb[1]);
+  cudaFree(c->colsum_part);
   cudaFree(c->params);
   cudaFree(c->grads);
   for (int l = 0; l < B2_MAX_LAYERS; ++l) cudaFree(c->act_buf[l]);
@@ -297,8 +438,17 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
     B2_CHECK_ARG(dims[i] >= 1, "b2_create: dims[%d] = %d must be >= 1", i, dims[i]);
   B2_CHECK_ARG(act == B2_ACT_IDENTITY || act == B2_ACT_SIGMOID, "b2_create: unknown activation %d", act);
   B2_CHECK_ARG(loss == B2_LOSS_SSE_SUM || loss == B2_LOSS_SOFTMAX_CE_MEAN, "b2_create: unknown loss %d", loss);
-  B2_CHECK_ARG(precision == B2_PREC_FP32,
-               "b2_create: precision %d not available in this build (fp32 only)", precision);
+  B2_CHECK_ARG(precision == B2_PREC_FP32 || precision == B2_PREC_BF16_FP32ACC, "b2_create: unknown precision %d", precision);
+  if (precision == B2_PREC_BF16_FP32ACC) {
+    // tensor-core path: hidden layers are tcgen05 GEMMs (TMA needs 16-byte row pitches), the output layer is narrow
+    B2_CHECK_ARG(n_layers >= 2 && act == B2_ACT_SIGMOID && loss == B2_LOSS_SOFTMAX_CE_MEAN,
+                 "b2_create: the bf16 path needs >= 2 layers, sigmoid hidden layers and the softmax-CE head");
+    for (int i = 0; i < n_layers; ++i)
+      B2_CHECK_ARG(dims[i] % 8 == 0, "b2_create: the bf16 path needs dims[%d] = %d to be a multiple of 8", i, dims[i]);
+    B2_CHECK_ARG(dims[n_layers] <= 16, "b2_create: the bf16 path needs <= 16 outputs, got %d", dims[n_layers]);
+    B2_CHECK_ARG((long)dims[n_layers - 1] * dims[n_layers] * 4 <= 200 * 1024,
+                 "b2_create: output layer %d x %d does not fit the narrow-layer kernel", dims[n_layers - 1], dims[n_layers]);
+  }
   B2_CHECK_ARG(max_local_batch >= 1, "b2_create: max_local_batch must be >= 1");
 
   int ndev = 0;
@@ -340,6 +490,10 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
     if (sp > cap) sp = cap;
     if (sp > 256) sp = 256;
     if (sp < 1) sp = 1;
+    if (precision == B2_PREC_BF16_FP32ACC) {
+      // only the narrow output layer writes partials (the GEMMs store dW directly)
+      sp = (l == n_layers - 1) ? b2_skinny_bwd_slices(max_local_batch, dims[l], c->sm_count) : 0;
+    }
     c->splits[l] = (int)sp;
     c->part_off[l] = soff;
     soff += sp * part_stride(c, l);
@@ -366,10 +520,26 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
 
   B2_ALLOC(c->params, c->P);
   B2_ALLOC(c->grads, c->P + 4);
-  for (int l = 0; l < n_layers - 1; ++l) B2_ALLOC(c->act_buf[l], (long)max_local_batch * dims[l + 1]);
   B2_ALLOC(c->z_last, (long)max_local_batch * dims[n_layers]);
-  B2_ALLOC(c->dz[0], (long)max_local_batch * maxw);
-  if (n_layers > 1) B2_ALLOC(c->dz[1], (long)max_local_batch * maxw);
+  if (precision == B2_PREC_BF16_FP32ACC) {
+    // bf16 buffers are sized in floats / 2 (dims are multiples of 8)
+    B2_ALLOC(c->dz[0], (long)max_local_batch * dims[n_layers]);
+    B2_ALLOC(c->xb, (long)max_local_batch * dims[0] / 2);
+    long hid = 0;
+    for (int l = 0; l < n_layers - 1; ++l) {
+      B2_ALLOC(c->ab[l], (long)max_local_batch * dims[l + 1] / 2);
+      B2_ALLOC(c->wb[l], (long)dims[l] * dims[l + 1] / 2);
+      if (dims[l + 1] > hid) hid = dims[l + 1];
+    }
+    B2_ALLOC(c->dzb[0], (long)max_local_batch * hid / 2);
+    if (n_layers > 2) B2_ALLOC(c->dzb[1], (long)max_local_batch * hid / 2);
+    B2_ALLOC(c->colsum_part, (long)b2_colsum_slices(max_local_batch, (int)hid, c->sm_count) * hid + 16);
+    c->wb_stale = 1;
+  } else {
+    for (int l = 0; l < n_layers - 1; ++l) B2_ALLOC(c->act_buf[l], (long)max_local_batch * dims[l + 1]);
+    B2_ALLOC(c->dz[0], (long)max_local_batch * maxw);
+    if (n_layers > 1) B2_ALLOC(c->dz[1], (long)max_local_batch * maxw);
+  }
   B2_ALLOC(c->scratch, c->scratch_floats);
   B2_ALLOC(c->global_step_dev, 1);
   B2_ALLOC(c->eval_acc_dev, 2);
@@ -424,7 +594,9 @@ extern "C" long b2_launch_count(const b2_ctx* ctx) { return ctx ? ctx->launches 
 
 extern "C" const char* b2_kernel_class_name(int k) {
   static const char* names[B2_KERNEL_CLASSES] = {"dense_fwd", "loss_head", "wgrad", "dgrad", "reduce_apply",
-                                                 "fused_linear_step", "fused_linear_reduce", "allreduce_apply"};
+                                                 "fused_linear_step", "fused_linear_reduce", "allreduce_apply",
+                                                 "gemm_fwd_tcgen05", "gemm_dgrad_tcgen05", "gemm_wgrad_tcgen05",
+                                                 "mixed_aux"};
   return (k >= 0 && k < B2_KERNEL_CLASSES) ? names[k] : "?";
 }
 
@@ -458,6 +630,7 @@ extern "C" int b2_params_set(b2_ctx* ctx, int layer, const float* W_dev, const f
   if (b_dev)
     B2_CUDA(cudaMemcpyAsync(ctx->params + ctx->b_off[layer], b_dev, (size_t)b_size(ctx, layer) * sizeof(float),
                             cudaMemcpyDefault, s));
+  ctx->wb_stale = 1;
   return B2_OK;
 }
 
@@ -610,7 +783,8 @@ extern "C" int b2_eval(b2_ctx* ctx, const void* x_dev, const void* y_dev, long r
   int dummy[B2_MAX_LAYERS];
   for (long r0 = 0; r0 < rows; r0 += ctx->max_local_batch) {
     const int n = (int)((rows - r0 < ctx->max_local_batch) ? rows - r0 : ctx->max_local_batch);
-    int rc = enqueue_layered(ctx, xp + r0 * in, yp + r0 * outd, n, inv_B, 0, dummy, s);
+    int rc = is_mixed(ctx) ? enqueue_forward_mixed(ctx, xp + r0 * in, yp + r0 * outd, n, inv_B, s)
+                           : enqueue_layered(ctx, xp + r0 * in, yp + r0 * outd, n, inv_B, 0, dummy, s);
     if (rc) return rc;
     float* head = ctx->scratch + ctx->head_part_off;
     rc = b2_launch_eval_accumulate(head, head + ctx->head_blocks, ctx->head_blocks, ctx->eval_acc_dev, s);

@@ -82,6 +82,14 @@ struct b2_ctx {
   int opt_no_peer;                 // B2_OPT_NO_PEER_EXCHANGE
   unsigned peer_step;              // exchanges enqueued so far
 
+  // bf16-operand / fp32-accumulate path (precision == B2_PREC_BF16_FP32ACC): tensor-core GEMMs for the hidden layers
+  void* xb;                        // [max_local_batch, dims[0]] bf16 copy of the step's inputs
+  void* ab[B2_MAX_LAYERS];         // bf16 activations of the hidden layers
+  void* dzb[2];                    // bf16 gradients w.r.t. hidden pre-activations (ping-pong)
+  void* wb[B2_MAX_LAYERS];         // bf16 copies of the hidden layers' weights, refreshed by the SGD apply
+  float* colsum_part;              // bias-gradient partials of the hidden layers
+  int wb_stale;                    // parameters were set from outside: refresh the bf16 copies first
+
   // optional per-kernel event timing (B2_OPT_KERNEL_TIMING)
   int opt_timing;
   struct b2_timed* timed;
@@ -154,3 +162,16 @@ int b2_launch_peer_allreduce_apply(const b2_peer_args& a, float* params, float* 
 // ---- launcher (gemm_tcgen05.cu): bf16 tensor-core GEMM with fused epilogues ------------------------------
 int b2_launch_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
                         const float* bias, const void* act, void* out, int sm_count, cudaStream_t s);
+
+// ---- launchers (mixed_aux.cu): CUDA-core kernels of the bf16 path ------------------------------------------
+int b2_launch_cast_bf16(const float* src, void* dst, long n, int sm_count, cudaStream_t s);
+int b2_launch_skinny_fwd(const void* a, const float* W, const float* b, float* logits, int rows, int K, int C,
+                         int sm_count, cudaStream_t s);
+int b2_skinny_bwd_slices(int rows, int K, int sm_count);
+int b2_launch_skinny_bwd(const void* a, const float* dz, const float* W, void* dz_prev, float* partW, float* partB,
+                         long part_stride, int rows, int K, int C, int slices, cudaStream_t s);
+int b2_colsum_slices(int rows, int N, int sm_count);
+int b2_launch_colsum_bf16(const void* m, float* part, float* out, int rows, int N, int slices, cudaStream_t s);
+int b2_launch_sgd_apply_mixed(float* params, const float* grads, long P, float lr, int n_seg, const long* off,
+                              const long* size, void* const* wb, float* loss_trace, int* correct_trace,
+                              float* global_step, int sm_count, cudaStream_t s);
