@@ -26,12 +26,15 @@ sys.path.insert(0, ROOT)
 import numpy as np  # noqa: E402
 
 WORKLOADS = {
-    # name: (dims, act, loss, scaled_init, default local batch, description)
+    # name: (dims, act, loss, scaled_init, default local batch, description, precision)
     "c3": ([784, 10], 0, 1, True, 65536,
-           "784->10 dense + softmax-CE (simple.py-style single layer on MNIST-shaped rows), fp32"),
+           "784->10 dense + softmax-CE (simple.py-style single layer on MNIST-shaped rows), fp32", "fp32"),
     "c2": ([784, 100, 10], 1, 1, False, 65536,
-           "784-100-10 sigmoid MLP + softmax-CE (distributed.py model), fp32"),
+           "784-100-10 sigmoid MLP + softmax-CE (distributed.py model), fp32", "fp32"),
+    "c5": ([784, 4096, 4096, 10], 1, 1, True, 65536,
+           "784-4096-4096-10 sigmoid MLP + softmax-CE, bf16 operands / fp32 accumulate (tcgen05 GEMMs)", "bf16"),
 }
+CPU_SAMPLE_BATCH = {"c5": 2048}        # rows per CPU step where a full batch would take minutes on the host
 BYTES_PER_SAMPLE = 784 * 4 + 10 * 4   # x row + one-hot y row, each read once
 LR = 0.001
 HOST_POOL_ROWS = 1 << 17               # generated on the host with the fixed seed, tiled on the device
@@ -154,7 +157,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    dims, act, loss, scaled, dbatch, desc = WORKLOADS[args.workload]
+    dims, act, loss, scaled, dbatch, desc, precision = WORKLOADS[args.workload]
     batch = args.batch or dbatch
     global_batch = batch * world
     warmup = max(3, args.warmup)
@@ -165,7 +168,9 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return 0
-        r = cpu_reference_run(dims, act, loss, scaled, batch, args.steps, min(warmup, 5))
+        cbatch = min(batch, CPU_SAMPLE_BATCH.get(args.workload, batch))
+        r = cpu_reference_run(dims, act, loss, scaled, cbatch, args.steps, min(warmup, 5), budget_s=90.0)
+        batch = cbatch
         line = {"impl": "reference", "metric": "training samples/sec", "value": r["value"], "unit": "samples/s",
                 "n_gpus": args.gpus, "steps": r["steps"], "warmup": min(warmup, 5), "ms_per_step": r["ms_per_step"],
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -211,19 +216,19 @@ def main():
     cfg["pool_rows"] = pool_rows
     cfg["l2"] = "inputs larger than L2: %.2f GB pool, consecutive batches" % (pool_rows * BYTES_PER_SAMPLE / 1e9)
 
-    tr = pkg.DenseTrainer(dims, act, loss, max_local_batch=batch, device=local_rank)
+    tr = pkg.DenseTrainer(dims, act, loss, max_local_batch=batch, device=local_rank, precision=precision)
     Ws, bs = synthetic.make_weights(dims, scaled)
     tr.set_params(Ws, bs)
     if world > 1:
         uid = [pkg.DenseTrainer.new_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         tr.init_comm(rank, world, uid[0])
-        if not args.no_peer:
+        if not args.no_peer and tr.param_count <= (1 << 20):
             # map every rank's gradient buffer over NVLink: the exchange + SGD apply become one kernel
             hs = [None] * world
             dist.all_gather_object(hs, tr.peer_export())
             tr.peer_import(hs)
-        cfg["gradient_exchange"] = "nccl all-reduce + apply" if args.no_peer else "one-shot peer-memory all-reduce fused with SGD apply"
+        cfg["gradient_exchange"] = "nccl all-reduce + apply" if (args.no_peer or tr.param_count > (1 << 20)) else "one-shot peer-memory all-reduce fused with SGD apply"
 
     # ---- value: device-resident pool -----------------------------------------------------
     lt, ct = tr.train_steps(x_pool, y_pool, batch, warmup, first_row=0, lr=LR)
@@ -250,20 +255,43 @@ def main():
 
     # ---- roofline: per-kernel device times over the same steps (events on the launch stream) ----
     tr.kernel_timing(True)
-    tsteps = min(args.steps, 200)
+    tsteps = min(args.steps, 200 if precision == "fp32" else 20)
     tr.train_steps(x_pool, y_pool, batch, tsteps, first_row=0, lr=LR)
     kt = tr.kernel_times()
     tr.kernel_timing(False)
-    dom = max(kt.items(), key=lambda kv: kv[1][0])
-    dom_ms = dom[1][0] / dom[1][1]
     total_ms = sum(v[0] for v in kt.values())
-    peak, peak_src = _peaks()
-    achieved = batch * BYTES_PER_SAMPLE / (dom_ms / 1e3) / 1e9
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": _traffic_bytes(args.workload), "kernel": dom[0], "kernel_ms": dom_ms,
-                "kernel_share_of_step": dom[1][0] / total_ms, "peak_source": "of " + peak_src,
-                "algorithmic_bytes_per_launch": batch * BYTES_PER_SAMPLE,
-                "kernel_ms_by_class": {k: v[0] / v[1] for k, v in kt.items()}}
+    if precision == "bf16":
+        # tensor-core bound: flops of the three GEMM classes (2*in*out per layer and product)
+        hid = [(dims[i], dims[i + 1]) for i in range(len(dims) - 2)]
+        fl = {"gemm_fwd_tcgen05": sum(2.0 * a * b for a, b in hid) * batch,
+              "gemm_wgrad_tcgen05": sum(2.0 * a * b for a, b in hid) * batch,
+              "gemm_dgrad_tcgen05": sum(2.0 * a * b for a, b in hid[1:]) * batch}
+        gemm_ms = sum(kt[k][0] for k in fl if k in kt) / tsteps
+        gemm_flops = sum(fl.values())
+        peak_tf = 1406.5
+        src = "fallback"
+        try:
+            pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            peak_tf, src = float(pk["bf16_tflops_sustained"]), "measured (MEASURED_PEAKS.json bf16_tflops_sustained, cuBLAS loop)"
+        except Exception:
+            pass
+        achieved = gemm_flops / (gemm_ms / 1e3) / 1e12
+        roofline = {"bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
+                    "traffic": _traffic_bytes(args.workload), "kernel": "gemm_bf16_kernel (tcgen05; fwd+dgrad+wgrad launches)",
+                    "kernel_ms": gemm_ms, "kernel_share_of_step": gemm_ms * tsteps / total_ms, "peak_source": "of " + src,
+                    "algorithmic_flops_per_step": gemm_flops,
+                    "per_class_tflops": {k: fl[k] / (kt[k][0] / tsteps / 1e3) / 1e12 for k in fl if k in kt},
+                    "kernel_ms_by_class": {k: v[0] / tsteps for k, v in kt.items()}}
+    else:
+        dom = max(kt.items(), key=lambda kv: kv[1][0])
+        dom_ms = dom[1][0] / dom[1][1]
+        peak, peak_src = _peaks()
+        achieved = batch * BYTES_PER_SAMPLE / (dom_ms / 1e3) / 1e9
+        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": _traffic_bytes(args.workload), "kernel": dom[0], "kernel_ms": dom_ms,
+                    "kernel_share_of_step": dom[1][0] / total_ms, "peak_source": "of " + peak_src,
+                    "algorithmic_bytes_per_launch": batch * BYTES_PER_SAMPLE,
+                    "kernel_ms_by_class": {k: v[0] / v[1] for k, v in kt.items()}}
 
     # ---- e2e: host feeds through the sess.run-shaped call ------------------------------------
     e2e = None
@@ -295,17 +323,18 @@ def main():
     # ---- cpu_baseline: rank 0, N=1 only, bounded sample -----------------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        r = cpu_reference_run(dims, act, loss, scaled, batch, 400, 2, budget_s=12.0)
+        cbatch = min(batch, CPU_SAMPLE_BATCH.get(args.workload, batch))
+        r = cpu_reference_run(dims, act, loss, scaled, cbatch, 400, 2, budget_s=12.0)
         cpu = {"value": r["value"], "unit": "samples/s", "cores": r["threads"], "kind": "port",
                "sample": "%d steps of %d rows in %.1f s, torch-CPU restatement of the TF1 graph, all host threads"
-                         % (r["steps"], batch, r["seconds"]),
+                         % (r["steps"], cbatch, r["seconds"]),
                "first_loss_cpu": r["first_loss"], "first_loss_gpu": first_loss}
 
     if rank == 0:
         line = {"metric": "training samples/sec", "value": value, "unit": "samples/s", "n_gpus": world,
                 "steps": args.steps, "warmup": warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
+                "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if precision == "bf16" else "f32",
+                "data": "synthetic", "config": cfg, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
                 "gpu_launches": launches, "loss_first": first_loss, "loss_last": last_loss}
         print(json.dumps(line))
     tr.close()

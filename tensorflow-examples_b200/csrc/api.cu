@@ -187,6 +187,17 @@ int refresh_bf16_weights(b2_ctx* c, cudaStream_t s) {
   return B2_OK;
 }
 
+// slices of the output layer's weight-gradient GEMM (split over the batch) and of its bias column sums
+inline int narrow_slices(const b2_ctx* c, int rows) {
+  const int L = c->n_layers - 1;
+  const int tiles_m = (c->dims[L] + 127) / 128;
+  int sp = (c->sm_count + tiles_m - 1) / tiles_m;
+  const int num_kb = (rows + 63) / 64;
+  if (sp > num_kb) sp = num_kb;
+  if (sp > 16) sp = 16;
+  return sp < 1 ? 1 : sp;
+}
+
 // forward + loss head; leaves logits in z_last, dz of the output layer (fp32) in dz[0], head partials in scratch
 int enqueue_forward_mixed(b2_ctx* c, const float* x, const float* y, int rows, float inv_B, cudaStream_t s) {
   const int n = c->n_layers;
@@ -209,9 +220,16 @@ int enqueue_forward_mixed(b2_ctx* c, const float* x, const float* y, int rows, f
     a_in = c->ab[l];
   }
   {
+    // output layer (distributed.py:98): W_out [K,10] padded to a bf16 [K,64] operand, logits = a . W_out + b
     timed_scope t(c, B2_K_MIXED_AUX, s);
-    rc = b2_launch_skinny_fwd(a_in, c->params + c->w_off[n - 1], c->params + c->b_off[n - 1], c->z_last, rows,
-                              c->dims[n - 1], c->dims[n], c->sm_count, s);
+    rc = b2_launch_pad_cast64(c->params + c->w_off[n - 1], c->wb[n - 1], c->dims[n - 1], c->dims[n], c->sm_count, s);
+  }
+  if (rc) return rc;
+  c->launches++;
+  {
+    timed_scope t(c, B2_K_GEMM_FWD, s);
+    rc = b2_launch_gemm_bf16_ex(a_in, 0, c->wb[n - 1], 1, rows, 64, c->dims[n - 1], 3, c->params + c->b_off[n - 1],
+                                nullptr, c->z_last, c->dims[n], c->dims[n], 1, 0, c->sm_count, s);
   }
   if (rc) return rc;
   c->launches++;
@@ -232,15 +250,31 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
   const float inv_B = 1.0f / (float)global_batch;
   int rc = enqueue_forward_mixed(c, x, y, rows, inv_B, s);
   if (rc) return rc;
-  // ---- output layer: dz_prev, dW partials, db partials in one pass over the last hidden activations ----
+  // ---- output layer on the tensor cores: dz padded to bf16 [rows,64] ----
   const int L = n - 1;
-  const int slices = b2_skinny_bwd_slices(rows, c->dims[L], c->sm_count);
+  const int slices = narrow_slices(c, rows);
   float* pw = c->scratch + c->part_off[L];
   float* pb = pw + round4(w_size(c, L));
   {
     timed_scope t(c, B2_K_MIXED_AUX, s);
-    rc = b2_launch_skinny_bwd(c->ab[L - 1], c->dz[0], c->params + c->w_off[L], c->dzb[0], pw, pb, part_stride(c, L),
-                              rows, c->dims[L], c->dims[n], slices, s);
+    rc = b2_launch_pad_cast64(c->dz[0], c->dzn, rows, c->dims[n], c->sm_count, s);
+    if (!rc) rc = b2_launch_colsum_f32_narrow(c->dz[0], pb, part_stride(c, L), rows, c->dims[n], slices, s);   // BiasAdd grad
+  }
+  if (rc) return rc;
+  c->launches += 2;
+  {
+    // dW_out partials = a^T . dz   (MatMul grad, transpose_a), K = batch cut into `slices` fixed pieces
+    timed_scope t(c, B2_K_GEMM_WGRAD, s);
+    rc = b2_launch_gemm_bf16_ex(c->ab[L - 1], 1, c->dzn, 1, c->dims[L], 64, rows, 2, nullptr, nullptr, pw, c->dims[n],
+                                c->dims[n], slices, part_stride(c, L), c->sm_count, s);
+  }
+  if (rc) return rc;
+  c->launches++;
+  {
+    // dz_prev = (dz . W_out^T) * a(1-a)   (MatMul grad transpose_b + SigmoidGrad); the reduction runs over the 64 padded classes
+    timed_scope t(c, B2_K_GEMM_DGRAD, s);
+    rc = b2_launch_gemm_bf16_ex(c->dzn, 0, c->wb[L], 0, rows, c->dims[L], 64, 1, nullptr, c->ab[L - 1], c->dzb[0],
+                                c->dims[L], c->dims[L], 1, 0, c->sm_count, s);
   }
   if (rc) return rc;
   c->launches++;
@@ -400,6 +434,7 @@ void free_ctx(b2_ctx* c) {
   cudaFree(c->dzb[0]);
   cudaFree(c->dzb[1]);
   cudaFree(c->colsum_part);
+  cudaFree(c->dzn);
   cudaFree(c->params);
   cudaFree(c->grads);
   for (int l = 0; l < B2_MAX_LAYERS; ++l) cudaFree(c->act_buf[l]);
@@ -446,8 +481,6 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
     for (int i = 0; i < n_layers; ++i)
       B2_CHECK_ARG(dims[i] % 8 == 0, "b2_create: the bf16 path needs dims[%d] = %d to be a multiple of 8", i, dims[i]);
     B2_CHECK_ARG(dims[n_layers] <= 16, "b2_create: the bf16 path needs <= 16 outputs, got %d", dims[n_layers]);
-    B2_CHECK_ARG((long)dims[n_layers - 1] * dims[n_layers] * 4 <= 200 * 1024,
-                 "b2_create: output layer %d x %d does not fit the narrow-layer kernel", dims[n_layers - 1], dims[n_layers]);
   }
   B2_CHECK_ARG(max_local_batch >= 1, "b2_create: max_local_batch must be >= 1");
 
@@ -492,7 +525,7 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
     if (sp < 1) sp = 1;
     if (precision == B2_PREC_BF16_FP32ACC) {
       // only the narrow output layer writes partials (the GEMMs store dW directly)
-      sp = (l == n_layers - 1) ? b2_skinny_bwd_slices(max_local_batch, dims[l], c->sm_count) : 0;
+      sp = (l == n_layers - 1) ? 16 : 0;   // narrow_slices() never exceeds 16
     }
     c->splits[l] = (int)sp;
     c->part_off[l] = soff;
@@ -531,6 +564,8 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
       B2_ALLOC(c->wb[l], (long)dims[l] * dims[l + 1] / 2);
       if (dims[l + 1] > hid) hid = dims[l + 1];
     }
+    B2_ALLOC(c->wb[n_layers - 1], (long)dims[n_layers - 1] * 64 / 2);   // output layer padded to 64 columns
+    B2_ALLOC(c->dzn, (long)max_local_batch * 64 / 2);
     B2_ALLOC(c->dzb[0], (long)max_local_batch * hid / 2);
     if (n_layers > 2) B2_ALLOC(c->dzb[1], (long)max_local_batch * hid / 2);
     B2_ALLOC(c->colsum_part, (long)b2_colsum_slices(max_local_batch, (int)hid, c->sm_count) * hid + 16);

@@ -88,6 +88,7 @@ struct b2_ctx {
   void* dzb[2];                    // bf16 gradients w.r.t. hidden pre-activations (ping-pong)
   void* wb[B2_MAX_LAYERS];         // bf16 copies of the hidden layers' weights, refreshed by the SGD apply
   float* colsum_part;              // bias-gradient partials of the hidden layers
+  void* dzn;                       // bf16 [max_local_batch, 64]: the output layer's dz, zero padded
   int wb_stale;                    // parameters were set from outside: refresh the bf16 copies first
 
   // optional per-kernel event timing (B2_OPT_KERNEL_TIMING)
@@ -162,14 +163,16 @@ int b2_launch_peer_allreduce_apply(const b2_peer_args& a, float* params, float* 
 // ---- launcher (gemm_tcgen05.cu): bf16 tensor-core GEMM with fused epilogues ------------------------------
 int b2_launch_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
                         const float* bias, const void* act, void* out, int sm_count, cudaStream_t s);
+int b2_launch_gemm_bf16_ex(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
+                           const float* bias, const void* act, void* out, int ldc, int n_store, int ksplits,
+                           long split_stride, int sm_count, cudaStream_t s);
 
 // ---- launchers (mixed_aux.cu): CUDA-core kernels of the bf16 path ------------------------------------------
 int b2_launch_cast_bf16(const float* src, void* dst, long n, int sm_count, cudaStream_t s);
-int b2_launch_skinny_fwd(const void* a, const float* W, const float* b, float* logits, int rows, int K, int C,
-                         int sm_count, cudaStream_t s);
-int b2_skinny_bwd_slices(int rows, int K, int sm_count);
-int b2_launch_skinny_bwd(const void* a, const float* dz, const float* W, void* dz_prev, float* partW, float* partB,
-                         long part_stride, int rows, int K, int C, int slices, cudaStream_t s);
+// fp32 [rows, C] -> bf16 [rows, 64], zero padded: makes the narrow output layer a legal tensor-core operand
+int b2_launch_pad_cast64(const float* src, void* dst, long rows, int C, int sm_count, cudaStream_t s);
+// bias gradient of the output layer: per-slice column sums of fp32 dz [rows, C] -> partB[slice*stride + c]
+int b2_launch_colsum_f32_narrow(const float* dz, float* partB, long part_stride, int rows, int C, int slices, cudaStream_t s);
 int b2_colsum_slices(int rows, int N, int sm_count);
 int b2_launch_colsum_bf16(const void* m, float* part, float* out, int rows, int N, int slices, cudaStream_t s);
 int b2_launch_sgd_apply_mixed(float* params, const float* grads, long P, float lr, int n_seg, const long* off,

@@ -12,7 +12,7 @@
 // Persistent grid (one CTA per SM), 128 x 256 output tiles, BLOCK_K = 64, 4-stage TMA ring.
 //   warp 0      TMA producer (one elected lane)
 //   warp 1      allocates TMEM (2 x 256 columns: two accumulator buffers) and issues tcgen05.mma
-//   warps 2-5   epilogue: tcgen05.ld accumulators -> registers -> fused epilogue -> global, while the
+//   warps 2-9   epilogue: tcgen05.ld accumulators -> registers -> fused epilogue -> global, while the
 //               next tile's MMAs already fill the other accumulator buffer
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -23,7 +23,7 @@ namespace tg {
 
 constexpr int BLOCK_M = 128, BLOCK_K = 64, UMMA_K = 16;
 constexpr int STAGES = 4;
-constexpr int THREADS = 192;
+constexpr int THREADS = 320;   // TMA warp, MMA warp, 8 epilogue warps (two per TMEM lane quarter, splitting the columns)
 constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;   // 16 KB
 
 template <int BLOCK_N>
@@ -112,10 +112,20 @@ struct Params {
   int M, N, K;
   int a_mn, b_mn;          // 1 = MN-major operand (global [K, M] / [K, N] row-major), 0 = K-major ([M, K] / [N, K])
   int epi;
-  const float* bias;       // EPI_BIAS_*: [N]
-  const __nv_bfloat16* act;  // EPI_DSIGMOID: [M, N] activations a; out = acc * a * (1 - a)
-  void* out;               // bf16 or fp32 [M, N] row-major
+  const float* bias;       // EPI_BIAS_*: [n_store]
+  const __nv_bfloat16* act;  // EPI_DSIGMOID: [M, ldc] activations a; out = acc * a * (1 - a)
+  void* out;               // bf16 or fp32 [M, ldc] row-major; only columns < n_store are written
+  int ldc, n_store;
+  int ksplits;             // > 1: the K range is cut into this many slices, slice z writes out + z*split_stride
+  long split_stride;       //      (fixed-order partials; a reduction kernel adds them)
 };
+
+__device__ __forceinline__ float fast_sigmoid(float z) {
+  // sigmoid(z) = 0.5 * tanh(z/2) + 0.5 ; one MUFU op.  The result is rounded to bf16 (8 bits) right after.
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.5f * z));
+  return fmaf(0.5f, t, 0.5f);
+}
 
 template <int BLOCK_N>
 __global__ void __launch_bounds__(THREADS, 1)
@@ -135,12 +145,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_m = (p.M + BLOCK_M - 1) / BLOCK_M, tiles_n = (p.N + BLOCK_N - 1) / BLOCK_N;
-  const int ntiles = tiles_m * tiles_n;
-  const int num_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+  const int mn_tiles = tiles_m * tiles_n;
+  const int ntiles = mn_tiles * p.ksplits;
+  const int num_kb_total = (p.K + BLOCK_K - 1) / BLOCK_K;
+  const int kb_per = (num_kb_total + p.ksplits - 1) / p.ksplits;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 4); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -159,8 +171,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (lane == 0) {
       int it = 0;
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int m0 = (tile / tiles_n) * BLOCK_M, n0 = (tile % tiles_n) * BLOCK_N;
-        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        const int mn = tile % mn_tiles, z = tile / mn_tiles;
+        const int m0 = (mn / tiles_n) * BLOCK_M, n0 = (mn % tiles_n) * BLOCK_N;
+        const int kb_begin = z * kb_per, kb_end = min(num_kb_total, kb_begin + kb_per);
+        for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
           const int s = it % STAGES;
           mbar_wait(&empty[s], ((it / STAGES) & 1) ^ 1);
           mbar_expect_tx(&full[s], C::STAGE_BYTES);
@@ -196,7 +210,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         mbar_wait(&tempty[acc], ((t >> 1) & 1) ^ 1);       // epilogue has drained this accumulator buffer
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
-        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        const int z = tile / mn_tiles;
+        const int kb_begin = z * kb_per, kb_end = min(num_kb_total, kb_begin + kb_per);
+        for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
           const int s = it % STAGES;
           mbar_wait(&full[s], (it / STAGES) & 1);
           tc_fence_after();
@@ -204,7 +220,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const uint64_t db = make_desc(smem_u32(smB + s * C::B_STAGE_BYTES), p.b_mn);
 #pragma unroll
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
-            tc_mma(d_tmem, da + (uint64_t)(k * a_step), db + (uint64_t)(k * b_step), idesc, (kb | k) != 0);
+            tc_mma(d_tmem, da + (uint64_t)(k * a_step), db + (uint64_t)(k * b_step), idesc, (kb != kb_begin) || (k != 0));
           tc_commit(&empty[s]);                             // frees the smem stage when these MMAs retire
         }
         tc_commit(&tfull[acc]);                             // accumulator complete
@@ -213,24 +229,32 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else {
     // ------------------------------------ epilogue ------------------------------------
     const int quarter = warp & 3;                           // TMEM lanes 32*quarter .. +31 belong to this warp
+    const int chalf = (warp - 2) >> 2;                      // which half of the tile's columns this warp drains
     int t = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t) {
       const int acc = t & 1;
-      const int m0 = (tile / tiles_n) * BLOCK_M, n0 = (tile % tiles_n) * BLOCK_N;
+      const int mn = tile % mn_tiles, z = tile / mn_tiles;
+      const int m0 = (mn / tiles_n) * BLOCK_M, n0 = (mn % tiles_n) * BLOCK_N;
       mbar_wait(&tfull[acc], (t >> 1) & 1);
       tc_fence_after();
       const int row = m0 + quarter * 32 + lane;
       const bool row_ok = row < p.M;
+      const bool empty_split = z * kb_per >= num_kb_total;   // a K slice past the end contributes zeros
 #pragma unroll 1
-      for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+      for (int c0 = chalf * (BLOCK_N / 2); c0 < (chalf + 1) * (BLOCK_N / 2); c0 += 32) {
         uint32_t r[32];
         tc_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BLOCK_N + c0), r);
+        if (empty_split) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) r[j] = 0u;
+        }
         const int n = n0 + c0;
-        if (!row_ok || n >= p.N) continue;
-        const size_t off = (size_t)row * p.N + n;
+        if (!row_ok || n >= p.n_store) continue;
+        const size_t off = (size_t)z * p.split_stride + (size_t)row * p.ldc + n;
+        const bool vec_ok = (n + 32 <= p.n_store) && ((p.ldc & 7) == 0);
         if (p.epi == EPI_STORE_F32 || p.epi == EPI_BIAS_F32) {
           float* o = reinterpret_cast<float*>(p.out) + off;
-          if (n + 32 <= p.N) {
+          if (vec_ok) {
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
               float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
@@ -242,16 +266,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               *reinterpret_cast<float4*>(o + j) = v;
             }
           } else {
-            for (int j = 0; j < 32 && n + j < p.N; ++j)
+            for (int j = 0; j < 32 && n + j < p.n_store; ++j)
               o[j] = __uint_as_float(r[j]) + (p.epi == EPI_BIAS_F32 ? p.bias[n + j] : 0.f);
           }
-        } else if (n + 32 > p.N) {
+        } else if (!vec_ok) {
           // ragged last column chunk: element-wise
           __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + off;
-          for (int j = 0; j < 32 && n + j < p.N; ++j) {
+          for (int j = 0; j < 32 && n + j < p.n_store; ++j) {
             float v = __uint_as_float(r[j]);
             if (p.epi == EPI_BIAS_SIGMOID_BF16) {
-              v = 1.0f / (1.0f + __expf(-(v + p.bias[n + j])));
+              v = fast_sigmoid(v + p.bias[n + j]);
             } else {
               const float a = __bfloat162float(p.act[off + j]);
               v = v * a * (1.0f - a);
@@ -268,8 +292,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               const float bb[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
               for (int u = 0; u < 4; ++u) {
-                const float z = __uint_as_float(r[j + u]) + bb[u];
-                v[j + u] = 1.0f / (1.0f + __expf(-z));     // distributed.py:97 (bf16 output absorbs the intrinsic's error)
+                v[j + u] = fast_sigmoid(__uint_as_float(r[j + u]) + bb[u]);   // distributed.py:97
               }
             }
           } else {
@@ -349,35 +372,15 @@ static int make_map(CUtensorMap* m, const void* base, long rows, long cols, int 
 
 }  // namespace tg
 
-// A: K-major -> global [M, K]; MN-major -> global [K, M].   B: K-major -> [N, K]; MN-major -> [K, N].
-int b2_launch_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
-                        const float* bias, const void* act, void* out, int sm_count, cudaStream_t s) {
+template <int BN>
+static int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const tg::Params& p, int sm_count, cudaStream_t s) {
   using namespace tg;
-  if ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B) | reinterpret_cast<uintptr_t>(out)) & 15) {
-    b2_set_error("gemm_bf16: operands must be 16-byte aligned");
-    return B2_ERR_ARG;
-  }
-  if ((a_mn ? M : K) % 8 || (b_mn ? N : K) % 8 || N % 8) {
-    b2_set_error("gemm_bf16: leading dimensions must be multiples of 8 elements (M=%d N=%d K=%d)", M, N, K);
-    return B2_ERR_ARG;
-  }
-  int rc = get_encode();
-  if (rc) return rc;
-  constexpr int BN = 256;
-  CUtensorMap ta, tb;
-  rc = a_mn ? make_map(&ta, A, K, M, BLOCK_K) : make_map(&ta, A, M, K, BLOCK_M);
-  if (rc) return rc;
-  rc = b_mn ? make_map(&tb, B, K, N, BLOCK_K) : make_map(&tb, B, N, K, BN);
-  if (rc) return rc;
-  Params p;
-  p.M = M; p.N = N; p.K = K; p.a_mn = a_mn; p.b_mn = b_mn; p.epi = epi;
-  p.bias = bias; p.act = reinterpret_cast<const __nv_bfloat16*>(act); p.out = out;
   static bool attr = false;
   if (!attr) {
     B2_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
     attr = true;
   }
-  const int tiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + BN - 1) / BN);
+  const int tiles = ((p.M + BLOCK_M - 1) / BLOCK_M) * ((p.N + BN - 1) / BN) * p.ksplits;
   const int grid = tiles < sm_count ? tiles : sm_count;
   gemm_bf16_kernel<BN><<<grid, THREADS, Cfg<BN>::SMEM_BYTES, s>>>(ta, tb, p);
   cudaError_t e = cudaGetLastError();
@@ -386,4 +389,45 @@ int b2_launch_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int M,
     return B2_ERR_CUDA;
   }
   return B2_OK;
+}
+
+// A: K-major -> global [M, K]; MN-major -> global [K, M].   B: K-major -> [N, K]; MN-major -> [K, N].
+// out: [M, ldc], columns < n_store written.  ksplits > 1 cuts K into slices; slice z writes out + z*split_stride.
+int b2_launch_gemm_bf16_ex(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
+                           const float* bias, const void* act, void* out, int ldc, int n_store, int ksplits,
+                           long split_stride, int sm_count, cudaStream_t s) {
+  using namespace tg;
+  if ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) {
+    b2_set_error("gemm_bf16: operands must be 16-byte aligned");
+    return B2_ERR_ARG;
+  }
+  if ((a_mn ? M : K) % 8 || (b_mn ? N : K) % 8) {
+    b2_set_error("gemm_bf16: operand row pitches must be multiples of 8 elements (M=%d N=%d K=%d)", M, N, K);
+    return B2_ERR_ARG;
+  }
+  int rc = get_encode();
+  if (rc) return rc;
+  const int BN = (N <= 64) ? 64 : 256;
+  CUtensorMap ta, tb;
+  rc = a_mn ? make_map(&ta, A, K, M, BLOCK_K) : make_map(&ta, A, M, K, BLOCK_M);
+  if (rc) return rc;
+  rc = b_mn ? make_map(&tb, B, K, N, BLOCK_K) : make_map(&tb, B, N, K, BN);
+  if (rc) return rc;
+  Params p;
+  p.M = M; p.N = N; p.K = K; p.a_mn = a_mn; p.b_mn = b_mn; p.epi = epi;
+  p.bias = bias; p.act = reinterpret_cast<const __nv_bfloat16*>(act); p.out = out;
+  p.ldc = ldc; p.n_store = n_store;
+  const int num_kb = (K + BLOCK_K - 1) / BLOCK_K;
+  p.ksplits = ksplits < 1 ? 1 : (ksplits > num_kb ? num_kb : ksplits);
+  p.split_stride = split_stride;
+  return BN == 64 ? launch_bn<64>(ta, tb, p, sm_count, s) : launch_bn<256>(ta, tb, p, sm_count, s);
+}
+
+int b2_launch_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
+                        const float* bias, const void* act, void* out, int sm_count, cudaStream_t s) {
+  if (N % 8) {
+    b2_set_error("gemm_bf16: N must be a multiple of 8 (N=%d)", N);
+    return B2_ERR_ARG;
+  }
+  return b2_launch_gemm_bf16_ex(A, a_mn, B, b_mn, M, N, K, epi, bias, act, out, N, N, 1, 0, sm_count, s);
 }
