@@ -30,7 +30,7 @@ dims, act, scaled, lb, steps = %(dims)r, %(act)d, %(scaled)r, %(lb)d, %(steps)d
 gb = lb * world
 x, y = synthetic.make_pool(gb * steps)
 Ws, bs = synthetic.make_weights(dims, scaled)
-tr = b2.DenseTrainer(dims, act, b2.LOSS_SOFTMAX_CE, max_local_batch=lb, device=rank)
+tr = b2.DenseTrainer(dims, act, b2.LOSS_SOFTMAX_CE, max_local_batch=lb, device=rank, precision=%(prec)r)
 tr.set_params(Ws, bs)
 uid = [b2.DenseTrainer.new_unique_id() if rank == 0 else None]
 dist.broadcast_object_list(uid, src=0)
@@ -51,14 +51,15 @@ dist.destroy_process_group()
 
 
 @pytest.mark.parametrize("peer", [1, 0], ids=["peer-memory", "nccl"])
-@pytest.mark.parametrize("dims,act,scaled", [([784, 10], 0, True), ([784, 100, 10], 1, False)])
-def test_n_rank_trace_equals_single_process_oracle(cuda_device, tmp_path, dims, act, scaled, peer):
+@pytest.mark.parametrize("dims,act,scaled,prec", [([784, 10], 0, True, "fp32"), ([784, 100, 10], 1, False, "fp32"),
+                                                  ([784, 256, 128, 10], 1, True, "bf16")])
+def test_n_rank_trace_equals_single_process_oracle(cuda_device, tmp_path, dims, act, scaled, prec, peer):
     world = min(torch.cuda.device_count(), 4)
     if world < 2:
         pytest.skip("needs at least 2 GPUs")
     lb, steps = 96, 12
     script = tmp_path / "worker.py"
-    script.write_text(WORKER % dict(root=ROOT, dims=dims, act=act, scaled=scaled, lb=lb, steps=steps, out=str(tmp_path), peer=peer))
+    script.write_text(WORKER % dict(root=ROOT, dims=dims, act=act, scaled=scaled, lb=lb, steps=steps, out=str(tmp_path), peer=peer, prec=prec))
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % world,
                         "--master-addr", "127.0.0.1", "--master-port", "29611", str(script)],
                        capture_output=True, text=True, timeout=900)
@@ -66,14 +67,15 @@ def test_n_rank_trace_equals_single_process_oracle(cuda_device, tmp_path, dims, 
     gb = lb * world
     x, y = synthetic.make_pool(gb * steps)
     Ws, bs = synthetic.make_weights(dims, scaled)
-    g = oracle.TF1Graph(dims, act, oracle.LOSS_SOFTMAX_CE, Ws, bs)
+    g = oracle.TF1Graph(dims, act, oracle.LOSS_SOFTMAX_CE, Ws, bs, precision=prec)
     want = [g.train_step(x[s * gb:(s + 1) * gb], y[s * gb:(s + 1) * gb], 0.001) for s in range(steps)]
     outs = [np.load(tmp_path / ("rank%d.npz" % r_)) for r_ in range(world)]
+    ltol, wtol, ctol = (1e-5, 1e-5, 1) if prec == "fp32" else (2e-3, 2e-3, 4)
     for o in outs:
         for s in range(steps):
-            assert abs(float(o["loss"][s]) - float(want[s][0])) <= 1e-5 * max(1.0, abs(float(want[s][0])))
-            assert abs(int(o["correct"][s]) - want[s][1]) <= 1
-        assert np.abs(o["W0"] - g.W[0]).max() <= 1e-5 * max(1.0, float(np.abs(g.W[0]).max()))
+            assert abs(float(o["loss"][s]) - float(want[s][0])) <= ltol * max(1.0, abs(float(want[s][0])))
+            assert abs(int(o["correct"][s]) - want[s][1]) <= ctol
+        assert np.abs(o["W0"] - g.W[0]).max() <= wtol * max(1.0, float(np.abs(g.W[0]).max()))
         assert o["gs"] == np.float32(steps)
         np.testing.assert_array_equal(o["W0"], outs[0]["W0"])      # replicas stay bit-identical
         np.testing.assert_array_equal(o["loss"], outs[0]["loss"])
