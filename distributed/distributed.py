@@ -43,6 +43,8 @@ flags.DEFINE_integer("train_rows", 55000, "synthetic pool: training rows (mnist.
 flags.DEFINE_integer("test_rows", 10000, "synthetic pool: test rows (mnist.test)")
 flags.DEFINE_boolean("shuffle", True, "reshuffle the training pool every epoch, as next_batch does (distributed.py:146)")
 flags.DEFINE_integer("shuffle_seed", 0, "seed of the per-epoch permutation (the reference's is unseeded)")
+flags.DEFINE_string("logs_path", "", "TensorBoard event directory; the reference hard-codes /tmp/mnist/ (distributed.py:49). "
+                    "Empty (default) writes no event files")
 flags.DEFINE_boolean("peer_exchange", True, "workers on one NVLink box sum gradients through peer memory instead of NCCL")
 flags.DEFINE_boolean("strict_reference_bugs", False,
                      "reproduce distributed.py:165 literally: the 'Time Taken' line raises TypeError")
@@ -113,6 +115,10 @@ def main(argv):
         model.peer_import([bytes(store.get("b2_peer_%d" % r)) for r in range(role.world)])
     cl.store_barrier(store, role, "b2_comm_ready")
 
+    # writer = tf.summary.FileWriter(logs_path, graph=...)   distributed.py:138 -- every worker writes its own file
+    from tensorflow_examples_b200.summaries import SummaryWriter
+    writer = SummaryWriter(FLAGS.logs_path)
+
     begin_time = time.time()
     frequency = FLAGS.frequency
     batch_count = cl.steps_per_epoch(num_examples, batch_size, role.world)       # distributed.py:142
@@ -139,6 +145,10 @@ def main(argv):
             torch.cuda.synchronize(dev)
             cost = float(loss_trace[n - 1].item())
             step = model.global_step - np.float32(1)      # the value fetched with the last step (pre-increment)
+            if writer.enabled:                            # writer.add_summary(summary, step) for every step   distributed.py:151
+                lt, ct = loss_trace[:n].cpu().numpy(), correct_trace[:n].cpu().numpy()
+                for k in range(n):
+                    writer.add_scalars(int(step) - (n - 1) + k, lt[k], ct[k] / float(global_batch))
             elapsed_time = time.time() - start_time                               # distributed.py:155-156
             start_time = time.time()
             print(report.progress_line(step, epoch, i - 1, batch_count, cost, elapsed_time, frequency))
@@ -148,6 +158,7 @@ def main(argv):
     print(report.accuracy_line(correct / float(test_x.shape[0])))
     print(report.time_taken_line(time.time() - begin_time, FLAGS.strict_reference_bugs))   # distributed.py:165
     print(report.final_cost_line(cost))                                                    # distributed.py:166
+    writer.close()
     cl.store_barrier(store, role, "b2_done")
     model.close()                                                                          # sv.stop()  distributed.py:168
     print("done with training")                                                            # distributed.py:169

@@ -76,3 +76,21 @@ def test_distributed_py_strict_bug_mode_raises_like_the_reference(cuda_device):
                      "--test_rows=200", "--training_epochs=1", "--strict_reference_bugs", "--data_dir=/nonexistent"])
     assert r.returncode != 0 and "TypeError: not all arguments converted during string formatting" in r.stderr
     assert "Acc: " in r.stdout                                                      # distributed.py:164 ran first
+
+
+def test_distributed_py_writes_tensorboard_scalars(cuda_device, tmp_path):
+    """distributed.py:121-125,138,151: cost and accuracy scalars, one event per step."""
+    pytest.importorskip("tensorboard")
+    r = _run_worker(["--ps_hosts=a:1", "--worker_hosts=127.0.0.1:2223", "--job_name=worker", "--train_rows=1000",
+                     "--test_rows=200", "--training_epochs=1", "--data_dir=/nonexistent", "--logs_path=%s" % tmp_path])
+    assert r.returncode == 0, r.stderr[-2000:]
+    from tensorboard.backend.event_processing.event_file_loader import EventFileLoader
+    files = [f for f in os.listdir(tmp_path) if "tfevents" in f]
+    assert files
+    tags = {}
+    for ev in EventFileLoader(os.path.join(tmp_path, files[0])).Load():
+        for v in ev.summary.value:
+            tags.setdefault(v.tag, []).append((ev.step, v.simple_value if v.HasField("simple_value") else float(v.tensor.float_val[0])))
+    assert len(tags["cost"]) == 10 and len(tags["accuracy"]) == 10          # 1000 rows / batch 100
+    assert [s for s, _ in tags["cost"]] == list(range(10))
+    assert all(0.0 <= a <= 1.0 for _, a in tags["accuracy"])
