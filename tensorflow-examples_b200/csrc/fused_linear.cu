@@ -360,8 +360,7 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
           if (active) {
             const float* xp = sm.x + (slot * STAGE_ROWS) * XSTRIDE + 4 * kg;
             const float* dp = sm.dz + buf * DZ_BUF + (q * STAGE_ROWS) * DZ_ROW + 8 * h;
-#pragma unroll 2
-            for (int rr = 0; rr < nrows; ++rr) {
+            auto bwd_row = [&](int rr) {
               const ulonglong2 x0 = *reinterpret_cast<const ulonglong2*>(xp + rr * XSTRIDE);
               const ulonglong2 x1 = *reinterpret_cast<const ulonglong2*>(xp + rr * XSTRIDE + K / 2);
               const float4 d03 = *reinterpret_cast<const float4*>(dp + rr * DZ_ROW);
@@ -375,6 +374,13 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
                 gacc[2][c] = ffma2(x1.x, dd, gacc[2][c]);
                 gacc[3][c] = ffma2(x1.y, dd, gacc[3][c]);
               }
+            };
+            if (nrows == STAGE_ROWS) {
+              // the common case, fully unrolled: addresses become immediates, no loop bookkeeping, loads hoisted freely
+#pragma unroll
+              for (int rr = 0; rr < STAGE_ROWS; ++rr) bwd_row(rr);
+            } else {
+              for (int rr = 0; rr < nrows; ++rr) bwd_row(rr);
             }
           }
           __syncwarp();
