@@ -125,7 +125,7 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
     int rc;
     {
       timed_scope t(c, B2_K_DENSE_FWD, s);
-      rc = b2_launch_dense_fwd(a_in, c->params + c->w_off[l], c->params + c->b_off[l], out, rows,
+      rc = b2_launch_sgemm_fwd(a_in, c->params + c->w_off[l], c->params + c->b_off[l], out, rows,
                                c->dims[l + 1], c->dims[l], (l == n - 1) ? B2_ACT_IDENTITY : c->act, s);
     }
     if (rc) return rc;
@@ -154,8 +154,8 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
     float* pb = pw + round4(w_size(c, l));
     {
       timed_scope t(c, B2_K_WGRAD, s);
-      rc = b2_launch_wgrad(a_prev, c->dz[cur], pw, pb, part_stride(c, l), rows, c->dims[l],
-                           c->dims[l + 1], sp, s);
+      rc = b2_launch_sgemm_wgrad(a_prev, c->dz[cur], pw, pb, part_stride(c, l), rows, c->dims[l],
+                                 c->dims[l + 1], sp, s);
     }
     if (rc) return rc;
     c->launches++;
@@ -517,7 +517,8 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
   // scratch: per-layer split partials, then the loss-head partials
   long soff = 0;
   for (int l = 0; l < n_layers; ++l) {
-    const long tiles = (long)((dims[l] + 63) / 64) * ((dims[l + 1] + 63) / 64);
+    const int bn = dims[l + 1] <= 64 ? 64 : (dims[l + 1] <= 112 ? 112 : 128);   // column tile of the wgrad kernel
+    const long tiles = (long)((dims[l] + 127) / 128) * ((dims[l + 1] + bn - 1) / bn);
     long sp = (4L * c->sm_count + tiles - 1) / tiles;
     const long cap = (max_local_batch + 63) / 64;
     if (sp > cap) sp = cap;

@@ -99,12 +99,6 @@ struct b2_ctx {
 struct b2_timed { cudaEvent_t a, b; int cls; };
 
 // ---- launchers (kernels_layered.cu) --------------------------------------------------------------
-// C[M,N] = act(A[M,K] @ W[K,N] + bias[N])
-int b2_launch_dense_fwd(const float* A, const float* W, const float* bias, float* C, int M, int N,
-                        int K, int act, cudaStream_t s);
-// partial[z][K*N] = A[rows of split z]^T @ dZ ; bias partial[z][N] = column sums of dZ
-int b2_launch_wgrad(const float* A, const float* dZ, float* partW, float* partB, long part_stride,
-                    int M, int Kin, int N, int splits, cudaStream_t s);
 // dA[M,Kin] = (dZ[M,N] @ W[Kin,N]^T) * act'(Aout)
 int b2_launch_dgrad(const float* dZ, const float* W, const float* Aout, float* dA, int M, int Kin,
                     int N, int act, cudaStream_t s);
@@ -178,3 +172,9 @@ int b2_launch_colsum_bf16(const void* m, float* part, float* out, int rows, int 
 int b2_launch_sgd_apply_mixed(float* params, const float* grads, long P, float lr, int n_seg, const long* off,
                               const long* size, void* const* wb, float* loss_trace, int* correct_trace,
                               float* global_step, int sm_count, cudaStream_t s);
+
+// ---- launchers (sgemm_ffma2.cu): fp32 FFMA2 GEMM micro-kernel for the generic layer path --------------------
+int b2_launch_sgemm_fwd(const float* A, const float* W, const float* bias, float* C, int M, int N, int K, int act,
+                        cudaStream_t s);
+int b2_launch_sgemm_wgrad(const float* A, const float* dZ, float* partW, float* partB, long part_stride, int rows,
+                          int Kin, int N, int splits, cudaStream_t s);

@@ -1,7 +1,8 @@
 // Generic fp32 layer kernels (CUDA cores) for any [in, hidden..., out] stack:
-//   K1 dense forward          matmul + bias + activation       distributed.py:96-98, simple.py:16
+//   K1 dense forward          matmul + bias + activation       distributed.py:96-98, simple.py:16   (sgemm_ffma2.cu)
 //   K2 loss head              softmax-CE / SSE forward+backward  distributed.py:99-102,117-118, simple.py:20
-//   K3 gradient reductions    dW = A^T dZ, db = colsum(dZ), dA   TF1 MatMul/BiasAdd/Sigmoid gradients
+//   K3 gradient reductions    dW = A^T dZ, db = colsum(dZ)      TF1 MatMul/BiasAdd gradients         (sgemm_ffma2.cu)
+//                             dA = dZ W^T * act'                 TF1 MatMul/Sigmoid gradients        (dgrad_kernel, here)
 //   K4 reduce + SGD apply     var -= lr * grad, global_step += 1  distributed.py:107-108, simple.py:22-23
 // All batch-dimension reductions are split into fixed slices and summed in a fixed order: no float
 // atomics, so a step is bit-reproducible.
@@ -14,197 +15,6 @@ namespace {
 constexpr int BM = 64, BN = 64, BK = 16;
 constexpr int PADT = 4;  // smem row padding (floats)
 
-__device__ __forceinline__ float act_fwd(float z, int act) {
-  // distributed.py:97 tf.nn.sigmoid
-  return act == B2_ACT_SIGMOID ? 1.0f / (1.0f + expf(-z)) : z;
-}
-
-// ---------------------------------------------------------------------------------------------
-// K1: C[M,N] = act(A[M,K] @ W[K,N] + bias[N]).  64x64 tile, 256 threads, 4x4 micro-tile.
-// ---------------------------------------------------------------------------------------------
-template <bool VEC_A, bool VEC_W>
-__global__ void __launch_bounds__(256)
-dense_fwd_kernel(const float* __restrict__ A, const float* __restrict__ W,
-                 const float* __restrict__ bias, float* __restrict__ C, int M, int N, int K, int act) {
-  __shared__ __align__(16) float As[BK][BM + PADT];  // As[k][m]
-  __shared__ __align__(16) float Bs[BK][BN + PADT];  // Bs[k][n]
-  const int tid = threadIdx.x;
-  const int tx = tid & 15, ty = tid >> 4;
-  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
-
-  float acc[4][4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-
-  const int a_row = tid >> 2, a_kq = (tid & 3) * 4;   // A tile: 64 rows x 16 k
-  const int w_k = tid >> 4, w_nq = (tid & 15) * 4;    // W tile: 16 k x 64 n
-
-  for (int k0 = 0; k0 < K; k0 += BK) {
-    {
-      const int m = m0 + a_row, k = k0 + a_kq;
-      float v[4] = {0.f, 0.f, 0.f, 0.f};
-      if (m < M) {
-        if (VEC_A) {
-          if (k < K) {
-            const float4 t = *reinterpret_cast<const float4*>(A + (size_t)m * K + k);
-            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            if (k + j < K) v[j] = A[(size_t)m * K + k + j];
-        }
-      }
-#pragma unroll
-      for (int j = 0; j < 4; ++j) As[a_kq + j][a_row] = v[j];
-    }
-    {
-      const int k = k0 + w_k, n = n0 + w_nq;
-      float v[4] = {0.f, 0.f, 0.f, 0.f};
-      if (k < K) {
-        if (VEC_W) {
-          if (n < N) {
-            const float4 t = *reinterpret_cast<const float4*>(W + (size_t)k * N + n);
-            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            if (n + j < N) v[j] = W[(size_t)k * N + n + j];
-        }
-      }
-      *reinterpret_cast<float4*>(&Bs[w_k][w_nq]) = make_float4(v[0], v[1], v[2], v[3]);
-    }
-    __syncthreads();
-#pragma unroll
-    for (int kk = 0; kk < BK; ++kk) {
-      const float4 a = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
-      const float4 b = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
-      const float av[4] = {a.x, a.y, a.z, a.w};
-      const float bv[4] = {b.x, b.y, b.z, b.w};
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
-    }
-    __syncthreads();
-  }
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int m = m0 + ty * 4 + i;
-    if (m >= M) continue;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int n = n0 + tx * 4 + j;
-      if (n < N) C[(size_t)m * N + n] = act_fwd(acc[i][j] + bias[n], act);
-    }
-  }
-}
-
-// ---------------------------------------------------------------------------------------------
-// K3a: weight / bias gradient of one layer over one batch slice.
-//   partW[z][k][n] = sum_{m in slice z} A[m][k] * dZ[m][n]      (MatMul grad, transpose_a)
-//   partB[z][n]    = sum_{m in slice z} dZ[m][n]                (BiasAdd grad)
-// grid = (ceil(N/64), ceil(Kin/64), splits)
-// ---------------------------------------------------------------------------------------------
-template <bool VEC_A, bool VEC_Z>
-__global__ void __launch_bounds__(256)
-wgrad_kernel(const float* __restrict__ A, const float* __restrict__ dZ, float* __restrict__ partW,
-             float* __restrict__ partB, long part_stride, int M, int Kin, int N, int chunk) {
-  __shared__ __align__(16) float As[BK][BM + PADT];  // As[m][k]
-  __shared__ __align__(16) float Zs[BK][BN + PADT];  // Zs[m][n]
-  const int tid = threadIdx.x;
-  const int tx = tid & 15, ty = tid >> 4;
-  const int n0 = blockIdx.x * BN, k0 = blockIdx.y * BM;
-  const int z = blockIdx.z;
-  const int m_begin = z * chunk;
-  const int m_end = min(M, m_begin + chunk);
-
-  float acc[4][4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-  float bacc[4] = {0.f, 0.f, 0.f, 0.f};
-
-  const int l_m = tid >> 4, l_q = (tid & 15) * 4;  // both tiles: 16 rows x 64 cols
-
-  for (int mb = m_begin; mb < m_end; mb += BK) {
-    const int m = mb + l_m;
-    {
-      const int k = k0 + l_q;
-      float v[4] = {0.f, 0.f, 0.f, 0.f};
-      if (m < m_end) {
-        if (VEC_A) {
-          if (k < Kin) {
-            const float4 t = *reinterpret_cast<const float4*>(A + (size_t)m * Kin + k);
-            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            if (k + j < Kin) v[j] = A[(size_t)m * Kin + k + j];
-        }
-      }
-      *reinterpret_cast<float4*>(&As[l_m][l_q]) = make_float4(v[0], v[1], v[2], v[3]);
-    }
-    {
-      const int n = n0 + l_q;
-      float v[4] = {0.f, 0.f, 0.f, 0.f};
-      if (m < m_end) {
-        if (VEC_Z) {
-          if (n < N) {
-            const float4 t = *reinterpret_cast<const float4*>(dZ + (size_t)m * N + n);
-            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            if (n + j < N) v[j] = dZ[(size_t)m * N + n + j];
-        }
-      }
-      *reinterpret_cast<float4*>(&Zs[l_m][l_q]) = make_float4(v[0], v[1], v[2], v[3]);
-    }
-    __syncthreads();
-#pragma unroll
-    for (int mm = 0; mm < BK; ++mm) {
-      const float4 a = *reinterpret_cast<const float4*>(&As[mm][ty * 4]);
-      const float4 b = *reinterpret_cast<const float4*>(&Zs[mm][tx * 4]);
-      const float av[4] = {a.x, a.y, a.z, a.w};
-      const float bv[4] = {b.x, b.y, b.z, b.w};
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
-      if (ty == 0) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) bacc[j] += bv[j];
-      }
-    }
-    __syncthreads();
-  }
-  float* pw = partW + (size_t)z * part_stride;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int k = k0 + ty * 4 + i;
-    if (k >= Kin) continue;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int n = n0 + tx * 4 + j;
-      if (n < N) pw[(size_t)k * N + n] = acc[i][j];
-    }
-  }
-  if (blockIdx.y == 0 && ty == 0) {
-    float* pb = partB + (size_t)z * part_stride;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int n = n0 + tx * 4 + j;
-      if (n < N) pb[n] = bacc[j];
-    }
-  }
-}
 
 // ---------------------------------------------------------------------------------------------
 // K3b: dA[M,Kin] = (dZ[M,N] @ W[Kin,N]^T) * act'(Aout)       (MatMul grad transpose_b + SigmoidGrad)
@@ -479,34 +289,6 @@ inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
       return B2_ERR_CUDA;                                                               \
     }                                                                                   \
   } while (0)
-
-int b2_launch_dense_fwd(const float* A, const float* W, const float* bias, float* C, int M, int N,
-                        int K, int act, cudaStream_t s) {
-  dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM);
-  const bool va = (K % 4 == 0) && aligned16(A);
-  const bool vw = (N % 4 == 0) && aligned16(W);
-  if (va && vw) dense_fwd_kernel<true, true><<<grid, 256, 0, s>>>(A, W, bias, C, M, N, K, act);
-  else if (va) dense_fwd_kernel<true, false><<<grid, 256, 0, s>>>(A, W, bias, C, M, N, K, act);
-  else if (vw) dense_fwd_kernel<false, true><<<grid, 256, 0, s>>>(A, W, bias, C, M, N, K, act);
-  else dense_fwd_kernel<false, false><<<grid, 256, 0, s>>>(A, W, bias, C, M, N, K, act);
-  B2_LAUNCH_CHECK();
-  return B2_OK;
-}
-
-int b2_launch_wgrad(const float* A, const float* dZ, float* partW, float* partB, long part_stride,
-                    int M, int Kin, int N, int splits, cudaStream_t s) {
-  int chunk = (M + splits - 1) / splits;
-  chunk = ((chunk + BK - 1) / BK) * BK;
-  dim3 grid((N + BN - 1) / BN, (Kin + BM - 1) / BM, splits);
-  const bool va = (Kin % 4 == 0) && aligned16(A);
-  const bool vz = (N % 4 == 0) && aligned16(dZ);
-  if (va && vz) wgrad_kernel<true, true><<<grid, 256, 0, s>>>(A, dZ, partW, partB, part_stride, M, Kin, N, chunk);
-  else if (va) wgrad_kernel<true, false><<<grid, 256, 0, s>>>(A, dZ, partW, partB, part_stride, M, Kin, N, chunk);
-  else if (vz) wgrad_kernel<false, true><<<grid, 256, 0, s>>>(A, dZ, partW, partB, part_stride, M, Kin, N, chunk);
-  else wgrad_kernel<false, false><<<grid, 256, 0, s>>>(A, dZ, partW, partB, part_stride, M, Kin, N, chunk);
-  B2_LAUNCH_CHECK();
-  return B2_OK;
-}
 
 int b2_launch_dgrad(const float* dZ, const float* W, const float* Aout, float* dA, int M, int Kin,
                     int N, int act, cudaStream_t s) {
