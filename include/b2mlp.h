@@ -158,7 +158,8 @@ int b2_eval(b2_ctx* ctx, const void* x_dev, const void* y_dev, long rows, float*
  * (distributed.py:148-150; simple.py:35).  x_host / y_host are HOST buffers holding this rank's
  * `rows` rows; they are copied to the device, one step runs, and the pre-update loss and
  * correct-row count come back to the host.  Synchronous.  This is the end-to-end path bench.py
- * reports as `e2e`.  global_batch = rows * nranks.
+ * reports as `e2e`.  global_batch = rows * nranks.  The call runs on a stream the context owns and
+ * synchronises it; do not interleave it with b2_train_steps work still in flight on another stream.
  */
 int b2_session_run_train(b2_ctx* ctx, const float* x_host, const float* y_host, int rows, float lr,
                          float* loss_out, int* correct_out);

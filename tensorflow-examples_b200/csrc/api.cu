@@ -187,6 +187,10 @@ int refresh_bf16_weights(b2_ctx* c, cudaStream_t s) {
   return B2_OK;
 }
 
+// the dgrad GEMM that produces the dz of layer l-1 (width dims[l]) can also emit its bias-gradient partials when every
+// 32-column chunk of its output is full (vector epilogue)
+inline bool fused_colsum(const b2_ctx* c, int l) { return c->dims[l] % 32 == 0; }
+
 // slices of the output layer's weight-gradient GEMM (split over the batch) and of its bias column sums
 inline int narrow_slices(const b2_ctx* c, int rows) {
   const int L = c->n_layers - 1;
@@ -229,7 +233,7 @@ int enqueue_forward_mixed(b2_ctx* c, const float* x, const float* y, int rows, f
   {
     timed_scope t(c, B2_K_GEMM_FWD, s);
     rc = b2_launch_gemm_bf16_ex(a_in, 0, c->wb[n - 1], 1, rows, 64, c->dims[n - 1], 3, c->params + c->b_off[n - 1],
-                                nullptr, c->z_last, c->dims[n], c->dims[n], 1, 0, c->sm_count, s);
+                                nullptr, c->z_last, c->dims[n], c->dims[n], 1, 0, nullptr, c->sm_count, s);
   }
   if (rc) return rc;
   c->launches++;
@@ -266,7 +270,7 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
     // dW_out partials = a^T . dz   (MatMul grad, transpose_a), K = batch cut into `slices` fixed pieces
     timed_scope t(c, B2_K_GEMM_WGRAD, s);
     rc = b2_launch_gemm_bf16_ex(c->ab[L - 1], 1, c->dzn, 1, c->dims[L], 64, rows, 2, nullptr, nullptr, pw, c->dims[n],
-                                c->dims[n], slices, part_stride(c, L), c->sm_count, s);
+                                c->dims[n], slices, part_stride(c, L), nullptr, c->sm_count, s);
   }
   if (rc) return rc;
   c->launches++;
@@ -274,21 +278,27 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
     // dz_prev = (dz . W_out^T) * a(1-a)   (MatMul grad transpose_b + SigmoidGrad); the reduction runs over the 64 padded classes
     timed_scope t(c, B2_K_GEMM_DGRAD, s);
     rc = b2_launch_gemm_bf16_ex(c->dzn, 0, c->wb[L], 0, rows, c->dims[L], 64, 1, nullptr, c->ab[L - 1], c->dzb[0],
-                                c->dims[L], c->dims[L], 1, 0, c->sm_count, s);
+                                c->dims[L], c->dims[L], 1, 0, fused_colsum(c, L) ? c->colsum_part : nullptr, c->sm_count, s);
   }
   if (rc) return rc;
   c->launches++;
+  bool colsum_pending = fused_colsum(c, L);   // the bias gradient of layer L-1 sits in colsum_part as 32-row partials
   int cur = 0;
   for (int l = L - 1; l >= 0; --l) {
     // dz of layer l (bf16 [rows, dims[l+1]]) is in dzb[cur]
     const void* a_prev = (l == 0) ? c->xb : c->ab[l - 1];
     {
       timed_scope t(c, B2_K_MIXED_AUX, s);
-      rc = b2_launch_colsum_bf16(c->dzb[cur], c->colsum_part, c->grads + c->b_off[l], rows, c->dims[l + 1],
-                                 b2_colsum_slices(rows, c->dims[l + 1], c->sm_count), s);
+      if (colsum_pending) {
+        rc = b2_launch_colsum_finish(c->colsum_part, c->grads + c->b_off[l], c->dims[l + 1], (rows + 31) / 32, s);
+        c->launches += 1;
+      } else {
+        rc = b2_launch_colsum_bf16(c->dzb[cur], c->colsum_part, c->grads + c->b_off[l], rows, c->dims[l + 1],
+                                   b2_colsum_slices(rows, c->dims[l + 1], c->sm_count), s);
+        c->launches += 2;
+      }
     }
     if (rc) return rc;
-    c->launches += 2;
     {
       // dW = a_prev^T . dz     both operands MN-major (global [rows, in] and [rows, out]); fp32 straight into grads
       timed_scope t(c, B2_K_GEMM_WGRAD, s);
@@ -300,8 +310,10 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
     if (l > 0) {
       // dz_prev = (dz . W^T) * a(1-a)   A = dz K-major [rows, out], B = W [in, out] K-major
       timed_scope t(c, B2_K_GEMM_DGRAD, s);
-      rc = b2_launch_gemm_bf16(c->dzb[cur], 0, c->wb[l], 0, rows, c->dims[l], c->dims[l + 1], 1, nullptr, c->ab[l - 1],
-                               c->dzb[cur ^ 1], c->sm_count, s);
+      colsum_pending = fused_colsum(c, l);
+      rc = b2_launch_gemm_bf16_ex(c->dzb[cur], 0, c->wb[l], 0, rows, c->dims[l], c->dims[l + 1], 1, nullptr, c->ab[l - 1],
+                                  c->dzb[cur ^ 1], c->dims[l], c->dims[l], 1, 0, colsum_pending ? c->colsum_part : nullptr,
+                                  c->sm_count, s);
       if (rc) return rc;
       c->launches++;
       cur ^= 1;
@@ -569,7 +581,12 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
     B2_ALLOC(c->dzn, (long)max_local_batch * 64 / 2);
     B2_ALLOC(c->dzb[0], (long)max_local_batch * hid / 2);
     if (n_layers > 2) B2_ALLOC(c->dzb[1], (long)max_local_batch * hid / 2);
-    B2_ALLOC(c->colsum_part, (long)b2_colsum_slices(max_local_batch, (int)hid, c->sm_count) * hid + 16);
+    {
+      long sl = b2_colsum_slices(max_local_batch, (int)hid, c->sm_count);
+      const long blocks32 = ((max_local_batch + 127) / 128) * 4;   // one partial row per 32-row block of every 128-row GEMM tile
+      if (blocks32 > sl) sl = blocks32;
+      B2_ALLOC(c->colsum_part, sl * hid + 16);
+    }
     c->wb_stale = 1;
   } else {
     for (int l = 0; l < n_layers - 1; ++l) B2_ALLOC(c->act_buf[l], (long)max_local_batch * dims[l + 1]);

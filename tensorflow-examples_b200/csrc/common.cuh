@@ -159,7 +159,9 @@ int b2_launch_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int M,
                         const float* bias, const void* act, void* out, int sm_count, cudaStream_t s);
 int b2_launch_gemm_bf16_ex(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
                            const float* bias, const void* act, void* out, int ldc, int n_store, int ksplits,
-                           long split_stride, int sm_count, cudaStream_t s);
+                           long split_stride, float* colsum_part, int sm_count, cudaStream_t s);
+// second stage of the bias gradients whose first stage is fused into the dgrad epilogue: out[c] = sum_z part[z][c]
+int b2_launch_colsum_finish(const float* part, float* out, int N, int slices, cudaStream_t s);
 
 // ---- launchers (mixed_aux.cu): CUDA-core kernels of the bf16 path ------------------------------------------
 int b2_launch_cast_bf16(const float* src, void* dst, long n, int sm_count, cudaStream_t s);

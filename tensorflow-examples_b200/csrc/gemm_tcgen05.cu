@@ -118,6 +118,8 @@ struct Params {
   int ldc, n_store;
   int ksplits;             // > 1: the K range is cut into this many slices, slice z writes out + z*split_stride
   long split_stride;       //      (fixed-order partials; a reduction kernel adds them)
+  float* colsum_part;      // EPI_DSIGMOID only, may be NULL: [ceil(M/32)][ldc] column sums of the bf16 OUTPUT over each
+                           //      32-row block (the layer's bias gradient, finished by colsum_finish)
 };
 
 __device__ __forceinline__ float fast_sigmoid(float z) {
@@ -242,17 +244,25 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const bool empty_split = z * kb_per >= num_kb_total;   // a K slice past the end contributes zeros
 #pragma unroll 1
       for (int c0 = chalf * (BLOCK_N / 2); c0 < (chalf + 1) * (BLOCK_N / 2); c0 += 32) {
+        const int n = n0 + c0;
+        const size_t off = (size_t)z * p.split_stride + (size_t)row * p.ldc + n;
+        const bool vec_ok = (n + 32 <= p.n_store) && ((p.ldc & 7) == 0);
+        // the activations this chunk is multiplied with: issue the loads before waiting on tensor memory
+        uint4 aq[4];
+        if (p.epi == EPI_DSIGMOID_BF16 && vec_ok) {
+          const uint4* ap = reinterpret_cast<const uint4*>(p.act + off);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) aq[j] = row_ok ? ap[j] : make_uint4(0u, 0u, 0u, 0u);
+        }
         uint32_t r[32];
         tc_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BLOCK_N + c0), r);
         if (empty_split) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) r[j] = 0u;
         }
-        const int n = n0 + c0;
-        if (!row_ok || n >= p.n_store) continue;
-        const size_t off = (size_t)z * p.split_stride + (size_t)row * p.ldc + n;
-        const bool vec_ok = (n + 32 <= p.n_store) && ((p.ldc & 7) == 0);
+        if (n >= p.n_store) continue;                       // warp-uniform
         if (p.epi == EPI_STORE_F32 || p.epi == EPI_BIAS_F32) {
+          if (!row_ok) continue;
           float* o = reinterpret_cast<float*>(p.out) + off;
           if (vec_ok) {
 #pragma unroll
@@ -270,7 +280,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               o[j] = __uint_as_float(r[j]) + (p.epi == EPI_BIAS_F32 ? p.bias[n + j] : 0.f);
           }
         } else if (!vec_ok) {
-          // ragged last column chunk: element-wise
+          // ragged last column chunk: element-wise (no fused column sums here)
+          if (!row_ok) continue;
           __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + off;
           for (int j = 0; j < 32 && n + j < p.n_store; ++j) {
             float v = __uint_as_float(r[j]);
@@ -283,7 +294,6 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             o[j] = __float2bfloat16_rn(v);
           }
         } else {
-          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + off;
           float v[32];
           if (p.epi == EPI_BIAS_SIGMOID_BF16) {
 #pragma unroll
@@ -296,10 +306,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               }
             }
           } else {
-            const uint4* ap = reinterpret_cast<const uint4*>(p.act + off);
 #pragma unroll
             for (int j = 0; j < 32; j += 8) {
-              const uint4 q = ap[j / 8];
+              const uint4 q = aq[j / 8];
               const uint32_t w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
               for (int u = 0; u < 4; ++u) {
@@ -309,15 +318,38 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               }
             }
           }
+          uint32_t w[16];
 #pragma unroll
-          for (int j = 0; j < 32; j += 8) {
-            uint32_t w[4];
+          for (int u = 0; u < 16; ++u) {
+            const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * u], v[2 * u + 1]);
+            w[u] = *reinterpret_cast<const uint32_t*>(&h);
+          }
+          if (row_ok) {
+            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + off;
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              const __nv_bfloat162 h = __floats2bfloat162_rn(v[j + 2 * u], v[j + 2 * u + 1]);
-              w[u] = *reinterpret_cast<const uint32_t*>(&h);
+            for (int j = 0; j < 4; ++j)
+              *reinterpret_cast<uint4*>(o + 8 * j) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+          }
+          if (p.epi == EPI_DSIGMOID_BF16 && p.colsum_part != nullptr) {
+            // BiasAdd gradient fused in: sum the ROUNDED outputs over this warp's 32 rows with a reduce-scatter
+            // butterfly (lanes whose bit is set keep the upper half), so lane L ends with column n+L.
+            float cs[32];
+#pragma unroll
+            for (int u = 0; u < 16; ++u) {
+              cs[2 * u] = row_ok ? __uint_as_float(w[u] << 16) : 0.f;
+              cs[2 * u + 1] = row_ok ? __uint_as_float(w[u] & 0xFFFF0000u) : 0.f;
             }
-            *reinterpret_cast<uint4*>(o + j) = make_uint4(w[0], w[1], w[2], w[3]);
+#pragma unroll
+            for (int hw = 16; hw >= 1; hw >>= 1) {
+              const bool up = (lane & hw) != 0;
+#pragma unroll
+              for (int i = 0; i < hw; ++i) {
+                const float send = up ? cs[i] : cs[i + hw];
+                const float keep = up ? cs[i + hw] : cs[i];
+                cs[i] = keep + __shfl_xor_sync(0xffffffffu, send, hw);
+              }
+            }
+            p.colsum_part[(size_t)((m0 + quarter * 32) >> 5) * p.ldc + n + lane] = cs[0];
           }
         }
       }
@@ -375,10 +407,13 @@ static int make_map(CUtensorMap* m, const void* base, long rows, long cols, int 
 template <int BN>
 static int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const tg::Params& p, int sm_count, cudaStream_t s) {
   using namespace tg;
-  static bool attr = false;
-  if (!attr) {
+  // the shared-memory opt-in is per device: remember which devices of this process have it
+  static unsigned long long attr_done = 0ull;
+  int dev = 0;
+  B2_CUDA(cudaGetDevice(&dev));
+  if (dev >= 64 || !((attr_done >> dev) & 1ull)) {
     B2_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
-    attr = true;
+    if (dev < 64) attr_done |= 1ull << dev;
   }
   const int tiles = ((p.M + BLOCK_M - 1) / BLOCK_M) * ((p.N + BN - 1) / BN) * p.ksplits;
   const int grid = tiles < sm_count ? tiles : sm_count;
@@ -395,7 +430,7 @@ static int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const tg::Par
 // out: [M, ldc], columns < n_store written.  ksplits > 1 cuts K into slices; slice z writes out + z*split_stride.
 int b2_launch_gemm_bf16_ex(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
                            const float* bias, const void* act, void* out, int ldc, int n_store, int ksplits,
-                           long split_stride, int sm_count, cudaStream_t s) {
+                           long split_stride, float* colsum_part, int sm_count, cudaStream_t s) {
   using namespace tg;
   if ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) {
     b2_set_error("gemm_bf16: operands must be 16-byte aligned");
@@ -420,6 +455,7 @@ int b2_launch_gemm_bf16_ex(const void* A, int a_mn, const void* B, int b_mn, int
   const int num_kb = (K + BLOCK_K - 1) / BLOCK_K;
   p.ksplits = ksplits < 1 ? 1 : (ksplits > num_kb ? num_kb : ksplits);
   p.split_stride = split_stride;
+  p.colsum_part = colsum_part;
   return BN == 64 ? launch_bn<64>(ta, tb, p, sm_count, s) : launch_bn<256>(ta, tb, p, sm_count, s);
 }
 
@@ -429,5 +465,5 @@ int b2_launch_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int M,
     b2_set_error("gemm_bf16: N must be a multiple of 8 (N=%d)", N);
     return B2_ERR_ARG;
   }
-  return b2_launch_gemm_bf16_ex(A, a_mn, B, b_mn, M, N, K, epi, bias, act, out, N, N, 1, 0, sm_count, s);
+  return b2_launch_gemm_bf16_ex(A, a_mn, B, b_mn, M, N, K, epi, bias, act, out, N, N, 1, 0, nullptr, sm_count, s);
 }

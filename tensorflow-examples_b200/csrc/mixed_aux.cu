@@ -100,13 +100,30 @@ colsum_bf16_kernel(const __nv_bfloat16* __restrict__ m, float* __restrict__ part
   part[(size_t)blockIdx.y * N + 2 * c2 + 1] = s1;
 }
 
+// Stage 2: out[c] = sum over slices, in a fixed order.  Block = 32 columns x 8 interleaved slice groups.
 __global__ void __launch_bounds__(256)
 colsum_finish_kernel(const float* __restrict__ part, float* __restrict__ out, int N, int slices) {
-  const int c = blockIdx.x * 256 + threadIdx.x;
-  if (c >= N) return;
+  __shared__ float sh[8][33];
+  const int cl = threadIdx.x & 31, zg = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cl;
   float s = 0.f;
-  for (int z = 0; z < slices; ++z) s += part[(size_t)z * N + c];
-  out[c] = s;
+  if (c < N) {
+    int z = zg;
+    for (; z + 24 < slices; z += 32) {
+      const float v0 = part[(size_t)z * N + c], v1 = part[(size_t)(z + 8) * N + c], v2 = part[(size_t)(z + 16) * N + c],
+                  v3 = part[(size_t)(z + 24) * N + c];
+      s += v0; s += v1; s += v2; s += v3;
+    }
+    for (; z < slices; z += 8) s += part[(size_t)z * N + c];
+  }
+  sh[zg][cl] = s;
+  __syncthreads();
+  if (zg == 0 && c < N) {
+    float t = sh[0][cl];
+#pragma unroll
+    for (int u = 1; u < 8; ++u) t += sh[u][cl];
+    out[c] = t;
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -189,7 +206,13 @@ int b2_launch_colsum_bf16(const void* m, float* part, float* out, int rows, int 
   const int rps = (rows + slices - 1) / slices;
   mx::colsum_bf16_kernel<<<dim3(bx, slices), 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(m), part, rows, N, rps);
   MX_CHECK();
-  mx::colsum_finish_kernel<<<(N + 255) / 256, 256, 0, s>>>(part, out, N, slices);
+  mx::colsum_finish_kernel<<<(N + 31) / 32, 256, 0, s>>>(part, out, N, slices);
+  MX_CHECK();
+  return B2_OK;
+}
+
+int b2_launch_colsum_finish(const float* part, float* out, int N, int slices, cudaStream_t s) {
+  mx::colsum_finish_kernel<<<(N + 31) / 32, 256, 0, s>>>(part, out, N, slices);
   MX_CHECK();
   return B2_OK;
 }
