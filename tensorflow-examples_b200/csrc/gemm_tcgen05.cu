@@ -16,6 +16,7 @@
 //               next tile's MMAs already fill the other accumulator buffer
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -67,10 +68,33 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
       ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_2d_mc(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar, uint16_t mask) {
+  // the tile lands at the same shared-memory offset in every CTA of `mask` and completes bytes on each one's barrier
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(mask)
+      : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tc_commit_mc(uint64_t* bar, uint16_t mask) {
+  // arrive on the barrier at this offset in every CTA of the cluster named by `mask`
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                   smem_u32(bar)),
+               "h"(mask)
                : "memory");
 }
 __device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
@@ -129,10 +153,18 @@ __device__ __forceinline__ float fast_sigmoid(float z) {
   return fmaf(0.5f, t, 0.5f);
 }
 
-template <int BLOCK_N>
+// CL = CTAs per cluster.  The CL CTAs of a cluster work on CL vertically adjacent output tiles (same columns), so
+// they need the same B tile: each loads 1/CL of it and TMA-multicasts that share into every CTA's shared memory.
+// That cuts the L2 -> SM traffic per k-block from 48 KB to 32 KB (CL = 2) / 24 KB (CL = 4) per CTA, which is what
+// bounds the single-CTA kernel (128x256x64 MMAs consume operands faster than L2 can deliver 48 KB per k-block).
+template <int BLOCK_N, int CL>
 __global__ void __launch_bounds__(THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Params p) {
   using C = Cfg<BLOCK_N>;
+  static_assert(CL == 1 || (BLOCK_N / 64) % CL == 0, "each CTA multicasts a whole number of 64-column atoms");
+  const int cta_rank = CL == 1 ? 0 : (int)cluster_ctarank();
+  const int cluster_id = blockIdx.x / CL, num_clusters = gridDim.x / CL;
+  constexpr uint16_t kMask = (uint16_t)((1u << CL) - 1u);
   extern __shared__ unsigned char smem_raw[];
   // 1024-byte alignment: required by the 128B swizzle atoms (descriptor base_offset = 0)
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -147,13 +179,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_m = (p.M + BLOCK_M - 1) / BLOCK_M, tiles_n = (p.N + BLOCK_N - 1) / BLOCK_N;
-  const int mn_tiles = tiles_m * tiles_n;
+  const int tiles_ms = (tiles_m + CL - 1) / CL;            // groups of CL vertically adjacent tiles
+  const int mn_tiles = tiles_ms * tiles_n;
   const int ntiles = mn_tiles * p.ksplits;
   const int num_kb_total = (p.K + BLOCK_K - 1) / BLOCK_K;
   const int kb_per = (num_kb_total + p.ksplits - 1) / p.ksplits;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], CL); }
     for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -165,6 +198,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
   tc_fence_before();
   __syncthreads();
+  if (CL > 1) cluster_sync_all();                            // every CTA's barriers exist before anyone multicasts
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -172,9 +206,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ------------------------------------ TMA producer ------------------------------------
     if (lane == 0) {
       int it = 0;
-      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      for (int tile = cluster_id; tile < ntiles; tile += num_clusters) {
         const int mn = tile % mn_tiles, z = tile / mn_tiles;
-        const int m0 = (mn / tiles_n) * BLOCK_M, n0 = (mn % tiles_n) * BLOCK_N;
+        const int m0 = ((mn / tiles_n) * CL + cta_rank) * BLOCK_M, n0 = (mn % tiles_n) * BLOCK_N;
         const int kb_begin = z * kb_per, kb_end = min(num_kb_total, kb_begin + kb_per);
         for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
           const int s = it % STAGES;
@@ -189,11 +223,25 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           } else {
             tma_load_2d(a_dst, &tmA, k0, m0, &full[s]);
           }
-          if (p.b_mn) {
+          if (CL == 1) {
+            if (p.b_mn) {
 #pragma unroll
-            for (int b = 0; b < BLOCK_N / 64; ++b) tma_load_2d(b_dst + b * (BLOCK_K * 128), &tmB, n0 + 64 * b, k0, &full[s]);
+              for (int b = 0; b < BLOCK_N / 64; ++b) tma_load_2d(b_dst + b * (BLOCK_K * 128), &tmB, n0 + 64 * b, k0, &full[s]);
+            } else {
+              tma_load_2d(b_dst, &tmB, k0, n0, &full[s]);
+            }
+          } else if (p.b_mn) {
+            // my share of the B tile: 64-column atoms cta_rank*APC .. , multicast to the whole cluster
+            constexpr int APC = (BLOCK_N / 64) / CL;
+#pragma unroll
+            for (int b = 0; b < APC; ++b) {
+              const int atom = cta_rank * APC + b;
+              tma_load_2d_mc(b_dst + atom * (BLOCK_K * 128), &tmB, n0 + 64 * atom, k0, &full[s], kMask);
+            }
           } else {
-            tma_load_2d(b_dst, &tmB, k0, n0, &full[s]);
+            // K-major B: rows cta_rank*(BLOCK_N/CL) .. of the tile (the tensor map's box is BLOCK_N/CL rows high)
+            constexpr int RPC = BLOCK_N / CL;
+            tma_load_2d_mc(b_dst + cta_rank * RPC * 128, &tmB, k0, n0 + cta_rank * RPC, &full[s], kMask);
           }
         }
       }
@@ -207,7 +255,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const uint32_t a_step = p.a_mn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;   // descriptor units of 16 B
       const uint32_t b_step = p.b_mn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
       int it = 0, t = 0;
-      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t) {
+      for (int tile = cluster_id; tile < ntiles; tile += num_clusters, ++t) {
         const int acc = t & 1;
         mbar_wait(&tempty[acc], ((t >> 1) & 1) ^ 1);       // epilogue has drained this accumulator buffer
         tc_fence_after();
@@ -223,7 +271,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
             tc_mma(d_tmem, da + (uint64_t)(k * a_step), db + (uint64_t)(k * b_step), idesc, (kb != kb_begin) || (k != 0));
-          tc_commit(&empty[s]);                             // frees the smem stage when these MMAs retire
+          if (CL == 1) tc_commit(&empty[s]);                // frees the smem stage when these MMAs retire
+          else tc_commit_mc(&empty[s], kMask);              // ... in every CTA: their multicasts write into my B stage too
         }
         tc_commit(&tfull[acc]);                             // accumulator complete
       }
@@ -233,10 +282,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int quarter = warp & 3;                           // TMEM lanes 32*quarter .. +31 belong to this warp
     const int chalf = (warp - 2) >> 2;                      // which half of the tile's columns this warp drains
     int t = 0;
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t) {
+    for (int tile = cluster_id; tile < ntiles; tile += num_clusters, ++t) {
       const int acc = t & 1;
       const int mn = tile % mn_tiles, z = tile / mn_tiles;
-      const int m0 = (mn / tiles_n) * BLOCK_M, n0 = (mn % tiles_n) * BLOCK_N;
+      const int m0 = ((mn / tiles_n) * CL + cta_rank) * BLOCK_M, n0 = (mn % tiles_n) * BLOCK_N;
       mbar_wait(&tfull[acc], (t >> 1) & 1);
       tc_fence_after();
       const int row = m0 + quarter * 32 + lane;
@@ -276,22 +325,26 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               *reinterpret_cast<float4*>(o + j) = v;
             }
           } else {
-            for (int j = 0; j < 32 && n + j < p.n_store; ++j)
-              o[j] = __uint_as_float(r[j]) + (p.epi == EPI_BIAS_F32 ? p.bias[n + j] : 0.f);
+#pragma unroll
+            for (int j = 0; j < 32; ++j)      // fully unrolled: r[] must stay in registers
+              if (n + j < p.n_store) o[j] = __uint_as_float(r[j]) + (p.epi == EPI_BIAS_F32 ? p.bias[n + j] : 0.f);
           }
         } else if (!vec_ok) {
           // ragged last column chunk: element-wise (no fused column sums here)
           if (!row_ok) continue;
           __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + off;
-          for (int j = 0; j < 32 && n + j < p.n_store; ++j) {
-            float v = __uint_as_float(r[j]);
-            if (p.epi == EPI_BIAS_SIGMOID_BF16) {
-              v = fast_sigmoid(v + p.bias[n + j]);
-            } else {
-              const float a = __bfloat162float(p.act[off + j]);
-              v = v * a * (1.0f - a);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            if (n + j < p.n_store) {
+              float v = __uint_as_float(r[j]);
+              if (p.epi == EPI_BIAS_SIGMOID_BF16) {
+                v = fast_sigmoid(v + p.bias[n + j]);
+              } else {
+                const float a = __bfloat162float(p.act[off + j]);
+                v = v * a * (1.0f - a);
+              }
+              o[j] = __float2bfloat16_rn(v);
             }
-            o[j] = __float2bfloat16_rn(v);
           }
         } else {
           float v[32];
@@ -339,16 +392,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               cs[2 * u] = row_ok ? __uint_as_float(w[u] << 16) : 0.f;
               cs[2 * u + 1] = row_ok ? __uint_as_float(w[u] & 0xFFFF0000u) : 0.f;
             }
-#pragma unroll
-            for (int hw = 16; hw >= 1; hw >>= 1) {
-              const bool up = (lane & hw) != 0;
-#pragma unroll
-              for (int i = 0; i < hw; ++i) {
-                const float send = up ? cs[i] : cs[i + hw];
-                const float keep = up ? cs[i + hw] : cs[i];
-                cs[i] = keep + __shfl_xor_sync(0xffffffffu, send, hw);
-              }
+#define B2_BFLY(HW)                                                                 \
+            {                                                                          \
+              const bool up = (lane & HW) != 0;                                        \
+              _Pragma("unroll") for (int i = 0; i < HW; ++i) {                          \
+                const float send = up ? cs[i] : cs[i + HW];                            \
+                const float keep = up ? cs[i + HW] : cs[i];                            \
+                cs[i] = keep + __shfl_xor_sync(0xffffffffu, send, HW);                 \
+              }                                                                        \
             }
+            B2_BFLY(16) B2_BFLY(8) B2_BFLY(4) B2_BFLY(2) B2_BFLY(1)
+#undef B2_BFLY
             p.colsum_part[(size_t)((m0 + quarter * 32) >> 5) * p.ldc + n + lane] = cs[0];
           }
         }
@@ -360,6 +414,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
   tc_fence_before();
   __syncthreads();
+  if (CL > 1) cluster_sync_all();                            // nobody leaves while a peer can still write into it
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::TMEM_COLS)
@@ -404,7 +459,7 @@ static int make_map(CUtensorMap* m, const void* base, long rows, long cols, int 
 
 }  // namespace tg
 
-template <int BN>
+template <int BN, int CL>
 static int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const tg::Params& p, int sm_count, cudaStream_t s) {
   using namespace tg;
   // the shared-memory opt-in is per device: remember which devices of this process have it
@@ -412,13 +467,27 @@ static int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const tg::Par
   int dev = 0;
   B2_CUDA(cudaGetDevice(&dev));
   if (dev >= 64 || !((attr_done >> dev) & 1ull)) {
-    B2_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
+    B2_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
     if (dev < 64) attr_done |= 1ull << dev;
   }
-  const int tiles = ((p.M + BLOCK_M - 1) / BLOCK_M) * ((p.N + BN - 1) / BN) * p.ksplits;
-  const int grid = tiles < sm_count ? tiles : sm_count;
-  gemm_bf16_kernel<BN><<<grid, THREADS, Cfg<BN>::SMEM_BYTES, s>>>(ta, tb, p);
-  cudaError_t e = cudaGetLastError();
+  const int tiles_ms = ((p.M + BLOCK_M - 1) / BLOCK_M + CL - 1) / CL;
+  const int groups = tiles_ms * ((p.N + BN - 1) / BN) * p.ksplits;
+  int clusters = sm_count / CL;
+  if (clusters > groups) clusters = groups;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(clusters * CL);
+  cfg.blockDim = dim3(THREADS);
+  cfg.dynamicSmemBytes = Cfg<BN>::SMEM_BYTES;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CL;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<BN, CL>, ta, tb, p);
   if (e != cudaSuccess) {
     b2_set_error("gemm_bf16 launch failed: %s", cudaGetErrorString(e));
     return B2_ERR_CUDA;
@@ -443,10 +512,14 @@ int b2_launch_gemm_bf16_ex(const void* A, int a_mn, const void* B, int b_mn, int
   int rc = get_encode();
   if (rc) return rc;
   const int BN = (N <= 64) ? 64 : 256;
+  // cluster size: 2 CTAs share each B tile by multicast when there are at least two rows of tiles to pair up
+  const char* env = getenv("B2_GEMM_CLUSTER");
+  int CL = (BN == 256 && M > BLOCK_M) ? 2 : 1;
+  if (env && *env && BN == 256) CL = atoi(env) == 4 ? 4 : (atoi(env) == 1 ? 1 : 2);
   CUtensorMap ta, tb;
   rc = a_mn ? make_map(&ta, A, K, M, BLOCK_K) : make_map(&ta, A, M, K, BLOCK_M);
   if (rc) return rc;
-  rc = b_mn ? make_map(&tb, B, K, N, BLOCK_K) : make_map(&tb, B, N, K, BN);
+  rc = b_mn ? make_map(&tb, B, K, N, BLOCK_K) : make_map(&tb, B, N, K, BN / CL);
   if (rc) return rc;
   Params p;
   p.M = M; p.N = N; p.K = K; p.a_mn = a_mn; p.b_mn = b_mn; p.epi = epi;
@@ -456,7 +529,10 @@ int b2_launch_gemm_bf16_ex(const void* A, int a_mn, const void* B, int b_mn, int
   p.ksplits = ksplits < 1 ? 1 : (ksplits > num_kb ? num_kb : ksplits);
   p.split_stride = split_stride;
   p.colsum_part = colsum_part;
-  return BN == 64 ? launch_bn<64>(ta, tb, p, sm_count, s) : launch_bn<256>(ta, tb, p, sm_count, s);
+  if (BN == 64) return launch_bn<64, 1>(ta, tb, p, sm_count, s);
+  if (CL == 4) return launch_bn<256, 4>(ta, tb, p, sm_count, s);
+  if (CL == 2) return launch_bn<256, 2>(ta, tb, p, sm_count, s);
+  return launch_bn<256, 1>(ta, tb, p, sm_count, s);
 }
 
 int b2_launch_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
