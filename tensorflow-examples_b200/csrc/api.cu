@@ -125,8 +125,13 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
     int rc;
     {
       timed_scope t(c, B2_K_DENSE_FWD, s);
-      rc = b2_launch_sgemm_fwd(a_in, c->params + c->w_off[l], c->params + c->b_off[l], out, rows,
-                               c->dims[l + 1], c->dims[l], (l == n - 1) ? B2_ACT_IDENTITY : c->act, s);
+      const int act_l = (l == n - 1) ? B2_ACT_IDENTITY : c->act;
+      if (b2_small_m_fwd_applies(rows, c->dims[l]))
+        rc = b2_launch_small_m_fwd(a_in, c->params + c->w_off[l], c->params + c->b_off[l], out, rows, c->dims[l + 1],
+                                   c->dims[l], act_l, s);
+      else
+        rc = b2_launch_sgemm_fwd(a_in, c->params + c->w_off[l], c->params + c->b_off[l], out, rows, c->dims[l + 1],
+                                 c->dims[l], act_l, s);
     }
     if (rc) return rc;
     c->launches++;

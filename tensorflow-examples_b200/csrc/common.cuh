@@ -180,3 +180,7 @@ int b2_launch_sgemm_fwd(const float* A, const float* W, const float* bias, float
                         cudaStream_t s);
 int b2_launch_sgemm_wgrad(const float* A, const float* dZ, float* partW, float* partB, long part_stride, int rows,
                           int Kin, int N, int splits, cudaStream_t s);
+// forward for small batches (M <= 256): column-sliced, K split over the lanes of a warp
+bool b2_small_m_fwd_applies(int M, int K);
+int b2_launch_small_m_fwd(const float* A, const float* W, const float* bias, float* C, int M, int N, int K, int act,
+                          cudaStream_t s);

@@ -236,3 +236,102 @@ int b2_launch_sgemm_wgrad(const float* A, const float* dZ, float* partW, float* 
   p.partW = partW; p.partB = partB; p.part_stride = part_stride;
   return sg::launch<sg::EPI_WGRAD>(p, splits, s);
 }
+
+// ---------------------------------------------------------------------------------------------
+// Forward for SMALL batches (M <= 256 rows, e.g. the reference's shipped batch of 100): the tiled kernel above
+// would put the whole K loop on one or two CTAs.  Here a CTA owns 8 output columns (its slice of W sits in shared
+// memory), its warps share the rows, and the lanes of a warp split K -- x is read coalesced, each row ends with a
+// warp-shuffle reduction.  grid = ceil(N/8); latency ~ one pass over K/32 elements per row.
+// ---------------------------------------------------------------------------------------------
+namespace sg {
+
+constexpr int SM_COLS = 8, SM_THREADS = 256;
+
+__global__ void __launch_bounds__(SM_THREADS)
+small_m_fwd_kernel(const float* __restrict__ A, const float* __restrict__ W, const float* __restrict__ bias,
+                   float* __restrict__ C, int M, int N, int K, int act) {
+  extern __shared__ __align__(16) float s_w[];   // [K][8]
+  const int n0 = blockIdx.x * SM_COLS;
+  for (int i0 = 0; i0 < K * SM_COLS; i0 += 8 * SM_THREADS) {
+    float v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {          // eight independent loads in flight per thread
+      const int i = i0 + u * SM_THREADS + threadIdx.x;
+      const int k = i >> 3, c = i & 7;
+      v[u] = (i < K * SM_COLS && n0 + c < N) ? W[(size_t)k * N + n0 + c] : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int i = i0 + u * SM_THREADS + threadIdx.x;
+      if (i < K * SM_COLS) s_w[i] = v[u];
+    }
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // blockIdx.y cuts the rows into gridDim.y interleaved groups so that a small batch still fills many SMs
+  for (int m = blockIdx.y * (SM_THREADS / 32) + warp; m < M; m += gridDim.y * (SM_THREADS / 32)) {
+    const float* xr = A + (size_t)m * K;
+    float acc[SM_COLS];
+#pragma unroll
+    for (int c = 0; c < SM_COLS; ++c) acc[c] = 0.f;
+    for (int kc = 0; kc < K; kc += 1024) {
+      // all of this lane's x values of the chunk are requested before any is used: one memory latency per row
+      float xv[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const int k = kc + lane + 32 * i;
+        xv[i] = k < K ? xr[k] : 0.f;
+      }
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const int k = kc + lane + 32 * i;
+        if (k < K) {
+          const float x = xv[i];
+          const float4 w0 = *reinterpret_cast<const float4*>(s_w + k * SM_COLS);
+          const float4 w1 = *reinterpret_cast<const float4*>(s_w + k * SM_COLS + 4);
+          acc[0] = fmaf(x, w0.x, acc[0]); acc[1] = fmaf(x, w0.y, acc[1]);
+          acc[2] = fmaf(x, w0.z, acc[2]); acc[3] = fmaf(x, w0.w, acc[3]);
+          acc[4] = fmaf(x, w1.x, acc[4]); acc[5] = fmaf(x, w1.y, acc[5]);
+          acc[6] = fmaf(x, w1.z, acc[6]); acc[7] = fmaf(x, w1.w, acc[7]);
+        }
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < SM_COLS; ++c) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], o);
+    }
+    if (lane < SM_COLS && n0 + lane < N) {
+      float z = acc[0];
+#pragma unroll
+      for (int c = 1; c < SM_COLS; ++c) z = (lane == c) ? acc[c] : z;
+      z += bias[n0 + lane];
+      C[(size_t)m * N + n0 + lane] = act == B2_ACT_SIGMOID ? 1.0f / (1.0f + expf(-z)) : z;
+    }
+  }
+}
+
+}  // namespace sg
+
+bool b2_small_m_fwd_applies(int M, int K) { return M <= 256 && (size_t)K * sg::SM_COLS * sizeof(float) <= 160 * 1024; }
+
+int b2_launch_small_m_fwd(const float* A, const float* W, const float* bias, float* C, int M, int N, int K, int act,
+                          cudaStream_t s) {
+  const int smem = K * sg::SM_COLS * (int)sizeof(float);
+  static int attr_smem = 48 * 1024;   // opt-in only ever grows; per process (one device per process in this library's use)
+  if (smem > attr_smem) {
+    B2_CUDA(cudaFuncSetAttribute(sg::small_m_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_smem = smem;
+  }
+  const int col_blocks = (N + sg::SM_COLS - 1) / sg::SM_COLS;
+  int row_groups = (M + 15) / 16;                       // about two rows per warp
+  if (row_groups * col_blocks > 592) row_groups = (592 + col_blocks - 1) / col_blocks;
+  if (row_groups < 1) row_groups = 1;
+  sg::small_m_fwd_kernel<<<dim3(col_blocks, row_groups), sg::SM_THREADS, smem, s>>>(A, W, bias, C, M, N, K, act);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    b2_set_error("small_m_fwd launch failed: %s", cudaGetErrorString(e));
+    return B2_ERR_CUDA;
+  }
+  return B2_OK;
+}
