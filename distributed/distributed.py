@@ -45,6 +45,8 @@ flags.DEFINE_boolean("shuffle", True, "reshuffle the training pool every epoch, 
 flags.DEFINE_integer("shuffle_seed", 0, "seed of the per-epoch permutation (the reference's is unseeded)")
 flags.DEFINE_string("logs_path", "", "TensorBoard event directory; the reference hard-codes /tmp/mnist/ (distributed.py:49). "
                     "Empty (default) writes no event files")
+flags.DEFINE_integer("async_period", 0, "k > 0: emulate the reference's asynchronous parameter-server updates -- every worker "
+                     "applies its own gradients, replicas are averaged every k steps; 0 (default): synchronous all-reduce")
 flags.DEFINE_boolean("peer_exchange", True, "workers on one NVLink box sum gradients through peer memory instead of NCCL")
 flags.DEFINE_boolean("strict_reference_bugs", False,
                      "reproduce distributed.py:165 literally: the 'Time Taken' line raises TypeError")
@@ -113,6 +115,8 @@ def main(argv):
         # the other workers' GPU memory over NVLink, fused with the SGD apply
         store.set("b2_peer_%d" % role.rank, model.peer_export())
         model.peer_import([bytes(store.get("b2_peer_%d" % r)) for r in range(role.world)])
+    if role.world > 1 and FLAGS.async_period > 0:
+        model.set_async_period(FLAGS.async_period)
     cl.store_barrier(store, role, "b2_comm_ready")
 
     # writer = tf.summary.FileWriter(logs_path, graph=...)   distributed.py:138 -- every worker writes its own file

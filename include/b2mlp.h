@@ -52,7 +52,12 @@ enum { B2_PREC_FP32 = 0, B2_PREC_BF16_FP32ACC = 1 };       /* BASELINE.json conf
 enum {
   B2_OPT_FORCE_LAYERED = 1,  /* value 1: never use the single-kernel fused step, even when the shape allows it */
   B2_OPT_KERNEL_TIMING = 2,  /* value 1: bracket every kernel launch with CUDA events (see b2_kernel_times) */
-  B2_OPT_NO_PEER_EXCHANGE = 3 /* value 1: use the NCCL all-reduce even when peer memory is mapped (b2_peer_import) */
+  B2_OPT_NO_PEER_EXCHANGE = 3, /* value 1: use the NCCL all-reduce even when peer memory is mapped (b2_peer_import) */
+  B2_OPT_ASYNC_PERIOD = 5     /* value k > 0: emulate the reference's ASYNCHRONOUS parameter-server training
+                                 (distributed.py:107-113: plain GradientDescentOptimizer, SyncReplicas commented out):
+                                 every worker applies its own gradients locally (mean over ITS batch) and the replicas'
+                                 parameters are averaged every k steps; k = 1 reproduces the synchronous update.
+                                 value 0 (default): synchronous all-reduce data parallelism */
 };
 
 /* Kernel classes reported by b2_kernel_times. */

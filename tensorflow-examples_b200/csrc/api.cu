@@ -342,7 +342,7 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
   }
   if (rc) return rc;
   c->launches++;
-  if (c->nranks > 1) {
+  if (c->nranks > 1 && c->async_period == 0) {
     timed_scope t(c, B2_K_ALLREDUCE_APPLY, s);
     B2_NCCL(g_nccl.AllReduce(c->grads, c->grads, (size_t)(c->P + 4), kNcclFloat, kNcclSum, c->nccl_comm, s));
   }
@@ -364,7 +364,7 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
                  float* loss_trace, int* correct_trace, cudaStream_t s) {
   if (is_mixed(c)) return enqueue_step_mixed(c, x, y, rows, global_batch, lr, loss_trace, correct_trace, s);
   const float inv_B = 1.0f / (float)global_batch;
-  const int apply = (c->nranks == 1) ? 1 : 0;
+  const int apply = (c->nranks == 1 || c->async_period > 0) ? 1 : 0;
   const bool use_peer = !apply && c->peer_ready && !c->opt_no_peer;
   const int peer_buf = (int)(c->peer_step & 1u);
   // where this rank's reduced vector goes: the exported peer buffer (parity of the step) or the private one
@@ -636,6 +636,10 @@ extern "C" int b2_set_option(b2_ctx* ctx, int option, int value) {
     case B2_OPT_FORCE_LAYERED: ctx->opt_force_layered = value ? 1 : 0; return B2_OK;
     case B2_OPT_KERNEL_TIMING: ctx->opt_timing = value ? 1 : 0; return B2_OK;
     case B2_OPT_NO_PEER_EXCHANGE: ctx->opt_no_peer = value ? 1 : 0; return B2_OK;
+    case B2_OPT_ASYNC_PERIOD:
+      B2_CHECK_ARG(value >= 0, "b2_set_option: async period must be >= 0");
+      ctx->async_period = value;
+      return B2_OK;
     default: b2_set_error("b2_set_option: unknown option %d", option); return B2_ERR_ARG;
   }
 }
@@ -819,10 +823,23 @@ extern "C" int b2_train_steps(b2_ctx* ctx, const void* x_pool_dev, const void* y
   const int in = ctx->dims[0], outd = ctx->dims[ctx->n_layers];
   for (int i = 0; i < n_steps; ++i) {
     const long start = (first_row + (long)i * global_batch) % span + (long)ctx->rank * local_batch;
-    int rc = enqueue_step(ctx, xp + start * in, yp + start * outd, local_batch, global_batch, lr,
+    const bool async = ctx->async_period > 0 && ctx->nranks > 1;
+    int rc = enqueue_step(ctx, xp + start * in, yp + start * outd, local_batch, async ? (long)local_batch : global_batch, lr,
                           loss_trace_dev ? loss_trace_dev + i : nullptr,
                           correct_trace_dev ? correct_trace_dev + i : nullptr, s);
     if (rc) return rc;
+    if (async) {
+      // the workers of the reference update the ps variables independently; here the replicas drift for
+      // `async_period` local steps and are then averaged (parameters, not gradients)
+      ctx->global_step_host += (float)(ctx->nranks - 1);       // global_step counts every worker's update (distributed.py:108)
+      if (++ctx->async_count % ctx->async_period == 0) {
+        B2_NCCL(g_nccl.AllReduce(ctx->params, ctx->params, (size_t)ctx->P, kNcclFloat, kNcclSum, ctx->nccl_comm, s));
+        rc = b2_launch_scale(ctx->params, ctx->P, 1.0f / (float)ctx->nranks, ctx->sm_count, s);
+        if (rc) return rc;
+        ctx->launches++;
+        ctx->wb_stale = 1;
+      }
+    }
   }
   return B2_OK;
 }

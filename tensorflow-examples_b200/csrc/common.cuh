@@ -80,6 +80,8 @@ struct b2_ctx {
   void* peer_base[B2_MAX_PEERS];   // mapped base of every rank's buffer (own entry = peer_local)
   int peer_ready;
   int opt_no_peer;                 // B2_OPT_NO_PEER_EXCHANGE
+  int async_period;                // B2_OPT_ASYNC_PERIOD (0 = synchronous)
+  long async_count;                // local steps since the context was created
   unsigned peer_step;              // exchanges enqueued so far
 
   // bf16-operand / fp32-accumulate path (precision == B2_PREC_BF16_FP32ACC): tensor-core GEMMs for the hidden layers
@@ -128,6 +130,7 @@ int b2_launch_sgd_apply(float* params, const float* grads, long P, float lr, flo
 int b2_launch_eval_accumulate(const float* loss_part, const float* correct_part, int blocks,
                               float* acc, cudaStream_t s);
 int b2_launch_eval_finish(const float* acc, float* loss_out, long* correct_out, cudaStream_t s);
+int b2_launch_scale(float* p, long n, float a, int sm_count, cudaStream_t s);   // p[i] *= a
 
 // ---- launchers (fused_linear.cu): single dense layer 784 -> 10 + softmax-CE head, one kernel --------
 bool b2_fused_linear_supported(int in_dim, int out_dim, int loss);

@@ -262,6 +262,10 @@ sgd_apply_kernel(float* __restrict__ params, const float* __restrict__ grads, lo
   }
 }
 
+__global__ void __launch_bounds__(256) scale_kernel(float* __restrict__ p, long n, float a) {
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) p[i] *= a;
+}
+
 __global__ void eval_accumulate_kernel(const float* __restrict__ loss_part,
                                        const float* __restrict__ correct_part, int blocks,
                                        float* __restrict__ acc) {
@@ -332,6 +336,15 @@ int b2_launch_sgd_apply(float* params, const float* grads, long P, float lr, flo
   if (blocks < 1) blocks = 1;
   sgd_apply_kernel<<<(int)blocks, 256, 0, s>>>(params, grads, P, lr, loss_trace, correct_trace,
                                                global_step);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_launch_scale(float* p, long n, float a, int sm_count, cudaStream_t s) {
+  long blocks = (n + 255) / 256;
+  if (blocks > 8L * sm_count) blocks = 8L * sm_count;
+  if (blocks < 1) blocks = 1;
+  scale_kernel<<<(int)blocks, 256, 0, s>>>(p, n, a);
   B2_LAUNCH_CHECK();
   return B2_OK;
 }

@@ -157,6 +157,11 @@ class DenseTrainer:
         assert len(blob) == self.nranks * _ffi.PEER_HANDLE_BYTES
         _ffi.check(self._lib, self._lib.b2_peer_import(self._h, ctypes.create_string_buffer(blob, len(blob))))
 
+    def set_async_period(self, k):
+        """k > 0: emulate the reference's asynchronous parameter-server training (local updates, replicas averaged
+        every k steps; distributed.py:107-113).  0: synchronous all-reduce (default)."""
+        self.set_option(_ffi.OPT_ASYNC_PERIOD, int(k))
+
     def use_peer_exchange(self, on=True):
         self.set_option(_ffi.OPT_NO_PEER_EXCHANGE, 0 if on else 1)
 

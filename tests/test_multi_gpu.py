@@ -35,6 +35,8 @@ tr.set_params(Ws, bs)
 uid = [b2.DenseTrainer.new_unique_id() if rank == 0 else None]
 dist.broadcast_object_list(uid, src=0)
 tr.init_comm(rank, world, uid[0])
+if %(async_k)d:
+    tr.set_async_period(%(async_k)d)
 if %(peer)d:
     hs = [None] * world
     dist.all_gather_object(hs, tr.peer_export())
@@ -59,7 +61,7 @@ def test_n_rank_trace_equals_single_process_oracle(cuda_device, tmp_path, dims, 
         pytest.skip("needs at least 2 GPUs")
     lb, steps = 96, 12
     script = tmp_path / "worker.py"
-    script.write_text(WORKER % dict(root=ROOT, dims=dims, act=act, scaled=scaled, lb=lb, steps=steps, out=str(tmp_path), peer=peer, prec=prec))
+    script.write_text(WORKER % dict(root=ROOT, dims=dims, act=act, scaled=scaled, lb=lb, steps=steps, out=str(tmp_path), peer=peer, prec=prec, async_k=0))
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % world,
                         "--master-addr", "127.0.0.1", "--master-port", "29611", str(script)],
                        capture_output=True, text=True, timeout=900)
@@ -110,3 +112,35 @@ def test_reference_command_lines_1ps_2workers(cuda_device):
         want.append(float(lo))
     for got, w in zip(costs[0], want):
         assert abs(float(got) - w) <= 1e-4 + 1e-5 * w
+
+
+@pytest.mark.parametrize("period", [1, 4])
+def test_async_emulation_mode(cuda_device, tmp_path, period):
+    """distributed.py:107-113 trains asynchronously (SyncReplicas is commented out).  The emulation lets every rank apply
+    its own gradients and averages the replicas every `period` steps: with period 1 that IS the synchronous update
+    (mean of the per-rank mean gradients), with a longer period the replicas drift but re-converge at every average."""
+    world = min(torch.cuda.device_count(), 2)
+    if world < 2:
+        pytest.skip("needs at least 2 GPUs")
+    dims, act, scaled, lb, steps = [784, 100, 10], 1, False, 64, 8
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER % dict(root=ROOT, dims=dims, act=act, scaled=scaled, lb=lb, steps=steps, out=str(tmp_path),
+                                    peer=0, prec="fp32", async_k=period))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % world,
+                        "--master-addr", "127.0.0.1", "--master-port", "29613", str(script)],
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-3000:]
+    outs = [np.load(tmp_path / ("rank%d.npz" % r_)) for r_ in range(world)]
+    np.testing.assert_array_equal(outs[0]["W0"], outs[1]["W0"])       # steps is a multiple of the period: just averaged
+    assert outs[0]["gs"] == np.float32(steps * world)                  # global_step counts every worker's update
+    gb = lb * world
+    x, y = synthetic.make_pool(gb * steps)
+    Ws, bs = synthetic.make_weights(dims, scaled)
+    g = oracle.TF1Graph(dims, act, oracle.LOSS_SOFTMAX_CE, Ws, bs)
+    for s in range(steps):
+        g.train_step(x[s * gb:(s + 1) * gb], y[s * gb:(s + 1) * gb], 0.001)
+    diff = np.abs(outs[0]["W0"] - g.W[0]).max()
+    if period == 1:
+        assert diff <= 1e-5 * max(1.0, float(np.abs(g.W[0]).max()))    # same update as synchronous data parallelism
+    else:
+        assert 0 < diff < 1e-2                                          # drifted, but still the same training run
