@@ -128,20 +128,16 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
 
   if (warp == P_WARP) {
     // =============================== P: producer ===============================
-    if (lane == 0) {
-      for (int s = 0; s < NSTAGES; ++s) {
-        mbar_init(&sm.full[s], 1);
-        mbar_init(&sm.empty[s], G_WARPS);
-      }
-      for (int b = 0; b < NBUF; ++b) {
-        mbar_init(&sm.part_full[b], F_WARPS);
-        mbar_init(&sm.part_empty[b], 1);
-        mbar_init(&sm.dz_full[b], 1);
-        mbar_init(&sm.dz_empty[b], G_WARPS);
-      }
-      mbar_init(&sm.w_full, 1);
-      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
+    // one barrier per lane, initialised in parallel
+    if (lane < NSTAGES) mbar_init(&sm.full[lane], 1);
+    else if (lane < 2 * NSTAGES) mbar_init(&sm.empty[lane - NSTAGES], G_WARPS);
+    else if (lane < 2 * NSTAGES + NBUF) mbar_init(&sm.part_full[lane - 2 * NSTAGES], F_WARPS);
+    else if (lane < 2 * NSTAGES + 2 * NBUF) mbar_init(&sm.part_empty[lane - 2 * NSTAGES - NBUF], 1);
+    else if (lane < 2 * NSTAGES + 3 * NBUF) mbar_init(&sm.dz_full[lane - 2 * NSTAGES - 2 * NBUF], 1);
+    else if (lane < 2 * NSTAGES + 4 * NBUF) mbar_init(&sm.dz_empty[lane - 2 * NSTAGES - 3 * NBUF], G_WARPS);
+    else if (lane == 2 * NSTAGES + 4 * NBUF) mbar_init(&sm.w_full, 1);
+    static_assert(2 * NSTAGES + 4 * NBUF + 1 <= 32, "one lane per barrier");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncwarp();
     asm volatile("bar.arrive 2, %0;" ::"n"(THREADS) : "memory");  // barriers are live
     const bool w_bulk = (reinterpret_cast<uintptr_t>(Wg) & 15u) == 0;
@@ -388,9 +384,11 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
         }
         if (lane == 0) mbar_arrive(&sm.dz_empty[buf]);
       }
-      // per-CTA weight-gradient partial: rows 4kg..4kg+3 and 392+4kg.. of dW[784][10], classes 5h..5h+4
+      // per-CTA weight-gradient partial: rows 4kg..4kg+3 and 392+4kg.. of dW[784][10], classes 5h..5h+4.
+      // Staged through the weight tile's shared memory (the forward team has finished with it: the last
+      // backward tile depends on the last forward tile) so that the global write below is fully coalesced.
       if (active) {
-        float* out = scratch + (size_t)blockIdx.x * SCRATCH_STRIDE + 5 * h;
+        float* out = sm.W + 5 * h;
 #pragma unroll
         for (int a = 0; a < 4; ++a) {
           const int k0 = (a < 2 ? 4 * kg : K / 2 + 4 * kg) + 2 * (a & 1);
@@ -398,14 +396,19 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
           for (int c = 0; c < 5; ++c) {
             float lo, hi;
             unpack2(gacc[a][c], lo, hi);
-            out[(size_t)k0 * NC + c] = lo;
-            out[(size_t)(k0 + 1) * NC + c] = hi;
+            out[k0 * NC + c] = lo;
+            out[(k0 + 1) * NC + c] = hi;
           }
         }
       }
     }
   }
   __syncthreads();
+  {
+    float4* dst = reinterpret_cast<float4*>(scratch + (size_t)blockIdx.x * SCRATCH_STRIDE);
+    const float4* src = reinterpret_cast<const float4*>(sm.W);
+    for (int i = tid; i < K * NC / 4; i += THREADS) dst[i] = src[i];
+  }
   // bias gradient, loss, correct count: fixed-order sums over the head warp's lanes
   if (tid < NC) {
     const int half = tid / 5, cc = tid - 5 * half;
