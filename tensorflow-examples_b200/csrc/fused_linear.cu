@@ -102,6 +102,11 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
       "l"(src), "r"(bytes), "r"(smem_u32(bar))
       : "memory");
 }
+// Programmatic dependent launch: the kernel may start while its predecessor on the stream is still running
+// (launch latency and prologue overlap); pdl_wait() blocks until the predecessor's writes are visible.  Both
+// are no-ops when the kernel was launched without the attribute.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 // packed fp32x2 FMA (SASS FFMA2): d.lo = a.lo*b.lo + c.lo, d.hi = a.hi*b.hi + c.hi
 __device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c) {
   u64 d;
@@ -125,9 +130,12 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int ntiles = (rows + TILE_ROWS - 1) / TILE_ROWS;
+  pdl_launch_dependents();   // the reduction kernel may be queued now; it waits for this grid before reading scratch
 
   if (warp == P_WARP) {
     // =============================== P: producer ===============================
+    // x and y do not depend on the previous step, so their loads start right away; W and b (updated by the
+    // previous step's reduce + SGD kernel) are only touched after pdl_wait().
     // one barrier per lane, initialised in parallel
     if (lane < NSTAGES) mbar_init(&sm.full[lane], 1);
     else if (lane < 2 * NSTAGES) mbar_init(&sm.empty[lane - NSTAGES], G_WARPS);
@@ -140,21 +148,27 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncwarp();
     asm volatile("bar.arrive 2, %0;" ::"n"(THREADS) : "memory");  // barriers are live
-    const bool w_bulk = (reinterpret_cast<uintptr_t>(Wg) & 15u) == 0;
-    if (w_bulk) {
-      if (lane == 0) {
-        bulk_g2s(sm.W, Wg, K * NC * 4, &sm.w_full);
-        mbar_arrive_expect_tx(&sm.w_full, K * NC * 4);
-      }
-    } else {
-      for (int i = lane; i < K * NC; i += 32) sm.W[i] = Wg[i];
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&sm.w_full);
-    }
     const bool y_aligned = (reinterpret_cast<uintptr_t>(y_) & 15u) == 0;
+    const bool w_bulk = (reinterpret_cast<uintptr_t>(Wg) & 15u) == 0;
+    bool w_issued = false;
+    auto issue_w = [&]() {
+      pdl_wait();                                            // W was written by the previous step's kernels
+      if (w_bulk) {
+        if (lane == 0) {
+          bulk_g2s(sm.W, Wg, K * NC * 4, &sm.w_full);
+          mbar_arrive_expect_tx(&sm.w_full, K * NC * 4);
+        }
+      } else {
+        for (int i = lane; i < K * NC; i += 32) sm.W[i] = Wg[i];
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.w_full);
+      }
+      w_issued = true;
+    };
     int n = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       for (int q = 0; q < STAGES_PER_TILE; ++q, ++n) {
+        if (n == STAGES_PER_TILE && !w_issued) issue_w();   // first tile's rows are in flight: now fetch the weights
         const int slot = n % NSTAGES;
         const uint32_t phase = (uint32_t)(n / NSTAGES) & 1u;
         mbar_wait(&sm.empty[slot], phase ^ 1u);
@@ -180,6 +194,7 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
           mbar_arrive_expect_tx(&sm.full[slot], (uint32_t)(nrows * ROW_BYTES + (y_bulk ? nrows * NC * 4 : 0)));
       }
     }
+    if (!w_issued) issue_w();
   } else {
     asm volatile("bar.sync 2, %0;" ::"n"(THREADS) : "memory");
 
@@ -256,6 +271,7 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
       float db[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
       float loss_acc = 0.f, corr_acc = 0.f;
       float bias5[5];
+      pdl_wait();                                            // b was written by the previous step's kernels
 #pragma unroll
       for (int cc = 0; cc < 5; ++cc) bias5[cc] = bg[5 * half + cc];
       int i_t = 0;
@@ -404,6 +420,7 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
     }
   }
   __syncthreads();
+  pdl_wait();   // the previous reduction kernel must have finished reading scratch before it is overwritten
   {
     float4* dst = reinterpret_cast<float4*>(scratch + (size_t)blockIdx.x * SCRATCH_STRIDE);
     const float4* src = reinterpret_cast<const float4*>(sm.W);
@@ -437,6 +454,8 @@ fused_linear_reduce_kernel(const float* __restrict__ scratch, int grid, float* _
                            float* __restrict__ loss_trace, int* __restrict__ correct_trace,
                            float* __restrict__ global_step, long P) {
   __shared__ float sh[RED_Q][RED_OUT];
+  pdl_launch_dependents();   // the next step kernel may start its prologue and its x loads
+  pdl_wait();                // the step kernel's partials must be complete and visible
   const int o = threadIdx.x & (RED_OUT - 1), q = threadIdx.x / RED_OUT;
   const int i = blockIdx.x * RED_OUT + o;
   const int per = (grid + RED_Q - 1) / RED_Q;
@@ -494,9 +513,18 @@ int b2_launch_fused_linear_step(const float* x, const float* y, int rows, const 
                                 const float* b, float* scratch, int grid, float inv_global_batch,
                                 cudaStream_t s) {
   const int smem = (int)sizeof(fl::Smem);
-  fl::fused_linear_step_kernel<<<grid, fl::THREADS, smem, s>>>(x, y, rows, W, b, scratch,
-                                                               inv_global_batch);
-  cudaError_t e = cudaGetLastError();
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(fl::THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, fl::fused_linear_step_kernel, x, y, rows, W, b, scratch, inv_global_batch);
   if (e != cudaSuccess) {
     b2_set_error("fused_linear_step launch failed: %s", cudaGetErrorString(e));
     return B2_ERR_CUDA;
@@ -507,9 +535,18 @@ int b2_launch_fused_linear_step(const float* x, const float* y, int rows, const 
 int b2_launch_fused_linear_reduce(const float* scratch, int grid, float* grads, float* params,
                                   int apply, float lr, float* loss_trace, int* correct_trace,
                                   float* global_step, long P, cudaStream_t s) {
-  fl::fused_linear_reduce_kernel<<<(fl::RED_N + fl::RED_OUT - 1) / fl::RED_OUT, fl::RED_OUT * fl::RED_Q, 0, s>>>(
-      scratch, grid, grads, params, apply, lr, loss_trace, correct_trace, global_step, P);
-  cudaError_t e = cudaGetLastError();
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((fl::RED_N + fl::RED_OUT - 1) / fl::RED_OUT);
+  cfg.blockDim = dim3(fl::RED_OUT * fl::RED_Q);
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, fl::fused_linear_reduce_kernel, (const float*)scratch, grid, grads, params, apply,
+                                     lr, loss_trace, correct_trace, global_step, P);
   if (e != cudaSuccess) {
     b2_set_error("fused_linear_reduce launch failed: %s", cudaGetErrorString(e));
     return B2_ERR_CUDA;
