@@ -32,6 +32,10 @@ __global__ void __launch_bounds__(256)
 peer_allreduce_apply_kernel(b2_peer_args a, float* __restrict__ params, float* __restrict__ grads_out, long P,
                             unsigned step1, int buf, float lr, float* __restrict__ loss_trace,
                             int* __restrict__ correct_trace, float* __restrict__ global_step) {
+  // programmatic dependent launch: the next step kernel may start its prologue and its x loads now; this kernel
+  // itself may have been started early and waits here for the reduction kernel that wrote my vector
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   // publish: my vector for this step was written by the previous kernel on this stream
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     __threadfence_system();
@@ -72,9 +76,18 @@ int b2_launch_peer_allreduce_apply(const b2_peer_args& a, float* params, float* 
   long blocks = (P + 2 + 255) / 256;
   if (blocks > 2L * sm_count) blocks = 2L * sm_count;   // all blocks resident: they spin on remote flags
   if (blocks < 1) blocks = 1;
-  peer_allreduce_apply_kernel<<<(int)blocks, 256, 0, s>>>(a, params, grads_out, P, step1, buf, lr, loss_trace,
-                                                          correct_trace, global_step);
-  cudaError_t e = cudaGetLastError();
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)blocks);
+  cfg.blockDim = dim3(256);
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, peer_allreduce_apply_kernel, a, params, grads_out, P, step1, buf, lr, loss_trace,
+                                     correct_trace, global_step);
   if (e != cudaSuccess) {
     b2_set_error("peer_allreduce_apply launch failed: %s", cudaGetErrorString(e));
     return B2_ERR_CUDA;
