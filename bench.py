@@ -154,6 +154,8 @@ def main():
     ap.add_argument("--no-secondary", action="store_true",
                     help="skip the second line (scaled-up MLP, c5) that a default 1-GPU run embeds as `secondary`")
     ap.add_argument("--no-peer", action="store_true", help="multi-GPU: use the NCCL all-reduce instead of the peer-memory kernel")
+    ap.add_argument("--no-overlap", action="store_true",
+                    help="multi-GPU bf16 path: one all-reduce after the backward pass instead of overlapped per-layer buckets")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -231,6 +233,10 @@ def main():
             dist.all_gather_object(hs, tr.peer_export())
             tr.peer_import(hs)
         cfg["gradient_exchange"] = "nccl all-reduce + apply" if (args.no_peer or tr.param_count > (1 << 20)) else "one-shot peer-memory all-reduce fused with SGD apply"
+        if precision == "bf16":
+            tr.overlap_exchange(not args.no_overlap)
+            cfg["gradient_exchange"] = ("nccl all-reduce after the backward pass + apply" if args.no_overlap else
+                                        "nccl all-reduce per layer bucket on a second stream, overlapped with the backward pass, + apply")
 
     # ---- value: device-resident pool -----------------------------------------------------
     lt, ct = tr.train_steps(x_pool, y_pool, batch, warmup, first_row=0, lr=LR)

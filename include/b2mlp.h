@@ -53,6 +53,8 @@ enum {
   B2_OPT_FORCE_LAYERED = 1,  /* value 1: never use the single-kernel fused step, even when the shape allows it */
   B2_OPT_KERNEL_TIMING = 2,  /* value 1: bracket every kernel launch with CUDA events (see b2_kernel_times) */
   B2_OPT_NO_PEER_EXCHANGE = 3, /* value 1: use the NCCL all-reduce even when peer memory is mapped (b2_peer_import) */
+  B2_OPT_NO_BUCKET_OVERLAP = 4, /* value 1 (bf16 path, nranks > 1): one all-reduce after the backward pass instead of
+                                 per-layer buckets on a second stream that overlap the remaining backward GEMMs */
   B2_OPT_ASYNC_PERIOD = 5     /* value k > 0: emulate the reference's ASYNCHRONOUS parameter-server training
                                  (distributed.py:107-113: plain GradientDescentOptimizer, SyncReplicas commented out):
                                  every worker applies its own gradients locally (mean over ITS batch) and the replicas'

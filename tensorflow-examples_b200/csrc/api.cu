@@ -34,6 +34,7 @@ typedef int (*pfn_ncclCommInitRank)(void**, int, nccl_uid, int);
 typedef int (*pfn_ncclCommDestroy)(void*);
 typedef int (*pfn_ncclAllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t);
 typedef const char* (*pfn_ncclGetErrorString)(int);
+typedef int (*pfn_ncclGroup)(void);
 struct nccl_api {
   void* handle;
   pfn_ncclGetUniqueId GetUniqueId;
@@ -41,8 +42,9 @@ struct nccl_api {
   pfn_ncclCommDestroy CommDestroy;
   pfn_ncclAllReduce AllReduce;
   pfn_ncclGetErrorString GetErrorString;
+  pfn_ncclGroup GroupStart, GroupEnd;
 };
-nccl_api g_nccl = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+nccl_api g_nccl = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 constexpr int kNcclFloat = 7;  // ncclFloat32
 constexpr int kNcclSum = 0;    // ncclSum
 
@@ -64,8 +66,10 @@ int load_nccl() {
   g_nccl.CommDestroy = (pfn_ncclCommDestroy)dlsym(h, "ncclCommDestroy");
   g_nccl.AllReduce = (pfn_ncclAllReduce)dlsym(h, "ncclAllReduce");
   g_nccl.GetErrorString = (pfn_ncclGetErrorString)dlsym(h, "ncclGetErrorString");
+  g_nccl.GroupStart = (pfn_ncclGroup)dlsym(h, "ncclGroupStart");
+  g_nccl.GroupEnd = (pfn_ncclGroup)dlsym(h, "ncclGroupEnd");
   if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.CommDestroy || !g_nccl.AllReduce ||
-      !g_nccl.GetErrorString) {
+      !g_nccl.GetErrorString || !g_nccl.GroupStart || !g_nccl.GroupEnd) {
     b2_set_error("NCCL library lacks a required symbol");
     return B2_ERR_NCCL;
   }
@@ -288,6 +292,9 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
   if (rc) return rc;
   c->launches++;
   bool colsum_pending = fused_colsum(c, L);   // the bias gradient of layer L-1 sits in colsum_part as 32-row partials
+  const bool exchange = c->nranks > 1 && c->async_period == 0;
+  const bool overlap = exchange && !c->opt_no_overlap && !c->opt_timing && c->comm_stream != nullptr;
+  bool bucketed[B2_MAX_LAYERS] = {};
   int cur = 0;
   for (int l = L - 1; l >= 0; --l) {
     // dz of layer l (bf16 [rows, dims[l+1]]) is in dzb[cur]
@@ -312,6 +319,15 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
     }
     if (rc) return rc;
     c->launches++;
+    if (overlap && l > 0) {
+      // this layer's weight gradient is final -> sum it over the ranks on the second stream while the
+      // dgrad / wgrad GEMMs of the layers below keep the tensor cores busy on this one
+      B2_CUDA(cudaEventRecord(c->ev_bucket, s));
+      B2_CUDA(cudaStreamWaitEvent(c->comm_stream, c->ev_bucket, 0));
+      B2_NCCL(g_nccl.AllReduce(c->grads + c->w_off[l], c->grads + c->w_off[l], (size_t)w_size(c, l), kNcclFloat, kNcclSum,
+                               c->nccl_comm, c->comm_stream));
+      bucketed[l] = true;
+    }
     if (l > 0) {
       // dz_prev = (dz . W^T) * a(1-a)   A = dz K-major [rows, out], B = W [in, out] K-major
       timed_scope t(c, B2_K_GEMM_DGRAD, s);
@@ -342,9 +358,24 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
   }
   if (rc) return rc;
   c->launches++;
-  if (c->nranks > 1 && c->async_period == 0) {
+  if (exchange) {
+    // everything that was not sent as a bucket: the first layer's weights, all biases, the output layer, loss and correct
     timed_scope t(c, B2_K_ALLREDUCE_APPLY, s);
-    B2_NCCL(g_nccl.AllReduce(c->grads, c->grads, (size_t)(c->P + 4), kNcclFloat, kNcclSum, c->nccl_comm, s));
+    B2_NCCL(g_nccl.GroupStart());
+    long from = 0;
+    for (int l = 0; l <= n; ++l) {
+      const bool cut = l < n && bucketed[l];
+      const long to = l == n ? c->P + 4 : (cut ? c->w_off[l] : -1);
+      if (to < 0) continue;
+      if (to > from)
+        B2_NCCL(g_nccl.AllReduce(c->grads + from, c->grads + from, (size_t)(to - from), kNcclFloat, kNcclSum, c->nccl_comm, s));
+      if (cut) from = c->w_off[l] + w_size(c, l);
+    }
+    B2_NCCL(g_nccl.GroupEnd());
+    if (overlap) {
+      B2_CUDA(cudaEventRecord(c->ev_comm_done, c->comm_stream));
+      B2_CUDA(cudaStreamWaitEvent(s, c->ev_comm_done, 0));
+    }
   }
   long off[B2_MAX_LAYERS], size[B2_MAX_LAYERS];
   for (int l = 0; l < L; ++l) { off[l] = c->w_off[l]; size[l] = w_size(c, l); }
@@ -443,6 +474,9 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
 void free_ctx(b2_ctx* c) {
   if (!c) return;
   if (c->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
+  if (c->comm_stream) cudaStreamDestroy(c->comm_stream);
+  if (c->ev_bucket) cudaEventDestroy(c->ev_bucket);
+  if (c->ev_comm_done) cudaEventDestroy(c->ev_comm_done);
   for (int p = 0; p < B2_MAX_PEERS; ++p)
     if (c->peer_base[p] && c->peer_base[p] != (void*)c->peer_local) cudaIpcCloseMemHandle(c->peer_base[p]);
   cudaFree(c->peer_local);
@@ -636,6 +670,7 @@ extern "C" int b2_set_option(b2_ctx* ctx, int option, int value) {
     case B2_OPT_FORCE_LAYERED: ctx->opt_force_layered = value ? 1 : 0; return B2_OK;
     case B2_OPT_KERNEL_TIMING: ctx->opt_timing = value ? 1 : 0; return B2_OK;
     case B2_OPT_NO_PEER_EXCHANGE: ctx->opt_no_peer = value ? 1 : 0; return B2_OK;
+    case B2_OPT_NO_BUCKET_OVERLAP: ctx->opt_no_overlap = value ? 1 : 0; return B2_OK;
     case B2_OPT_ASYNC_PERIOD:
       B2_CHECK_ARG(value >= 0, "b2_set_option: async period must be >= 0");
       ctx->async_period = value;
@@ -741,6 +776,11 @@ extern "C" int b2_comm_init(b2_ctx* ctx, int rank, int nranks, const void* uniqu
     b2_set_error("ncclCommInitRank failed: %s", g_nccl.GetErrorString(r));
     ctx->nccl_comm = nullptr; ctx->rank = 0; ctx->nranks = 1;
     return B2_ERR_NCCL;
+  }
+  if (is_mixed(ctx)) {
+    B2_CUDA(cudaStreamCreateWithFlags(&ctx->comm_stream, cudaStreamNonBlocking));
+    B2_CUDA(cudaEventCreateWithFlags(&ctx->ev_bucket, cudaEventDisableTiming));
+    B2_CUDA(cudaEventCreateWithFlags(&ctx->ev_comm_done, cudaEventDisableTiming));
   }
   return B2_OK;
 }

@@ -83,6 +83,10 @@ struct b2_ctx {
   int async_period;                // B2_OPT_ASYNC_PERIOD (0 = synchronous)
   long async_count;                // local steps since the context was created
   unsigned peer_step;              // exchanges enqueued so far
+  // bucketed all-reduce of the wide layers' weight gradients, overlapped with the rest of the backward pass
+  cudaStream_t comm_stream;        // created by b2_comm_init when nranks > 1
+  cudaEvent_t ev_bucket, ev_comm_done;
+  int opt_no_overlap;              // B2_OPT_NO_BUCKET_OVERLAP
 
   // bf16-operand / fp32-accumulate path (precision == B2_PREC_BF16_FP32ACC): tensor-core GEMMs for the hidden layers
   void* xb;                        // [max_local_batch, dims[0]] bf16 copy of the step's inputs

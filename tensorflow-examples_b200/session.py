@@ -165,6 +165,11 @@ class DenseTrainer:
     def use_peer_exchange(self, on=True):
         self.set_option(_ffi.OPT_NO_PEER_EXCHANGE, 0 if on else 1)
 
+    def overlap_exchange(self, on=True):
+        """bf16 path, several ranks: all-reduce each wide layer's weight gradient on a second stream while the backward
+        pass of the layers below it runs (default), or send everything in one all-reduce after the backward pass."""
+        self.set_option(_ffi.OPT_NO_BUCKET_OVERLAP, 0 if on else 1)
+
     # -- the hot path ---------------------------------------------------------------------------
     def train_steps(self, x_pool, y_pool, local_batch, n_steps, first_row=0, lr=0.001,
                     loss_trace=None, correct_trace=None):
