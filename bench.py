@@ -141,6 +141,109 @@ def cpu_reference_run(dims, act, loss, scaled, batch, steps, warmup, budget_s=No
             "first_loss": losses[0], "ms_per_step": 1e3 * dt / done}
 
 
+# ---- batch-size sweep / strong scaling: `bench.py --sweep` --------------------
+SWEEP_POINTS = {
+    # name: (dims, act, loss, scaled init, precision, flop/sample)
+    "c3": ([784, 10], 0, 1, True, "fp32", 31360),
+    "c3-sse": ([784, 10], 0, 0, True, "fp32", 31360),          # simple.py's SSE-sum head on the same layer
+    "c2": ([784, 100, 10], 1, 1, False, "fp32", 319600),
+}
+FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.92e9 / 1e12               # 148 SMs x 128 FMA lanes x 2 flop x 1.92 GHz (spec-derived)
+
+
+def cpu_numpy_run(dims, act, loss, scaled, batch, budget_s):
+    from oracle.tf1_graph import TF1Graph
+    from tensorflow_examples_b200 import synthetic
+    x, y = synthetic.make_pool(2 * batch)
+    Ws, bs = synthetic.make_weights(dims, scaled)
+    g = TF1Graph(dims, act, loss, Ws, bs)
+    g.train_step(x[:batch], y[:batch], LR)
+    t0, done = time.perf_counter(), 0
+    while done < 50 and time.perf_counter() - t0 < budget_s:
+        o = (done % 2) * batch
+        g.train_step(x[o:o + batch], y[o:o + batch], LR)
+        done += 1
+    return batch * done / (time.perf_counter() - t0), done
+
+
+def sweep_main(args):
+    """For every (workload, batch) point: `steps` training steps over a device-resident pool, CUDA events on the launch
+    stream after `warmup` untimed steps, max over ranks; samples/s, the fraction of the HBM ceiling (3176 B/sample over
+    the measured copy bandwidth) and of the spec-derived CUDA-core fp32 ceiling.  --sweep-cpu times the torch-CPU and
+    numpy restatements beside it (rank 0).  Points below B ~ 16384 are launch-latency bound."""
+    import torch
+    import tensorflow_examples_b200 as pkg
+    from tensorflow_examples_b200 import synthetic
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    peak_gbs, _ = _peaks()
+    batches = [int(b) for b in args.sweep_batches.split(",")]
+    hx, hy = synthetic.make_pool(HOST_POOL_ROWS)
+    pool_rows = max(2 * max(batches) * (1 if args.strong else world), 1 << 19)
+    reps = (pool_rows + HOST_POOL_ROWS - 1) // HOST_POOL_ROWS
+    x_pool = torch.from_numpy(hx).to(dev).repeat(reps, 1)[:pool_rows].contiguous()
+    y_pool = torch.from_numpy(hy).to(dev).repeat(reps, 1)[:pool_rows].contiguous()
+    rows_out = []
+    for name in args.sweep_points.split(","):
+        dims, act, loss, scaled, prec, flops = SWEEP_POINTS[name]
+        for B in batches:
+            local = B // world if args.strong else B
+            if local < 1 or (args.strong and B % world):
+                continue
+            gb = local * world
+            tr = pkg.DenseTrainer(dims, act, loss, max_local_batch=local, device=local_rank, precision=prec)
+            tr.set_params(*synthetic.make_weights(dims, scaled))
+            if world > 1:
+                uid = [pkg.DenseTrainer.new_unique_id() if rank == 0 else None]
+                dist.broadcast_object_list(uid, src=0)
+                tr.init_comm(rank, world, uid[0])
+                hs = [None] * world
+                dist.all_gather_object(hs, tr.peer_export())
+                tr.peer_import(hs)
+            lt, _ = tr.train_steps(x_pool, y_pool, local, args.warmup, first_row=0, lr=LR)
+            torch.cuda.synchronize(dev)
+            if dist is not None:
+                dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            lt, _ = tr.train_steps(x_pool, y_pool, local, args.steps, first_row=(args.warmup * gb) % pool_rows, lr=LR)
+            e1.record()
+            torch.cuda.synchronize(dev)
+            ms = e0.elapsed_time(e1)
+            if dist is not None:
+                t = torch.tensor([ms], dtype=torch.float64, device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms = float(t.item())
+            sps = gb * args.steps / (ms / 1e3)
+            row = {"point": name, "dims": dims, "head": "sse-sum" if loss == 0 else "softmax-ce-mean", "n_gpus": world,
+                   "scaling": "strong" if args.strong else "weak", "global_batch": gb, "local_batch": local,
+                   "us_per_step": 1e3 * ms / args.steps, "samples_per_s": sps,
+                   "hbm_frac": sps / world * BYTES_PER_SAMPLE / (peak_gbs * 1e9),
+                   "fp32_frac": sps / world * flops / (FP32_PEAK_TFLOPS * 1e12), "last_loss": float(lt[args.steps - 1].item())}
+            if args.sweep_cpu and rank == 0:
+                r = cpu_reference_run(dims, act, loss, scaled, gb, 50, 2, budget_s=4.0)
+                row["cpu_torch_samples_per_s"], row["cpu_threads"] = r["value"], r["threads"]
+                row["cpu_numpy_samples_per_s"], _ = cpu_numpy_run(dims, act, loss, scaled, gb, 4.0)
+            tr.close()
+            if rank == 0:
+                rows_out.append(row)
+                print(json.dumps(row), flush=True)
+    if rank == 0:
+        os.makedirs(os.path.dirname(os.path.abspath(args.sweep_out)), exist_ok=True)
+        json.dump({"hbm_peak_gbs": peak_gbs, "fp32_peak_tflops_spec": FP32_PEAK_TFLOPS, "steps": args.steps,
+                   "warmup": args.warmup, "cpu_count": os.cpu_count(), "rows": rows_out}, open(args.sweep_out, "w"), indent=1)
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -156,7 +259,15 @@ def main():
     ap.add_argument("--no-peer", action="store_true", help="multi-GPU: use the NCCL all-reduce instead of the peer-memory kernel")
     ap.add_argument("--no-overlap", action="store_true",
                     help="multi-GPU bf16 path: one all-reduce after the backward pass instead of overlapped per-layer buckets")
+    ap.add_argument("--sweep", action="store_true", help="batch-size sweep of c3 / c3 with the SSE head / 784-100-10 instead of the headline line")
+    ap.add_argument("--sweep-out", default=os.path.join(ROOT, "gpurun_out", "sweep.json"))
+    ap.add_argument("--sweep-points", default="c3,c3-sse,c2")
+    ap.add_argument("--sweep-batches", default="256,1024,4096,16384,65536")
+    ap.add_argument("--sweep-cpu", action="store_true", help="sweep: also time the CPU restatements on rank 0")
+    ap.add_argument("--strong", action="store_true", help="sweep: the batch is the GLOBAL batch, split over the ranks")
     args = ap.parse_args()
+    if args.sweep:
+        return sweep_main(args)
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -55,6 +55,10 @@ enum {
   B2_OPT_NO_PEER_EXCHANGE = 3, /* value 1: use the NCCL all-reduce even when peer memory is mapped (b2_peer_import) */
   B2_OPT_NO_BUCKET_OVERLAP = 4, /* value 1 (bf16 path, nranks > 1): one all-reduce after the backward pass instead of
                                  per-layer buckets on a second stream that overlap the remaining backward GEMMs */
+  B2_OPT_NO_SPLIT3 = 6,      /* value 1 (fp32): keep the wide layers' GEMMs on the CUDA cores instead of the fp32-accurate
+                                 three-plane bf16 split on the tensor cores (gemm_split3.cu) */
+  B2_OPT_NO_NARROW_HEAD = 7, /* value 1 (fp32, >= 2 layers): run the output layer as separate forward / loss-head / wgrad /
+                                 dgrad kernels instead of the single narrow-head kernel (narrow_head.cu) */
   B2_OPT_ASYNC_PERIOD = 5     /* value k > 0: emulate the reference's ASYNCHRONOUS parameter-server training
                                  (distributed.py:107-113: plain GradientDescentOptimizer, SyncReplicas commented out):
                                  every worker applies its own gradients locally (mean over ITS batch) and the replicas'

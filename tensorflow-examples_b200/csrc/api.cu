@@ -119,18 +119,38 @@ bool use_fused_linear(const b2_ctx* c) {
          b2_fused_linear_supported(c->dims[0], c->dims[1], c->loss);
 }
 
+inline int round8(int v) { return (v + 7) & ~7; }
+// a wide fp32 layer goes to the tensor cores (three-plane split) once the batch is large enough to fill them
+inline bool use_split3(const b2_ctx* c, int l, int rows) {
+  return c->s3_in[l] != nullptr && !c->opt_no_split3 && rows >= 1024;
+}
+
+// the output layer (forward, loss head and its whole backward) as one kernel when it is narrow enough (narrow_head.cu)
+inline bool use_narrow_head(const b2_ctx* c) {
+  const int n = c->n_layers;
+  return c->precision == B2_PREC_FP32 && n >= 2 && !c->opt_no_narrow_head && b2_narrow_head_applies(c->dims[n - 1], c->dims[n]);
+}
+
 // Enqueue forward + loss head (+ backward partials) for `rows` rows.  train == 0: forward and head only.
 int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float inv_B, int train,
                     int* splits_used, cudaStream_t s) {
   const int n = c->n_layers;
   const float* a_in = x;
-  for (int l = 0; l < n; ++l) {
+  const bool narrow = use_narrow_head(c);
+  for (int l = 0; l < (narrow ? n - 1 : n); ++l) {
     float* out = (l == n - 1) ? c->z_last : c->act_buf[l];
     int rc;
     {
       timed_scope t(c, B2_K_DENSE_FWD, s);
       const int act_l = (l == n - 1) ? B2_ACT_IDENTITY : c->act;
-      if (b2_small_m_fwd_applies(rows, c->dims[l]))
+      if (use_split3(c, l, rows)) {
+        const int K = c->dims[l], N = c->dims[l + 1], ldn = round8(N);
+        rc = b2_launch_split3(a_in, c->s3_in[l], rows, K, K, K, (long)c->max_local_batch * K, c->sm_count, s);
+        if (!rc) rc = b2_launch_split3(c->params + c->w_off[l], c->s3_w[l], K, N, N, ldn, (long)K * ldn, c->sm_count, s);
+        if (!rc) rc = b2_launch_gemm_split3(c->s3_in[l], 0, K, (long)c->max_local_batch * K, c->s3_w[l], 1, ldn, (long)K * ldn,
+                                            rows, N, K, 0, act_l, c->params + c->b_off[l], out, N, 1, 0, c->sm_count, s);
+        c->launches += 2;
+      } else if (b2_small_m_fwd_applies(rows, c->dims[l]))
         rc = b2_launch_small_m_fwd(a_in, c->params + c->w_off[l], c->params + c->b_off[l], out, rows, c->dims[l + 1],
                                    c->dims[l], act_l, s);
       else
@@ -143,28 +163,59 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
   }
   float* head = c->scratch + c->head_part_off;
   int rc;
-  {
+  int cur = 0, l_top = n - 1;
+  if (narrow) {
+    // forward, loss head, dW / db partials and dz of the layer below, all from one pass over the activations
+    const int L = n - 1;
+    const int grid = b2_narrow_head_grid(rows, c->sm_count);
+    float* pw = c->scratch + c->part_off[L];
+    timed_scope t(c, B2_K_LOSS_HEAD, s);
+    rc = b2_launch_narrow_head(a_in, y, c->params + c->w_off[L], c->params + c->b_off[L], c->dz[1], pw,
+                               pw + round4(w_size(c, L)), part_stride(c, L), head, head + c->head_blocks, rows, c->dims[L],
+                               c->dims[n], c->act, c->loss, train, inv_B, grid, s);
+    c->head_used = grid;
+    if (train) splits_used[L] = grid;
+    cur = 1;
+    l_top = L - 1;
+  } else {
     timed_scope t(c, B2_K_LOSS_HEAD, s);
     rc = b2_launch_loss_head(c->z_last, y, c->dz[0], head, head + c->head_blocks, rows, c->dims[n],
                              c->loss, inv_B, c->head_blocks, s);
+    c->head_used = c->head_blocks;
   }
   if (rc) return rc;
   c->launches++;
   if (!train) return B2_OK;
-  int cur = 0;
-  for (int l = n - 1; l >= 0; --l) {
+  for (int l = l_top; l >= 0; --l) {
     const float* a_prev = (l == 0) ? x : c->act_buf[l - 1];
     int sp = c->splits[l];
     const int max_sp = (rows + 63) / 64;
     if (sp > max_sp) sp = max_sp;
+    if (use_split3(c, l, rows)) {
+      // 128 x 128 tensor-core tiles: about two K slices per SM are enough to balance the persistent grid
+      const int tiles = ((c->dims[l] + 127) / 128) * ((c->dims[l + 1] + 127) / 128);
+      const int want = (2 * c->sm_count + tiles - 1) / tiles;
+      if (sp > want) sp = want;
+    }
     if (sp < 1) sp = 1;
     splits_used[l] = sp;
     float* pw = c->scratch + c->part_off[l];
     float* pb = pw + round4(w_size(c, l));
     {
       timed_scope t(c, B2_K_WGRAD, s);
-      rc = b2_launch_sgemm_wgrad(a_prev, c->dz[cur], pw, pb, part_stride(c, l), rows, c->dims[l],
-                                 c->dims[l + 1], sp, s);
+      if (use_split3(c, l, rows)) {
+        // the input planes are still there from the forward pass; dz is split here, its column sums are the bias gradient
+        const int K = c->dims[l], N = c->dims[l + 1], ldn = round8(N);
+        const long dzp = (long)c->max_local_batch * ldn;
+        rc = b2_launch_split3(c->dz[cur], c->s3_dz, rows, N, N, ldn, dzp, c->sm_count, s);
+        if (!rc) rc = b2_launch_colsum_f32(c->dz[cur], pb, part_stride(c, l), rows, N, sp, s);
+        if (!rc) rc = b2_launch_gemm_split3(c->s3_in[l], 1, K, (long)c->max_local_batch * K, c->s3_dz, 1, ldn, dzp, K, N, rows,
+                                            1, 0, nullptr, pw, N, sp, part_stride(c, l), c->sm_count, s);
+        c->launches += 2;
+      } else {
+        rc = b2_launch_sgemm_wgrad(a_prev, c->dz[cur], pw, pb, part_stride(c, l), rows, c->dims[l],
+                                   c->dims[l + 1], sp, s);
+      }
     }
     if (rc) return rc;
     c->launches++;
@@ -351,6 +402,7 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
   a.P = c->P;
   a.head_part_off = c->head_part_off;
   a.head_blocks = c->head_blocks;
+  a.head_corr_off = c->head_part_off + c->head_blocks;
   {
     timed_scope t(c, B2_K_REDUCE_APPLY, s);
     rc = b2_launch_reduce(a, c->scratch, c->grads, c->params, 0, lr, nullptr, nullptr, c->global_step_dev,
@@ -433,7 +485,8 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
     }
     a.P = c->P;
     a.head_part_off = c->head_part_off;
-    a.head_blocks = c->head_blocks;
+    a.head_blocks = c->head_used;
+    a.head_corr_off = c->head_part_off + c->head_blocks;
     {
       timed_scope t(c, B2_K_REDUCE_APPLY, s);
       rc = b2_launch_reduce(a, c->scratch, gvec, c->params, apply, lr, loss_trace, correct_trace,
@@ -480,6 +533,8 @@ void free_ctx(b2_ctx* c) {
   for (int p = 0; p < B2_MAX_PEERS; ++p)
     if (c->peer_base[p] && c->peer_base[p] != (void*)c->peer_local) cudaIpcCloseMemHandle(c->peer_base[p]);
   cudaFree(c->peer_local);
+  for (int l = 0; l < B2_MAX_LAYERS; ++l) { cudaFree(c->s3_in[l]); cudaFree(c->s3_w[l]); }
+  cudaFree(c->s3_dz);
   cudaFree(c->xb);
   for (int l = 0; l < B2_MAX_LAYERS; ++l) { cudaFree(c->ab[l]); cudaFree(c->wb[l]); }
   cudaFree(c->dzb[0]);
@@ -579,6 +634,10 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
       // only the narrow output layer writes partials (the GEMMs store dW directly)
       sp = (l == n_layers - 1) ? 16 : 0;   // narrow_slices() never exceeds 16
     }
+    if (precision == B2_PREC_FP32 && n_layers >= 2 && l == n_layers - 1 && b2_narrow_head_applies(dims[l], dims[l + 1])) {
+      const long g = b2_narrow_head_grid(max_local_batch, c->sm_count);   // one partial per CTA of the narrow-head kernel
+      if (sp < g) sp = g;
+    }
     c->splits[l] = (int)sp;
     c->part_off[l] = soff;
     soff += sp * part_stride(c, l);
@@ -629,6 +688,15 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
     c->wb_stale = 1;
   } else {
     for (int l = 0; l < n_layers - 1; ++l) B2_ALLOC(c->act_buf[l], (long)max_local_batch * dims[l + 1]);
+    // wide layers (K >= 256, N >= 32) get three-plane bf16 copies for the tensor-core path; floats = 3 planes * elements / 2
+    long s3_ldn = 0;
+    for (int l = 0; l < n_layers && max_local_batch >= 1024; ++l) {
+      if (dims[l] < 256 || dims[l] % 8 || dims[l + 1] < 32) continue;
+      B2_ALLOC(c->s3_in[l], 3L * max_local_batch * dims[l] / 2 + 8);
+      B2_ALLOC(c->s3_w[l], 3L * dims[l] * round8(dims[l + 1]) / 2 + 8);
+      if (round8(dims[l + 1]) > s3_ldn) s3_ldn = round8(dims[l + 1]);
+    }
+    if (s3_ldn) B2_ALLOC(c->s3_dz, 3L * max_local_batch * s3_ldn / 2 + 8);
     B2_ALLOC(c->dz[0], (long)max_local_batch * maxw);
     if (n_layers > 1) B2_ALLOC(c->dz[1], (long)max_local_batch * maxw);
   }
@@ -670,6 +738,8 @@ extern "C" int b2_set_option(b2_ctx* ctx, int option, int value) {
     case B2_OPT_FORCE_LAYERED: ctx->opt_force_layered = value ? 1 : 0; return B2_OK;
     case B2_OPT_KERNEL_TIMING: ctx->opt_timing = value ? 1 : 0; return B2_OK;
     case B2_OPT_NO_PEER_EXCHANGE: ctx->opt_no_peer = value ? 1 : 0; return B2_OK;
+    case B2_OPT_NO_NARROW_HEAD: ctx->opt_no_narrow_head = value ? 1 : 0; return B2_OK;
+    case B2_OPT_NO_SPLIT3: ctx->opt_no_split3 = value ? 1 : 0; return B2_OK;
     case B2_OPT_NO_BUCKET_OVERLAP: ctx->opt_no_overlap = value ? 1 : 0; return B2_OK;
     case B2_OPT_ASYNC_PERIOD:
       B2_CHECK_ARG(value >= 0, "b2_set_option: async period must be >= 0");
@@ -902,7 +972,8 @@ extern "C" int b2_eval(b2_ctx* ctx, const void* x_dev, const void* y_dev, long r
                            : enqueue_layered(ctx, xp + r0 * in, yp + r0 * outd, n, inv_B, 0, dummy, s);
     if (rc) return rc;
     float* head = ctx->scratch + ctx->head_part_off;
-    rc = b2_launch_eval_accumulate(head, head + ctx->head_blocks, ctx->head_blocks, ctx->eval_acc_dev, s);
+    rc = b2_launch_eval_accumulate(head, head + ctx->head_blocks, is_mixed(ctx) ? ctx->head_blocks : ctx->head_used,
+                                   ctx->eval_acc_dev, s);
     if (rc) return rc;
     ctx->launches++;
   }

@@ -97,6 +97,14 @@ struct b2_ctx {
   void* dzn;                       // bf16 [max_local_batch, 64]: the output layer's dz, zero padded
   int wb_stale;                    // parameters were set from outside: refresh the bf16 copies first
 
+  // fp32 layers on the tensor cores (gemm_split3.cu): three bf16 planes of a wide layer's input, weights and dz
+  void* s3_in[B2_MAX_LAYERS];      // [3][max_local_batch, dims[l]]; NULL = this layer stays on the CUDA cores
+  void* s3_w[B2_MAX_LAYERS];       // [3][dims[l], round8(dims[l+1])]
+  void* s3_dz;                     // [3][max_local_batch, round8(widest eligible dims[l+1])]
+  int opt_no_split3;               // B2_OPT_NO_SPLIT3
+  int opt_no_narrow_head;          // B2_OPT_NO_NARROW_HEAD
+  int head_used;                   // loss / correct partials written by the last forward (<= head_blocks)
+
   // optional per-kernel event timing (B2_OPT_KERNEL_TIMING)
   int opt_timing;
   struct b2_timed* timed;
@@ -121,8 +129,9 @@ struct b2_reduce_args {
   long part_off[B2_MAX_LAYERS];
   int splits[B2_MAX_LAYERS];
   long P;
-  long head_part_off;
-  int head_blocks;
+  long head_part_off;   // loss partials
+  long head_corr_off;   // correct-count partials
+  int head_blocks;      // how many of each
 };
 int b2_launch_reduce(const b2_reduce_args& a, const float* scratch, float* grads, float* params,
                      int apply, float lr, float* loss_trace, int* correct_trace,
@@ -168,6 +177,19 @@ int b2_launch_gemm_bf16_ex(const void* A, int a_mn, const void* B, int b_mn, int
                            const float* bias, const void* act, void* out, int ldc, int n_store, int ksplits,
                            long split_stride, float* colsum_part, int sm_count, cudaStream_t s);
 // second stage of the bias gradients whose first stage is fused into the dgrad epilogue: out[c] = sum_z part[z][c]
+// narrow_head.cu: output layer (<= 128 inputs, <= 16 classes) forward + loss head + backward in one kernel
+bool b2_narrow_head_applies(int K, int C);
+int b2_narrow_head_grid(int rows, int sm_count);
+int b2_launch_narrow_head(const float* a, const float* y, const float* W, const float* b, float* dz_prev, float* partW,
+                          float* partB, long part_stride, float* loss_part, float* correct_part, int rows, int K, int C,
+                          int act, int loss, int train, float inv_B, int grid, cudaStream_t s);
+// gemm_split3.cu: fp32-accurate GEMM as six bf16 tensor-core products over three-plane splits of the operands
+int b2_launch_split3(const float* in, void* planes, long rows, int cols, int ld_in, int ld_out, long plane_stride,
+                     int sm_count, cudaStream_t s);
+int b2_launch_colsum_f32(const float* dz, float* partB, long part_stride, int rows, int N, int slices, cudaStream_t s);
+int b2_launch_gemm_split3(const void* A, int a_mn, long lda, long a_plane, const void* B, int b_mn, long ldb, long b_plane,
+                          int M, int N, int K, int epi, int act, const float* bias, float* out, int ldc, int ksplits,
+                          long split_stride, int sm_count, cudaStream_t s);
 int b2_launch_colsum_finish(const float* part, float* out, int N, int slices, cudaStream_t s);
 
 // ---- launchers (mixed_aux.cu): CUDA-core kernels of the bf16 path ------------------------------------------

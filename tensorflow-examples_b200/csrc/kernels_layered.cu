@@ -208,34 +208,68 @@ __device__ float block0_head_sum(const float* __restrict__ part, int n) {
   return warp_sum(v);
 }
 
+// Layers with many partials (the narrow-head kernel writes one per CTA) are summed by a warp per output (lanes stride
+// over the partials, then a fixed shuffle tree); the others by a thread per output, eight loads in flight.
+constexpr int REDUCE_WARP_MODE_SPLITS = 64;
+
+__device__ __forceinline__ void reduce_locate(const b2_reduce_args& a, bool warp_mode, long e, int& l, long& src, long& dst) {
+  long r = e;
+  for (l = 0; l < a.n_layers; ++l) {
+    if ((a.splits[l] > REDUCE_WARP_MODE_SPLITS) != warp_mode) continue;
+    const long sz = a.w_size[l] + a.b_size[l];
+    if (r < sz) break;
+    r -= sz;
+  }
+  if (r < a.w_size[l]) { src = r; dst = a.w_off[l] + r; }
+  else { src = ((a.w_size[l] + 3) & ~3L) + (r - a.w_size[l]); dst = a.b_off[l] + (r - a.w_size[l]); }
+}
+
 __global__ void __launch_bounds__(256)
 reduce_kernel(b2_reduce_args a, const float* __restrict__ scratch, float* __restrict__ grads,
               float* __restrict__ params, int apply, float lr, float* __restrict__ loss_trace,
-              int* __restrict__ correct_trace, float* __restrict__ global_step, long total) {
-  for (long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
-       e += (long)gridDim.x * blockDim.x) {
-    // locate (layer, segment) of logical element e
-    long r = e;
-    int l = 0;
-    for (; l < a.n_layers; ++l) {
-      const long sz = a.w_size[l] + a.b_size[l];
-      if (r < sz) break;
-      r -= sz;
+              int* __restrict__ correct_trace, float* __restrict__ global_step, long total_thread, long total_warp,
+              int blocks_thread) {
+  if ((int)blockIdx.x < blocks_thread) {
+    const long e = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < total_thread) {
+      int l; long src, dst;
+      reduce_locate(a, false, e, l, src, dst);
+      const long pstride = ((a.w_size[l] + 3) & ~3L) + ((a.b_size[l] + 3) & ~3L);
+      const float* p = scratch + a.part_off[l] + src;
+      const int S = a.splits[l];
+      float g = 0.f;
+      int s = 0;
+      for (; s + 8 <= S; s += 8) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = p[(size_t)(s + u) * pstride];
+        g += ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+      }
+      for (; s < S; ++s) g += p[(size_t)s * pstride];
+      grads[dst] = g;
+      if (apply) params[dst] -= lr * g;
     }
-    const long pstride = ((a.w_size[l] + 3) & ~3L) + ((a.b_size[l] + 3) & ~3L);
-    long src, dst;
-    if (r < a.w_size[l]) { src = r; dst = a.w_off[l] + r; }
-    else { src = ((a.w_size[l] + 3) & ~3L) + (r - a.w_size[l]); dst = a.b_off[l] + (r - a.w_size[l]); }
-    const float* p = scratch + a.part_off[l] + src;
-    float g = 0.f;
-    const int S = a.splits[l];
-    for (int s = 0; s < S; ++s) g += p[(size_t)s * pstride];
-    grads[dst] = g;
-    if (apply) params[dst] -= lr * g;
+  } else {
+    const int lane = threadIdx.x & 31;
+    const long e = (long)(blockIdx.x - blocks_thread) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (e < total_warp) {
+      int l; long src, dst;
+      reduce_locate(a, true, e, l, src, dst);
+      const long pstride = ((a.w_size[l] + 3) & ~3L) + ((a.b_size[l] + 3) & ~3L);
+      const float* p = scratch + a.part_off[l] + src;
+      const int S = a.splits[l];
+      float g = 0.f;
+      for (int s = lane; s < S; s += 32) g += p[(size_t)s * pstride];
+      g = warp_sum(g);
+      if (lane == 0) {
+        grads[dst] = g;
+        if (apply) params[dst] -= lr * g;
+      }
+    }
   }
   if (blockIdx.x == 0 && threadIdx.x < 32) {
     const float loss = block0_head_sum(scratch + a.head_part_off, a.head_blocks);
-    const float corr = block0_head_sum(scratch + a.head_part_off + a.head_blocks, a.head_blocks);
+    const float corr = block0_head_sum(scratch + a.head_corr_off, a.head_blocks);
     if (threadIdx.x == 0) {
       grads[a.P] = loss;
       grads[a.P + 1] = corr;
@@ -316,14 +350,17 @@ int b2_launch_loss_head(const float* z, const float* y, float* dz, float* loss_p
 int b2_launch_reduce(const b2_reduce_args& a, const float* scratch, float* grads, float* params,
                      int apply, float lr, float* loss_trace, int* correct_trace,
                      float* global_step, int sm_count, cudaStream_t s) {
-  long total = 0;
-  for (int l = 0; l < a.n_layers; ++l) total += a.w_size[l] + a.b_size[l];
-  long blocks = (total + 255) / 256;
-  const long cap = (long)sm_count * 8;
-  if (blocks > cap) blocks = cap;
+  (void)sm_count;
+  long total_thread = 0, total_warp = 0;
+  for (int l = 0; l < a.n_layers; ++l) {
+    if (a.splits[l] > REDUCE_WARP_MODE_SPLITS) total_warp += a.w_size[l] + a.b_size[l];
+    else total_thread += a.w_size[l] + a.b_size[l];
+  }
+  const long blocks_thread = (total_thread + 255) / 256, blocks_warp = (total_warp + 7) / 8;
+  long blocks = blocks_thread + blocks_warp;
   if (blocks < 1) blocks = 1;
-  reduce_kernel<<<(int)blocks, 256, 0, s>>>(a, scratch, grads, params, apply, lr, loss_trace,
-                                            correct_trace, global_step, total);
+  reduce_kernel<<<(int)blocks, 256, 0, s>>>(a, scratch, grads, params, apply, lr, loss_trace, correct_trace, global_step,
+                                            total_thread, total_warp, (int)blocks_thread);
   B2_LAUNCH_CHECK();
   return B2_OK;
 }

@@ -165,6 +165,16 @@ class DenseTrainer:
     def use_peer_exchange(self, on=True):
         self.set_option(_ffi.OPT_NO_PEER_EXCHANGE, 0 if on else 1)
 
+    def tensor_core_fp32(self, on=True):
+        """fp32 models: run the wide layers' GEMMs on the tensor cores as fp32-accurate three-plane bf16 splits
+        (default for batches >= 1024), or keep them on the CUDA cores."""
+        self.set_option(_ffi.OPT_NO_SPLIT3, 0 if on else 1)
+
+    def fused_output_layer(self, on=True):
+        """fp32 models with >= 2 layers: output layer forward + loss head + backward as one kernel (default) or as the
+        separate layer kernels."""
+        self.set_option(_ffi.OPT_NO_NARROW_HEAD, 0 if on else 1)
+
     def overlap_exchange(self, on=True):
         """bf16 path, several ranks: all-reduce each wide layer's weight gradient on a second stream while the backward
         pass of the layers below it runs (default), or send everything in one all-reduce after the backward pass."""
