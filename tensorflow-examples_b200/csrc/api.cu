@@ -147,8 +147,10 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
         const int K = c->dims[l], N = c->dims[l + 1], ldn = round8(N);
         rc = b2_launch_split3(a_in, c->s3_in[l], rows, K, K, K, (long)c->max_local_batch * K, c->sm_count, s);
         if (!rc) rc = b2_launch_split3(c->params + c->w_off[l], c->s3_w[l], K, N, N, ldn, (long)K * ldn, c->sm_count, s);
+        int bq = 256, one = 1;
+        b2_gemm_split3_plan(rows, N, K, 1, c->sm_count, &bq, &one);
         if (!rc) rc = b2_launch_gemm_split3(c->s3_in[l], 0, K, (long)c->max_local_batch * K, c->s3_w[l], 1, ldn, (long)K * ldn,
-                                            rows, N, K, 0, act_l, c->params + c->b_off[l], out, N, 1, 0, c->sm_count, s);
+                                            rows, N, K, 0, act_l, c->params + c->b_off[l], out, N, bq, 1, 0, c->sm_count, s);
         c->launches += 2;
       } else if (b2_small_m_fwd_applies(rows, c->dims[l]))
         rc = b2_launch_small_m_fwd(a_in, c->params + c->w_off[l], c->params + c->b_off[l], out, rows, c->dims[l + 1],
@@ -170,10 +172,13 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
     const int grid = b2_narrow_head_grid(rows, c->sm_count);
     float* pw = c->scratch + c->part_off[L];
     timed_scope t(c, B2_K_LOSS_HEAD, s);
+    const bool emit_db = train && c->nh_db_off >= 0;
     rc = b2_launch_narrow_head(a_in, y, c->params + c->w_off[L], c->params + c->b_off[L], c->dz[1], pw,
-                               pw + round4(w_size(c, L)), part_stride(c, L), head, head + c->head_blocks, rows, c->dims[L],
+                               pw + round4(w_size(c, L)), part_stride(c, L), emit_db ? c->scratch + c->nh_db_off : nullptr,
+                               round4(c->dims[L]), head, head + c->head_blocks, rows, c->dims[L],
                                c->dims[n], c->act, c->loss, train, inv_B, grid, s);
     c->head_used = grid;
+    c->nh_db_used = emit_db ? 1 : 0;
     if (train) splits_used[L] = grid;
     cur = 1;
     l_top = L - 1;
@@ -182,6 +187,7 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
     rc = b2_launch_loss_head(c->z_last, y, c->dz[0], head, head + c->head_blocks, rows, c->dims[n],
                              c->loss, inv_B, c->head_blocks, s);
     c->head_used = c->head_blocks;
+    c->nh_db_used = 0;
   }
   if (rc) return rc;
   c->launches++;
@@ -191,12 +197,8 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
     int sp = c->splits[l];
     const int max_sp = (rows + 63) / 64;
     if (sp > max_sp) sp = max_sp;
-    if (use_split3(c, l, rows)) {
-      // 128 x 128 tensor-core tiles: about two K slices per SM are enough to balance the persistent grid
-      const int tiles = ((c->dims[l] + 127) / 128) * ((c->dims[l + 1] + 127) / 128);
-      const int want = (2 * c->sm_count + tiles - 1) / tiles;
-      if (sp > want) sp = want;
-    }
+    int s3_bq = 256;
+    if (use_split3(c, l, rows)) b2_gemm_split3_plan(c->dims[l], c->dims[l + 1], rows, sp, c->sm_count, &s3_bq, &sp);
     if (sp < 1) sp = 1;
     splits_used[l] = sp;
     float* pw = c->scratch + c->part_off[l];
@@ -208,9 +210,10 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
         const int K = c->dims[l], N = c->dims[l + 1], ldn = round8(N);
         const long dzp = (long)c->max_local_batch * ldn;
         rc = b2_launch_split3(c->dz[cur], c->s3_dz, rows, N, N, ldn, dzp, c->sm_count, s);
-        if (!rc) rc = b2_launch_colsum_f32(c->dz[cur], pb, part_stride(c, l), rows, N, sp, s);
+        if (!rc && !(c->nh_db_used && l == n - 2))
+          rc = b2_launch_colsum_f32(c->dz[cur], pb, part_stride(c, l), rows, N, sp, s);
         if (!rc) rc = b2_launch_gemm_split3(c->s3_in[l], 1, K, (long)c->max_local_batch * K, c->s3_dz, 1, ldn, dzp, K, N, rows,
-                                            1, 0, nullptr, pw, N, sp, part_stride(c, l), c->sm_count, s);
+                                            1, 0, nullptr, pw, N, s3_bq, sp, part_stride(c, l), c->sm_count, s);
         c->launches += 2;
       } else {
         rc = b2_launch_sgemm_wgrad(a_prev, c->dz[cur], pw, pb, part_stride(c, l), rows, c->dims[l],
@@ -398,6 +401,7 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
   a.w_off[0] = c->w_off[L]; a.b_off[0] = c->b_off[L];
   a.w_size[0] = w_size(c, L); a.b_size[0] = b_size(c, L);
   a.part_off[0] = c->part_off[L];
+  a.pstride[0] = part_stride(c, L);
   a.splits[0] = slices;
   a.P = c->P;
   a.head_part_off = c->head_part_off;
@@ -482,6 +486,18 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
       a.w_size[l] = w_size(c, l);
       a.b_size[l] = b_size(c, l);
       a.part_off[l] = c->part_off[l];
+      a.pstride[l] = part_stride(c, l);
+    }
+    if (c->nh_db_used) {
+      // the bias gradient of layer L-1 was summed per CTA by the narrow-head kernel: reduce it as a layer of its own
+      const int L = c->n_layers - 1, e = c->n_layers;
+      a.b_size[L - 1] = 0;
+      a.w_off[e] = 0; a.w_size[e] = 0;
+      a.b_off[e] = c->b_off[L - 1]; a.b_size[e] = b_size(c, L - 1);
+      a.part_off[e] = c->nh_db_off;
+      a.pstride[e] = round4(c->dims[L]);
+      a.splits[e] = a.splits[L];
+      a.n_layers = e + 1;
     }
     a.P = c->P;
     a.head_part_off = c->head_part_off;
@@ -649,6 +665,13 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
   }
   c->head_part_off = soff;
   soff += 2L * c->head_blocks;
+  soff = (soff + 3) & ~3L;
+  c->nh_db_off = -1;
+  if (precision == B2_PREC_FP32 && n_layers >= 2 && n_layers < B2_MAX_LAYERS &&
+      b2_narrow_head_applies(dims[n_layers - 1], dims[n_layers])) {
+    c->nh_db_off = soff;
+    soff += (long)b2_narrow_head_grid(max_local_batch, c->sm_count) * round4(dims[n_layers - 1]);
+  }
   c->scratch_floats = soff;
 
 #define B2_ALLOC(ptr, nfloats)                                                         \

@@ -104,6 +104,8 @@ struct b2_ctx {
   int opt_no_split3;               // B2_OPT_NO_SPLIT3
   int opt_no_narrow_head;          // B2_OPT_NO_NARROW_HEAD
   int head_used;                   // loss / correct partials written by the last forward (<= head_blocks)
+  long nh_db_off;                  // scratch offset of the narrow-head kernel's bias-gradient partials for layer L-1, or -1
+  int nh_db_used;                  // the last backward pass left layer L-1's bias gradient there (one partial per CTA)
 
   // optional per-kernel event timing (B2_OPT_KERNEL_TIMING)
   int opt_timing;
@@ -127,6 +129,7 @@ struct b2_reduce_args {
   long w_off[B2_MAX_LAYERS], b_off[B2_MAX_LAYERS];
   long w_size[B2_MAX_LAYERS], b_size[B2_MAX_LAYERS];
   long part_off[B2_MAX_LAYERS];
+  long pstride[B2_MAX_LAYERS];   // floats between two partials of a layer
   int splits[B2_MAX_LAYERS];
   long P;
   long head_part_off;   // loss partials
@@ -181,15 +184,16 @@ int b2_launch_gemm_bf16_ex(const void* A, int a_mn, const void* B, int b_mn, int
 bool b2_narrow_head_applies(int K, int C);
 int b2_narrow_head_grid(int rows, int sm_count);
 int b2_launch_narrow_head(const float* a, const float* y, const float* W, const float* b, float* dz_prev, float* partW,
-                          float* partB, long part_stride, float* loss_part, float* correct_part, int rows, int K, int C,
+                          float* partB, long part_stride, float* partD, long strideD, float* loss_part, float* correct_part, int rows, int K, int C,
                           int act, int loss, int train, float inv_B, int grid, cudaStream_t s);
 // gemm_split3.cu: fp32-accurate GEMM as six bf16 tensor-core products over three-plane splits of the operands
 int b2_launch_split3(const float* in, void* planes, long rows, int cols, int ld_in, int ld_out, long plane_stride,
                      int sm_count, cudaStream_t s);
 int b2_launch_colsum_f32(const float* dz, float* partB, long part_stride, int rows, int N, int slices, cudaStream_t s);
+void b2_gemm_split3_plan(int M, int N, int K, int max_splits, int sm_count, int* block_q, int* splits);
 int b2_launch_gemm_split3(const void* A, int a_mn, long lda, long a_plane, const void* B, int b_mn, long ldb, long b_plane,
-                          int M, int N, int K, int epi, int act, const float* bias, float* out, int ldc, int ksplits,
-                          long split_stride, int sm_count, cudaStream_t s);
+                          int M, int N, int K, int epi, int act, const float* bias, float* out, int ldc, int block_q,
+                          int ksplits, long split_stride, int sm_count, cudaStream_t s);
 int b2_launch_colsum_finish(const float* part, float* out, int N, int slices, cudaStream_t s);
 
 // ---- launchers (mixed_aux.cu): CUDA-core kernels of the bf16 path ------------------------------------------

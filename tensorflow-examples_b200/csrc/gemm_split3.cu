@@ -9,13 +9,17 @@
 // each exact in the fp32 accumulator (8 x 8 bit mantissas); the dropped terms are <= 2^-24 relative, i.e. below fp32
 // rounding.  Six bf16 MMAs cost what three TF32 MMAs would, and the planes take 6 B per element instead of 8.
 //
-// Kernel: persistent, one CTA per SM, 128 x 128 output tiles, BLOCK_K = 32.  A shared-memory stage holds the three
-// planes of the A tile and the three planes of the B tile (48 KB; four stages), so every plane is fetched once per
-// k-block and all six products read it from shared memory.  (BLOCK_K = 64 with two 96 KB stages measured 2.5x
-// slower: one stage in flight cannot cover the load latency.)  K-major tiles have 64-byte rows -> 64B swizzle;
-// MN-major tiles keep the 128B swizzle (64 MN elements per k row).
+// Kernel: persistent, one CTA per SM.  The products this path exists for have one NARROW output dimension (the 100
+// hidden units) and one long one (batch rows in the forward pass, 784 input features in the weight gradient), so the
+// narrow side goes on the 128 TMEM lanes (UMMA "A", called P here) and the long side on up to 256 accumulator columns
+// (UMMA "B", called Q): 128 x BLOCK_Q x 16 MMAs with BLOCK_Q ~ 208-256 fetch 12 KB of operands per 128+ tensor-pipe
+// clocks, where 128 x 128 tiles (the first version, 2.2x slower) were bound by shared-memory operand fetch.  The
+// accumulator is the TRANSPOSE of the output tile; the epilogue stores it transposed, which also makes the stores
+// coalesced (a warp's 32 lanes are 32 consecutive output columns).
+// BLOCK_K = 32; a stage holds the three planes of the P tile (24 KB) and of the Q tile (<= 48 KB); three stages.
+// K-major tiles have 64-byte rows -> 64B swizzle; MN-major tiles keep the 128B swizzle (64 MN elements per k row).
 //   warp 0      TMA producer (3-D tensor maps: column, row, plane)
-//   warp 1      TMEM allocation + tcgen05.mma issue (24 MMAs per stage), two accumulator buffers
+//   warp 1      TMEM allocation + tcgen05.mma issue (12 MMAs per stage), two accumulator buffers
 //   warps 2-5   epilogue (one per TMEM lane quarter)
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -28,26 +32,27 @@
 namespace s3 {
 using namespace tcx;
 
-constexpr int BLOCK_M = 128, BLOCK_N = 128, BLOCK_K = 32, UMMA_K = 16;
-constexpr int STAGES = 4, PLANES = 3;
+constexpr int BLOCK_P = 128, MAX_BLOCK_Q = 256, BLOCK_K = 32, UMMA_K = 16;
+constexpr int STAGES = 3, PLANES = 3;
 constexpr int THREADS = 192;
-constexpr int TILE_BYTES = 128 * BLOCK_K * 2;                 // one plane of an operand tile: 8 KB
-constexpr int STAGE_BYTES = 2 * PLANES * TILE_BYTES;          // 48 KB
+constexpr int P_TILE_BYTES = BLOCK_P * BLOCK_K * 2;           // one plane of the P tile: 8 KB
+constexpr int Q_TILE_BYTES = MAX_BLOCK_Q * BLOCK_K * 2;       // one plane of the Q tile: 16 KB
+constexpr int STAGE_BYTES = PLANES * (P_TILE_BYTES + Q_TILE_BYTES);   // 72 KB
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
-constexpr int TMEM_COLS = 2 * BLOCK_N;
+constexpr int TMEM_COLS = 2 * MAX_BLOCK_Q;
 
 enum { EPI_BIAS_ACT_F32 = 0, EPI_STORE_F32 = 1 };
 
 struct Params {
-  int M, N, K;
-  int a_mn, b_mn;          // 1 = MN-major operand (global [K, M] / [K, N] row-major planes), 0 = K-major ([M, K] / [N, K])
+  int NP, NQ, K;           // narrow extent (lanes), long extent (columns), reduction length
+  int block_q;             // columns per tile: multiple of 16, <= 256
+  int p_mn, q_mn;          // 1 = MN-major operand (global [K, NP] / [K, NQ] row-major planes), 0 = K-major ([NP, K] / [NQ, K])
   int epi, act;
-  const float* bias;       // EPI_BIAS_ACT_F32: [N]
-  float* out;              // fp32 [M, ldc] row-major
+  const float* bias;       // EPI_BIAS_ACT_F32: [NP]
+  float* out;              // fp32 [NQ, ldc] row-major: out[q * ldc + p]
   int ldc;
   int ksplits;             // EPI_STORE_F32: K cut into slices, slice z writes out + z*split_stride (fixed-order partials)
   long split_stride;
-  int debug;
 };
 
 // Shared-memory matrix descriptor (bit layout as in gemm_tcgen05.cu).
@@ -62,7 +67,7 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, bool mn_major) {
 }
 
 __global__ void __launch_bounds__(THREADS, 1)
-gemm_split3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Params p) {
+gemm_split3_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmQ, Params p) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
@@ -73,11 +78,14 @@ gemm_split3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tiles_m = (p.M + BLOCK_M - 1) / BLOCK_M, tiles_n = (p.N + BLOCK_N - 1) / BLOCK_N;
-  const int mn_tiles = tiles_m * tiles_n;
-  const int ntiles = mn_tiles * p.ksplits;
+  const int BQ = p.block_q;
+  const int tiles_p = (p.NP + BLOCK_P - 1) / BLOCK_P, tiles_q = (p.NQ + BQ - 1) / BQ;
+  const int pq_tiles = tiles_p * tiles_q;
+  const int ntiles = pq_tiles * p.ksplits;
   const int num_kb_total = (p.K + BLOCK_K - 1) / BLOCK_K;
   const int kb_per = (num_kb_total + p.ksplits - 1) / p.ksplits;
+  const int q_atoms = (BQ + 63) / 64;                              // MN-major Q tile: 64-column boxes
+  const uint32_t stage_tx = PLANES * (P_TILE_BYTES + (p.q_mn ? q_atoms * BLOCK_K * 128 : BQ * BLOCK_K * 2));
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
@@ -99,31 +107,29 @@ gemm_split3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     if (lane == 0) {
       int it = 0;
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int mn = tile % mn_tiles, z = tile / mn_tiles;
-        const int m0 = (mn / tiles_n) * BLOCK_M, n0 = (mn % tiles_n) * BLOCK_N;
+        const int pq = tile % pq_tiles, z = tile / pq_tiles;
+        const int p0 = (pq % tiles_p) * BLOCK_P, q0 = (pq / tiles_p) * BQ;
         const int kb_begin = z * kb_per, kb_end = min(num_kb_total, kb_begin + kb_per);
         for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
           const int s = it % STAGES;
           mbar_wait(&empty[s], ((it / STAGES) & 1) ^ 1);
-          if ((p.debug & 1) && it >= STAGES) { mbar_arrive(&full[s]); continue; }
-          mbar_expect_tx(&full[s], STAGE_BYTES);
+          mbar_expect_tx(&full[s], stage_tx);
           const int k0 = kb * BLOCK_K;
           unsigned char* st = smem + s * STAGE_BYTES;
 #pragma unroll
           for (int pl = 0; pl < PLANES; ++pl) {
-            unsigned char* a_dst = st + pl * TILE_BYTES;
-            unsigned char* b_dst = st + (PLANES + pl) * TILE_BYTES;
-            if (p.a_mn) {
-              tma_load_3d(a_dst, &tmA, m0, k0, pl, &full[s]);
-              tma_load_3d(a_dst + BLOCK_K * 128, &tmA, m0 + 64, k0, pl, &full[s]);
+            unsigned char* p_dst = st + pl * P_TILE_BYTES;
+            unsigned char* q_dst = st + PLANES * P_TILE_BYTES + pl * Q_TILE_BYTES;
+            if (p.p_mn) {
+              tma_load_3d(p_dst, &tmP, p0, k0, pl, &full[s]);
+              tma_load_3d(p_dst + BLOCK_K * 128, &tmP, p0 + 64, k0, pl, &full[s]);
             } else {
-              tma_load_3d(a_dst, &tmA, k0, m0, pl, &full[s]);
+              tma_load_3d(p_dst, &tmP, k0, p0, pl, &full[s]);
             }
-            if (p.b_mn) {
-              tma_load_3d(b_dst, &tmB, n0, k0, pl, &full[s]);
-              tma_load_3d(b_dst + BLOCK_K * 128, &tmB, n0 + 64, k0, pl, &full[s]);
+            if (p.q_mn) {
+              for (int a = 0; a < q_atoms; ++a) tma_load_3d(q_dst + a * (BLOCK_K * 128), &tmQ, q0 + 64 * a, k0, pl, &full[s]);
             } else {
-              tma_load_3d(b_dst, &tmB, k0, n0, pl, &full[s]);
+              tma_load_3d(q_dst, &tmQ, k0, q0, pl, &full[s]);
             }
           }
         }
@@ -132,33 +138,33 @@ gemm_split3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   } else if (warp == 1) {
     if (lane == 0) {
       // instruction descriptor: D = F32, A = B = BF16, operand majors, N >> 3, M >> 4
-      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16) |
-                             ((uint32_t)(BLOCK_N >> 3) << 17) | ((uint32_t)(BLOCK_M >> 4) << 24);
-      const uint32_t a_step = p.a_mn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
-      const uint32_t b_step = p.b_mn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)p.p_mn << 15) | ((uint32_t)p.q_mn << 16) |
+                             ((uint32_t)(BQ >> 3) << 17) | ((uint32_t)(BLOCK_P >> 4) << 24);
+      const uint32_t p_step = p.p_mn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+      const uint32_t q_step = p.q_mn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
       int it = 0, t = 0;
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t) {
         const int acc = t & 1;
         mbar_wait(&tempty[acc], ((t >> 1) & 1) ^ 1);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
-        const int z = tile / mn_tiles;
+        const uint32_t d_tmem = tmem_base + acc * MAX_BLOCK_Q;
+        const int z = tile / pq_tiles;
         const int kb_begin = z * kb_per, kb_end = min(num_kb_total, kb_begin + kb_per);
         for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
           const int s = it % STAGES;
           mbar_wait(&full[s], (it / STAGES) & 1);
           tc_fence_after();
           const uint32_t st = smem_u32(smem + s * STAGE_BYTES);
-          // the six kept partial products, smallest weight first: (a3,b1) (a2,b2) (a1,b3) (a2,b1) (a1,b2) (a1,b1)
-          constexpr int PA[6] = {2, 1, 0, 1, 0, 0};
-          constexpr int PB[6] = {0, 1, 2, 0, 1, 0};
+          // the six kept partial products, smallest weight first: (p3,q1) (p2,q2) (p1,q3) (p2,q1) (p1,q2) (p1,q1)
+          constexpr int PP[6] = {2, 1, 0, 1, 0, 0};
+          constexpr int PQ[6] = {0, 1, 2, 0, 1, 0};
 #pragma unroll
           for (int q = 0; q < 6; ++q) {
-            const uint64_t da = make_desc(st + PA[q] * TILE_BYTES, p.a_mn);
-            const uint64_t db = make_desc(st + (PLANES + PB[q]) * TILE_BYTES, p.b_mn);
+            const uint64_t dp = make_desc(st + PP[q] * P_TILE_BYTES, p.p_mn);
+            const uint64_t dq = make_desc(st + PLANES * P_TILE_BYTES + PQ[q] * Q_TILE_BYTES, p.q_mn);
 #pragma unroll
             for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
-              tc_mma(d_tmem, da + (uint64_t)(k * a_step), db + (uint64_t)(k * b_step), idesc,
+              tc_mma(d_tmem, dp + (uint64_t)(k * p_step), dq + (uint64_t)(k * q_step), idesc,
                      (kb != kb_begin) || (q != 0) || (k != 0));
           }
           tc_commit(&empty[s]);
@@ -171,43 +177,31 @@ gemm_split3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     int t = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t) {
       const int acc = t & 1;
-      const int mn = tile % mn_tiles, z = tile / mn_tiles;
-      const int m0 = (mn / tiles_n) * BLOCK_M, n0 = (mn % tiles_n) * BLOCK_N;
+      const int pq = tile % pq_tiles, z = tile / pq_tiles;
+      const int p0 = (pq % tiles_p) * BLOCK_P, q0 = (pq / tiles_p) * BQ;
       mbar_wait(&tfull[acc], (t >> 1) & 1);
       tc_fence_after();
-      const int row = m0 + quarter * 32 + lane;
-      const bool row_ok = row < p.M;
+      const int pi = p0 + quarter * 32 + lane;              // this thread's output column (narrow index)
+      const bool p_ok = pi < p.NP;
       const bool empty_split = z * kb_per >= num_kb_total;
-      const bool vec4 = (p.ldc & 3) == 0 && (p.split_stride & 3) == 0;
+      const float bias = (p.epi == EPI_BIAS_ACT_F32 && p_ok) ? p.bias[pi] : 0.f;
+      float* obase = p.out + (size_t)z * p.split_stride + pi;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
-        const int n = n0 + c0;
-        if (n >= p.N) break;                                // warp-uniform
+      for (int c0 = 0; c0 < BQ; c0 += 32) {
+        if (q0 + c0 >= p.NQ) break;                         // warp-uniform
         uint32_t r[32];
-        tc_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BLOCK_N + c0), r);
-        if (empty_split) {
+        tc_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * MAX_BLOCK_Q + c0), r);
+        if (!p_ok) continue;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) r[j] = 0u;
-        }
-        if (!row_ok || (p.debug & 2)) continue;
-        float* o = p.out + (size_t)z * p.split_stride + (size_t)row * p.ldc + n;
-#pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          float v[4];
-#pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            v[u] = __uint_as_float(r[j + u]);
+        for (int j = 0; j < 32; ++j) {
+          const int qi = q0 + c0 + j;
+          if (c0 + j < BQ && qi < p.NQ) {
+            float v = empty_split ? 0.f : __uint_as_float(r[j]);
             if (p.epi == EPI_BIAS_ACT_F32) {
-              const float zv = v[u] + (n + j + u < p.N ? p.bias[n + j + u] : 0.f);
-              v[u] = p.act == B2_ACT_SIGMOID ? 1.0f / (1.0f + expf(-zv)) : zv;       // distributed.py:97
+              v += bias;
+              if (p.act == B2_ACT_SIGMOID) v = 1.0f / (1.0f + expf(-v));         // distributed.py:97
             }
-          }
-          if (vec4 && n + j + 4 <= p.N) {
-            *reinterpret_cast<float4*>(o + j) = make_float4(v[0], v[1], v[2], v[3]);
-          } else {
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-              if (n + j + u < p.N) o[j + u] = v[u];
+            obase[(size_t)qi * p.ldc] = v;                  // lanes = consecutive columns of one output row: coalesced
           }
         }
       }
@@ -339,28 +333,58 @@ int b2_launch_colsum_f32(const float* dz, float* partB, long part_stride, int ro
   return B2_OK;
 }
 
+// Tile width along the long dimension and number of K slices: fewest waves of the persistent grid, widest tile on ties.
+// max_splits <= 1: no K split (the forward pass).
+void b2_gemm_split3_plan(int M, int N, int K, int max_splits, int sm_count, int* block_q, int* splits) {
+  using namespace s3;
+  const int num_kb = (K + BLOCK_K - 1) / BLOCK_K;
+  const long tp = (N + BLOCK_P - 1) / BLOCK_P;
+  long best_cost = -1;
+  for (int bq = 256; bq >= 128; bq -= 16) {
+    const long tq = (M + bq - 1) / bq;
+    long S = 1;
+    if (max_splits > 1) {
+      S = sm_count / (tp * tq);
+      if (S > max_splits) S = max_splits;
+      if (S > num_kb) S = num_kb;
+      if (S < 1) S = 1;
+    }
+    const long waves = (tp * tq * S + sm_count - 1) / sm_count;
+    const long kb_per = (num_kb + S - 1) / S;
+    const long cost = waves * kb_per * (bq + 64);
+    if (best_cost < 0 || cost < best_cost) { best_cost = cost; *block_q = bq; *splits = (int)S; }
+  }
+}
+
+// out[M, ldc] (fp32) = A[M, K] . B[K, N], both operands as three bf16 planes.
 // A planes: K-major -> [3][M, lda] (K real columns); MN-major -> [3][K, lda] (M real columns).  B planes likewise with N.
-// out: fp32 [M, ldc].  epi 0: act(acc + bias); epi 1: raw partial sums, K cut into `ksplits` slices.
+// N is the narrow side (TMEM lanes), M the long one (accumulator columns, block_q per tile from b2_gemm_split3_plan).
+// epi 0: act(acc + bias[n]); epi 1: raw partial sums, K cut into `ksplits` slices, slice z at out + z*split_stride.
 int b2_launch_gemm_split3(const void* A, int a_mn, long lda, long a_plane, const void* B, int b_mn, long ldb, long b_plane,
-                          int M, int N, int K, int epi, int act, const float* bias, float* out, int ldc, int ksplits,
-                          long split_stride, int sm_count, cudaStream_t s) {
+                          int M, int N, int K, int epi, int act, const float* bias, float* out, int ldc, int block_q,
+                          int ksplits, long split_stride, int sm_count, cudaStream_t s) {
   using namespace s3;
   if (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) || lda % 8 || ldb % 8 || a_plane % 8 ||
       b_plane % 8) {
     b2_set_error("gemm_split3: planes must be 16-byte aligned with pitches that are multiples of 8 elements");
     return B2_ERR_ARG;
   }
-  CUtensorMap ta, tb;
-  int rc = a_mn ? make_map3(&ta, A, K, M, lda, a_plane, BLOCK_K, true) : make_map3(&ta, A, M, K, lda, a_plane, BLOCK_M, false);
+  if (block_q < 16 || block_q > MAX_BLOCK_Q || block_q % 16) {
+    b2_set_error("gemm_split3: tile width %d must be a multiple of 16 in [16, 256]", block_q);
+    return B2_ERR_ARG;
+  }
+  // P = the B operand (narrow side), Q = the A operand (long side)
+  CUtensorMap tp, tq;
+  int rc = b_mn ? make_map3(&tp, B, K, N, ldb, b_plane, BLOCK_K, true) : make_map3(&tp, B, N, K, ldb, b_plane, BLOCK_P, false);
   if (rc) return rc;
-  rc = b_mn ? make_map3(&tb, B, K, N, ldb, b_plane, BLOCK_K, true) : make_map3(&tb, B, N, K, ldb, b_plane, BLOCK_N, false);
+  rc = a_mn ? make_map3(&tq, A, K, M, lda, a_plane, BLOCK_K, true) : make_map3(&tq, A, M, K, lda, a_plane, block_q, false);
   if (rc) return rc;
   Params p;
-  p.M = M; p.N = N; p.K = K; p.a_mn = a_mn; p.b_mn = b_mn; p.epi = epi; p.act = act; p.bias = bias; p.out = out; p.ldc = ldc;
+  p.NP = N; p.NQ = M; p.K = K; p.block_q = block_q; p.p_mn = b_mn; p.q_mn = a_mn; p.epi = epi; p.act = act; p.bias = bias;
+  p.out = out; p.ldc = ldc;
   const int num_kb = (K + BLOCK_K - 1) / BLOCK_K;
   p.ksplits = (epi != EPI_STORE_F32 || ksplits < 1) ? 1 : (ksplits > num_kb ? num_kb : ksplits);
   p.split_stride = split_stride;
-  { const char* e = getenv("B2_S3_DEBUG"); p.debug = e ? atoi(e) : 0; }
   static unsigned long long attr_done = 0ull;
   int dev = 0;
   B2_CUDA(cudaGetDevice(&dev));
@@ -368,9 +392,9 @@ int b2_launch_gemm_split3(const void* A, int a_mn, long lda, long a_plane, const
     B2_CUDA(cudaFuncSetAttribute(gemm_split3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     if (dev < 64) attr_done |= 1ull << dev;
   }
-  const int ntiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + BLOCK_N - 1) / BLOCK_N) * p.ksplits;
-  const int grid = ntiles < sm_count ? ntiles : sm_count;
-  gemm_split3_kernel<<<grid, THREADS, SMEM_BYTES, s>>>(ta, tb, p);
+  const long ntiles = (long)((N + BLOCK_P - 1) / BLOCK_P) * ((M + block_q - 1) / block_q) * p.ksplits;
+  const int grid = ntiles < sm_count ? (int)ntiles : sm_count;
+  gemm_split3_kernel<<<grid, THREADS, SMEM_BYTES, s>>>(tp, tq, p);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { b2_set_error("gemm_split3 launch failed: %s", cudaGetErrorString(e)); return B2_ERR_CUDA; }
   return B2_OK;

@@ -234,7 +234,7 @@ reduce_kernel(b2_reduce_args a, const float* __restrict__ scratch, float* __rest
     if (e < total_thread) {
       int l; long src, dst;
       reduce_locate(a, false, e, l, src, dst);
-      const long pstride = ((a.w_size[l] + 3) & ~3L) + ((a.b_size[l] + 3) & ~3L);
+      const long pstride = a.pstride[l];
       const float* p = scratch + a.part_off[l] + src;
       const int S = a.splits[l];
       float g = 0.f;
@@ -255,7 +255,7 @@ reduce_kernel(b2_reduce_args a, const float* __restrict__ scratch, float* __rest
     if (e < total_warp) {
       int l; long src, dst;
       reduce_locate(a, true, e, l, src, dst);
-      const long pstride = ((a.w_size[l] + 3) & ~3L) + ((a.b_size[l] + 3) & ~3L);
+      const long pstride = a.pstride[l];
       const float* p = scratch + a.part_off[l] + src;
       const int S = a.splits[l];
       float g = 0.f;

@@ -29,6 +29,8 @@ struct Args {
   float* partW;          // partW[cta*stride + k*C + c], partB[cta*stride + c]   (train)
   float* partB;
   long part_stride;
+  float* partD;          // partD[cta*strideD + k]: column sums of dz_prev = the bias gradient of the layer below (train)
+  long strideD;
   float* loss_part;      // [gridDim.x]
   float* correct_part;   // [gridDim.x]
   int rows, K, C, act, loss, train;
@@ -86,7 +88,7 @@ narrow_head_kernel(Args p) {
   float wreg[16], accW[16], accB[16];
 #pragma unroll
   for (int i = 0; i < 16; ++i) { wreg[i] = 0.f; accW[i] = 0.f; accB[i] = 0.f; }
-  float loss_acc = 0.f, corr_acc = 0.f;
+  float loss_acc = 0.f, corr_acc = 0.f, accD = 0.f;
   if (tid == 0) {
     tcx::mbar_init(bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -256,7 +258,9 @@ narrow_head_kernel(Args p) {
             for (int j = 0; j < CH; ++j) accB[8 * hh + j] += dzr[8 * hh + j];
           }
         }
-        p.dz_prev[(size_t)(row0 + rr) * K + kk] = p.act == B2_ACT_SIGMOID ? g * av * (1.0f - av) : g;
+        const float dzp = p.act == B2_ACT_SIGMOID ? g * av * (1.0f - av) : g;
+        p.dz_prev[(size_t)(row0 + rr) * K + kk] = dzp;
+        accD += dzp;                           // BiasAdd gradient of the layer below
       }
     }
   }
@@ -272,6 +276,7 @@ narrow_head_kernel(Args p) {
         sx[kk * 17 + i] = accW[i];
         if (kk == 0) sx[128 * 17 + i] = accB[i];
       }
+      sx[129 * 17 + kk] = accD;
     }
     __syncthreads();
     if (half == 0 && kk < K) {
@@ -285,6 +290,7 @@ narrow_head_kernel(Args p) {
           if (kk == 0) pb[c] = accB[i] + sx[128 * 17 + i];
         }
       }
+      if (p.partD) p.partD[(size_t)blockIdx.x * p.strideD + kk] = accD + sx[129 * 17 + kk];
     }
   }
   loss_acc = warp_sum(loss_acc);
@@ -303,7 +309,7 @@ narrow_head_kernel(Args p) {
 
 inline int smem_bytes(int K) {
   int act = (TR * (K + 1) + 3) & ~3;
-  if (act < 129 * 17) act = (129 * 17 + 3) & ~3;     // the tile doubles as scratch for the final combine
+  if (act < 129 * 17 + 128) act = (129 * 17 + 128 + 3) & ~3;     // the tile doubles as scratch for the final combine
   return (act + KMAX * 16 + TR * 16 + 16 + 4) * (int)sizeof(float);
 }
 
@@ -319,7 +325,7 @@ int b2_narrow_head_grid(int rows, int sm_count) {
 }
 
 int b2_launch_narrow_head(const float* a, const float* y, const float* W, const float* b, float* dz_prev, float* partW,
-                          float* partB, long part_stride, float* loss_part, float* correct_part, int rows, int K, int C,
+                          float* partB, long part_stride, float* partD, long strideD, float* loss_part, float* correct_part, int rows, int K, int C,
                           int act, int loss, int train, float inv_B, int grid, cudaStream_t s) {
   if (!b2_narrow_head_applies(K, C)) { b2_set_error("narrow_head: unsupported shape %d -> %d", K, C); return B2_ERR_ARG; }
   const int smem = nh::smem_bytes(K);
@@ -339,7 +345,7 @@ int b2_launch_narrow_head(const float* a, const float* y, const float* W, const 
     if (dev < 64) attr_done |= 1ull << dev;
   }
   nh::Args p;
-  p.a = a; p.y = y; p.W = W; p.b = b; p.dz_prev = dz_prev; p.partW = partW; p.partB = partB; p.part_stride = part_stride;
+  p.a = a; p.y = y; p.W = W; p.b = b; p.dz_prev = dz_prev; p.partW = partW; p.partB = partB; p.part_stride = part_stride; p.partD = partD; p.strideD = strideD;
   p.loss_part = loss_part; p.correct_part = correct_part; p.rows = rows; p.K = K; p.C = C; p.act = act; p.loss = loss;
   p.train = train; p.inv_B = inv_B;
   switch ((C + 1) / 2) {
