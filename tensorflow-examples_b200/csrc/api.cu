@@ -122,7 +122,7 @@ bool use_fused_linear(const b2_ctx* c) {
 inline int round8(int v) { return (v + 7) & ~7; }
 // a wide fp32 layer goes to the tensor cores (three-plane split) once the batch is large enough to fill them
 inline bool use_split3(const b2_ctx* c, int l, int rows) {
-  return c->s3_in[l] != nullptr && !c->opt_no_split3 && rows >= 1024;
+  return c->s3_w[l] != nullptr && !c->opt_no_split3 && rows >= 1024;
 }
 
 // the output layer (forward, loss head and its whole backward) as one kernel when it is narrow enough (narrow_head.cu)
@@ -145,13 +145,12 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
       const int act_l = (l == n - 1) ? B2_ACT_IDENTITY : c->act;
       if (use_split3(c, l, rows)) {
         const int K = c->dims[l], N = c->dims[l + 1], ldn = round8(N);
-        rc = b2_launch_split3(a_in, c->s3_in[l], rows, K, K, K, (long)c->max_local_batch * K, c->sm_count, s);
-        if (!rc) rc = b2_launch_split3(c->params + c->w_off[l], c->s3_w[l], K, N, N, ldn, (long)K * ldn, c->sm_count, s);
-        int bq = 256, one = 1;
+        rc = b2_launch_split3(c->params + c->w_off[l], c->s3_w[l], K, N, N, ldn, (long)K * ldn, c->sm_count, s);
+        int bq = 224, one = 1;
         b2_gemm_split3_plan(rows, N, K, 1, c->sm_count, &bq, &one);
-        if (!rc) rc = b2_launch_gemm_split3(c->s3_in[l], 0, K, (long)c->max_local_batch * K, c->s3_w[l], 1, ldn, (long)K * ldn,
-                                            rows, N, K, 0, act_l, c->params + c->b_off[l], out, N, bq, 1, 0, c->sm_count, s);
-        c->launches += 2;
+        if (!rc) rc = b2_launch_gemm_split3(a_in, 0, K, c->s3_w[l], 1, ldn, (long)K * ldn, rows, N, K, 0, act_l,
+                                            c->params + c->b_off[l], out, N, bq, 1, 0, c->sm_count, s);
+        c->launches += 1;
       } else if (b2_small_m_fwd_applies(rows, c->dims[l]))
         rc = b2_launch_small_m_fwd(a_in, c->params + c->w_off[l], c->params + c->b_off[l], out, rows, c->dims[l + 1],
                                    c->dims[l], act_l, s);
@@ -197,7 +196,7 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
     int sp = c->splits[l];
     const int max_sp = (rows + 63) / 64;
     if (sp > max_sp) sp = max_sp;
-    int s3_bq = 256;
+    int s3_bq = 224;
     if (use_split3(c, l, rows)) b2_gemm_split3_plan(c->dims[l], c->dims[l + 1], rows, sp, c->sm_count, &s3_bq, &sp);
     if (sp < 1) sp = 1;
     splits_used[l] = sp;
@@ -206,14 +205,14 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
     {
       timed_scope t(c, B2_K_WGRAD, s);
       if (use_split3(c, l, rows)) {
-        // the input planes are still there from the forward pass; dz is split here, its column sums are the bias gradient
+        // dz is split into planes here (the layer input is split inside the GEMM); its column sums are the bias gradient
         const int K = c->dims[l], N = c->dims[l + 1], ldn = round8(N);
         const long dzp = (long)c->max_local_batch * ldn;
         rc = b2_launch_split3(c->dz[cur], c->s3_dz, rows, N, N, ldn, dzp, c->sm_count, s);
         if (!rc && !(c->nh_db_used && l == n - 2))
           rc = b2_launch_colsum_f32(c->dz[cur], pb, part_stride(c, l), rows, N, sp, s);
-        if (!rc) rc = b2_launch_gemm_split3(c->s3_in[l], 1, K, (long)c->max_local_batch * K, c->s3_dz, 1, ldn, dzp, K, N, rows,
-                                            1, 0, nullptr, pw, N, s3_bq, sp, part_stride(c, l), c->sm_count, s);
+        if (!rc) rc = b2_launch_gemm_split3(a_prev, 1, K, c->s3_dz, 1, ldn, dzp, K, N, rows, 1, 0, nullptr, pw, N, s3_bq, sp,
+                                            part_stride(c, l), c->sm_count, s);
         c->launches += 2;
       } else {
         rc = b2_launch_sgemm_wgrad(a_prev, c->dz[cur], pw, pb, part_stride(c, l), rows, c->dims[l],
@@ -549,7 +548,7 @@ void free_ctx(b2_ctx* c) {
   for (int p = 0; p < B2_MAX_PEERS; ++p)
     if (c->peer_base[p] && c->peer_base[p] != (void*)c->peer_local) cudaIpcCloseMemHandle(c->peer_base[p]);
   cudaFree(c->peer_local);
-  for (int l = 0; l < B2_MAX_LAYERS; ++l) { cudaFree(c->s3_in[l]); cudaFree(c->s3_w[l]); }
+  for (int l = 0; l < B2_MAX_LAYERS; ++l) cudaFree(c->s3_w[l]);
   cudaFree(c->s3_dz);
   cudaFree(c->xb);
   for (int l = 0; l < B2_MAX_LAYERS; ++l) { cudaFree(c->ab[l]); cudaFree(c->wb[l]); }
@@ -714,8 +713,7 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
     // wide layers (K >= 256, N >= 32) get three-plane bf16 copies for the tensor-core path; floats = 3 planes * elements / 2
     long s3_ldn = 0;
     for (int l = 0; l < n_layers && max_local_batch >= 1024; ++l) {
-      if (dims[l] < 256 || dims[l] % 8 || dims[l + 1] < 32) continue;
-      B2_ALLOC(c->s3_in[l], 3L * max_local_batch * dims[l] / 2 + 8);
+      if (dims[l] < 256 || dims[l] % 4 || dims[l + 1] < 32) continue;
       B2_ALLOC(c->s3_w[l], 3L * dims[l] * round8(dims[l + 1]) / 2 + 8);
       if (round8(dims[l + 1]) > s3_ldn) s3_ldn = round8(dims[l + 1]);
     }

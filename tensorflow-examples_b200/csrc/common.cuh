@@ -97,9 +97,9 @@ struct b2_ctx {
   void* dzn;                       // bf16 [max_local_batch, 64]: the output layer's dz, zero padded
   int wb_stale;                    // parameters were set from outside: refresh the bf16 copies first
 
-  // fp32 layers on the tensor cores (gemm_split3.cu): three bf16 planes of a wide layer's input, weights and dz
-  void* s3_in[B2_MAX_LAYERS];      // [3][max_local_batch, dims[l]]; NULL = this layer stays on the CUDA cores
-  void* s3_w[B2_MAX_LAYERS];       // [3][dims[l], round8(dims[l+1])]
+  // fp32 layers on the tensor cores (gemm_split3.cu): three bf16 planes of a wide layer's weights and dz (the layer
+  // input is split inside the GEMM kernel)
+  void* s3_w[B2_MAX_LAYERS];       // [3][dims[l], round8(dims[l+1])]; NULL = this layer stays on the CUDA cores
   void* s3_dz;                     // [3][max_local_batch, round8(widest eligible dims[l+1])]
   int opt_no_split3;               // B2_OPT_NO_SPLIT3
   int opt_no_narrow_head;          // B2_OPT_NO_NARROW_HEAD
@@ -191,7 +191,7 @@ int b2_launch_split3(const float* in, void* planes, long rows, int cols, int ld_
                      int sm_count, cudaStream_t s);
 int b2_launch_colsum_f32(const float* dz, float* partB, long part_stride, int rows, int N, int slices, cudaStream_t s);
 void b2_gemm_split3_plan(int M, int N, int K, int max_splits, int sm_count, int* block_q, int* splits);
-int b2_launch_gemm_split3(const void* A, int a_mn, long lda, long a_plane, const void* B, int b_mn, long ldb, long b_plane,
+int b2_launch_gemm_split3(const float* A, int a_mn, long lda, const void* B, int b_mn, long ldb, long b_plane,
                           int M, int N, int K, int epi, int act, const float* bias, float* out, int ldc, int block_q,
                           int ksplits, long split_stride, int sm_count, cudaStream_t s);
 int b2_launch_colsum_finish(const float* part, float* out, int N, int slices, cudaStream_t s);
