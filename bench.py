@@ -110,7 +110,7 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_reference_run(dims, act, loss, scaled, batch, steps, warmup, budget_s=None):
+def cpu_reference_run(dims, act, loss, scaled, batch, steps, warmup, budget_s=None, lr=LR):
     """The reference's CPU implementation of the step (oracle/torch_cpu.py, all host threads)."""
     import torch
     from oracle.torch_cpu import TorchCPUGraph
@@ -127,12 +127,12 @@ def cpu_reference_run(dims, act, loss, scaled, batch, steps, warmup, budget_s=No
     losses = []
     for s in range(warmup):
         sl = slice((s % nb) * batch, (s % nb) * batch + batch)
-        losses.append(g.train_step(xt[sl], yt[sl], LR)[0])
+        losses.append(g.train_step(xt[sl], yt[sl], lr)[0])
     t0 = time.perf_counter()
     done = 0
     for s in range(warmup, warmup + steps):
         sl = slice((s % nb) * batch, (s % nb) * batch + batch)
-        losses.append(g.train_step(xt[sl], yt[sl], LR)[0])
+        losses.append(g.train_step(xt[sl], yt[sl], lr)[0])
         done += 1
         if budget_s and time.perf_counter() - t0 > budget_s:
             break
@@ -143,25 +143,26 @@ def cpu_reference_run(dims, act, loss, scaled, batch, steps, warmup, budget_s=No
 
 # ---- batch-size sweep / strong scaling: `bench.py --sweep` --------------------
 SWEEP_POINTS = {
-    # name: (dims, act, loss, scaled init, precision, flop/sample)
-    "c3": ([784, 10], 0, 1, True, "fp32", 31360),
-    "c3-sse": ([784, 10], 0, 0, True, "fp32", 31360),          # simple.py's SSE-sum head on the same layer
-    "c2": ([784, 100, 10], 1, 1, False, "fp32", 319600),
+    # name: (dims, act, loss, scaled init, precision, flop/sample, learning rate)
+    "c3": ([784, 10], 0, 1, True, "fp32", 31360, LR),
+    # simple.py's SSE-SUM head on the same layer; its gradient grows with the batch, so the step is 1e-9
+    "c3-sse": ([784, 10], 0, 0, True, "fp32", 31360, 1e-9),
+    "c2": ([784, 100, 10], 1, 1, False, "fp32", 319600, LR),
 }
 FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.92e9 / 1e12               # 148 SMs x 128 FMA lanes x 2 flop x 1.92 GHz (spec-derived)
 
 
-def cpu_numpy_run(dims, act, loss, scaled, batch, budget_s):
+def cpu_numpy_run(dims, act, loss, scaled, batch, budget_s, lr=LR):
     from oracle.tf1_graph import TF1Graph
     from tensorflow_examples_b200 import synthetic
     x, y = synthetic.make_pool(2 * batch)
     Ws, bs = synthetic.make_weights(dims, scaled)
     g = TF1Graph(dims, act, loss, Ws, bs)
-    g.train_step(x[:batch], y[:batch], LR)
+    g.train_step(x[:batch], y[:batch], lr)
     t0, done = time.perf_counter(), 0
     while done < 50 and time.perf_counter() - t0 < budget_s:
         o = (done % 2) * batch
-        g.train_step(x[o:o + batch], y[o:o + batch], LR)
+        g.train_step(x[o:o + batch], y[o:o + batch], lr)
         done += 1
     return batch * done / (time.perf_counter() - t0), done
 
@@ -192,7 +193,7 @@ def sweep_main(args):
     y_pool = torch.from_numpy(hy).to(dev).repeat(reps, 1)[:pool_rows].contiguous()
     rows_out = []
     for name in args.sweep_points.split(","):
-        dims, act, loss, scaled, prec, flops = SWEEP_POINTS[name]
+        dims, act, loss, scaled, prec, flops, lr = SWEEP_POINTS[name]
         for B in batches:
             local = B // world if args.strong else B
             if local < 1 or (args.strong and B % world):
@@ -207,13 +208,13 @@ def sweep_main(args):
                 hs = [None] * world
                 dist.all_gather_object(hs, tr.peer_export())
                 tr.peer_import(hs)
-            lt, _ = tr.train_steps(x_pool, y_pool, local, args.warmup, first_row=0, lr=LR)
+            lt, _ = tr.train_steps(x_pool, y_pool, local, args.warmup, first_row=0, lr=lr)
             torch.cuda.synchronize(dev)
             if dist is not None:
                 dist.barrier()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-            lt, _ = tr.train_steps(x_pool, y_pool, local, args.steps, first_row=(args.warmup * gb) % pool_rows, lr=LR)
+            lt, _ = tr.train_steps(x_pool, y_pool, local, args.steps, first_row=(args.warmup * gb) % pool_rows, lr=lr)
             e1.record()
             torch.cuda.synchronize(dev)
             ms = e0.elapsed_time(e1)
@@ -228,9 +229,9 @@ def sweep_main(args):
                    "hbm_frac": sps / world * BYTES_PER_SAMPLE / (peak_gbs * 1e9),
                    "fp32_frac": sps / world * flops / (FP32_PEAK_TFLOPS * 1e12), "last_loss": float(lt[args.steps - 1].item())}
             if args.sweep_cpu and rank == 0:
-                r = cpu_reference_run(dims, act, loss, scaled, gb, 50, 2, budget_s=4.0)
+                r = cpu_reference_run(dims, act, loss, scaled, gb, 50, 2, budget_s=4.0, lr=lr)
                 row["cpu_torch_samples_per_s"], row["cpu_threads"] = r["value"], r["threads"]
-                row["cpu_numpy_samples_per_s"], _ = cpu_numpy_run(dims, act, loss, scaled, gb, 4.0)
+                row["cpu_numpy_samples_per_s"], _ = cpu_numpy_run(dims, act, loss, scaled, gb, 4.0, lr)
             tr.close()
             if rank == 0:
                 rows_out.append(row)

@@ -463,7 +463,7 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
     {
       timed_scope t(c, B2_K_FUSED_STEP, s);
       rc = b2_launch_fused_linear_step(x, y, rows, c->params + c->w_off[0], c->params + c->b_off[0],
-                                       c->fused_scratch, grid, inv_B, s);
+                                       c->fused_scratch, grid, inv_B, c->loss, s);
     }
     if (rc) return rc;
     {

@@ -155,7 +155,7 @@ long b2_fused_linear_stride(void);
 int b2_fused_linear_smem_bytes(void);
 int b2_fused_linear_tile_rows(void);
 int b2_launch_fused_linear_step(const float* x, const float* y, int rows, const float* W,
-                                const float* b, float* scratch, int grid, float inv_global_batch,
+                                const float* b, float* scratch, int grid, float inv_global_batch, int loss,
                                 cudaStream_t s);
 int b2_launch_fused_linear_reduce(const float* scratch, int grid, float* grads, float* params,
                                   int apply, float lr, float* loss_trace, int* correct_trace,

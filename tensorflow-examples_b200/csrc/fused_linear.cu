@@ -125,7 +125,7 @@ __device__ __forceinline__ void unpack2(u64 v, float& lo, float& hi) {
 __global__ void __launch_bounds__(THREADS, 1)
 fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ y_, int rows,
                          const float* __restrict__ Wg, const float* __restrict__ bg,
-                         float* __restrict__ scratch, float inv_B) {
+                         float* __restrict__ scratch, float inv_B, int loss_kind) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -297,50 +297,67 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
         for (int cc = 0; cc < 5; ++cc) t[cc] = tp[cc];
         __syncwarp();
         if (lane == 0) mbar_arrive(&sm.part_empty[buf]);                    // F may overwrite the partials
-        float m = fmaxf(fmaxf(fmaxf(z[0], z[1]), fmaxf(z[2], z[3])), z[4]);
-        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 16));
-        float e[5], ssum = 0.f;
+        float dval[5], rowloss;
+        bool hit = false;
+        if (loss_kind == B2_LOSS_SSE_SUM) {
+          // simple.py:20 on this layer: loss = sum (z - y)^2, dz = 2 (z - y); no accuracy
+          float l = 0.f;
 #pragma unroll
-        for (int cc = 0; cc < 5; ++cc) { e[cc] = expf(z[cc] - m); ssum += e[cc]; }
-        ssum += __shfl_xor_sync(0xffffffffu, ssum, 16);
-        const float inv = 1.0f / ssum;
-        float y[5], l = 0.f, sy = 0.f;
-        float bv = -INFINITY, lv = -INFINITY;
-        int bi = 0, li = 0;
+          for (int cc = 0; cc < 5; ++cc) {
+            const float d = z[cc] - t[cc];
+            l = fmaf(d, d, l);
+            dval[cc] = 2.0f * d;
+          }
+          const float l_o = __shfl_xor_sync(0xffffffffu, l, 16);
+          rowloss = half ? (l_o + l) : (l + l_o);
+        } else {
+          float m = fmaxf(fmaxf(fmaxf(z[0], z[1]), fmaxf(z[2], z[3])), z[4]);
+          m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 16));
+          float e[5], ssum = 0.f;
 #pragma unroll
-        for (int cc = 0; cc < 5; ++cc) {
-          y[cc] = e[cc] * inv;
-          l -= t[cc] * logf(y[cc]);            // un-fused log(softmax) as in the reference
-          sy += t[cc];
-          if (y[cc] > bv) { bv = y[cc]; bi = 5 * half + cc; }
-          if (t[cc] > lv) { lv = t[cc]; li = 5 * half + cc; }
-        }
-        // combine the two class halves (lane ^ 16); the l sum is formed low half first on both lanes
-        const float l_o = __shfl_xor_sync(0xffffffffu, l, 16);
-        const float sy_o = __shfl_xor_sync(0xffffffffu, sy, 16);
-        const float rowloss = half ? (l_o + l) : (l + l_o);
-        sy = half ? (sy_o + sy) : (sy + sy_o);
-        {
-          const float ov = __shfl_xor_sync(0xffffffffu, bv, 16);
-          const int oi = __shfl_xor_sync(0xffffffffu, bi, 16);
-          if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
-          const float ov2 = __shfl_xor_sync(0xffffffffu, lv, 16);
-          const int oi2 = __shfl_xor_sync(0xffffffffu, li, 16);
-          if (ov2 > lv || (ov2 == lv && oi2 < li)) { lv = ov2; li = oi2; }
+          for (int cc = 0; cc < 5; ++cc) { e[cc] = expf(z[cc] - m); ssum += e[cc]; }
+          ssum += __shfl_xor_sync(0xffffffffu, ssum, 16);
+          const float inv = 1.0f / ssum;
+          float y[5], l = 0.f, sy = 0.f;
+          float bv = -INFINITY, lv = -INFINITY;
+          int bi = 0, li = 0;
+#pragma unroll
+          for (int cc = 0; cc < 5; ++cc) {
+            y[cc] = e[cc] * inv;
+            l -= t[cc] * logf(y[cc]);            // un-fused log(softmax) as in the reference
+            sy += t[cc];
+            if (y[cc] > bv) { bv = y[cc]; bi = 5 * half + cc; }
+            if (t[cc] > lv) { lv = t[cc]; li = 5 * half + cc; }
+          }
+          // combine the two class halves (lane ^ 16); the l sum is formed low half first on both lanes
+          const float l_o = __shfl_xor_sync(0xffffffffu, l, 16);
+          const float sy_o = __shfl_xor_sync(0xffffffffu, sy, 16);
+          rowloss = half ? (l_o + l) : (l + l_o);
+          sy = half ? (sy_o + sy) : (sy + sy_o);
+          {
+            const float ov = __shfl_xor_sync(0xffffffffu, bv, 16);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, 16);
+            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+            const float ov2 = __shfl_xor_sync(0xffffffffu, lv, 16);
+            const int oi2 = __shfl_xor_sync(0xffffffffu, li, 16);
+            if (ov2 > lv || (ov2 == lv && oi2 < li)) { lv = ov2; li = oi2; }
+          }
+          hit = bi == li;
+#pragma unroll
+          for (int cc = 0; cc < 5; ++cc) dval[cc] = (y[cc] * sy - t[cc]) * inv_B;
         }
         const bool ract = row < valid;
         mbar_wait(&sm.dz_empty[buf], par ^ 1u);                            // G is done with this dz buffer
         float* dp = sm.dz + buf * DZ_BUF + row * DZ_ROW + 8 * half;
 #pragma unroll
         for (int cc = 0; cc < 5; ++cc) {
-          float d = (y[cc] * sy - t[cc]) * inv_B;
-          if (!ract) d = 0.f;
+          const float d = ract ? dval[cc] : 0.f;
           dp[cc] = d;
           db[cc] += d;
         }
         if (half == 0 && ract) {
           loss_acc += rowloss;
-          corr_acc += (bi == li) ? 1.0f : 0.0f;
+          corr_acc += hit ? 1.0f : 0.0f;
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&sm.dz_full[buf]);
@@ -435,7 +452,7 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
   } else if (tid == 32) {
     float v = 0.f;
     for (int r = 0; r < 16; ++r) v += sm.red_loss[r];
-    scratch[(size_t)blockIdx.x * SCRATCH_STRIDE + LOSS_IDX] = v * inv_B;
+    scratch[(size_t)blockIdx.x * SCRATCH_STRIDE + LOSS_IDX] = loss_kind == B2_LOSS_SSE_SUM ? v : v * inv_B;
   } else if (tid == 64) {
     float v = 0.f;
     for (int r = 0; r < 16; ++r) v += sm.red_corr[r];
@@ -495,7 +512,7 @@ fused_linear_reduce_kernel(const float* __restrict__ scratch, int grid, float* _
 }  // namespace fl
 
 bool b2_fused_linear_supported(int in_dim, int out_dim, int loss) {
-  return in_dim == fl::K && out_dim == fl::NC && loss == B2_LOSS_SOFTMAX_CE_MEAN;
+  return in_dim == fl::K && out_dim == fl::NC && (loss == B2_LOSS_SOFTMAX_CE_MEAN || loss == B2_LOSS_SSE_SUM);
 }
 int b2_fused_linear_grid(int sm_count) { return sm_count; }
 long b2_fused_linear_stride(void) { return fl::SCRATCH_STRIDE; }
@@ -510,7 +527,7 @@ int b2_fused_linear_prepare(void) {
 }
 
 int b2_launch_fused_linear_step(const float* x, const float* y, int rows, const float* W,
-                                const float* b, float* scratch, int grid, float inv_global_batch,
+                                const float* b, float* scratch, int grid, float inv_global_batch, int loss,
                                 cudaStream_t s) {
   const int smem = (int)sizeof(fl::Smem);
   cudaLaunchConfig_t cfg;
@@ -524,7 +541,7 @@ int b2_launch_fused_linear_step(const float* x, const float* y, int rows, const 
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, fl::fused_linear_step_kernel, x, y, rows, W, b, scratch, inv_global_batch);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, fl::fused_linear_step_kernel, x, y, rows, W, b, scratch, inv_global_batch, loss);
   if (e != cudaSuccess) {
     b2_set_error("fused_linear_step launch failed: %s", cudaGetErrorString(e));
     return B2_ERR_CUDA;
@@ -652,7 +669,7 @@ extern "C" int b2_linear_step_noalloc(const float* x_dev, const float* y_dev, in
   cudaStream_t s = (cudaStream_t)stream;
   const float inv_B = 1.0f / (float)global_batch;
   fl::fused_linear_step_kernel<<<grid, fl::THREADS, (int)sizeof(fl::Smem), s>>>(x_dev, y_dev, rows, W_dev, b_dev,
-                                                                              st.scratch, inv_B);
+                                                                              st.scratch, inv_B, (int)B2_LOSS_SOFTMAX_CE_MEAN);
   B2_CUDA(cudaGetLastError());
   fl::noalloc_reduce_apply_kernel<<<(7852 + 127) / 128, 128, 0, s>>>(grid, W_dev, b_dev, lr, loss_dev, correct_dev);
   B2_CUDA(cudaGetLastError());

@@ -118,3 +118,29 @@ def test_small_batch_uses_narrow_head_only(cuda_device):
     Ws, bs = synthetic.make_weights(dims, False)
     want = _oracle(dims, oracle.ACT_SIGMOID, oracle.LOSS_SOFTMAX_CE, Ws, bs, x, y, batch, steps, 0.001)
     _check(_train(dims, pkg.ACT_SIGMOID, pkg.LOSS_SOFTMAX_CE, Ws, bs, x, y, batch, steps, 0.001), want, slack=1)
+
+
+def test_sse_head_on_the_fused_single_layer_kernel(cuda_device):
+    """784 -> 10 with simple.py's sum-of-squares loss: the SSE branch of the fused single-kernel step, against the
+    oracle and against the layered kernels (B2_OPT_FORCE_LAYERED)."""
+    dims, batch, steps, lr = [784, 10], 3000, 4, 1e-6
+    x, y = synthetic.make_pool(batch * steps)
+    Ws, bs = synthetic.make_weights(dims, True)
+    g = oracle.TF1Graph(dims, oracle.ACT_IDENTITY, oracle.LOSS_SSE, Ws, bs)
+    want = [g.train_step(x[s * batch:(s + 1) * batch], y[s * batch:(s + 1) * batch], lr)[0] for s in range(steps)]
+    outs = []
+    for layered in (False, True):
+        tr = pkg.DenseTrainer(dims, pkg.ACT_IDENTITY, pkg.LOSS_SSE, max_local_batch=batch, device=0)
+        tr.force_layered(layered)
+        tr.set_params(Ws, bs)
+        lt, _ = tr.train_steps(torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda(), batch, steps, lr=lr)
+        torch.cuda.synchronize()
+        W, b = tr.get_params()
+        tr.close()
+        lt = lt.cpu().numpy()
+        for s in range(steps):
+            assert abs(float(lt[s]) - float(want[s])) <= LOSS_RTOL * max(1.0, abs(float(want[s])))
+        assert np.abs(W[0] - g.W[0]).max() <= W_RTOL * max(1.0, float(np.abs(g.W[0]).max()))
+        assert np.abs(b[0] - g.b[0]).max() <= W_RTOL * max(1.0, float(np.abs(g.W[0]).max()))
+        outs.append(lt)
+    np.testing.assert_allclose(outs[0], outs[1], rtol=LOSS_RTOL)
