@@ -48,6 +48,12 @@ flags.DEFINE_string("logs_path", "", "TensorBoard event directory; the reference
 flags.DEFINE_integer("async_period", 0, "k > 0: emulate the reference's asynchronous parameter-server updates -- every worker "
                      "applies its own gradients, replicas are averaged every k steps; 0 (default): synchronous all-reduce")
 flags.DEFINE_boolean("peer_exchange", True, "workers on one NVLink box sum gradients through peer memory instead of NCCL")
+flags.DEFINE_string("tf_op_seeds", "", "two integers 'a,b': draw W1 and W2 with TensorFlow 1.x's own generator for "
+                    "tf.set_random_seed(2) (distributed.py:83) and these op seeds (the graph's op counter at "
+                    "distributed.py:85 and :86, which depends on the TensorFlow version). Empty: fixed-seed numpy weights.")
+flags.DEFINE_string("restore_path", "", "start from variables saved by --save_path instead of fresh ones")
+flags.DEFINE_string("save_path", "", "chief worker: write the variables to this .npz when training ends "
+                    "(the reference keeps no checkpoint: Supervisor(logdir=None), distributed.py:129-131)")
 flags.DEFINE_boolean("strict_reference_bugs", False,
                      "reproduce distributed.py:165 literally: the 'Time Taken' line raises TypeError")
 FLAGS = flags.FLAGS
@@ -103,8 +109,13 @@ def main(argv):
     dims = [784, 100, 10]
     model = b2.DenseTrainer(dims, b2.ACT_SIGMOID, b2.LOSS_SOFTMAX_CE, max_local_batch=max(batch_size, 4096),
                             device=device_index)
-    Ws, bs = synthetic.make_weights(dims, scaled=False)
-    model.set_params(Ws, bs)
+    if FLAGS.restore_path:
+        model.restore(FLAGS.restore_path)
+    elif FLAGS.tf_op_seeds:
+        model.init_random_normal(2, [int(t) for t in FLAGS.tf_op_seeds.split(",")])   # distributed.py:83-91
+    else:
+        Ws, bs = synthetic.make_weights(dims, scaled=False)
+        model.set_params(Ws, bs)
     print("Variables initialized ...")                                           # distributed.py:127
 
     # sv = tf.train.Supervisor(is_chief=(task_index == 0), ...); prepare_or_wait_for_session   distributed.py:129-135
@@ -163,6 +174,8 @@ def main(argv):
     print(report.time_taken_line(time.time() - begin_time, FLAGS.strict_reference_bugs))   # distributed.py:165
     print(report.final_cost_line(cost))                                                    # distributed.py:166
     writer.close()
+    if FLAGS.save_path and role.rank == 0:
+        model.save(FLAGS.save_path)
     cl.store_barrier(store, role, "b2_done")
     model.close()                                                                          # sv.stop()  distributed.py:168
     print("done with training")                                                            # distributed.py:169

@@ -217,6 +217,17 @@ int b2_linear_step_noalloc(const float* x_dev, const float* y_dev, int rows, lon
 int b2_matmul_bf16(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
                    const float* bias, const void* act, void* out, b2_stream_t stream);
 
+/*
+ * tf.random_normal(shape, mean, stddev) on the device, for distributed.py:85-86 (initial weights): fills out_dev[0..n)
+ * with the values TensorFlow 1.x's CPU kernel produces for an op whose attributes are (seed, seed2) -- Philox4x32-10
+ * keyed by `seed`, counter offset `seed2`, four Box-Muller normals per Philox block.  With tf.set_random_seed(2)
+ * (distributed.py:83) `seed` is 2 and `seed2` is the graph's op counter at the time the op was created, which depends
+ * on the TensorFlow version; callers that know it can start from the reference's own initial weights instead of
+ * injecting them.  Restated from TensorFlow's published algorithm; not verifiable against TensorFlow on this box.
+ */
+int b2_random_normal(float* out_dev, long n, unsigned long long seed, unsigned long long seed2, float mean, float stddev,
+                     b2_stream_t stream);
+
 /* The float32 `global_step` variable (distributed.py:68-70,108) as of the last enqueued step. */
 float b2_global_step(const b2_ctx* ctx);
 

@@ -11,7 +11,7 @@ EXPORTS = [
     "b2_version", "b2_last_error", "b2_create", "b2_destroy", "b2_set_option", "b2_param_count",
     "b2_params_set", "b2_params_get", "b2_get_unique_id", "b2_comm_init", "b2_train_steps", "b2_eval",
     "b2_session_run_train", "b2_global_step", "b2_launch_count", "b2_kernel_times", "b2_kernel_class_name",
-    "b2_linear_step_noalloc", "b2_peer_export", "b2_peer_import", "b2_matmul_bf16",
+    "b2_linear_step_noalloc", "b2_peer_export", "b2_peer_import", "b2_matmul_bf16", "b2_random_normal",
 ]
 
 UNIQUE_ID_BYTES = 128
@@ -94,6 +94,9 @@ def load_library():
     lib.b2_matmul_bf16.argtypes = [c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                    c_void_p, c_void_p]
     lib.b2_matmul_bf16.restype = c_int
+    lib.b2_random_normal.argtypes = [c_void_p, ctypes.c_long, ctypes.c_ulonglong, ctypes.c_ulonglong, ctypes.c_float,
+                                     ctypes.c_float, c_void_p]
+    lib.b2_random_normal.restype = c_int
     _LIB = lib
     return lib
 

@@ -125,6 +125,44 @@ class DenseTrainer:
         torch.cuda.synchronize(self.torch_device)
         return [w.cpu().numpy() for w in Ws], [b.cpu().numpy() for b in bs]
 
+    def init_random_normal(self, seed, op_seeds, stddev=1.0):
+        """Initialise the variables the way distributed.py:83-91 does: every W[l] = tf.random_normal(shape, stddev) drawn
+        on the device with TensorFlow 1.x's generator for op attributes (seed, op_seeds[l]) -- seed is the graph seed
+        of tf.set_random_seed (2 in the reference), op_seeds[l] the op counter TensorFlow assigned to that
+        tf.random_normal (version-dependent, hence explicit) -- and every bias zero (distributed.py:90-91)."""
+        torch = _torch()
+        assert len(op_seeds) == self.n_layers
+        Ws, bs = [], []
+        for l in range(self.n_layers):
+            W = torch.empty(self.dims[l], self.dims[l + 1], dtype=torch.float32, device=self.torch_device)
+            _ffi.check(self._lib, self._lib.b2_random_normal(W.data_ptr(), W.numel(), int(seed), int(op_seeds[l]), 0.0,
+                                                             float(stddev), self._stream()))
+            b = torch.zeros(self.dims[l + 1], dtype=torch.float32, device=self.torch_device)
+            _ffi.check(self._lib, self._lib.b2_params_set(self._h, l, W.data_ptr(), b.data_ptr(), self._stream()))
+            Ws.append(W)
+            bs.append(b)
+        torch.cuda.synchronize(self.torch_device)
+
+    # -- save / restore (the reference builds no Saver: Supervisor(logdir=None), distributed.py:129-131) ------------
+    def save(self, path):
+        """Write the variables and global_step to a .npz (keys W0, b0, W1, ... and global_step)."""
+        Ws, bs = self.get_params()
+        arrays = {"global_step": np.float32(self.global_step), "dims": np.asarray(self.dims, dtype=np.int64)}
+        for l in range(self.n_layers):
+            arrays["W%d" % l] = Ws[l]
+            arrays["b%d" % l] = bs[l]
+        with open(path, "wb") as f:
+            np.savez(f, **arrays)
+
+    def restore(self, path):
+        """Load variables written by save().  global_step restarts at 0 (it lives on the device and counts the steps of
+        this context); the saved value is returned so that a caller can offset its own step display."""
+        with np.load(path) as d:
+            if list(d["dims"]) != list(self.dims):
+                raise ValueError("checkpoint %s holds dims %s, this model is %s" % (path, list(d["dims"]), list(self.dims)))
+            self.set_params([d["W%d" % l] for l in range(self.n_layers)], [d["b%d" % l] for l in range(self.n_layers)])
+            return np.float32(d["global_step"])
+
     # -- data parallel ------------------------------------------------------------------------
     @staticmethod
     def new_unique_id():

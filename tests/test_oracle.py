@@ -164,3 +164,25 @@ def test_torch_cpu_baseline_matches_numpy_oracle():
         lb, cb = b.train_step(xt[sl], yt[sl], 0.001)
         assert abs(float(la) - lb) <= 1e-5 * abs(float(la)) and ca == cb
     np.testing.assert_allclose(a.W[0], b.W[0].numpy(), rtol=1e-4, atol=1e-5)
+
+
+# ---- tf.random_normal restatement (oracle/tf1_random.py) ---------------------------------------------------------
+def test_philox4x32_10_known_answers():
+    """The block function behind tf.random_normal against the Random123 known-answer vectors."""
+    from oracle import tf1_random
+    for ctr, key, want in tf1_random.KAT:
+        got = tf1_random.philox4x32_10(np.array([ctr], dtype=np.uint32), key)[0]
+        assert tuple(int(v) for v in got) == want
+
+
+def test_random_normal_stream_properties():
+    from oracle import tf1_random
+    a = tf1_random.random_normal((784, 100), 2, 11)
+    assert a.dtype == np.float32 and a.shape == (784, 100)
+    assert abs(float(a.mean())) < 0.02 and abs(float(a.std()) - 1.0) < 0.02 and float(np.abs(a).max()) < 6.0
+    # deterministic; a different op seed is a different stream; the first n values do not depend on n (4 per block)
+    np.testing.assert_array_equal(a, tf1_random.random_normal((784, 100), 2, 11))
+    assert not np.array_equal(a, tf1_random.random_normal((784, 100), 2, 12))
+    np.testing.assert_array_equal(a.reshape(-1)[:1001], tf1_random.random_normal((1001,), 2, 11))
+    b = tf1_random.random_normal((1000,), 2, 11, mean=3.0, stddev=0.5)
+    np.testing.assert_allclose(b, a.reshape(-1)[:1000] * np.float32(0.5) + np.float32(3.0), rtol=0, atol=1e-6)

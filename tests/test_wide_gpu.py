@@ -144,3 +144,27 @@ def test_sse_head_on_the_fused_single_layer_kernel(cuda_device):
         assert np.abs(b[0] - g.b[0]).max() <= W_RTOL * max(1.0, float(np.abs(g.W[0]).max()))
         outs.append(lt)
     np.testing.assert_allclose(outs[0], outs[1], rtol=LOSS_RTOL)
+
+
+def test_device_random_normal_matches_the_oracle(cuda_device, tmp_path):
+    """b2_random_normal (tf.random_normal restated, distributed.py:85-86) against oracle/tf1_random.py: the Philox
+    integers are exact, the Box-Muller floats differ only by the device's logf / sincosf rounding; then save / restore."""
+    from oracle import tf1_random
+    dims = [784, 100, 10]
+    tr = pkg.DenseTrainer(dims, pkg.ACT_SIGMOID, pkg.LOSS_SOFTMAX_CE, max_local_batch=128, device=0)
+    tr.init_random_normal(2, [7, 1234567890123])
+    W, b = tr.get_params()
+    for l, op_seed in enumerate([7, 1234567890123]):
+        want = tf1_random.random_normal((dims[l], dims[l + 1]), 2, op_seed)
+        assert np.abs(W[l] - want).max() <= 2e-6, float(np.abs(W[l] - want).max())
+        assert not b[l].any()
+    p = str(tmp_path / "vars.npz")
+    tr.save(p)
+    tr2 = pkg.DenseTrainer(dims, pkg.ACT_SIGMOID, pkg.LOSS_SOFTMAX_CE, max_local_batch=128, device=0)
+    assert tr2.restore(p) == np.float32(0)
+    W2, b2 = tr2.get_params()
+    for l in range(2):
+        np.testing.assert_array_equal(W[l], W2[l])
+        np.testing.assert_array_equal(b[l], b2[l])
+    tr.close()
+    tr2.close()
