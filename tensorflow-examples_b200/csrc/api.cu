@@ -466,6 +466,21 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
                                        c->fused_scratch, grid, inv_B, c->loss, s);
     }
     if (rc) return rc;
+    if (use_peer && c->peer_fx) {
+      // reduction + exchange + apply in one kernel (push over NVLink, per-block flags)
+      b2_fx_args a;
+      memset(&a, 0, sizeof(a));
+      a.rank = c->rank; a.nranks = c->nranks;
+      for (int p = 0; p < c->nranks; ++p) a.region[p] = (unsigned long long*)c->peer_base[p];
+      timed_scope t(c, B2_K_ALLREDUCE_APPLY, s);
+      rc = b2_launch_fused_linear_reduce_exchange(c->fused_scratch, grid, a, c->peer_step + 1, peer_buf, c->grads, c->params, lr,
+                                                  loss_trace, correct_trace, c->global_step_dev, c->P, s);
+      if (rc) return rc;
+      c->peer_step++;
+      c->launches += 2;
+      c->global_step_host += 1.0f;
+      return B2_OK;
+    }
     {
       timed_scope t(c, B2_K_FUSED_REDUCE, s);
       rc = b2_launch_fused_linear_reduce(c->fused_scratch, grid, gvec, c->params, apply, lr,
@@ -898,7 +913,9 @@ extern "C" int b2_peer_export(b2_ctx* ctx, void* handle_out64) {
   B2_CUDA(cudaSetDevice(ctx->device));
   if (!ctx->peer_local) {
     ctx->peer_stride = ctx->P + 4;
-    const size_t bytes = (size_t)(2 * ctx->peer_stride) * sizeof(float) + 256;   // two vectors + the step flag
+    // generic layout: two vectors + the step flag.  The fused 784->10 path uses the push layout of b2_fx_args instead.
+    ctx->peer_fx = use_fused_linear(ctx) ? 1 : 0;
+    const size_t bytes = ctx->peer_fx ? B2_FX_REGION_BYTES : (size_t)(2 * ctx->peer_stride) * sizeof(float) + 256;
     B2_CUDA(cudaMalloc((void**)&ctx->peer_local, bytes));
     B2_CUDA(cudaMemset(ctx->peer_local, 0, bytes));
   }

@@ -79,6 +79,7 @@ struct b2_ctx {
   long peer_stride;                // floats per vector (P + 4)
   void* peer_base[B2_MAX_PEERS];   // mapped base of every rank's buffer (own entry = peer_local)
   int peer_ready;
+  int peer_fx;                     // the exported buffer has the push layout of b2_fx_args (fused 784->10 path)
   int opt_no_peer;                 // B2_OPT_NO_PEER_EXCHANGE
   int async_period;                // B2_OPT_ASYNC_PERIOD (0 = synchronous)
   long async_count;                // local steps since the context was created
@@ -172,6 +173,23 @@ struct b2_peer_args {
 int b2_launch_peer_allreduce_apply(const b2_peer_args& a, float* params, float* grads_out, long P, unsigned step1,
                                    int buf, float lr, float* loss_trace, int* correct_trace, float* global_step,
                                    int sm_count, cudaStream_t s);
+
+// ---- fused 784->10 path, several ranks: reduction of the per-CTA partials + gradient exchange + SGD apply in ONE
+// kernel (fused_linear.cu).  Every rank exports a region of 8-byte cells {float value, uint32 step stamp}:
+//   cells [2 step parities][B2_MAX_PEERS sources][B2_FX_SLOT]
+// The thread that owns output i PUSHES {its reduced value, step} into cell [parity][my rank][i] of every peer's region
+// (one aligned 8-byte remote store over NVLink), then polls its own cells [parity][p][i] in local memory until their
+// stamp is this step's and adds the N contributions in rank order.
+#define B2_FX_SLOT 7872            /* 246 blocks x 32 outputs >= 7852 */
+#define B2_FX_BLOCKS 246
+#define B2_FX_REGION_BYTES ((size_t)(2 * B2_MAX_PEERS * B2_FX_SLOT) * 8)
+struct b2_fx_args {
+  int rank, nranks;
+  unsigned long long* region[B2_MAX_PEERS];   // every rank's region (own entry = local memory, the others = peer mappings)
+};
+int b2_launch_fused_linear_reduce_exchange(const float* scratch, int grid, const b2_fx_args& a, unsigned step1, int parity,
+                                           float* grads, float* params, float lr, float* loss_trace, int* correct_trace,
+                                           float* global_step, long P, cudaStream_t s);
 
 // ---- launcher (gemm_tcgen05.cu): bf16 tensor-core GEMM with fused epilogues ------------------------------
 int b2_launch_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,

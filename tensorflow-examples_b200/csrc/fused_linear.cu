@@ -509,6 +509,86 @@ fused_linear_reduce_kernel(const float* __restrict__ scratch, int grid, float* _
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Several ranks: the same reduction, then the gradient exchange and the SGD apply in the same kernel (region layout:
+// b2_fx_args in common.cuh).  Every reduced value travels with its step stamp in ONE 8-byte store {value, step}
+// straight into the peers' memory over NVLink; the receiving thread polls its own 8 bytes in LOCAL memory until the
+// stamp is this step's.  An aligned 8-byte store arrives whole, so there is no separate flag, no fence between data
+// and flag, no block- or grid-wide step between "my partials are reduced" and "the sum is applied": the critical
+// path is one NVLink one-way trip.  Two slots alternate by step parity: a rank can be at most one step ahead of a
+// peer (it needs the peer's values of step s to finish step s), so slot s&1 is never overwritten before it was read.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void fx_st_pair(unsigned long long* p, float v, unsigned stamp) {
+  asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(stamp) : "memory");
+}
+__device__ __forceinline__ void fx_ld_pair(const unsigned long long* p, float& v, unsigned& stamp) {
+  unsigned a, b;
+  asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "l"(p) : "memory");
+  v = __uint_as_float(a);
+  stamp = b;
+}
+
+__global__ void __launch_bounds__(RED_OUT * RED_Q)
+fused_linear_reduce_exchange_kernel(const float* __restrict__ scratch, int grid, b2_fx_args a, unsigned step1, int parity,
+                                    float* __restrict__ grads, float* __restrict__ params, float lr,
+                                    float* __restrict__ loss_trace, int* __restrict__ correct_trace,
+                                    float* __restrict__ global_step, long P) {
+  __shared__ float sh[RED_Q][RED_OUT];
+  pdl_launch_dependents();   // the next step kernel may start its prologue and its x loads
+  pdl_wait();                // the step kernel's partials must be complete and visible
+  const int o = threadIdx.x & (RED_OUT - 1), q = threadIdx.x / RED_OUT;
+  const int i = blockIdx.x * RED_OUT + o;
+  const int per = (grid + RED_Q - 1) / RED_Q;
+  const int c0 = q * per, c1 = min(grid, c0 + per);
+  float g = 0.f;
+  if (i < RED_N) {
+    const float* p = scratch + i;
+    int c = c0;
+    for (; c + 8 <= c1; c += 8) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = p[(size_t)(c + u) * SCRATCH_STRIDE];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) g += v[u];
+    }
+    for (; c < c1; ++c) g += p[(size_t)c * SCRATCH_STRIDE];
+  }
+  sh[q][o] = g;
+  __syncthreads();
+  if (q != 0 || i >= RED_N) return;
+  g = ((sh[0][o] + sh[1][o]) + sh[2][o]) + sh[3][o];       // this rank's value of output i
+  const size_t slot = ((size_t)parity * B2_MAX_PEERS) * B2_FX_SLOT;
+  for (int p = 0; p < a.nranks; ++p)                       // push {value, step} to every peer
+    if (p != a.rank) fx_st_pair(a.region[p] + slot + (size_t)a.rank * B2_FX_SLOT + i, g, step1);
+  float sum = 0.f;
+  const unsigned long long* mine = a.region[a.rank] + slot + i;
+  for (int p = 0; p < a.nranks; ++p) {                     // rank order: the same sum on every rank
+    float v = g;
+    if (p != a.rank) {
+      unsigned stamp;
+      unsigned spins = 0;
+      for (;;) {
+        fx_ld_pair(mine + (size_t)p * B2_FX_SLOT, v, stamp);
+        if (stamp == step1) break;
+        if (++spins > (1u << 26)) __trap();                // a dead peer must not hang this GPU for ever
+      }
+    }
+    sum += v;
+  }
+  if (i < K * NC + NC) {
+    grads[i] = sum;
+    params[i] -= lr * sum;                                 // distributed.py:107-108
+  } else if (i == LOSS_IDX) {
+    grads[P] = sum;
+    if (loss_trace) *loss_trace = sum;
+  } else {
+    grads[P + 1] = sum;
+    if (correct_trace) *correct_trace = (int)(sum + 0.5f);
+    *global_step += 1.0f;
+  }
+}
+
 }  // namespace fl
 
 bool b2_fused_linear_supported(int in_dim, int out_dim, int loss) {
@@ -544,6 +624,30 @@ int b2_launch_fused_linear_step(const float* x, const float* y, int rows, const 
   cudaError_t e = cudaLaunchKernelEx(&cfg, fl::fused_linear_step_kernel, x, y, rows, W, b, scratch, inv_global_batch, loss);
   if (e != cudaSuccess) {
     b2_set_error("fused_linear_step launch failed: %s", cudaGetErrorString(e));
+    return B2_ERR_CUDA;
+  }
+  return B2_OK;
+}
+
+
+int b2_launch_fused_linear_reduce_exchange(const float* scratch, int grid, const b2_fx_args& a, unsigned step1, int parity,
+                                           float* grads, float* params, float lr, float* loss_trace, int* correct_trace,
+                                           float* global_step, long P, cudaStream_t s) {
+  static_assert((fl::RED_N + fl::RED_OUT - 1) / fl::RED_OUT == B2_FX_BLOCKS, "exchange region layout");
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(B2_FX_BLOCKS);
+  cfg.blockDim = dim3(fl::RED_OUT * fl::RED_Q);
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, fl::fused_linear_reduce_exchange_kernel, scratch, grid, a, step1, parity, grads,
+                                     params, lr, loss_trace, correct_trace, global_step, P);
+  if (e != cudaSuccess) {
+    b2_set_error("fused_linear_reduce_exchange launch failed: %s", cudaGetErrorString(e));
     return B2_ERR_CUDA;
   }
   return B2_OK;
