@@ -409,7 +409,7 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
   {
     timed_scope t(c, B2_K_REDUCE_APPLY, s);
     rc = b2_launch_reduce(a, c->scratch, c->grads, c->params, 0, lr, nullptr, nullptr, c->global_step_dev,
-                          c->sm_count, s);
+                          c->sm_count, nullptr, s);
   }
   if (rc) return rc;
   c->launches++;
@@ -452,9 +452,15 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
   const float inv_B = 1.0f / (float)global_batch;
   const int apply = (c->nranks == 1 || c->async_period > 0) ? 1 : 0;
   const bool use_peer = !apply && c->peer_ready && !c->opt_no_peer;
-  const int peer_buf = (int)(c->peer_step & 1u);
-  // where this rank's reduced vector goes: the exported peer buffer (parity of the step) or the private one
-  float* gvec = use_peer ? c->peer_local + (long)peer_buf * c->peer_stride : c->grads;
+  // gradient exchange inside the kernel that finishes the local reduction (b2_fx_args): push over NVLink, poll locally
+  b2_fx_args fx;
+  memset(&fx, 0, sizeof(fx));
+  if (use_peer) {
+    fx.rank = c->rank; fx.nranks = c->nranks; fx.stride = c->peer_stride;
+    fx.step1 = c->peer_step + 1;
+    fx.parity = (int)(c->peer_step & 1u);
+    for (int p = 0; p < c->nranks; ++p) fx.region[p] = (unsigned long long*)c->peer_base[p];
+  }
   int rc;
   if (use_fused_linear(c)) {
     const int tr = b2_fused_linear_tile_rows();
@@ -466,15 +472,10 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
                                        c->fused_scratch, grid, inv_B, c->loss, s);
     }
     if (rc) return rc;
-    if (use_peer && c->peer_fx) {
-      // reduction + exchange + apply in one kernel (push over NVLink, per-block flags)
-      b2_fx_args a;
-      memset(&a, 0, sizeof(a));
-      a.rank = c->rank; a.nranks = c->nranks;
-      for (int p = 0; p < c->nranks; ++p) a.region[p] = (unsigned long long*)c->peer_base[p];
+    if (use_peer) {
       timed_scope t(c, B2_K_ALLREDUCE_APPLY, s);
-      rc = b2_launch_fused_linear_reduce_exchange(c->fused_scratch, grid, a, c->peer_step + 1, peer_buf, c->grads, c->params, lr,
-                                                  loss_trace, correct_trace, c->global_step_dev, c->P, s);
+      rc = b2_launch_fused_linear_reduce_exchange(c->fused_scratch, grid, fx, c->grads, c->params, lr, loss_trace,
+                                                  correct_trace, c->global_step_dev, c->P, s);
       if (rc) return rc;
       c->peer_step++;
       c->launches += 2;
@@ -483,7 +484,7 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
     }
     {
       timed_scope t(c, B2_K_FUSED_REDUCE, s);
-      rc = b2_launch_fused_linear_reduce(c->fused_scratch, grid, gvec, c->params, apply, lr,
+      rc = b2_launch_fused_linear_reduce(c->fused_scratch, grid, c->grads, c->params, apply, lr,
                                          loss_trace, correct_trace, c->global_step_dev, c->P, s);
     }
     if (rc) return rc;
@@ -519,28 +520,18 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
     a.head_corr_off = c->head_part_off + c->head_blocks;
     {
       timed_scope t(c, B2_K_REDUCE_APPLY, s);
-      rc = b2_launch_reduce(a, c->scratch, gvec, c->params, apply, lr, loss_trace, correct_trace,
-                            c->global_step_dev, c->sm_count, s);
+      rc = b2_launch_reduce(a, c->scratch, c->grads, c->params, use_peer ? 1 : apply, lr, loss_trace, correct_trace,
+                            c->global_step_dev, c->sm_count, use_peer ? &fx : nullptr, s);
     }
     if (rc) return rc;
     c->launches++;
+    if (use_peer) {
+      c->peer_step++;
+      c->global_step_host += 1.0f;
+      return B2_OK;
+    }
   }
-  if (!apply && use_peer) {
-    // one kernel: wait for the peers' vectors, add them in rank order over NVLink, apply SGD
-    b2_peer_args a;
-    memset(&a, 0, sizeof(a));
-    a.rank = c->rank; a.nranks = c->nranks; a.stride = c->peer_stride;
-    for (int p = 0; p < c->nranks; ++p) {
-      a.vec[p] = (const float*)c->peer_base[p];
-      a.flag[p] = (unsigned*)((float*)c->peer_base[p] + 2 * c->peer_stride);
-    }
-    timed_scope t(c, B2_K_ALLREDUCE_APPLY, s);
-    rc = b2_launch_peer_allreduce_apply(a, c->params, c->grads, c->P, c->peer_step + 1, peer_buf, lr, loss_trace,
-                                        correct_trace, c->global_step_dev, c->sm_count, s);
-    if (rc) return rc;
-    c->peer_step++;
-    c->launches++;
-  } else if (!apply) {
+  if (!apply) {
     // the parameter-server push/pull of the reference (distributed.py:63-65) becomes one
     // all-reduce of [gradients..., loss, correct]; every rank then applies the same update.
     timed_scope t(c, B2_K_ALLREDUCE_APPLY, s);
@@ -908,14 +899,14 @@ extern "C" int b2_peer_export(b2_ctx* ctx, void* handle_out64) {
   B2_CHECK_ARG(ctx && handle_out64, "b2_peer_export: NULL argument");
   B2_CHECK_ARG(ctx->nranks > 1, "b2_peer_export: call b2_comm_init with nranks > 1 first");
   B2_CHECK_ARG(ctx->nranks <= B2_MAX_PEERS, "b2_peer_export: at most %d ranks", B2_MAX_PEERS);
-  B2_CHECK_ARG(ctx->P + 4 <= (1L << 20), "b2_peer_export: parameter vector too large for the one-shot exchange "
+  B2_CHECK_ARG(ctx->P + 4 <= (1L << 18), "b2_peer_export: parameter vector too large for the one-shot exchange "
                "(%ld floats); the NCCL path is used", ctx->P + 4);
   B2_CUDA(cudaSetDevice(ctx->device));
   if (!ctx->peer_local) {
-    ctx->peer_stride = ctx->P + 4;
-    // generic layout: two vectors + the step flag.  The fused 784->10 path uses the push layout of b2_fx_args instead.
-    ctx->peer_fx = use_fused_linear(ctx) ? 1 : 0;
-    const size_t bytes = ctx->peer_fx ? B2_FX_REGION_BYTES : (size_t)(2 * ctx->peer_stride) * sizeof(float) + 256;
+    // cells [2 parities][B2_MAX_PEERS sources][stride] of 8 bytes (b2_fx_args); one stride serves the fused 784->10
+    // kernel's element numbering and the flat layout of the layered path
+    ctx->peer_stride = round4(ctx->P + 4) > B2_FX_SLOT ? round4(ctx->P + 4) : B2_FX_SLOT;
+    const size_t bytes = (size_t)(2 * B2_MAX_PEERS) * (size_t)ctx->peer_stride * 8;
     B2_CUDA(cudaMalloc((void**)&ctx->peer_local, bytes));
     B2_CUDA(cudaMemset(ctx->peer_local, 0, bytes));
   }

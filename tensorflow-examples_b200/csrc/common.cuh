@@ -74,12 +74,11 @@ struct b2_ctx {
   // data parallel
   int rank, nranks;
   void* nccl_comm;
-  // peer-memory exchange (optional, small models): my vectors [2][peer_stride] + step flag, and the peers' mappings
+  // peer-memory exchange (optional, small models): my region of {value, stamp} cells (b2_fx_args) and the peers' mappings
   float* peer_local;               // cudaMalloc'ed, exported with cudaIpcGetMemHandle
-  long peer_stride;                // floats per vector (P + 4)
+  long peer_stride;                // cells per source in the region
   void* peer_base[B2_MAX_PEERS];   // mapped base of every rank's buffer (own entry = peer_local)
   int peer_ready;
-  int peer_fx;                     // the exported buffer has the push layout of b2_fx_args (fused 784->10 path)
   int opt_no_peer;                 // B2_OPT_NO_PEER_EXCHANGE
   int async_period;                // B2_OPT_ASYNC_PERIOD (0 = synchronous)
   long async_count;                // local steps since the context was created
@@ -137,9 +136,11 @@ struct b2_reduce_args {
   long head_corr_off;   // correct-count partials
   int head_blocks;      // how many of each
 };
+struct b2_fx_args;
+// fx != NULL: every element is exchanged with the peers (b2_fx_args below) before the update is applied
 int b2_launch_reduce(const b2_reduce_args& a, const float* scratch, float* grads, float* params,
                      int apply, float lr, float* loss_trace, int* correct_trace,
-                     float* global_step, int sm_count, cudaStream_t s);
+                     float* global_step, int sm_count, const b2_fx_args* fx, cudaStream_t s);
 // params -= lr * grads after the all-reduce; trace writes; global_step += 1
 int b2_launch_sgd_apply(float* params, const float* grads, long P, float lr, float* loss_trace,
                         int* correct_trace, float* global_step, int sm_count, cudaStream_t s);
@@ -163,33 +164,55 @@ int b2_launch_fused_linear_reduce(const float* scratch, int grid, float* grads, 
                                   float* global_step, long P, cudaStream_t s);
 int b2_fused_linear_prepare(void);
 
-// ---- launcher (peer_allreduce.cu): one-shot all-reduce over NVLink peer memory fused with the SGD apply ----
-struct b2_peer_args {
-  int rank, nranks;
-  long stride;                          // floats between the two step-parity vectors
-  const float* vec[B2_MAX_PEERS];       // every rank's vector buffer (peer mappings)
-  unsigned* flag[B2_MAX_PEERS];         // every rank's step flag
-};
-int b2_launch_peer_allreduce_apply(const b2_peer_args& a, float* params, float* grads_out, long P, unsigned step1,
-                                   int buf, float lr, float* loss_trace, int* correct_trace, float* global_step,
-                                   int sm_count, cudaStream_t s);
-
-// ---- fused 784->10 path, several ranks: reduction of the per-CTA partials + gradient exchange + SGD apply in ONE
-// kernel (fused_linear.cu).  Every rank exports a region of 8-byte cells {float value, uint32 step stamp}:
-//   cells [2 step parities][B2_MAX_PEERS sources][B2_FX_SLOT]
-// The thread that owns output i PUSHES {its reduced value, step} into cell [parity][my rank][i] of every peer's region
-// (one aligned 8-byte remote store over NVLink), then polls its own cells [parity][p][i] in local memory until their
-// stamp is this step's and adds the N contributions in rank order.
-#define B2_FX_SLOT 7872            /* 246 blocks x 32 outputs >= 7852 */
+// ---- gradient exchange over NVLink peer memory, fused into the kernel that finishes the local reduction -------------
+// Every rank exports a region of 8-byte cells {float value, uint32 step stamp}:
+//   cells [2 step parities][B2_MAX_PEERS sources][stride]
+// The thread that owns gradient element i PUSHES {its locally reduced value, step} into cell [parity][my rank][i] of
+// every peer's region (one aligned 8-byte remote store), then polls its own cells [parity][p][i] in local memory until
+// their stamp is this step's and adds the N contributions in rank order (the same sum on every rank), applies SGD.
+// An aligned 8-byte store arrives whole, so there is no separate flag and no fence between data and flag; the
+// critical path is one NVLink one-way trip.  A rank can be at most one step ahead of a peer (it needs the peer's
+// values of step s to finish step s), so slot s & 1 is never overwritten before it was read.
+#define B2_FX_SLOT 7872            /* fused 784->10 kernel: 246 blocks x 32 outputs >= 7852 */
 #define B2_FX_BLOCKS 246
-#define B2_FX_REGION_BYTES ((size_t)(2 * B2_MAX_PEERS * B2_FX_SLOT) * 8)
 struct b2_fx_args {
   int rank, nranks;
+  long stride;                                // cells per source
+  unsigned step1;                             // stamp of this step (exchanges so far + 1)
+  int parity;
   unsigned long long* region[B2_MAX_PEERS];   // every rank's region (own entry = local memory, the others = peer mappings)
 };
-int b2_launch_fused_linear_reduce_exchange(const float* scratch, int grid, const b2_fx_args& a, unsigned step1, int parity,
-                                           float* grads, float* params, float lr, float* loss_trace, int* correct_trace,
-                                           float* global_step, long P, cudaStream_t s);
+#ifdef __CUDACC__
+// device side of the exchange: push my value of element i, wait for the peers' values of the same element, return the
+// sum in rank order.  Called by exactly one thread per element.
+__device__ __forceinline__ float b2_fx_exchange(const b2_fx_args& a, long i, float mine) {
+  const size_t slot = ((size_t)a.parity * B2_MAX_PEERS) * (size_t)a.stride;
+  for (int p = 0; p < a.nranks; ++p)
+    if (p != a.rank)
+      asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(a.region[p] + slot + (size_t)a.rank * a.stride + i),
+                   "r"(__float_as_uint(mine)), "r"(a.step1)
+                   : "memory");
+  const unsigned long long* cells = a.region[a.rank] + slot + i;
+  float sum = 0.f;
+  for (int p = 0; p < a.nranks; ++p) {
+    float v = mine;
+    if (p != a.rank) {
+      unsigned bits, stamp, spins = 0;
+      for (;;) {
+        asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(bits), "=r"(stamp) : "l"(cells + (size_t)p * a.stride) : "memory");
+        if (stamp == a.step1) break;
+        if (++spins > (1u << 26)) __trap();   // a dead peer must not hang this GPU for ever
+      }
+      v = __uint_as_float(bits);
+    }
+    sum += v;
+  }
+  return sum;
+}
+#endif
+int b2_launch_fused_linear_reduce_exchange(const float* scratch, int grid, const b2_fx_args& a, float* grads, float* params,
+                                           float lr, float* loss_trace, int* correct_trace, float* global_step, long P,
+                                           cudaStream_t s);
 
 // ---- launcher (gemm_tcgen05.cu): bf16 tensor-core GEMM with fused epilogues ------------------------------
 int b2_launch_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,

@@ -511,26 +511,12 @@ fused_linear_reduce_kernel(const float* __restrict__ scratch, int grid, float* _
 
 
 // ---------------------------------------------------------------------------------------------
-// Several ranks: the same reduction, then the gradient exchange and the SGD apply in the same kernel (region layout:
-// b2_fx_args in common.cuh).  Every reduced value travels with its step stamp in ONE 8-byte store {value, step}
-// straight into the peers' memory over NVLink; the receiving thread polls its own 8 bytes in LOCAL memory until the
-// stamp is this step's.  An aligned 8-byte store arrives whole, so there is no separate flag, no fence between data
-// and flag, no block- or grid-wide step between "my partials are reduced" and "the sum is applied": the critical
-// path is one NVLink one-way trip.  Two slots alternate by step parity: a rank can be at most one step ahead of a
-// peer (it needs the peer's values of step s to finish step s), so slot s&1 is never overwritten before it was read.
+// Several ranks: the same reduction, then the gradient exchange and the SGD apply in the same kernel (b2_fx_args /
+// b2_fx_exchange in common.cuh): no block- or grid-wide step between "my partials are reduced" and "the sum is
+// applied", and one kernel launch less than reduce + a separate exchange kernel.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void fx_st_pair(unsigned long long* p, float v, unsigned stamp) {
-  asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(stamp) : "memory");
-}
-__device__ __forceinline__ void fx_ld_pair(const unsigned long long* p, float& v, unsigned& stamp) {
-  unsigned a, b;
-  asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "l"(p) : "memory");
-  v = __uint_as_float(a);
-  stamp = b;
-}
-
 __global__ void __launch_bounds__(RED_OUT * RED_Q)
-fused_linear_reduce_exchange_kernel(const float* __restrict__ scratch, int grid, b2_fx_args a, unsigned step1, int parity,
+fused_linear_reduce_exchange_kernel(const float* __restrict__ scratch, int grid, b2_fx_args a,
                                     float* __restrict__ grads, float* __restrict__ params, float lr,
                                     float* __restrict__ loss_trace, int* __restrict__ correct_trace,
                                     float* __restrict__ global_step, long P) {
@@ -558,24 +544,7 @@ fused_linear_reduce_exchange_kernel(const float* __restrict__ scratch, int grid,
   __syncthreads();
   if (q != 0 || i >= RED_N) return;
   g = ((sh[0][o] + sh[1][o]) + sh[2][o]) + sh[3][o];       // this rank's value of output i
-  const size_t slot = ((size_t)parity * B2_MAX_PEERS) * B2_FX_SLOT;
-  for (int p = 0; p < a.nranks; ++p)                       // push {value, step} to every peer
-    if (p != a.rank) fx_st_pair(a.region[p] + slot + (size_t)a.rank * B2_FX_SLOT + i, g, step1);
-  float sum = 0.f;
-  const unsigned long long* mine = a.region[a.rank] + slot + i;
-  for (int p = 0; p < a.nranks; ++p) {                     // rank order: the same sum on every rank
-    float v = g;
-    if (p != a.rank) {
-      unsigned stamp;
-      unsigned spins = 0;
-      for (;;) {
-        fx_ld_pair(mine + (size_t)p * B2_FX_SLOT, v, stamp);
-        if (stamp == step1) break;
-        if (++spins > (1u << 26)) __trap();                // a dead peer must not hang this GPU for ever
-      }
-    }
-    sum += v;
-  }
+  const float sum = b2_fx_exchange(a, i, g);
   if (i < K * NC + NC) {
     grads[i] = sum;
     params[i] -= lr * sum;                                 // distributed.py:107-108
@@ -630,9 +599,9 @@ int b2_launch_fused_linear_step(const float* x, const float* y, int rows, const 
 }
 
 
-int b2_launch_fused_linear_reduce_exchange(const float* scratch, int grid, const b2_fx_args& a, unsigned step1, int parity,
-                                           float* grads, float* params, float lr, float* loss_trace, int* correct_trace,
-                                           float* global_step, long P, cudaStream_t s) {
+int b2_launch_fused_linear_reduce_exchange(const float* scratch, int grid, const b2_fx_args& a, float* grads, float* params,
+                                           float lr, float* loss_trace, int* correct_trace, float* global_step, long P,
+                                           cudaStream_t s) {
   static_assert((fl::RED_N + fl::RED_OUT - 1) / fl::RED_OUT == B2_FX_BLOCKS, "exchange region layout");
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
@@ -644,7 +613,7 @@ int b2_launch_fused_linear_reduce_exchange(const float* scratch, int grid, const
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, fl::fused_linear_reduce_exchange_kernel, scratch, grid, a, step1, parity, grads,
+  cudaError_t e = cudaLaunchKernelEx(&cfg, fl::fused_linear_reduce_exchange_kernel, scratch, grid, a, grads,
                                      params, lr, loss_trace, correct_trace, global_step, P);
   if (e != cudaSuccess) {
     b2_set_error("fused_linear_reduce_exchange launch failed: %s", cudaGetErrorString(e));

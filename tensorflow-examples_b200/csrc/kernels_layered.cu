@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(256)
 reduce_kernel(b2_reduce_args a, const float* __restrict__ scratch, float* __restrict__ grads,
               float* __restrict__ params, int apply, float lr, float* __restrict__ loss_trace,
               int* __restrict__ correct_trace, float* __restrict__ global_step, long total_thread, long total_warp,
-              int blocks_thread) {
+              int blocks_thread, b2_fx_args fx) {
   if ((int)blockIdx.x < blocks_thread) {
     const long e = (long)blockIdx.x * blockDim.x + threadIdx.x;
     if (e < total_thread) {
@@ -246,6 +246,7 @@ reduce_kernel(b2_reduce_args a, const float* __restrict__ scratch, float* __rest
         g += ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
       }
       for (; s < S; ++s) g += p[(size_t)s * pstride];
+      if (fx.nranks > 1) g = b2_fx_exchange(fx, dst, g);
       grads[dst] = g;
       if (apply) params[dst] -= lr * g;
     }
@@ -262,15 +263,20 @@ reduce_kernel(b2_reduce_args a, const float* __restrict__ scratch, float* __rest
       for (int s = lane; s < S; s += 32) g += p[(size_t)s * pstride];
       g = warp_sum(g);
       if (lane == 0) {
+        if (fx.nranks > 1) g = b2_fx_exchange(fx, dst, g);
         grads[dst] = g;
         if (apply) params[dst] -= lr * g;
       }
     }
   }
   if (blockIdx.x == 0 && threadIdx.x < 32) {
-    const float loss = block0_head_sum(scratch + a.head_part_off, a.head_blocks);
-    const float corr = block0_head_sum(scratch + a.head_corr_off, a.head_blocks);
+    float loss = block0_head_sum(scratch + a.head_part_off, a.head_blocks);
+    float corr = block0_head_sum(scratch + a.head_corr_off, a.head_blocks);
     if (threadIdx.x == 0) {
+      if (fx.nranks > 1) {
+        loss = b2_fx_exchange(fx, a.P, loss);
+        corr = b2_fx_exchange(fx, a.P + 1, corr);
+      }
       grads[a.P] = loss;
       grads[a.P + 1] = corr;
       if (apply) {
@@ -349,8 +355,10 @@ int b2_launch_loss_head(const float* z, const float* y, float* dz, float* loss_p
 
 int b2_launch_reduce(const b2_reduce_args& a, const float* scratch, float* grads, float* params,
                      int apply, float lr, float* loss_trace, int* correct_trace,
-                     float* global_step, int sm_count, cudaStream_t s) {
+                     float* global_step, int sm_count, const b2_fx_args* fx, cudaStream_t s) {
   (void)sm_count;
+  b2_fx_args none;
+  memset(&none, 0, sizeof(none));
   long total_thread = 0, total_warp = 0;
   for (int l = 0; l < a.n_layers; ++l) {
     if (a.splits[l] > REDUCE_WARP_MODE_SPLITS) total_warp += a.w_size[l] + a.b_size[l];
@@ -360,7 +368,7 @@ int b2_launch_reduce(const b2_reduce_args& a, const float* scratch, float* grads
   long blocks = blocks_thread + blocks_warp;
   if (blocks < 1) blocks = 1;
   reduce_kernel<<<(int)blocks, 256, 0, s>>>(a, scratch, grads, params, apply, lr, loss_trace, correct_trace, global_step,
-                                            total_thread, total_warp, (int)blocks_thread);
+                                            total_thread, total_warp, (int)blocks_thread, fx ? *fx : none);
   B2_LAUNCH_CHECK();
   return B2_OK;
 }
