@@ -127,11 +127,12 @@ int b2_get_unique_id(void* out128);
 int b2_comm_init(b2_ctx* ctx, int rank, int nranks, const void* unique_id128);
 
 /*
- * Optional fast path of the gradient exchange for models whose parameter vector is small (<= 1 Mi
- * floats): instead of calling NCCL, each rank leaves its gradient vector in a buffer that the other
- * ranks of the box have mapped over NVLink, and one kernel per rank adds all vectors in rank order and
- * applies the SGD update in the same pass.  This is what replaces the reference's per-step variable
- * pull + gradient push through the parameter server (distributed.py:63-65) on an NVSwitch box.
+ * Optional fast path of the gradient exchange for models whose parameter vector is small (<= 256 Ki
+ * floats): instead of calling NCCL, the kernel that finishes a rank's local gradient reduction pushes every
+ * element, tagged with the step number, straight into buffers the other ranks of the box have mapped over
+ * NVLink, waits for the peers' values of the same element in its own memory, adds them in rank order and
+ * applies the SGD update -- no separate collective, no extra kernel.  This is what replaces the reference's
+ * per-step variable pull + gradient push through the parameter server (distributed.py:63-65) on an NVSwitch box.
  * Call after b2_comm_init: b2_peer_export writes a 64-byte CUDA IPC handle; gather the handles of all
  * ranks (rank order) and pass the nranks*64 bytes to b2_peer_import on every rank.  All ranks must be
  * processes on one node with peer access between their GPUs; otherwise b2_peer_import fails and the
