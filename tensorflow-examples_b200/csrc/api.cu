@@ -172,7 +172,14 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
     float* pw = c->scratch + c->part_off[L];
     timed_scope t(c, B2_K_LOSS_HEAD, s);
     const bool emit_db = train && c->nh_db_off >= 0;
-    rc = b2_launch_narrow_head(a_in, y, c->params + c->w_off[L], c->params + c->b_off[L], c->dz[1], pw,
+    // the layer below runs its weight gradient on the tensor cores: hand it dz as bf16 planes straight from here; the
+    // fp32 copy is only needed when a further layer below needs the input gradient (dgrad) as well
+    const bool planes = train && L >= 1 && use_split3(c, L - 1, rows);
+    const int ldn = round8(c->dims[L]);
+    c->nh_planes_used = planes ? 1 : 0;
+    rc = b2_launch_narrow_head(a_in, y, c->params + c->w_off[L], c->params + c->b_off[L],
+                               (planes && L - 1 == 0 && emit_db) ? nullptr : c->dz[1], planes ? c->s3_dz : nullptr,
+                               (long)c->max_local_batch * ldn, ldn, pw,
                                pw + round4(w_size(c, L)), part_stride(c, L), emit_db ? c->scratch + c->nh_db_off : nullptr,
                                round4(c->dims[L]), head, head + c->head_blocks, rows, c->dims[L],
                                c->dims[n], c->act, c->loss, train, inv_B, grid, s);
@@ -187,6 +194,7 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
                              c->loss, inv_B, c->head_blocks, s);
     c->head_used = c->head_blocks;
     c->nh_db_used = 0;
+    c->nh_planes_used = 0;
   }
   if (rc) return rc;
   c->launches++;
@@ -208,12 +216,13 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
         // dz is split into planes here (the layer input is split inside the GEMM); its column sums are the bias gradient
         const int K = c->dims[l], N = c->dims[l + 1], ldn = round8(N);
         const long dzp = (long)c->max_local_batch * ldn;
-        rc = b2_launch_split3(c->dz[cur], c->s3_dz, rows, N, N, ldn, dzp, c->sm_count, s);
+        const bool from_head = c->nh_planes_used && l == n - 2;     // the narrow-head kernel already wrote the planes
+        rc = from_head ? B2_OK : b2_launch_split3(c->dz[cur], c->s3_dz, rows, N, N, ldn, dzp, c->sm_count, s);
+        if (!from_head) c->launches += 1;
         if (!rc && !(c->nh_db_used && l == n - 2))
           rc = b2_launch_colsum_f32(c->dz[cur], pb, part_stride(c, l), rows, N, sp, s);
         if (!rc) rc = b2_launch_gemm_split3(a_prev, 1, K, c->s3_dz, 1, ldn, dzp, K, N, rows, 1, 0, nullptr, pw, N, s3_bq, sp,
                                             part_stride(c, l), c->sm_count, s);
-        c->launches += 2;
       } else {
         rc = b2_launch_sgemm_wgrad(a_prev, c->dz[cur], pw, pb, part_stride(c, l), rows, c->dims[l],
                                    c->dims[l + 1], sp, s);
@@ -723,7 +732,10 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
       B2_ALLOC(c->s3_w[l], 3L * dims[l] * round8(dims[l + 1]) / 2 + 8);
       if (round8(dims[l + 1]) > s3_ldn) s3_ldn = round8(dims[l + 1]);
     }
-    if (s3_ldn) B2_ALLOC(c->s3_dz, 3L * max_local_batch * s3_ldn / 2 + 8);
+    if (s3_ldn) {
+      B2_ALLOC(c->s3_dz, 3L * max_local_batch * s3_ldn / 2 + 8);
+      cudaMemset(c->s3_dz, 0, (size_t)(3L * max_local_batch * s3_ldn / 2 + 8) * sizeof(float));   // pad columns stay zero
+    }
     B2_ALLOC(c->dz[0], (long)max_local_batch * maxw);
     if (n_layers > 1) B2_ALLOC(c->dz[1], (long)max_local_batch * maxw);
   }

@@ -105,6 +105,7 @@ struct b2_ctx {
   int opt_no_narrow_head;          // B2_OPT_NO_NARROW_HEAD
   int head_used;                   // loss / correct partials written by the last forward (<= head_blocks)
   long nh_db_off;                  // scratch offset of the narrow-head kernel's bias-gradient partials for layer L-1, or -1
+  int nh_planes_used;              // ... and dz of layer L-1 as bf16 planes in s3_dz
   int nh_db_used;                  // the last backward pass left layer L-1's bias gradient there (one partial per CTA)
 
   // optional per-kernel event timing (B2_OPT_KERNEL_TIMING)
@@ -224,7 +225,8 @@ int b2_launch_gemm_bf16_ex(const void* A, int a_mn, const void* B, int b_mn, int
 // narrow_head.cu: output layer (<= 128 inputs, <= 16 classes) forward + loss head + backward in one kernel
 bool b2_narrow_head_applies(int K, int C);
 int b2_narrow_head_grid(int rows, int sm_count);
-int b2_launch_narrow_head(const float* a, const float* y, const float* W, const float* b, float* dz_prev, float* partW,
+int b2_launch_narrow_head(const float* a, const float* y, const float* W, const float* b, float* dz_prev, void* dz_planes,
+                          long plane_stride, int ld_planes, float* partW,
                           float* partB, long part_stride, float* partD, long strideD, float* loss_part, float* correct_part, int rows, int K, int C,
                           int act, int loss, int train, float inv_B, int grid, cudaStream_t s);
 // gemm_split3.cu: fp32-accurate GEMM as six bf16 tensor-core products over three-plane splits of the operands

@@ -9,6 +9,7 @@
 //   dW = a^T . dz, db = column sums of dz            MatMul / BiasAdd gradients (per-CTA partials, fixed order)
 //   da = dz . W^T, dz_prev = da * a * (1 - a)        MatMul gradient (transpose_b) + SigmoidGrad -> global
 // HBM traffic per row: K floats in, K floats out (+ the labels).  train == 0 stops after the loss (evaluation).
+#include <cuda_bf16.h>
 #include <math.h>
 
 #include "common.cuh"
@@ -25,7 +26,10 @@ struct Args {
   const float* y;        // [rows, C] labels
   const float* W;        // [K, C]
   const float* b;        // [C]
-  float* dz_prev;        // [rows, K]   (train)
+  float* dz_prev;        // [rows, K] fp32, or NULL when only the planes are wanted   (train)
+  unsigned short* dz_planes;   // three bf16 planes [3][rows_max, ld_planes] of dz_prev for the tensor-core wgrad of the layer
+  long plane_stride;           // below (gemm_split3.cu), or NULL; elements between planes
+  int ld_planes;
   float* partW;          // partW[cta*stride + k*C + c], partB[cta*stride + c]   (train)
   float* partB;
   long part_stride;
@@ -259,7 +263,18 @@ narrow_head_kernel(Args p) {
           }
         }
         const float dzp = p.act == B2_ACT_SIGMOID ? g * av * (1.0f - av) : g;
-        p.dz_prev[(size_t)(row0 + rr) * K + kk] = dzp;
+        if (p.dz_prev) p.dz_prev[(size_t)(row0 + rr) * K + kk] = dzp;
+        if (p.dz_planes) {
+          // dzp = h1 + h2 + h3 exactly (three bf16 roundings of the running remainder), as split3_kernel writes them
+          float r = dzp;
+          unsigned short* pl = p.dz_planes + (size_t)(row0 + rr) * p.ld_planes + kk;
+#pragma unroll
+          for (int q = 0; q < 3; ++q) {
+            const unsigned short h = __bfloat16_as_ushort(__float2bfloat16_rn(r));
+            pl[(size_t)q * p.plane_stride] = h;
+            r -= __uint_as_float((unsigned)h << 16);
+          }
+        }
         accD += dzp;                           // BiasAdd gradient of the layer below
       }
     }
@@ -324,7 +339,8 @@ int b2_narrow_head_grid(int rows, int sm_count) {
   return tiles < cap ? (tiles < 1 ? 1 : tiles) : cap;
 }
 
-int b2_launch_narrow_head(const float* a, const float* y, const float* W, const float* b, float* dz_prev, float* partW,
+int b2_launch_narrow_head(const float* a, const float* y, const float* W, const float* b, float* dz_prev, void* dz_planes,
+                          long plane_stride, int ld_planes, float* partW,
                           float* partB, long part_stride, float* partD, long strideD, float* loss_part, float* correct_part, int rows, int K, int C,
                           int act, int loss, int train, float inv_B, int grid, cudaStream_t s) {
   if (!b2_narrow_head_applies(K, C)) { b2_set_error("narrow_head: unsupported shape %d -> %d", K, C); return B2_ERR_ARG; }
@@ -345,7 +361,8 @@ int b2_launch_narrow_head(const float* a, const float* y, const float* W, const 
     if (dev < 64) attr_done |= 1ull << dev;
   }
   nh::Args p;
-  p.a = a; p.y = y; p.W = W; p.b = b; p.dz_prev = dz_prev; p.partW = partW; p.partB = partB; p.part_stride = part_stride; p.partD = partD; p.strideD = strideD;
+  p.a = a; p.y = y; p.W = W; p.b = b; p.dz_prev = dz_prev; p.dz_planes = reinterpret_cast<unsigned short*>(dz_planes);
+  p.plane_stride = plane_stride; p.ld_planes = ld_planes; p.partW = partW; p.partB = partB; p.part_stride = part_stride; p.partD = partD; p.strideD = strideD;
   p.loss_part = loss_part; p.correct_part = correct_part; p.rows = rows; p.K = K; p.C = C; p.act = act; p.loss = loss;
   p.train = train; p.inv_B = inv_B;
   switch ((C + 1) / 2) {
