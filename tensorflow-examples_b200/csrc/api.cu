@@ -311,8 +311,15 @@ int enqueue_forward_mixed(b2_ctx* c, const float* x, const float* y, int rows, f
   float* head = c->scratch + c->head_part_off;
   {
     timed_scope t(c, B2_K_LOSS_HEAD, s);
-    rc = b2_launch_loss_head(c->z_last, y, c->dz[0], head, head + c->head_blocks, rows, c->dims[n], c->loss, inv_B,
-                             c->head_blocks, s);
+    if (c->dims[n] <= 16) {
+      // one thread per row: also writes dz as the padded bf16 operand of the output layer's tensor-core products and
+      // the per-block column sums of dz (its bias gradient)
+      rc = b2_launch_loss_head_rows(c->z_last, y, c->dzn, head, head + c->head_blocks, c->scratch + c->head_db_off, rows,
+                                    c->dims[n], c->loss, inv_B, c->head_blocks, s);
+    } else {
+      rc = b2_launch_loss_head(c->z_last, y, c->dz[0], head, head + c->head_blocks, rows, c->dims[n], c->loss, inv_B,
+                               c->head_blocks, s);
+    }
   }
   if (rc) return rc;
   c->launches++;
@@ -330,13 +337,14 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
   const int slices = narrow_slices(c, rows);
   float* pw = c->scratch + c->part_off[L];
   float* pb = pw + round4(w_size(c, L));
-  {
+  const bool head_rows = c->dims[n] <= 16;     // the row-thread loss head already left dzn and the db partials
+  if (!head_rows) {
     timed_scope t(c, B2_K_MIXED_AUX, s);
     rc = b2_launch_pad_cast64(c->dz[0], c->dzn, rows, c->dims[n], c->sm_count, s);
     if (!rc) rc = b2_launch_colsum_f32_narrow(c->dz[0], pb, part_stride(c, L), rows, c->dims[n], slices, s);   // BiasAdd grad
+    if (rc) return rc;
+    c->launches += 2;
   }
-  if (rc) return rc;
-  c->launches += 2;
   {
     // dW_out partials = a^T . dz   (MatMul grad, transpose_a), K = batch cut into `slices` fixed pieces
     timed_scope t(c, B2_K_GEMM_WGRAD, s);
@@ -345,15 +353,25 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
   }
   if (rc) return rc;
   c->launches++;
-  {
-    // dz_prev = (dz . W_out^T) * a(1-a)   (MatMul grad transpose_b + SigmoidGrad); the reduction runs over the 64 padded classes
+  // dz_prev = (dz . W_out^T) * a(1-a)   (MatMul grad transpose_b + SigmoidGrad)
+  const bool narrow_dgrad = c->dims[n] <= 16 && c->dims[L] % 8 == 0 && c->act == B2_ACT_SIGMOID;
+  int colsum_slices = (rows + 31) / 32;       // partial rows the dgrad left in colsum_part (bias gradient of layer L-1)
+  bool colsum_pending;
+  if (narrow_dgrad) {
+    // ten classes in the reduction: an element-wise pass on the CUDA cores, not a GEMM
+    timed_scope t(c, B2_K_GEMM_DGRAD, s);
+    rc = b2_launch_narrow_dgrad_bf16(c->dzn, c->wb[L], c->ab[L - 1], c->dzb[0], c->colsum_part, rows, c->dims[L], c->dims[n], s);
+    colsum_pending = true;
+    colsum_slices = b2_narrow_dgrad_slices(rows);
+  } else {
+    // the reduction runs over the 64 padded classes on the tensor cores
     timed_scope t(c, B2_K_GEMM_DGRAD, s);
     rc = b2_launch_gemm_bf16_ex(c->dzn, 0, c->wb[L], 0, rows, c->dims[L], 64, 1, nullptr, c->ab[L - 1], c->dzb[0],
                                 c->dims[L], c->dims[L], 1, 0, fused_colsum(c, L) ? c->colsum_part : nullptr, c->sm_count, s);
+    colsum_pending = fused_colsum(c, L);
   }
   if (rc) return rc;
   c->launches++;
-  bool colsum_pending = fused_colsum(c, L);   // the bias gradient of layer L-1 sits in colsum_part as 32-row partials
   const bool exchange = c->nranks > 1 && c->async_period == 0;
   const bool overlap = exchange && !c->opt_no_overlap && !c->opt_timing && c->comm_stream != nullptr;
   bool bucketed[B2_MAX_LAYERS] = {};
@@ -364,7 +382,7 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
     {
       timed_scope t(c, B2_K_MIXED_AUX, s);
       if (colsum_pending) {
-        rc = b2_launch_colsum_finish(c->colsum_part, c->grads + c->b_off[l], c->dims[l + 1], (rows + 31) / 32, s);
+        rc = b2_launch_colsum_finish(c->colsum_part, c->grads + c->b_off[l], c->dims[l + 1], colsum_slices, s);
         c->launches += 1;
       } else {
         rc = b2_launch_colsum_bf16(c->dzb[cur], c->colsum_part, c->grads + c->b_off[l], rows, c->dims[l + 1],
@@ -394,6 +412,7 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
       // dz_prev = (dz . W^T) * a(1-a)   A = dz K-major [rows, out], B = W [in, out] K-major
       timed_scope t(c, B2_K_GEMM_DGRAD, s);
       colsum_pending = fused_colsum(c, l);
+      colsum_slices = (rows + 31) / 32;
       rc = b2_launch_gemm_bf16_ex(c->dzb[cur], 0, c->wb[l], 0, rows, c->dims[l], c->dims[l + 1], 1, nullptr, c->ab[l - 1],
                                   c->dzb[cur ^ 1], c->dims[l], c->dims[l], 1, 0, colsum_pending ? c->colsum_part : nullptr,
                                   c->sm_count, s);
@@ -411,6 +430,16 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
   a.part_off[0] = c->part_off[L];
   a.pstride[0] = part_stride(c, L);
   a.splits[0] = slices;
+  if (head_rows) {
+    // the bias gradient comes from the loss head's per-block partials: a reduce "layer" of its own
+    a.b_size[0] = 0;
+    a.n_layers = 2;
+    a.w_off[1] = 0; a.w_size[1] = 0;
+    a.b_off[1] = c->b_off[L]; a.b_size[1] = b_size(c, L);
+    a.part_off[1] = c->head_db_off;
+    a.pstride[1] = 16;
+    a.splits[1] = c->head_blocks;
+  }
   a.P = c->P;
   a.head_part_off = c->head_part_off;
   a.head_blocks = c->head_blocks;
@@ -680,6 +709,8 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
   c->head_part_off = soff;
   soff += 2L * c->head_blocks;
   soff = (soff + 3) & ~3L;
+  c->head_db_off = soff;
+  soff += 16L * c->head_blocks;
   c->nh_db_off = -1;
   if (precision == B2_PREC_FP32 && n_layers >= 2 && n_layers < B2_MAX_LAYERS &&
       b2_narrow_head_applies(dims[n_layers - 1], dims[n_layers])) {

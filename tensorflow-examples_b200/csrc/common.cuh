@@ -104,6 +104,7 @@ struct b2_ctx {
   int opt_no_split3;               // B2_OPT_NO_SPLIT3
   int opt_no_narrow_head;          // B2_OPT_NO_NARROW_HEAD
   int head_used;                   // loss / correct partials written by the last forward (<= head_blocks)
+  long head_db_off;                // scratch offset of the row-thread loss head's bias-gradient partials [head_blocks][16]
   long nh_db_off;                  // scratch offset of the narrow-head kernel's bias-gradient partials for layer L-1, or -1
   int nh_planes_used;              // ... and dz of layer L-1 as bf16 planes in s3_dz
   int nh_db_used;                  // the last backward pass left layer L-1's bias gradient there (one partial per CTA)
@@ -244,6 +245,12 @@ int b2_launch_cast_bf16(const float* src, void* dst, long n, int sm_count, cudaS
 // fp32 [rows, C] -> bf16 [rows, 64], zero padded: makes the narrow output layer a legal tensor-core operand
 int b2_launch_pad_cast64(const float* src, void* dst, long rows, int C, int sm_count, cudaStream_t s);
 // bias gradient of the output layer: per-slice column sums of fp32 dz [rows, C] -> partB[slice*stride + c]
+// loss head, one thread per row (<= 16 classes): dz as padded bf16 [rows,64], loss / correct / db partials per block
+int b2_launch_loss_head_rows(const float* z, const float* y, void* dzn, float* loss_part, float* correct_part, float* db_part,
+                              int rows, int C, int loss, float inv_global_batch, int blocks, cudaStream_t s);
+int b2_narrow_dgrad_slices(int rows);
+int b2_launch_narrow_dgrad_bf16(const void* dzn, const void* wpad, const void* act, void* out, float* colsum_part, int rows,
+                                int K, int C, cudaStream_t s);
 int b2_launch_colsum_f32_narrow(const float* dz, float* partB, long part_stride, int rows, int C, int slices, cudaStream_t s);
 int b2_colsum_slices(int rows, int N, int sm_count);
 int b2_launch_colsum_bf16(const void* m, float* part, float* out, int rows, int N, int slices, cudaStream_t s);

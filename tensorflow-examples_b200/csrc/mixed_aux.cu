@@ -109,10 +109,12 @@ colsum_finish_kernel(const float* __restrict__ part, float* __restrict__ out, in
   float s = 0.f;
   if (c < N) {
     int z = zg;
-    for (; z + 24 < slices; z += 32) {
-      const float v0 = part[(size_t)z * N + c], v1 = part[(size_t)(z + 8) * N + c], v2 = part[(size_t)(z + 16) * N + c],
-                  v3 = part[(size_t)(z + 24) * N + c];
-      s += v0; s += v1; s += v2; s += v3;
+    for (; z + 8 * 15 < slices; z += 8 * 16) {          // sixteen independent loads in flight, added in slice order
+      float v[16];
+#pragma unroll
+      for (int u = 0; u < 16; ++u) v[u] = part[(size_t)(z + 8 * u) * N + c];
+#pragma unroll
+      for (int u = 0; u < 16; ++u) s += v[u];
     }
     for (; z < slices; z += 8) s += part[(size_t)z * N + c];
   }
@@ -139,17 +141,209 @@ struct ApplyArgs {
 __global__ void __launch_bounds__(256)
 sgd_apply_mixed_kernel(float* __restrict__ params, const float* __restrict__ grads, long P, float lr, ApplyArgs a,
                        float* __restrict__ loss_trace, int* __restrict__ correct_trace, float* __restrict__ global_step) {
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < P; i += (long)gridDim.x * blockDim.x) {
-    const float v = params[i] - lr * grads[i];
-    params[i] = v;
+  // four parameters per thread: every segment of the flat layout starts on a 16-byte boundary and P is a multiple of 4,
+  // so a float4 never straddles two segments
+  const long P4 = P >> 2;
+  for (long q = (long)blockIdx.x * blockDim.x + threadIdx.x; q < P4; q += (long)gridDim.x * blockDim.x) {
+    const long i = q << 2;
+    float4 p = reinterpret_cast<const float4*>(params)[q];
+    const float4 g = reinterpret_cast<const float4*>(grads)[q];
+    p.x -= lr * g.x; p.y -= lr * g.y; p.z -= lr * g.z; p.w -= lr * g.w;
+    reinterpret_cast<float4*>(params)[q] = p;
 #pragma unroll
-    for (int s = 0; s < B2_MAX_LAYERS; ++s)
-      if (s < a.n_seg && i >= a.off[s] && i < a.off[s] + a.size[s]) a.wb[s][i - a.off[s]] = __float2bfloat16_rn(v);
+    for (int s = 0; s < B2_MAX_LAYERS; ++s) {
+      if (s < a.n_seg && i >= a.off[s] && i < a.off[s] + a.size[s]) {
+        const long j = i - a.off[s];
+        __nv_bfloat16* w = a.wb[s] + j;
+        if (j + 4 <= a.size[s] && (j & 3) == 0) {
+          const __nv_bfloat162 lo = __floats2bfloat162_rn(p.x, p.y), hi = __floats2bfloat162_rn(p.z, p.w);
+          *reinterpret_cast<uint2*>(w) = make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi));
+        } else {
+          const float v[4] = {p.x, p.y, p.z, p.w};
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            if (j + u < a.size[s]) w[u] = __float2bfloat16_rn(v[u]);
+        }
+      }
+    }
   }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     if (loss_trace) *loss_trace = grads[P];
     if (correct_trace) *correct_trace = (int)(grads[P + 1] + 0.5f);
     *global_step += 1.0f;
+  }
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// Loss head of the bf16 path, one THREAD per row (<= 16 classes): softmax / loss / argmax / dz exactly as
+// loss_head_kernel composes them (distributed.py:99-102,117-118), and in the same pass
+//   * dz written as the zero-padded bf16 [rows, 64] operand the tensor-core products of the output layer read,
+//   * the column sums of dz (BiasAdd gradient of the output layer) as one partial row per block.
+// Replaces three launches (warp-per-row head, fp32 -> padded bf16 cast, 5-block column sum: 59 + 5 + 58 us at 65536 rows).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+loss_head_rows_kernel(const float* __restrict__ z, const float* __restrict__ y_, __nv_bfloat16* __restrict__ dzn,
+                      float* __restrict__ loss_part, float* __restrict__ correct_part, float* __restrict__ db_part,
+                      int rows, int C, int loss_kind, float inv_B) {
+  __shared__ float sh[8][18];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float db[16];
+#pragma unroll
+  for (int c = 0; c < 16; ++c) db[c] = 0.f;
+  float loss_acc = 0.f, corr_acc = 0.f;
+  for (long row = (long)blockIdx.x * blockDim.x + threadIdx.x; row < rows; row += (long)gridDim.x * blockDim.x) {
+    float zv[16], t[16], d[16];
+#pragma unroll
+    for (int c = 0; c < 16; ++c) {
+      zv[c] = c < C ? z[row * C + c] : -INFINITY;
+      t[c] = c < C ? y_[row * C + c] : 0.f;
+      d[c] = 0.f;
+    }
+    if (loss_kind == B2_LOSS_SSE_SUM) {
+      float l = 0.f;
+#pragma unroll
+      for (int c = 0; c < 16; ++c)
+        if (c < C) { const float e = zv[c] - t[c]; l = fmaf(e, e, l); d[c] = 2.0f * e; }
+      loss_acc += l;
+    } else {
+      float m = zv[0];
+#pragma unroll
+      for (int c = 1; c < 16; ++c) m = fmaxf(m, zv[c]);
+      float e[16], ssum = 0.f;
+#pragma unroll
+      for (int c = 0; c < 16; ++c) { e[c] = c < C ? expf(zv[c] - m) : 0.f; ssum += e[c]; }
+      const float inv = 1.0f / ssum;                         // softmax = exp(z - max) * (1 / sum)   [TF1]
+      float l = 0.f, sy = 0.f, bv = -INFINITY, lv = -INFINITY;
+      int bi = 0, li = 0;
+#pragma unroll
+      for (int c = 0; c < 16; ++c) {
+        if (c < C) {
+          const float yv = e[c] * inv;
+          l -= t[c] * logf(yv);                              // un-fused log(softmax), distributed.py:102
+          sy += t[c];
+          if (yv > bv) { bv = yv; bi = c; }                  // first index wins ties (argmax)
+          if (t[c] > lv) { lv = t[c]; li = c; }
+          e[c] = yv;
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < 16; ++c)
+        if (c < C) d[c] = (e[c] * sy - t[c]) * inv_B;
+      loss_acc += l;
+      corr_acc += (bi == li) ? 1.0f : 0.0f;
+    }
+    uint32_t w[8];
+#pragma unroll
+    for (int c = 0; c < 16; c += 2) {
+      const __nv_bfloat162 h = __floats2bfloat162_rn(d[c], d[c + 1]);
+      w[c >> 1] = *reinterpret_cast<const uint32_t*>(&h);
+      db[c] += d[c];
+      db[c + 1] += d[c + 1];
+    }
+    uint4* o = reinterpret_cast<uint4*>(dzn + row * NARROW);   // 64 bf16 = 128 B per row
+    o[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    o[1] = make_uint4(w[4], w[5], w[6], w[7]);
+#pragma unroll
+    for (int q = 2; q < 8; ++q) o[q] = make_uint4(0u, 0u, 0u, 0u);
+  }
+  // block sums in a fixed order: shuffle tree over the lanes, then the eight warps in order
+#pragma unroll
+  for (int c = 0; c < 16; ++c) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) db[c] += __shfl_xor_sync(0xffffffffu, db[c], o);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    loss_acc += __shfl_xor_sync(0xffffffffu, loss_acc, o);
+    corr_acc += __shfl_xor_sync(0xffffffffu, corr_acc, o);
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int c = 0; c < 16; ++c) sh[warp][c] = db[c];
+    sh[warp][16] = loss_acc;
+    sh[warp][17] = corr_acc;
+  }
+  __syncthreads();
+  if (threadIdx.x < 18) {
+    float v = 0.f;
+#pragma unroll
+    for (int wq = 0; wq < 8; ++wq) v += sh[wq][threadIdx.x];
+    if (threadIdx.x < 16) db_part[(size_t)blockIdx.x * 16 + threadIdx.x] = v;
+    else if (threadIdx.x == 16) loss_part[blockIdx.x] = (loss_kind == B2_LOSS_SSE_SUM) ? v : v * inv_B;
+    else correct_part[blockIdx.x] = v;
+  }
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// Input gradient of the 10-wide output layer on the bf16 path (TF1 MatMul gradient, transpose_b, then SigmoidGrad):
+//   dz_prev[r][j] = bf16( (sum_c dz[r][c] * W[j][c]) * a[r][j] * (1 - a[r][j]) )        r < rows, j < K (4096)
+// with K = 10 in the reduction this is an element-wise pass over two 512 MB matrices, not a GEMM: run through the
+// tensor-core kernel (K padded to 64) it was epilogue-bound (398 us at 65536 x 4096); here every thread owns 8 columns
+// (their 8 x C weights live in registers), streams rows, and also produces the column sums of the ROUNDED outputs (the
+// bias gradient of the layer below) as one partial row per 128-row block.
+// grid = (K / 512, ceil(rows / 128)), 256 threads = 64 column groups x 4 row lanes.
+// ---------------------------------------------------------------------------------------------
+constexpr int ND_COLS = 512, ND_ROWS = 128;
+
+template <int CT>   // classes rounded up to an even number: the weights of a thread's 8 columns live in 8 x CT registers
+__global__ void __launch_bounds__(256, 2)
+narrow_dgrad_bf16_kernel(const __nv_bfloat16* __restrict__ dzn, const __nv_bfloat16* __restrict__ wpad,
+                         const __nv_bfloat16* __restrict__ act, __nv_bfloat16* __restrict__ out,
+                         float* __restrict__ colsum_part, int rows, int K) {
+  __shared__ float sh[4][ND_COLS + 8];
+  const int cg = threadIdx.x & 63, rl = threadIdx.x >> 6;
+  const int j0 = blockIdx.x * ND_COLS + cg * 8;
+  const bool col_ok = j0 < K;                                   // K is a multiple of 8
+  float w[8][CT];
+#pragma unroll
+  for (int u = 0; u < 8; ++u) {
+    uint4 q0 = make_uint4(0u, 0u, 0u, 0u), q1 = q0;
+    if (col_ok) {
+      const uint4* wp = reinterpret_cast<const uint4*>(wpad + (size_t)(j0 + u) * NARROW);
+      q0 = wp[0]; q1 = wp[1];
+    }
+    const uint32_t ww[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+    for (int c = 0; c < CT / 2; ++c) { w[u][2 * c] = bf_lo(ww[c]); w[u][2 * c + 1] = bf_hi(ww[c]); }
+  }
+  float cs[8];
+#pragma unroll
+  for (int u = 0; u < 8; ++u) cs[u] = 0.f;
+  const int r_begin = blockIdx.y * ND_ROWS, r_end = min(rows, r_begin + ND_ROWS);
+#pragma unroll 2
+  for (int r = r_begin + rl; r < r_end; r += 4) {
+    const uint4* dp = reinterpret_cast<const uint4*>(dzn + (size_t)r * NARROW);
+    const uint4 d0 = dp[0], d1 = dp[1];
+    uint4 av = make_uint4(0u, 0u, 0u, 0u);
+    if (col_ok) av = *reinterpret_cast<const uint4*>(act + (size_t)r * K + j0);
+    const uint32_t dd[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+    float dz[CT];                                               // classes >= C are zero in dzn and in wpad
+#pragma unroll
+    for (int c = 0; c < CT / 2; ++c) { dz[2 * c] = bf_lo(dd[c]); dz[2 * c + 1] = bf_hi(dd[c]); }
+    const uint32_t aa[4] = {av.x, av.y, av.z, av.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int u = 0; u < 8; u += 2) {
+      float g0 = 0.f, g1 = 0.f;
+#pragma unroll
+      for (int c = 0; c < CT; ++c) { g0 = fmaf(dz[c], w[u][c], g0); g1 = fmaf(dz[c], w[u + 1][c], g1); }
+      const float a0 = bf_lo(aa[u >> 1]), a1 = bf_hi(aa[u >> 1]);
+      const __nv_bfloat162 h = __floats2bfloat162_rn(g0 * a0 * (1.0f - a0), g1 * a1 * (1.0f - a1));   // SigmoidGrad
+      o[u >> 1] = *reinterpret_cast<const uint32_t*>(&h);
+      cs[u] += bf_lo(o[u >> 1]);
+      cs[u + 1] += bf_hi(o[u >> 1]);
+    }
+    if (col_ok) *reinterpret_cast<uint4*>(out + (size_t)r * K + j0) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+  if (colsum_part == nullptr) return;
+#pragma unroll
+  for (int u = 0; u < 8; ++u) sh[rl][cg * 8 + u] = cs[u];
+  __syncthreads();
+  for (int j = threadIdx.x; j < ND_COLS; j += 256) {
+    const int col = blockIdx.x * ND_COLS + j;
+    if (col < K) colsum_part[(size_t)blockIdx.y * K + col] = ((sh[0][j] + sh[1][j]) + sh[2][j]) + sh[3][j];
   }
 }
 
@@ -179,6 +373,40 @@ int b2_launch_pad_cast64(const float* src, void* dst, long rows, int C, int sm_c
   if (blocks > 8L * sm_count) blocks = 8L * sm_count;
   if (blocks < 1) blocks = 1;
   mx::pad_cast64_kernel<<<(int)blocks, 256, 0, s>>>(src, reinterpret_cast<__nv_bfloat16*>(dst), rows, C);
+  MX_CHECK();
+  return B2_OK;
+}
+
+int b2_launch_loss_head_rows(const float* z, const float* y, void* dzn, float* loss_part, float* correct_part, float* db_part,
+                              int rows, int C, int loss, float inv_global_batch, int blocks, cudaStream_t s) {
+  if (C > 16) { b2_set_error("loss_head_rows: C must be <= 16"); return B2_ERR_ARG; }
+  mx::loss_head_rows_kernel<<<blocks, 256, 0, s>>>(z, y, reinterpret_cast<__nv_bfloat16*>(dzn), loss_part, correct_part, db_part,
+                                                   rows, C, loss, inv_global_batch);
+  MX_CHECK();
+  return B2_OK;
+}
+
+// dz_prev = (dzn . wpad^T) * act * (1 - act) for the narrow output layer; colsum_part (may be NULL) gets one partial row of
+// column sums per 128-row block: finish with b2_launch_colsum_finish(part, out, K, b2_narrow_dgrad_slices(rows))
+int b2_narrow_dgrad_slices(int rows) { return (rows + mx::ND_ROWS - 1) / mx::ND_ROWS; }
+int b2_launch_narrow_dgrad_bf16(const void* dzn, const void* wpad, const void* act, void* out, float* colsum_part, int rows,
+                                int K, int C, cudaStream_t s) {
+  if (K % 8 || C > 16) { b2_set_error("narrow_dgrad_bf16: K must be a multiple of 8 and C <= 16"); return B2_ERR_ARG; }
+  const dim3 grid((K + mx::ND_COLS - 1) / mx::ND_COLS, (rows + mx::ND_ROWS - 1) / mx::ND_ROWS);
+  const __nv_bfloat16* d = reinterpret_cast<const __nv_bfloat16*>(dzn);
+  const __nv_bfloat16* w = reinterpret_cast<const __nv_bfloat16*>(wpad);
+  const __nv_bfloat16* a = reinterpret_cast<const __nv_bfloat16*>(act);
+  __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+  switch ((C + 1) / 2) {
+    case 1: mx::narrow_dgrad_bf16_kernel<2><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
+    case 2: mx::narrow_dgrad_bf16_kernel<4><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
+    case 3: mx::narrow_dgrad_bf16_kernel<6><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
+    case 4: mx::narrow_dgrad_bf16_kernel<8><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
+    case 5: mx::narrow_dgrad_bf16_kernel<10><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
+    case 6: mx::narrow_dgrad_bf16_kernel<12><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
+    case 7: mx::narrow_dgrad_bf16_kernel<14><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
+    default: mx::narrow_dgrad_bf16_kernel<16><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
+  }
   MX_CHECK();
   return B2_OK;
 }
@@ -227,8 +455,9 @@ int b2_launch_sgd_apply_mixed(float* params, const float* grads, long P, float l
     a.size[i] = i < n_seg ? size[i] : 0;
     a.wb[i] = i < n_seg ? reinterpret_cast<__nv_bfloat16*>(wb[i]) : nullptr;
   }
-  long blocks = (P + 255) / 256;
+  long blocks = (P / 4 + 255) / 256;
   if (blocks > 8L * sm_count) blocks = 8L * sm_count;
+  if (blocks < 1) blocks = 1;
   mx::sgd_apply_mixed_kernel<<<(int)blocks, 256, 0, s>>>(params, grads, P, lr, a, loss_trace, correct_trace, global_step);
   MX_CHECK();
   return B2_OK;
