@@ -311,15 +311,10 @@ int enqueue_forward_mixed(b2_ctx* c, const float* x, const float* y, int rows, f
   float* head = c->scratch + c->head_part_off;
   {
     timed_scope t(c, B2_K_LOSS_HEAD, s);
-    if (c->dims[n] <= 16) {
-      // one thread per row: also writes dz as the padded bf16 operand of the output layer's tensor-core products and
-      // the per-block column sums of dz (its bias gradient)
-      rc = b2_launch_loss_head_rows(c->z_last, y, c->dzn, head, head + c->head_blocks, c->scratch + c->head_db_off, rows,
-                                    c->dims[n], c->loss, inv_B, c->head_blocks, s);
-    } else {
-      rc = b2_launch_loss_head(c->z_last, y, c->dz[0], head, head + c->head_blocks, rows, c->dims[n], c->loss, inv_B,
-                               c->head_blocks, s);
-    }
+    // one thread per row (b2_create limits this path to <= 16 classes): also writes dz as the padded bf16 operand of the
+    // output layer's tensor-core products and the per-block column sums of dz (its bias gradient)
+    rc = b2_launch_loss_head_rows(c->z_last, y, c->dzn, head, head + c->head_blocks, c->scratch + c->head_db_off, rows,
+                                  c->dims[n], c->loss, inv_B, c->head_blocks, s);
   }
   if (rc) return rc;
   c->launches++;
@@ -336,15 +331,7 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
   const int L = n - 1;
   const int slices = narrow_slices(c, rows);
   float* pw = c->scratch + c->part_off[L];
-  float* pb = pw + round4(w_size(c, L));
-  const bool head_rows = c->dims[n] <= 16;     // the row-thread loss head already left dzn and the db partials
-  if (!head_rows) {
-    timed_scope t(c, B2_K_MIXED_AUX, s);
-    rc = b2_launch_pad_cast64(c->dz[0], c->dzn, rows, c->dims[n], c->sm_count, s);
-    if (!rc) rc = b2_launch_colsum_f32_narrow(c->dz[0], pb, part_stride(c, L), rows, c->dims[n], slices, s);   // BiasAdd grad
-    if (rc) return rc;
-    c->launches += 2;
-  }
+  // (the loss head already left dz as the padded bf16 operand dzn and the bias-gradient partials)
   {
     // dW_out partials = a^T . dz   (MatMul grad, transpose_a), K = batch cut into `slices` fixed pieces
     timed_scope t(c, B2_K_GEMM_WGRAD, s);
@@ -354,21 +341,13 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
   if (rc) return rc;
   c->launches++;
   // dz_prev = (dz . W_out^T) * a(1-a)   (MatMul grad transpose_b + SigmoidGrad)
-  const bool narrow_dgrad = c->dims[n] <= 16 && c->dims[L] % 8 == 0 && c->act == B2_ACT_SIGMOID;
-  int colsum_slices = (rows + 31) / 32;       // partial rows the dgrad left in colsum_part (bias gradient of layer L-1)
-  bool colsum_pending;
-  if (narrow_dgrad) {
-    // ten classes in the reduction: an element-wise pass on the CUDA cores, not a GEMM
+  // ten classes in the reduction: an element-wise pass on the CUDA cores, not a GEMM; it also leaves the column sums of
+  // its output (bias gradient of layer L-1) as one partial row per 128-row block
+  int colsum_slices = b2_narrow_dgrad_slices(rows);
+  bool colsum_pending = true;
+  {
     timed_scope t(c, B2_K_GEMM_DGRAD, s);
     rc = b2_launch_narrow_dgrad_bf16(c->dzn, c->wb[L], c->ab[L - 1], c->dzb[0], c->colsum_part, rows, c->dims[L], c->dims[n], s);
-    colsum_pending = true;
-    colsum_slices = b2_narrow_dgrad_slices(rows);
-  } else {
-    // the reduction runs over the 64 padded classes on the tensor cores
-    timed_scope t(c, B2_K_GEMM_DGRAD, s);
-    rc = b2_launch_gemm_bf16_ex(c->dzn, 0, c->wb[L], 0, rows, c->dims[L], 64, 1, nullptr, c->ab[L - 1], c->dzb[0],
-                                c->dims[L], c->dims[L], 1, 0, fused_colsum(c, L) ? c->colsum_part : nullptr, c->sm_count, s);
-    colsum_pending = fused_colsum(c, L);
   }
   if (rc) return rc;
   c->launches++;
@@ -430,16 +409,14 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
   a.part_off[0] = c->part_off[L];
   a.pstride[0] = part_stride(c, L);
   a.splits[0] = slices;
-  if (head_rows) {
-    // the bias gradient comes from the loss head's per-block partials: a reduce "layer" of its own
-    a.b_size[0] = 0;
-    a.n_layers = 2;
-    a.w_off[1] = 0; a.w_size[1] = 0;
-    a.b_off[1] = c->b_off[L]; a.b_size[1] = b_size(c, L);
-    a.part_off[1] = c->head_db_off;
-    a.pstride[1] = 16;
-    a.splits[1] = c->head_blocks;
-  }
+  // the bias gradient comes from the loss head's per-block partials: a reduce "layer" of its own
+  a.b_size[0] = 0;
+  a.n_layers = 2;
+  a.w_off[1] = 0; a.w_size[1] = 0;
+  a.b_off[1] = c->b_off[L]; a.b_size[1] = b_size(c, L);
+  a.part_off[1] = c->head_db_off;
+  a.pstride[1] = 16;
+  a.splits[1] = c->head_blocks;
   a.P = c->P;
   a.head_part_off = c->head_part_off;
   a.head_blocks = c->head_blocks;

@@ -251,7 +251,6 @@ int b2_launch_loss_head_rows(const float* z, const float* y, void* dzn, float* l
 int b2_narrow_dgrad_slices(int rows);
 int b2_launch_narrow_dgrad_bf16(const void* dzn, const void* wpad, const void* act, void* out, float* colsum_part, int rows,
                                 int K, int C, cudaStream_t s);
-int b2_launch_colsum_f32_narrow(const float* dz, float* partB, long part_stride, int rows, int C, int slices, cudaStream_t s);
 int b2_colsum_slices(int rows, int N, int sm_count);
 int b2_launch_colsum_bf16(const void* m, float* part, float* out, int rows, int N, int slices, cudaStream_t s);
 int b2_launch_sgd_apply_mixed(float* params, const float* grads, long P, float lr, int n_seg, const long* off,

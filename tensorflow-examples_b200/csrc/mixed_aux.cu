@@ -2,7 +2,6 @@
 // (BASELINE.json configs[4], 784-4096-4096-10): everything whose shape is not a dense contraction.
 //   cast_bf16_kernel      fp32 -> bf16 (inputs x each step; weights inside the SGD apply)
 //   pad_cast64_kernel     fp32 [rows,C<=16] -> bf16 [rows,64]: the 10-wide output layer as a tensor-core operand
-//   colsum_f32_narrow     bias gradient of the output layer (fp32 dz), per-slice partials
 //   colsum_bf16_kernel    bias gradient of a hidden layer: column sums of a bf16 [rows,N] matrix (two stages)
 //   sgd_apply_mixed_kernel  var -= lr*grad on the fp32 masters + refresh of the bf16 weight copies
 // All reductions use fixed slices and a fixed order (no float atomics).
@@ -32,8 +31,7 @@ cast_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
 
 // ---------------------------------------------------------------------------------------------
 // The 10-wide output layer (distributed.py:98) is run on the tensor cores too, padded to 64 columns:
-// pad_cast64 makes bf16 [rows,64] copies of W_out [K,10] and of dz_out [rows,10]; its bias gradient
-// (column sums of the fp32 dz) is reduced here in fixed slices.
+// pad_cast64 makes the bf16 [K,64] copy of W_out [K,10] (dz_out arrives padded from loss_head_rows_kernel).
 // ---------------------------------------------------------------------------------------------
 constexpr int NARROW = 64;
 
@@ -53,25 +51,6 @@ pad_cast64_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst
       w[u] = *reinterpret_cast<const uint32_t*>(&h);
     }
     reinterpret_cast<uint4*>(dst)[i] = make_uint4(w[0], w[1], w[2], w[3]);
-  }
-}
-
-__global__ void __launch_bounds__(256)
-colsum_f32_narrow_kernel(const float* __restrict__ dz, float* __restrict__ partB, long part_stride, int rows, int C,
-                         int rows_per_slice) {
-  __shared__ float sh[16][17];
-  const int c = threadIdx.x & 15, sub = threadIdx.x >> 4;            // 16 columns x 16 row sub-slices
-  const int r0 = blockIdx.x * rows_per_slice, r1 = min(rows, r0 + rows_per_slice);
-  float s = 0.f;
-  if (c < C)
-    for (int r = r0 + sub; r < r1; r += 16) s += dz[(size_t)r * C + c];
-  sh[sub][c] = s;
-  __syncthreads();
-  if (sub == 0 && c < C) {
-    float t = 0.f;
-#pragma unroll
-    for (int u = 0; u < 16; ++u) t += sh[u][c];
-    partB[(size_t)blockIdx.x * part_stride + c] = t;
   }
 }
 
@@ -407,15 +386,6 @@ int b2_launch_narrow_dgrad_bf16(const void* dzn, const void* wpad, const void* a
     case 7: mx::narrow_dgrad_bf16_kernel<14><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
     default: mx::narrow_dgrad_bf16_kernel<16><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
   }
-  MX_CHECK();
-  return B2_OK;
-}
-
-int b2_launch_colsum_f32_narrow(const float* dz, float* partB, long part_stride, int rows, int C, int slices,
-                                cudaStream_t s) {
-  if (C > 16) { b2_set_error("colsum_f32_narrow: C must be <= 16"); return B2_ERR_ARG; }
-  const int rps = (rows + slices - 1) / slices;
-  mx::colsum_f32_narrow_kernel<<<slices, 256, 0, s>>>(dz, partB, part_stride, rows, C, rps);
   MX_CHECK();
   return B2_OK;
 }
