@@ -742,7 +742,6 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
     }
     if (s3_ldn) {
       B2_ALLOC(c->s3_dz, 3L * max_local_batch * s3_ldn / 2 + 8);
-      cudaMemset(c->s3_dz, 0, (size_t)(3L * max_local_batch * s3_ldn / 2 + 8) * sizeof(float));   // pad columns stay zero
     }
     B2_ALLOC(c->dz[0], (long)max_local_batch * maxw);
     if (n_layers > 1) B2_ALLOC(c->dz[1], (long)max_local_batch * maxw);
