@@ -678,7 +678,7 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
     c->part_off[l] = soff;
     soff += sp * part_stride(c, l);
   }
-  c->head_blocks = 2 * c->sm_count;
+  c->head_blocks = 4 * c->sm_count;   // also the capacity of the narrow-head kernel's loss / correct partials (one per CTA)
   {
     const int cap = (max_local_batch + 7) / 8;
     if (c->head_blocks > cap) c->head_blocks = cap;

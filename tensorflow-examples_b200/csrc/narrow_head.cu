@@ -49,7 +49,7 @@ __device__ __forceinline__ float warp_sum(float v) {
 
 // CH = classes per thread of a row pair = ceil(C / 2), a template parameter so that no issue slot is spent on padding
 template <int CH>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, 3)   // 80 registers: three CTAs per SM overlap each other's load / compute phases
 narrow_head_kernel(Args p) {
   extern __shared__ __align__(16) float smem[];
   const int K = p.K, C = p.C;
@@ -334,8 +334,9 @@ bool b2_narrow_head_applies(int K, int C) { return K >= 1 && K <= nh::KMAX && C 
 
 // number of CTAs (= number of partials written) for `rows` rows
 int b2_narrow_head_grid(int rows, int sm_count) {
+  // one tile per CTA while that stays within four CTAs' worth of partials per SM (three are resident at a time)
   const int tiles = (rows + nh::TR - 1) / nh::TR;
-  const int cap = 2 * sm_count;
+  const int cap = 4 * sm_count;
   return tiles < cap ? (tiles < 1 ? 1 : tiles) : cap;
 }
 

@@ -94,3 +94,35 @@ def test_distributed_py_writes_tensorboard_scalars(cuda_device, tmp_path):
     assert len(tags["cost"]) == 10 and len(tags["accuracy"]) == 10          # 1000 rows / batch 100
     assert [s for s, _ in tags["cost"]] == list(range(10))
     assert all(0.0 <= a <= 1.0 for _, a in tags["accuracy"])
+
+
+def test_distributed_py_tf_op_seeds_save_restore(cuda_device, tmp_path):
+    """--tf_op_seeds draws W1, W2 with the restated tf.random_normal stream (distributed.py:83-86); --save_path /
+    --restore_path carry the variables from one run into the next (the reference keeps no checkpoint)."""
+    from oracle import tf1_random
+    rows, test_rows, bs = 1100, 500, 100
+    common = ["--ps_hosts=127.0.0.1:2222", "--worker_hosts=127.0.0.1:2223", "--job_name=worker", "--task_index=0",
+              "--train_rows=%d" % rows, "--test_rows=%d" % test_rows, "--noshuffle", "--data_dir=/nonexistent"]
+    ckpt = str(tmp_path / "vars.npz")
+    r1 = _run_worker(common + ["--training_epochs=1", "--tf_op_seeds=11,17", "--save_path=" + ckpt])
+    assert r1.returncode == 0, r1.stderr[-2000:]
+    # the oracle from the same generator stream
+    x, y = synthetic.make_pool(rows + test_rows)
+    Ws = [tf1_random.random_normal((784, 100), 2, 11), tf1_random.random_normal((100, 10), 2, 17)]
+    bsz = [np.zeros(100, np.float32), np.zeros(10, np.float32)]
+    g = oracle.TF1Graph([784, 100, 10], oracle.ACT_SIGMOID, oracle.LOSS_SOFTMAX_CE, Ws, bsz)
+    cost = None
+    for i in range(rows // bs):
+        cost, _ = g.train_step(x[i * bs:(i + 1) * bs], y[i * bs:(i + 1) * bs], 0.001)
+    final1 = [l for l in r1.stdout.splitlines() if l.startswith("Final Computed Cost: ")][0]
+    assert abs(float(final1.split(": ")[1]) - float(cost)) <= 0.011, (final1, float(cost))
+    with np.load(ckpt) as d:
+        assert np.abs(d["W0"] - g.W[0]).max() <= 1e-4 and np.abs(d["W1"] - g.W[1]).max() <= 1e-4
+        assert float(d["global_step"]) == float(rows // bs)
+    # second run continues from the checkpoint: its first epoch is the oracle's second
+    r2 = _run_worker(common + ["--training_epochs=1", "--restore_path=" + ckpt])
+    assert r2.returncode == 0, r2.stderr[-2000:]
+    for i in range(rows // bs):
+        cost, _ = g.train_step(x[i * bs:(i + 1) * bs], y[i * bs:(i + 1) * bs], 0.001)
+    final2 = [l for l in r2.stdout.splitlines() if l.startswith("Final Computed Cost: ")][0]
+    assert abs(float(final2.split(": ")[1]) - float(cost)) <= 0.011, (final2, float(cost))
