@@ -20,7 +20,7 @@ void b2_set_error(const char* fmt, ...) {
 
 extern "C" const char* b2_last_error(void) { return g_err; }
 extern "C" const char* b2_version(void) {
-  return "b2mlp 0.2 sm_100a (fp32 layer kernels, fused 784->10 step, NCCL + NVLink peer-memory data parallel)";
+  return "b2mlp 0.3 sm_100a (fused 784->10 step, fp32 layers incl. tcgen05 three-plane split, bf16 tcgen05 path, NVLink in-kernel gradient exchange + NCCL)";
 }
 
 // ---------------------------------------------------------------------------------------------
