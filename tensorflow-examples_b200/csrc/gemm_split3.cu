@@ -479,7 +479,7 @@ void b2_gemm_split3_plan(int M, int N, int K, int max_splits, int sm_count, int*
   const int num_kb = (K + BLOCK_K - 1) / BLOCK_K;
   const long tp = (N + BLOCK_P - 1) / BLOCK_P;
   long best_cost = -1;
-  for (int bq = MAX_BLOCK_Q; bq >= 128; bq -= 16) {
+  for (int bq = MAX_BLOCK_Q; bq >= 32; bq -= 16) {      // narrow tiles only win when the long side is short (few tiles)
     const long tq = (M + bq - 1) / bq;
     long S = 1;
     if (max_splits > 1) {
