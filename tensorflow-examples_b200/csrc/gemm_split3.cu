@@ -168,6 +168,11 @@ gemm_split3_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
           --pf_ahead;
           const int f = it % F_STAGES, ps = it % P_STAGES;
           const int k0 = kb * BLOCK_K;
+          // the fp32 tile first: its staging slot frees up (conversion of k-block i-2 done) before the P slot does
+          mbar_wait(&f_empty[f], ((it / F_STAGES) & 1) ^ 1);
+          mbar_expect_tx(&f_full[f], (uint32_t)(BQ * BLOCK_K * 4));
+          if (p.q_mn) tma_load_2d(sm_f32 + f * F_STAGE_BYTES, &tmQ, q0, k0, &f_full[f]);    // [32 k rows][BQ] fp32
+          else tma_load_2d(sm_f32 + f * F_STAGE_BYTES, &tmQ, k0, q0, &f_full[f]);           // [BQ rows][32 k] fp32
           // P planes (from L2 mostly): three stages, so the request leaves two k-blocks before the MMAs need it
           mbar_wait(&p_empty[ps], ((it / P_STAGES) & 1) ^ 1);
           mbar_expect_tx(&p_full[ps], P_STAGE_BYTES);
@@ -181,10 +186,6 @@ gemm_split3_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
               tma_load_3d(p_dst, &tmP, k0, p0, pl, &p_full[ps]);
             }
           }
-          mbar_wait(&f_empty[f], ((it / F_STAGES) & 1) ^ 1);
-          mbar_expect_tx(&f_full[f], (uint32_t)(BQ * BLOCK_K * 4));
-          if (p.q_mn) tma_load_2d(sm_f32 + f * F_STAGE_BYTES, &tmQ, q0, k0, &f_full[f]);    // [32 k rows][BQ] fp32
-          else tma_load_2d(sm_f32 + f * F_STAGE_BYTES, &tmQ, k0, q0, &f_full[f]);           // [BQ rows][32 k] fp32
         }
       }
     }
