@@ -168,3 +168,18 @@ def test_device_random_normal_matches_the_oracle(cuda_device, tmp_path):
         np.testing.assert_array_equal(b[l], b2[l])
     tr.close()
     tr2.close()
+
+
+def test_random_normal_writes_exactly_n_values(cuda_device):
+    """A ragged count (not a multiple of the four values per Philox block) must not write past the n-th element."""
+    from oracle import tf1_random
+    from tensorflow_examples_b200 import _ffi
+    lib = _ffi.load_library()
+    buf = torch.full((1024,), 7.0, dtype=torch.float32, device="cuda")
+    for n in (1, 2, 3, 5, 1001):
+        buf.fill_(7.0)
+        _ffi.check(lib, lib.b2_random_normal(buf.data_ptr(), n, 2, 99, 0.0, 1.0, torch.cuda.current_stream().cuda_stream))
+        torch.cuda.synchronize()
+        got = buf.cpu().numpy()
+        assert np.abs(got[:n] - tf1_random.random_normal((n,), 2, 99)).max() <= 2e-6
+        assert (got[n:] == 7.0).all()
