@@ -357,12 +357,12 @@ def main():
         uid = [pkg.DenseTrainer.new_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         tr.init_comm(rank, world, uid[0])
-        if not args.no_peer and tr.param_count <= (1 << 18) - 4:
+        if not args.no_peer and tr.exchange_floats <= (1 << 18):
             # map every rank's gradient buffer over NVLink: the exchange + SGD apply become one kernel
             hs = [None] * world
             dist.all_gather_object(hs, tr.peer_export())
             tr.peer_import(hs)
-        cfg["gradient_exchange"] = "nccl all-reduce + apply" if (args.no_peer or tr.param_count > (1 << 18) - 4) else "pushed over NVLink peer memory inside the reduction kernel ({value, step} cells), fused with the SGD apply"
+        cfg["gradient_exchange"] = "nccl all-reduce + apply" if (args.no_peer or tr.exchange_floats > (1 << 18)) else "pushed over NVLink peer memory inside the reduction kernel ({value, step} cells), fused with the SGD apply"
         if precision == "bf16":
             tr.overlap_exchange(not args.no_overlap)
             cfg["gradient_exchange"] = ("nccl all-reduce after the backward pass + apply" if args.no_overlap else

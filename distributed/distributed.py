@@ -123,9 +123,27 @@ def main(argv):
     model.init_comm(role.rank, role.world, uid)
     if role.world > 1 and FLAGS.peer_exchange:
         # replica_device_setter's ps round trip (distributed.py:63-65) -> gradients summed straight out of
-        # the other workers' GPU memory over NVLink, fused with the SGD apply
-        store.set("b2_peer_%d" % role.rank, model.peer_export())
-        model.peer_import([bytes(store.get("b2_peer_%d" % r)) for r in range(role.world)])
+        # the other workers' GPU memory over NVLink, fused with the SGD apply.  Only when every worker is a
+        # process on THIS node with a GPU of its own; every rank publishes whether each stage worked for it
+        # and all of them take the same branch: peer exchange everywhere, or the NCCL all-reduce everywhere.
+        ok = cl.single_node(cluster) and role.world <= ngpu
+        handle = b"-"                            # "no handle from me"
+        if ok:
+            try:
+                handle = model.peer_export()
+            except b2.B2Error:
+                ok = False
+        store.set("b2_peer_%d" % role.rank, handle)
+        handles = [bytes(store.get("b2_peer_%d" % r)) for r in range(role.world)]
+        ok = ok and all(len(h) == 64 for h in handles)
+        if ok:
+            try:
+                model.peer_import(handles)
+            except b2.B2Error:
+                ok = False
+        store.set("b2_peer_ok_%d" % role.rank, b"1" if ok else b"0")
+        if not all(bytes(store.get("b2_peer_ok_%d" % r)) == b"1" for r in range(role.world)):
+            model.use_peer_exchange(False)      # somebody could not map a peer: everyone stays on NCCL
     if role.world > 1 and FLAGS.async_period > 0:
         model.set_async_period(FLAGS.async_period)
     cl.store_barrier(store, role, "b2_comm_ready")

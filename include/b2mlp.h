@@ -135,8 +135,11 @@ int b2_comm_init(b2_ctx* ctx, int rank, int nranks, const void* unique_id128);
  * per-step variable pull + gradient push through the parameter server (distributed.py:63-65) on an NVSwitch box.
  * Call after b2_comm_init: b2_peer_export writes a 64-byte CUDA IPC handle; gather the handles of all
  * ranks (rank order) and pass the nranks*64 bytes to b2_peer_import on every rank.  All ranks must be
- * processes on one node with peer access between their GPUs; otherwise b2_peer_import fails and the
- * NCCL path stays in use.
+ * processes on one node with peer access between their GPUs, one GPU per rank; otherwise b2_peer_import fails
+ * and the NCCL path stays in use (b2_set_option(B2_OPT_NO_PEER_EXCHANGE, 1) on EVERY rank once any rank failed:
+ * the ranks must take the same path).  The exchange kernels wait for a peer's values by polling and give up
+ * (device trap -> the next call returns B2_ERR_CUDA) after 2^26 polls, a few seconds: do not let two ranks share
+ * one GPU and do not stall one rank (debugger, long host-side pause between enqueued steps) while others run.
  */
 int b2_peer_export(b2_ctx* ctx, void* handle_out64);
 int b2_peer_import(b2_ctx* ctx, const void* handles);
@@ -151,7 +154,9 @@ int b2_peer_import(b2_ctx* ctx, const void* handles);
  *   the loss head's mean divides by global_batch (distributed.py:102 reduce_mean over the whole batch).
  * loss_trace_dev[s]    <- the PRE-update loss of step s over the global batch (what the reference fetches)
  * correct_trace_dev[s] <- number of rows of the global batch whose argmax matches the label's (distributed.py:117)
- * Either trace pointer may be NULL.
+ * Either trace pointer may be NULL.  x_pool_dev must be 16-byte aligned when dims[0] is a multiple of 4 (rows are
+ * fetched with bulk copies / TMA / 128-bit loads); both pools must be float-aligned.  Misaligned pointers are
+ * rejected with B2_ERR_ARG.
  */
 int b2_train_steps(b2_ctx* ctx, const void* x_pool_dev, const void* y_pool_dev, long pool_rows,
                    int local_batch, long global_batch, int n_steps, long first_row, float lr,
@@ -183,7 +188,8 @@ int b2_session_run_train(b2_ctx* ctx, const float* x_host, const float* y_host, 
  * latency-critical loop that cannot take the device-wide synchronisation an allocation implies, or
  * a host whose own memory pool already holds all of the device memory.  b2_create() allocates, so
  * those callers use this instead and pass every input and output themselves:
- *   x_dev [rows,784], y_dev [rows,10]   this call's batch (device, float32, row-major)
+ *   x_dev [rows,784], y_dev [rows,10]   this call's batch (device, float32, row-major; x_dev 16-byte aligned,
+ *                                       e.g. not a view at an odd float offset -- rejected with B2_ERR_ARG)
  *   W_dev [784,10], b_dev [10]          parameters, updated IN PLACE: var -= lr * grad
  *   loss_dev [1], correct_dev [1]       pre-update mean loss and correct-row count (either may be NULL)
  *   global_batch                        the divisor of the loss mean (= rows on a single GPU)

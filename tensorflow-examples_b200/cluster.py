@@ -35,6 +35,15 @@ def resolve_role(cluster, job_name, task_index):
                 int(port) if port else 2223)
 
 
+def single_node(cluster):
+    """True when every worker address names the same host (peer-memory exchange needs all ranks on one box)."""
+    hosts = {w.rpartition(":")[0] or w for w in cluster.worker}
+    if len(hosts) == 1:
+        return True
+    local = {"127.0.0.1", "localhost", "::1", "0.0.0.0"}
+    return hosts <= local
+
+
 def exchange_unique_id(role, make_id, timeout_s=300):
     """Chief publishes the 128-byte communicator id on a TCP store at worker_hosts[0]; everyone reads it.
 

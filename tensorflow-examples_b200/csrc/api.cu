@@ -957,6 +957,29 @@ extern "C" int b2_peer_import(b2_ctx* ctx, const void* handles) {
   return B2_OK;
 }
 
+// One data-parallel step as every public entry point runs it (b2_train_steps and b2_session_run_train must agree):
+// synchronous mode divides by the global batch and exchanges gradients inside enqueue_step; with B2_OPT_ASYNC_PERIOD
+// the step is local (mean over this rank's rows) and the replicas are averaged every `async_period` local steps.
+static int enqueue_step_dp(b2_ctx* ctx, const float* x, const float* y, int rows, float lr, float* loss_trace,
+                           int* correct_trace, cudaStream_t s) {
+  const bool async = ctx->async_period > 0 && ctx->nranks > 1;
+  int rc = enqueue_step(ctx, x, y, rows, async ? (long)rows : (long)rows * ctx->nranks, lr, loss_trace, correct_trace, s);
+  if (rc) return rc;
+  if (async) {
+    // the workers of the reference update the ps variables independently; here the replicas drift for
+    // `async_period` local steps and are then averaged (parameters, not gradients)
+    ctx->global_step_host += (float)(ctx->nranks - 1);       // global_step counts every worker's update (distributed.py:108)
+    if (++ctx->async_count % ctx->async_period == 0) {
+      B2_NCCL(g_nccl.AllReduce(ctx->params, ctx->params, (size_t)ctx->P, kNcclFloat, kNcclSum, ctx->nccl_comm, s));
+      rc = b2_launch_scale(ctx->params, ctx->P, 1.0f / (float)ctx->nranks, ctx->sm_count, s);
+      if (rc) return rc;
+      ctx->launches++;
+      ctx->wb_stale = 1;
+    }
+  }
+  return B2_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // the hot path
 // ---------------------------------------------------------------------------------------------
@@ -965,6 +988,11 @@ extern "C" int b2_train_steps(b2_ctx* ctx, const void* x_pool_dev, const void* y
                               float* loss_trace_dev, int* correct_trace_dev, b2_stream_t stream) {
   B2_CHECK_ARG(ctx != nullptr, "b2_train_steps: ctx is NULL");
   B2_CHECK_ARG(x_pool_dev && y_pool_dev, "b2_train_steps: NULL data pool");
+  // rows are fetched with bulk / TMA / 128-bit loads: a view at an odd float offset must be rejected here, not trap on the GPU
+  B2_CHECK_ARG((reinterpret_cast<uintptr_t>(x_pool_dev) & 15u) == 0 || ctx->dims[0] % 4 != 0,
+               "b2_train_steps: x_pool_dev must be 16-byte aligned");
+  B2_CHECK_ARG(((reinterpret_cast<uintptr_t>(x_pool_dev) | reinterpret_cast<uintptr_t>(y_pool_dev)) & 3u) == 0,
+               "b2_train_steps: the data pools must be float-aligned");
   B2_CHECK_ARG(local_batch >= 1 && local_batch <= ctx->max_local_batch,
                "b2_train_steps: local_batch %d outside [1, max_local_batch=%d]", local_batch, ctx->max_local_batch);
   B2_CHECK_ARG(global_batch == (long)local_batch * ctx->nranks,
@@ -981,23 +1009,10 @@ extern "C" int b2_train_steps(b2_ctx* ctx, const void* x_pool_dev, const void* y
   const int in = ctx->dims[0], outd = ctx->dims[ctx->n_layers];
   for (int i = 0; i < n_steps; ++i) {
     const long start = (first_row + (long)i * global_batch) % span + (long)ctx->rank * local_batch;
-    const bool async = ctx->async_period > 0 && ctx->nranks > 1;
-    int rc = enqueue_step(ctx, xp + start * in, yp + start * outd, local_batch, async ? (long)local_batch : global_batch, lr,
-                          loss_trace_dev ? loss_trace_dev + i : nullptr,
-                          correct_trace_dev ? correct_trace_dev + i : nullptr, s);
+    int rc = enqueue_step_dp(ctx, xp + start * in, yp + start * outd, local_batch, lr,
+                             loss_trace_dev ? loss_trace_dev + i : nullptr,
+                             correct_trace_dev ? correct_trace_dev + i : nullptr, s);
     if (rc) return rc;
-    if (async) {
-      // the workers of the reference update the ps variables independently; here the replicas drift for
-      // `async_period` local steps and are then averaged (parameters, not gradients)
-      ctx->global_step_host += (float)(ctx->nranks - 1);       // global_step counts every worker's update (distributed.py:108)
-      if (++ctx->async_count % ctx->async_period == 0) {
-        B2_NCCL(g_nccl.AllReduce(ctx->params, ctx->params, (size_t)ctx->P, kNcclFloat, kNcclSum, ctx->nccl_comm, s));
-        rc = b2_launch_scale(ctx->params, ctx->P, 1.0f / (float)ctx->nranks, ctx->sm_count, s);
-        if (rc) return rc;
-        ctx->launches++;
-        ctx->wb_stale = 1;
-      }
-    }
   }
   return B2_OK;
 }
@@ -1006,6 +1021,9 @@ extern "C" int b2_eval(b2_ctx* ctx, const void* x_dev, const void* y_dev, long r
                        long* correct_dev, b2_stream_t stream) {
   B2_CHECK_ARG(ctx != nullptr, "b2_eval: ctx is NULL");
   B2_CHECK_ARG(x_dev && y_dev && rows >= 1, "b2_eval: bad arguments");
+  B2_CHECK_ARG((reinterpret_cast<uintptr_t>(x_dev) & 15u) == 0 || ctx->dims[0] % 4 != 0, "b2_eval: x_dev must be 16-byte aligned");
+  B2_CHECK_ARG(((reinterpret_cast<uintptr_t>(x_dev) | reinterpret_cast<uintptr_t>(y_dev)) & 3u) == 0,
+               "b2_eval: x_dev and y_dev must be float-aligned");
   B2_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t s = (cudaStream_t)stream;
   const float* xp = (const float*)x_dev;
@@ -1046,8 +1064,7 @@ extern "C" int b2_session_run_train(b2_ctx* ctx, const float* x_host, const floa
   cudaStream_t s = ctx->own_stream;
   B2_CUDA(cudaMemcpyAsync(ctx->feed_x, x_host, (size_t)rows * in * sizeof(float), cudaMemcpyHostToDevice, s));
   B2_CUDA(cudaMemcpyAsync(ctx->feed_y, y_host, (size_t)rows * outd * sizeof(float), cudaMemcpyHostToDevice, s));
-  int rc = enqueue_step(ctx, ctx->feed_x, ctx->feed_y, rows, (long)rows * ctx->nranks, lr, ctx->fetch_dev,
-                        (int*)(ctx->fetch_dev + 1), s);
+  int rc = enqueue_step_dp(ctx, ctx->feed_x, ctx->feed_y, rows, lr, ctx->fetch_dev, (int*)(ctx->fetch_dev + 1), s);
   if (rc) return rc;
   B2_CUDA(cudaMemcpyAsync(ctx->fetch_host, ctx->fetch_dev, 2 * sizeof(float), cudaMemcpyDeviceToHost, s));
   B2_CUDA(cudaStreamSynchronize(s));

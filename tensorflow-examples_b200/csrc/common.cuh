@@ -172,8 +172,8 @@ int b2_fused_linear_prepare(void);
 // The thread that owns gradient element i PUSHES {its locally reduced value, step} into cell [parity][my rank][i] of
 // every peer's region (one aligned 8-byte remote store), then polls its own cells [parity][p][i] in local memory until
 // their stamp is this step's and adds the N contributions in rank order (the same sum on every rank), applies SGD.
-// An aligned 8-byte store arrives whole, so there is no separate flag and no fence between data and flag; the
-// critical path is one NVLink one-way trip.  A rank can be at most one step ahead of a peer (it needs the peer's
+// The cell is written and read with ONE .b64 access (single-copy atomic), so there is no separate flag and no fence
+// between data and flag; the critical path is one NVLink one-way trip.  A rank can be at most one step ahead of a peer (it needs the peer's
 // values of step s to finish step s), so slot s & 1 is never overwritten before it was read.
 #define B2_FX_SLOT 7872            /* fused 784->10 kernel: 246 blocks x 32 outputs >= 7852 */
 #define B2_FX_BLOCKS 246
@@ -189,23 +189,26 @@ struct b2_fx_args {
 // sum in rank order.  Called by exactly one thread per element.
 __device__ __forceinline__ float b2_fx_exchange(const b2_fx_args& a, long i, float mine) {
   const size_t slot = ((size_t)a.parity * B2_MAX_PEERS) * (size_t)a.stride;
+  // one 64-bit access per cell: {value (low word), stamp (high word)}.  A .b64 access is single-copy atomic by the PTX
+  // memory model, so a reader can never pair a new stamp with an old value (a .v2.u32 access gives no such guarantee)
+  const unsigned long long cell = ((unsigned long long)a.step1 << 32) | (unsigned long long)__float_as_uint(mine);
   for (int p = 0; p < a.nranks; ++p)
     if (p != a.rank)
-      asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(a.region[p] + slot + (size_t)a.rank * a.stride + i),
-                   "r"(__float_as_uint(mine)), "r"(a.step1)
+      asm volatile("st.relaxed.sys.global.b64 [%0], %1;" ::"l"(a.region[p] + slot + (size_t)a.rank * a.stride + i), "l"(cell)
                    : "memory");
   const unsigned long long* cells = a.region[a.rank] + slot + i;
   float sum = 0.f;
   for (int p = 0; p < a.nranks; ++p) {
     float v = mine;
     if (p != a.rank) {
-      unsigned bits, stamp, spins = 0;
+      unsigned long long got;
+      unsigned spins = 0;
       for (;;) {
-        asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(bits), "=r"(stamp) : "l"(cells + (size_t)p * a.stride) : "memory");
-        if (stamp == a.step1) break;
+        asm volatile("ld.relaxed.sys.global.b64 %0, [%1];" : "=l"(got) : "l"(cells + (size_t)p * a.stride) : "memory");
+        if ((unsigned)(got >> 32) == a.step1) break;
         if (++spins > (1u << 26)) __trap();   // a dead peer must not hang this GPU for ever
       }
-      v = __uint_as_float(bits);
+      v = __uint_as_float((unsigned)got);
     }
     sum += v;
   }

@@ -88,6 +88,13 @@ class DenseTrainer:
         return int(self._lib.b2_param_count(self._h))
 
     @property
+    def exchange_floats(self):
+        """Floats one gradient exchange carries: the flat parameter layout (every W / b segment padded to 16 bytes)
+        plus loss and correct count.  The peer-memory exchange takes at most 2**18 of them."""
+        r4 = lambda v: (v + 3) & ~3
+        return sum(r4(self.dims[l] * self.dims[l + 1]) + r4(self.dims[l + 1]) for l in range(self.n_layers)) + 4
+
+    @property
     def global_step(self):
         """distributed.py:68-70: a float32 counter of applied updates."""
         return np.float32(self._lib.b2_global_step(self._h))
@@ -246,13 +253,16 @@ class DenseTrainer:
         x_host / y_host: host float32 arrays (numpy, or pinned torch CPU tensors).  Synchronous.
         Returns (pre-update cost as np.float32, number of correct rows).
         """
-        xp, rows_x = _host_ptr(x_host, self.dims[0])
-        yp, rows_y = _host_ptr(y_host, self.dims[-1])
+        # the third element keeps a converted copy (python list, float64, non-contiguous view) alive until the C call,
+        # which reads the host buffers synchronously, has returned
+        xp, rows_x, keep_x = _host_ptr(x_host, self.dims[0])
+        yp, rows_y, keep_y = _host_ptr(y_host, self.dims[-1])
         assert rows_x == rows_y, "x and y_ feeds disagree on the number of rows"
         loss = ctypes.c_float()
         correct = ctypes.c_int()
         _ffi.check(self._lib, self._lib.b2_session_run_train(self._h, xp, yp, rows_x, float(lr),
                                                              ctypes.byref(loss), ctypes.byref(correct)))
+        del keep_x, keep_y
         return np.float32(loss.value), int(correct.value)
 
     def evaluate(self, x_dev, y_dev):
@@ -269,16 +279,13 @@ class DenseTrainer:
 
 
 def _host_ptr(a, width):
-    """(pointer, rows) of a host float32 buffer given as numpy array or torch CPU tensor."""
-    if isinstance(a, np.ndarray):
-        if a.dtype != np.float32 or not a.flags["C_CONTIGUOUS"]:
-            a = np.ascontiguousarray(a, dtype=np.float32)
-        _host_ptr.keep = a
-        return ctypes.c_void_p(a.ctypes.data), a.size // width
+    """(pointer, rows, keepalive) of a host float32 buffer given as numpy array, torch CPU tensor or nested list.
+    `keepalive` owns the memory the pointer refers to; the caller holds it for as long as the pointer is in use."""
     torch = _torch()
     if isinstance(a, torch.Tensor):
-        assert not a.is_cuda and a.dtype == torch.float32 and a.is_contiguous()
-        return ctypes.c_void_p(a.data_ptr()), a.numel() // width
-    a = np.ascontiguousarray(a, dtype=np.float32)
-    _host_ptr.keep = a
-    return ctypes.c_void_p(a.ctypes.data), a.size // width
+        assert not a.is_cuda, "feeds are host buffers"
+        if a.dtype != torch.float32 or not a.is_contiguous():
+            a = a.to(torch.float32).contiguous()
+        return ctypes.c_void_p(a.data_ptr()), a.numel() // width, a
+    a = np.ascontiguousarray(a, dtype=np.float32)      # no copy when it already is contiguous float32
+    return ctypes.c_void_p(a.ctypes.data), a.size // width, a
