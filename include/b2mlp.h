@@ -219,7 +219,8 @@ int b2_linear_step_noalloc(const float* x_dev, const float* y_dev, int rows, lon
  *          1: out(bf16) = acc * act * (1 - act)      input gradient through the sigmoid (act: bf16 [M,N])
  *          2: out(fp32) = acc                        weight gradient
  *          3: out(fp32) = acc + bias[N]              forward of a linear layer
- * All matrices are device pointers, 16-byte aligned, leading dimensions multiples of 8.
+ * All matrices are device pointers, 16-byte aligned, leading dimensions multiples of 8.  Through this entry point
+ * every CTA fetches its own operand tiles (no cluster multicast), because the pointers come from outside the library.
  */
 int b2_matmul_bf16(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
                    const float* bias, const void* act, void* out, b2_stream_t stream);

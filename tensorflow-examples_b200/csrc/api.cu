@@ -911,7 +911,7 @@ extern "C" int b2_matmul_bf16(const void* A, int a_mn, const void* B, int b_mn, 
   int dev = 0, sms = 0;
   B2_CUDA(cudaGetDevice(&dev));
   B2_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  return b2_launch_gemm_bf16(A, a_mn, B, b_mn, M, N, K, epi, bias, act, out, sms, (cudaStream_t)stream);
+  return b2_launch_gemm_bf16(A, a_mn, B, b_mn, M, N, K, epi, bias, act, out, sms, (cudaStream_t)stream, /*local_operands=*/0);
 }
 
 extern "C" int b2_peer_export(b2_ctx* ctx, void* handle_out64) {

@@ -220,11 +220,15 @@ int b2_launch_fused_linear_reduce_exchange(const float* scratch, int grid, const
                                            cudaStream_t s);
 
 // ---- launcher (gemm_tcgen05.cu): bf16 tensor-core GEMM with fused epilogues ------------------------------
+// local_operands: the caller vouches that A and B lie in THIS GPU's memory (the context's own buffers).  Only then may
+// CTA pairs share a B tile by TMA multicast; TMA multicast loads here read only this GPU's memory, since on B200 a TMA
+// multicast load from another GPU's memory hung the GPU.  The public b2_matmul_bf16, whose pointers come from outside,
+// passes 0 and every CTA fetches its own tiles.
 int b2_launch_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
-                        const float* bias, const void* act, void* out, int sm_count, cudaStream_t s);
+                        const float* bias, const void* act, void* out, int sm_count, cudaStream_t s, int local_operands = 1);
 int b2_launch_gemm_bf16_ex(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
                            const float* bias, const void* act, void* out, int ldc, int n_store, int ksplits,
-                           long split_stride, float* colsum_part, int sm_count, cudaStream_t s);
+                           long split_stride, float* colsum_part, int sm_count, cudaStream_t s, int local_operands = 1);
 // second stage of the bias gradients whose first stage is fused into the dgrad epilogue: out[c] = sum_z part[z][c]
 // narrow_head.cu: output layer (<= 128 inputs, <= 16 classes) forward + loss head + backward in one kernel
 bool b2_narrow_head_applies(int K, int C);

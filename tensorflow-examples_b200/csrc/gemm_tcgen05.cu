@@ -422,7 +422,7 @@ static int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const tg::Par
 // out: [M, ldc], columns < n_store written.  ksplits > 1 cuts K into slices; slice z writes out + z*split_stride.
 int b2_launch_gemm_bf16_ex(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
                            const float* bias, const void* act, void* out, int ldc, int n_store, int ksplits,
-                           long split_stride, float* colsum_part, int sm_count, cudaStream_t s) {
+                           long split_stride, float* colsum_part, int sm_count, cudaStream_t s, int local_operands) {
   using namespace tg;
   if ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) {
     b2_set_error("gemm_bf16: operands must be 16-byte aligned");
@@ -439,6 +439,7 @@ int b2_launch_gemm_bf16_ex(const void* A, int a_mn, const void* B, int b_mn, int
   const char* env = getenv("B2_GEMM_CLUSTER");
   int CL = (BN == 256 && M > BLOCK_M) ? 2 : 1;
   if (env && *env && BN == 256) CL = atoi(env) == 4 ? 4 : (atoi(env) == 1 ? 1 : 2);
+  if (!local_operands) CL = 1;   // operands of unknown origin: no multicast loads (see common.cuh)
   CUtensorMap ta, tb;
   rc = a_mn ? make_map(&ta, A, K, M, BLOCK_K) : make_map(&ta, A, M, K, BLOCK_M);
   if (rc) return rc;
@@ -459,10 +460,11 @@ int b2_launch_gemm_bf16_ex(const void* A, int a_mn, const void* B, int b_mn, int
 }
 
 int b2_launch_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int M, int N, int K, int epi,
-                        const float* bias, const void* act, void* out, int sm_count, cudaStream_t s) {
+                        const float* bias, const void* act, void* out, int sm_count, cudaStream_t s, int local_operands) {
   if (N % 8) {
     b2_set_error("gemm_bf16: N must be a multiple of 8 (N=%d)", N);
     return B2_ERR_ARG;
   }
-  return b2_launch_gemm_bf16_ex(A, a_mn, B, b_mn, M, N, K, epi, bias, act, out, N, N, 1, 0, nullptr, sm_count, s);
+  return b2_launch_gemm_bf16_ex(A, a_mn, B, b_mn, M, N, K, epi, bias, act, out, N, N, 1, 0, nullptr, sm_count, s,
+                                local_operands);
 }
