@@ -103,6 +103,8 @@ struct b2_ctx {
   void* s3_dz;                     // [3][max_local_batch, round8(widest eligible dims[l+1])]
   int opt_no_split3;               // B2_OPT_NO_SPLIT3
   int opt_no_narrow_head;          // B2_OPT_NO_NARROW_HEAD
+  int opt_no_persistent;           // B2_OPT_NO_PERSISTENT
+  unsigned* grid_bar;              // [2] grid-barrier counters of the persistent multi-step kernels
   int head_used;                   // loss / correct partials written by the last forward (<= head_blocks)
   long head_db_off;                // scratch offset of the row-thread loss head's bias-gradient partials [head_blocks][16]
   long nh_db_off;                  // scratch offset of the narrow-head kernel's bias-gradient partials for layer L-1, or -1
@@ -187,11 +189,12 @@ struct b2_fx_args {
 #ifdef __CUDACC__
 // device side of the exchange: push my value of element i, wait for the peers' values of the same element, return the
 // sum in rank order.  Called by exactly one thread per element.
-__device__ __forceinline__ float b2_fx_exchange(const b2_fx_args& a, long i, float mine) {
-  const size_t slot = ((size_t)a.parity * B2_MAX_PEERS) * (size_t)a.stride;
+// (step1, parity) are passed separately so that a kernel that runs several steps can advance them itself
+__device__ __forceinline__ float b2_fx_exchange_at(const b2_fx_args& a, unsigned step1, int parity, long i, float mine) {
+  const size_t slot = ((size_t)parity * B2_MAX_PEERS) * (size_t)a.stride;
   // one 64-bit access per cell: {value (low word), stamp (high word)}.  A .b64 access is single-copy atomic by the PTX
   // memory model, so a reader can never pair a new stamp with an old value (a .v2.u32 access gives no such guarantee)
-  const unsigned long long cell = ((unsigned long long)a.step1 << 32) | (unsigned long long)__float_as_uint(mine);
+  const unsigned long long cell = ((unsigned long long)step1 << 32) | (unsigned long long)__float_as_uint(mine);
   for (int p = 0; p < a.nranks; ++p)
     if (p != a.rank)
       asm volatile("st.relaxed.sys.global.b64 [%0], %1;" ::"l"(a.region[p] + slot + (size_t)a.rank * a.stride + i), "l"(cell)
@@ -205,7 +208,7 @@ __device__ __forceinline__ float b2_fx_exchange(const b2_fx_args& a, long i, flo
       unsigned spins = 0;
       for (;;) {
         asm volatile("ld.relaxed.sys.global.b64 %0, [%1];" : "=l"(got) : "l"(cells + (size_t)p * a.stride) : "memory");
-        if ((unsigned)(got >> 32) == a.step1) break;
+        if ((unsigned)(got >> 32) == step1) break;
         if (++spins > (1u << 26)) __trap();   // a dead peer must not hang this GPU for ever
       }
       v = __uint_as_float((unsigned)got);
@@ -214,10 +217,28 @@ __device__ __forceinline__ float b2_fx_exchange(const b2_fx_args& a, long i, flo
   }
   return sum;
 }
+__device__ __forceinline__ float b2_fx_exchange(const b2_fx_args& a, long i, float mine) {
+  return b2_fx_exchange_at(a, a.step1, a.parity, i, mine);
+}
 #endif
 int b2_launch_fused_linear_reduce_exchange(const float* scratch, int grid, const b2_fx_args& a, float* grads, float* params,
                                            float lr, float* loss_trace, int* correct_trace, float* global_step, long P,
                                            cudaStream_t s);
+
+// ---- persistent multi-step kernels: n_steps training steps per launch ------------------------------------------
+// fused_linear_ms.cu: the 784 -> 10 step kernel with the step boundary (partial reduction, [exchange], SGD apply, weight
+// reload) inside the kernel, behind two grid barriers; `bar` = 2 counters in device memory, `grid` <= SM count
+int b2_fused_linear_ms_prepare(void);
+int b2_launch_fused_linear_multistep(const float* x_pool, const float* y_pool, long span, long first_row, long global_batch,
+                                     long rank_off, int rows, int n_steps, float* params, float* grads, float* scratch,
+                                     unsigned* bar, int grid, float lr, int loss, float* loss_trace, int* correct_trace,
+                                     float* global_step, long P, const b2_fx_args* fx, cudaStream_t s);
+// tiny_steps.cu: whole runs of tiny models (<= 4 layers, widths <= 16, <= 32 rows per step) by one warp
+bool b2_tiny_steps_applies(int n_layers, const int* dims, int rows);
+int b2_launch_tiny_steps(int n_layers, const int* dims, int act, int loss, const long* w_off, const long* b_off, long P,
+                         const float* x_pool, const float* y_pool, long span, long first_row, long global_batch, int rows,
+                         int n_steps, float lr, float* params, float* grads, float* loss_trace, int* correct_trace,
+                         float* global_step, cudaStream_t s);
 
 // ---- launcher (gemm_tcgen05.cu): bf16 tensor-core GEMM with fused epilogues ------------------------------
 // local_operands: the caller vouches that A and B lie in THIS GPU's memory (the context's own buffers).  Only then may

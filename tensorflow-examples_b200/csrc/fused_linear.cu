@@ -364,7 +364,6 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
 // step's loss / correct count and bumps global_step (distributed.py:107-108).
 // Block = 32 outputs x 4 quarter-sums: thread (o, q) adds CTAs q*ceil(grid/4) .. in order, the four
 // quarters are then combined in order 0,1,2,3 -- the same association on every run.
-constexpr int RED_OUT = 32, RED_Q = 4, RED_N = 7852;
 __global__ void __launch_bounds__(RED_OUT * RED_Q)
 fused_linear_reduce_kernel(const float* __restrict__ scratch, int grid, float* __restrict__ grads,
                            float* __restrict__ params, int apply, float lr,

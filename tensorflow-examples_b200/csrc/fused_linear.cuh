@@ -25,6 +25,9 @@ constexpr int DZ_BUF = TILE_ROWS * DZ_ROW;
 constexpr int NBUF = 3;                        // partial-logit / dz buffers between the pipeline stages
 constexpr long SCRATCH_STRIDE = 7856;           // 7840 dW + 10 db + loss + correct, padded to 16 B
 constexpr int LOSS_IDX = 7850, CORRECT_IDX = 7851;
+// reduction over the per-CTA partials: 7852 outputs, each the sum of four quarter-sums of the grid (CTA order inside a
+// quarter, quarters combined 0,1,2,3) -- the same association in every kernel that reduces them
+constexpr int RED_OUT = 32, RED_Q = 4, RED_N = 7852;
 
 struct __align__(16) Smem {
   float W[K * NC];                             // 31360 B   [784][10], as in global memory
