@@ -59,6 +59,8 @@ enum {
                                  three-plane bf16 split on the tensor cores (gemm_split3.cu) */
   B2_OPT_NO_NARROW_HEAD = 7, /* value 1 (fp32, >= 2 layers): run the output layer as separate forward / loss-head / wgrad /
                                  dgrad kernels instead of the single narrow-head kernel (narrow_head.cu) */
+  B2_OPT_NO_PERSISTENT = 8,  /* value 1: b2_train_steps enqueues every step as separate kernel launches instead of running
+                                 all n_steps inside one persistent kernel where such a kernel exists (784 -> 10; tiny models) */
   B2_OPT_ASYNC_PERIOD = 5     /* value k > 0: emulate the reference's ASYNCHRONOUS parameter-server training
                                  (distributed.py:107-113: plain GradientDescentOptimizer, SyncReplicas commented out):
                                  every worker applies its own gradients locally (mean over ITS batch) and the replicas'
@@ -80,7 +82,8 @@ enum {
   B2_K_GEMM_DGRAD = 9,    /* tcgen05 GEMM: dZ W^T * act'           bf16 path */
   B2_K_GEMM_WGRAD = 10,   /* tcgen05 GEMM: A^T dZ                  bf16 path */
   B2_K_MIXED_AUX = 11,    /* casts, narrow output layer, bias column sums, SGD apply of the bf16 path */
-  B2_KERNEL_CLASSES = 12
+  B2_K_PERSISTENT_STEPS = 12, /* one launch = ALL steps of a b2_train_steps call (simple.py:34-35, distributed.py:145-150) */
+  B2_KERNEL_CLASSES = 13
 };
 
 #define B2_UNIQUE_ID_BYTES 128

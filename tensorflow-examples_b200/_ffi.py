@@ -17,11 +17,12 @@ EXPORTS = [
 UNIQUE_ID_BYTES = 128
 OPT_FORCE_LAYERED = 1
 OPT_KERNEL_TIMING = 2
-KERNEL_CLASSES = 12
+KERNEL_CLASSES = 13
 OPT_NO_PEER_EXCHANGE = 3
 OPT_NO_BUCKET_OVERLAP = 4
 OPT_NO_SPLIT3 = 6
 OPT_NO_NARROW_HEAD = 7
+OPT_NO_PERSISTENT = 8
 OPT_ASYNC_PERIOD = 5
 PEER_HANDLE_BYTES = 64
 

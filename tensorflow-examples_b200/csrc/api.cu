@@ -20,7 +20,7 @@ void b2_set_error(const char* fmt, ...) {
 
 extern "C" const char* b2_last_error(void) { return g_err; }
 extern "C" const char* b2_version(void) {
-  return "b2mlp 0.3 sm_100a (fused 784->10 step, fp32 layers incl. tcgen05 three-plane split, bf16 tcgen05 path, NVLink in-kernel gradient exchange + NCCL)";
+  return "b2mlp 0.4 sm_100a (fused 784->10 step + persistent multi-step kernels, fp32 layers incl. tcgen05 three-plane split, bf16 tcgen05 path, NVLink in-kernel gradient exchange + NCCL)";
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -590,6 +590,7 @@ void free_ctx(b2_ctx* c) {
   cudaFree(c->feed_x);
   cudaFree(c->feed_y);
   cudaFree(c->fetch_dev);
+  cudaFree(c->grid_bar);
   if (c->fetch_host) cudaFreeHost(c->fetch_host);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   if (c->timed) {
@@ -750,11 +751,12 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
   B2_ALLOC(c->global_step_dev, 1);
   B2_ALLOC(c->eval_acc_dev, 2);
   B2_ALLOC(c->fetch_dev, 2);
+  B2_ALLOC(c->grid_bar, 2);
   if (b2_fused_linear_supported(dims[0], dims[1], loss) && n_layers == 1) {
     c->fused_grid = b2_fused_linear_grid(c->sm_count);
     c->fused_stride = b2_fused_linear_stride();
     B2_ALLOC(c->fused_scratch, (long)c->fused_grid * c->fused_stride);
-    if (b2_fused_linear_prepare() != B2_OK) { free_ctx(c); return B2_ERR_CUDA; }
+    if (b2_fused_linear_prepare() != B2_OK || b2_fused_linear_ms_prepare() != B2_OK) { free_ctx(c); return B2_ERR_CUDA; }
   }
 #undef B2_ALLOC
   cudaError_t e = cudaMemset(c->params, 0, (size_t)c->P * sizeof(float));
@@ -787,6 +789,7 @@ extern "C" int b2_set_option(b2_ctx* ctx, int option, int value) {
     case B2_OPT_NO_NARROW_HEAD: ctx->opt_no_narrow_head = value ? 1 : 0; return B2_OK;
     case B2_OPT_NO_SPLIT3: ctx->opt_no_split3 = value ? 1 : 0; return B2_OK;
     case B2_OPT_NO_BUCKET_OVERLAP: ctx->opt_no_overlap = value ? 1 : 0; return B2_OK;
+    case B2_OPT_NO_PERSISTENT: ctx->opt_no_persistent = value ? 1 : 0; return B2_OK;
     case B2_OPT_ASYNC_PERIOD:
       B2_CHECK_ARG(value >= 0, "b2_set_option: async period must be >= 0");
       ctx->async_period = value;
@@ -809,7 +812,7 @@ extern "C" const char* b2_kernel_class_name(int k) {
   static const char* names[B2_KERNEL_CLASSES] = {"dense_fwd", "loss_head", "wgrad", "dgrad", "reduce_apply",
                                                  "fused_linear_step", "fused_linear_reduce", "allreduce_apply",
                                                  "gemm_fwd_tcgen05", "gemm_dgrad_tcgen05", "gemm_wgrad_tcgen05",
-                                                 "mixed_aux"};
+                                                 "mixed_aux", "persistent_steps"};
   return (k >= 0 && k < B2_KERNEL_CLASSES) ? names[k] : "?";
 }
 
@@ -980,6 +983,50 @@ static int enqueue_step_dp(b2_ctx* ctx, const float* x, const float* y, int rows
   return B2_OK;
 }
 
+// All n_steps in ONE launch where a persistent kernel exists for the model: the reference's hot loops (simple.py:34-35,
+// distributed.py:145-150) run inside the kernel.  Returns B2_NOT_PERSISTENT when the per-step path must be used.
+constexpr int B2_NOT_PERSISTENT = -1;
+static int enqueue_persistent(b2_ctx* c, const float* xp, const float* yp, long span, long first_row, int local_batch,
+                              long global_batch, int n_steps, float lr, float* loss_trace, int* correct_trace, cudaStream_t s) {
+  if (c->opt_no_persistent || c->opt_force_layered || c->precision != B2_PREC_FP32 || n_steps < 1) return B2_NOT_PERSISTENT;
+  if (c->nranks > 1 && c->async_period > 0) return B2_NOT_PERSISTENT;
+  if (c->nranks == 1 && b2_tiny_steps_applies(c->n_layers, c->dims, local_batch)) {
+    timed_scope t(c, B2_K_PERSISTENT_STEPS, s);
+    int rc = b2_launch_tiny_steps(c->n_layers, c->dims, c->act, c->loss, c->w_off, c->b_off, c->P, xp, yp, span, first_row,
+                                  global_batch, local_batch, n_steps, lr, c->params, c->grads, loss_trace, correct_trace,
+                                  c->global_step_dev, s);
+    if (rc) return rc;
+    c->launches += 1;
+    c->global_step_host += (float)n_steps;
+    return B2_OK;
+  }
+  if (use_fused_linear(c)) {
+    const bool use_peer = c->nranks > 1 && c->peer_ready && !c->opt_no_peer;
+    if (c->nranks > 1 && !use_peer) return B2_NOT_PERSISTENT;       // NCCL exchange: one launch sequence per step
+    b2_fx_args fx;
+    memset(&fx, 0, sizeof(fx));
+    if (use_peer) {
+      fx.rank = c->rank; fx.nranks = c->nranks; fx.stride = c->peer_stride;
+      fx.step1 = c->peer_step + 1;
+      fx.parity = (int)(c->peer_step & 1u);
+      for (int p = 0; p < c->nranks; ++p) fx.region[p] = (unsigned long long*)c->peer_base[p];
+    }
+    const int tr = b2_fused_linear_tile_rows();
+    int grid = (local_batch + tr - 1) / tr;
+    if (grid > c->fused_grid) grid = c->fused_grid;
+    timed_scope t(c, B2_K_PERSISTENT_STEPS, s);
+    int rc = b2_launch_fused_linear_multistep(xp, yp, span, first_row, global_batch, (long)c->rank * local_batch, local_batch,
+                                              n_steps, c->params, c->grads, c->fused_scratch, c->grid_bar, grid, lr, c->loss,
+                                              loss_trace, correct_trace, c->global_step_dev, c->P, use_peer ? &fx : nullptr, s);
+    if (rc) return rc;
+    if (use_peer) c->peer_step += (unsigned)n_steps;
+    c->launches += 1;
+    c->global_step_host += (float)n_steps;
+    return B2_OK;
+  }
+  return B2_NOT_PERSISTENT;
+}
+
 // ---------------------------------------------------------------------------------------------
 // the hot path
 // ---------------------------------------------------------------------------------------------
@@ -1007,6 +1054,11 @@ extern "C" int b2_train_steps(b2_ctx* ctx, const void* x_pool_dev, const void* y
   const float* xp = (const float*)x_pool_dev;
   const float* yp = (const float*)y_pool_dev;
   const int in = ctx->dims[0], outd = ctx->dims[ctx->n_layers];
+  {
+    int rc = enqueue_persistent(ctx, xp, yp, span, first_row, local_batch, global_batch, n_steps, lr, loss_trace_dev,
+                                correct_trace_dev, s);
+    if (rc != B2_NOT_PERSISTENT) return rc;
+  }
   for (int i = 0; i < n_steps; ++i) {
     const long start = (first_row + (long)i * global_batch) % span + (long)ctx->rank * local_batch;
     int rc = enqueue_step_dp(ctx, xp + start * in, yp + start * outd, local_batch, lr,

@@ -220,6 +220,11 @@ class DenseTrainer:
         separate layer kernels."""
         self.set_option(_ffi.OPT_NO_NARROW_HEAD, 0 if on else 1)
 
+    def persistent_steps(self, on=True):
+        """train_steps() runs all its steps inside ONE kernel launch where a persistent kernel exists for the model
+        (784 -> 10; tiny models such as simple.py's) -- the default -- or enqueues every step's kernels separately."""
+        self.set_option(_ffi.OPT_NO_PERSISTENT, 0 if on else 1)
+
     def overlap_exchange(self, on=True):
         """bf16 path, several ranks: all-reduce each wide layer's weight gradient on a second stream while the backward
         pass of the layers below it runs (default), or send everything in one all-reduce after the backward pass."""
