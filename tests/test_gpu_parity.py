@@ -214,3 +214,44 @@ def test_argument_errors_surface_as_exceptions(cuda_device):
     with pytest.raises(pkg.B2Error):
         tr.train_steps(x, y, 64, 1, first_row=3)  # not a multiple of the batch
     tr.close()
+
+
+# ---- distributed.py:99,102: the un-fused log(softmax) yields NaN when a probability underflows ---------------------
+@pytest.mark.parametrize("path", ["fused-784-10", "fused-per-step", "layered-784-10", "narrow-head-784-100-10", "tiny-4-3",
+                                  "layered-20-3"])
+def test_softmax_underflow_gives_nan_like_the_reference(cuda_device, path):
+    """The reference writes tf.log(tf.nn.softmax(z)) un-fused.  When one class's probability underflows to 0 the row's
+    term is 0 * log(0) = 0 * -inf = NaN and so is the fetched cost; every GPU path keeps that, exactly like the oracle
+    (tests/test_oracle.py::test_unfused_log_softmax_nan_is_reproduced)."""
+    if path in ("fused-784-10", "fused-per-step", "layered-784-10"):
+        dims, act = [784, 10], pkg.ACT_IDENTITY
+    elif path == "narrow-head-784-100-10":
+        dims, act = [784, 100, 10], pkg.ACT_SIGMOID
+    elif path == "tiny-4-3":
+        dims, act = [4, 3], pkg.ACT_IDENTITY
+    else:
+        dims, act = [20, 3], pkg.ACT_IDENTITY
+    batch = 48 if dims[0] > 16 else 8
+    rng = np.random.default_rng(5)
+    x = rng.random((batch, dims[0]), dtype=np.float32)
+    C = dims[-1]
+    y = np.zeros((batch, C), np.float32)
+    y[np.arange(batch), rng.integers(0, C, batch)] = 1.0
+    Ws, bs = synthetic.make_weights(dims, scaled=True)
+    bs[-1][0] = 300.0                         # class 0's logit towers over the rest: exp(z - max) underflows to 0 for them
+    g = oracle.TF1Graph(dims, act, oracle.LOSS_SOFTMAX_CE, Ws, bs)
+    want, _ = g.evaluate(x, y)
+    assert np.isnan(want)
+    tr = pkg.DenseTrainer(dims, act, pkg.LOSS_SOFTMAX_CE, max_local_batch=batch)
+    if path.startswith("layered"):
+        tr.force_layered(True)
+    if path == "fused-per-step":
+        tr.persistent_steps(False)
+    tr.set_params(Ws, bs)
+    xd, yd = torch.from_numpy(x).to(cuda_device), torch.from_numpy(y).to(cuda_device)
+    loss_eval, _ = tr.evaluate(xd, yd)
+    lt, _ = tr.train_steps(xd, yd, batch, 1, lr=0.001)
+    torch.cuda.synchronize()
+    assert np.isnan(float(loss_eval)), (path, loss_eval)
+    assert np.isnan(float(lt[0].item())), (path, float(lt[0].item()))
+    tr.close()

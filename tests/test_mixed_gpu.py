@@ -92,3 +92,75 @@ def test_c5_full_size_runs_and_matches_oracle_forward(cuda_device):
     assert np.isfinite(lt).all() and lt[2] < lt[0], lt
     assert abs(float(lt[0]) - float(np.log(10))) < 0.5          # scaled init: near-uniform predictions
     tr.close()
+
+
+def test_c5_full_width_training_step_matches_bf16_oracle(cuda_device):
+    """One TRAINING step of 784-4096-4096-10 (full widths: the 4096-wide tcgen05 wgrad / dgrad tiles) at batch 2048
+    against the bf16 oracle, including every weight matrix afterwards.  lr is large so that the update (lr * dW) stands
+    well clear of the fp32 rounding of W - lr*dW: the comparison is then a comparison of the gradients themselves."""
+    dims, batch, lr = [784, 4096, 4096, 10], 2048, 4.0
+    x, y = synthetic.make_pool(batch)
+    Ws, bs = synthetic.make_weights(dims, scaled=True)
+    tr = pkg.DenseTrainer(dims, pkg.ACT_SIGMOID, pkg.LOSS_SOFTMAX_CE, max_local_batch=batch, precision="bf16")
+    tr.set_params(Ws, bs)
+    lt, ct = tr.train_steps(torch.from_numpy(x).to(cuda_device), torch.from_numpy(y).to(cuda_device), batch, 1, lr=lr)
+    torch.cuda.synchronize()
+    gW, gb = tr.get_params()
+    tr.close()
+    g = oracle.TF1Graph(dims, oracle.ACT_SIGMOID, oracle.LOSS_SOFTMAX_CE, Ws, bs, precision="bf16")
+    amb = _ambiguous(g, x, 2e-2)
+    lo, co = g.train_step(x, y, lr)
+    assert abs(float(lt[0].item()) - float(lo)) <= 2e-3 * abs(float(lo))
+    assert abs(int(ct[0].item()) - co) <= amb
+    for l in range(3):
+        upd_o, upd_g = g.W[l] - Ws[l], gW[l] - Ws[l]                 # -lr * dW
+        scale = float(np.abs(upd_o).max())
+        assert scale > 0
+        # bf16 operands: one ulp of an activation or of a dz moves a product by 0.4 %; sums of 2048 of them agree far better
+        assert np.abs(upd_g - upd_o).max() <= 2e-2 * scale, ("dW", l, float(np.abs(upd_g - upd_o).max()), scale)
+        rel = np.linalg.norm(upd_g - upd_o) / np.linalg.norm(upd_o)
+        assert rel <= 3e-3, ("dW", l, float(rel))
+        bscale = float(np.abs(g.b[l] - bs[l]).max())
+        assert np.abs((gb[l] - bs[l]) - (g.b[l] - bs[l])).max() <= 2e-2 * bscale + 1e-7, ("db", l)
+
+
+def test_c5_full_size_gradient_is_the_sum_of_its_sub_batch_gradients(cuda_device):
+    """A size-independent property at BASELINE.json's full size (65536 rows), where the CPU oracle is too slow: the mean
+    gradient over the batch equals the mean of the 16 mean gradients of its 4096-row pieces, all taken from the same
+    initial weights.  The divisors are powers of two, so every bf16-rounded dz of the big step is exactly 1/16 of the
+    piece's; only the fp32 accumulation order (batch as the K dimension of the wgrad GEMM: 65536 vs 4096 deep) differs."""
+    dims, batch, pieces, lr = [784, 4096, 4096, 10], 65536, 16, 64.0
+    x, y = synthetic.make_pool(batch)
+    Ws, bs = synthetic.make_weights(dims, scaled=True)
+    xd, yd = torch.from_numpy(x).to(cuda_device), torch.from_numpy(y).to(cuda_device)
+    tr = pkg.DenseTrainer(dims, pkg.ACT_SIGMOID, pkg.LOSS_SOFTMAX_CE, max_local_batch=batch, precision="bf16")
+    W0 = [torch.from_numpy(w).to(cuda_device) for w in Ws]
+
+    def update(rows, first_row):
+        tr.set_params(Ws, bs)
+        lt, _ = tr.train_steps(xd, yd, rows, 1, first_row=first_row, lr=lr)
+        torch.cuda.synchronize()
+        out = []
+        for l in range(3):
+            W = torch.empty_like(W0[l])
+            b = torch.empty(dims[l + 1], dtype=torch.float32, device=cuda_device)
+            pkg._ffi.check(tr._lib, tr._lib.b2_params_get(tr._h, l, W.data_ptr(), b.data_ptr(), tr._stream()))
+            torch.cuda.synchronize()
+            out.append((W - W0[l]).double())
+        return out, float(lt[0].item())
+
+    big, loss_big = update(batch, 0)
+    acc, loss_acc = [torch.zeros_like(b) for b in big], 0.0
+    sub = batch // pieces
+    for i in range(pieces):
+        u, lo = update(sub, i * sub)
+        loss_acc += lo
+        for l in range(3):
+            acc[l] += u[l]
+    assert abs(loss_big - loss_acc / pieces) <= 1e-5 * abs(loss_big)
+    for l in range(3):
+        mean = acc[l] / pieces
+        scale = float(big[l].abs().max())
+        diff = float((big[l] - mean).abs().max())
+        assert scale > 0 and diff <= 2e-3 * scale, (l, diff, scale)
+    tr.close()

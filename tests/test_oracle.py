@@ -42,6 +42,18 @@ def test_simple_py_known_answer():
     assert abs(W64[0] - (-0.99999707)) < 1e-8 and abs(b64[0] - 0.99999139) < 1e-8
 
 
+def test_simple_py_1000_steps_equals_the_line_tensorflow_publishes():
+    """An EXTERNAL pin: TensorFlow 1.x's own "Getting Started" guide lists this very program (the source of
+    simple/simple.py:11-39) run for 1000 steps and prints
+        W: [-0.9999969] b: [ 0.99999082] loss: 5.69997e-11
+    (numpy 1.x spacing / 8 significant digits).  The restatement gives the same float32 values digit for digit."""
+    assert oracle.simple_py_report(1000) == "W: [-0.9999969] b: [0.9999908] loss 5.6999738e-11"
+    W, b, loss, _ = oracle.simple_py(1000)
+    assert "%.7f" % float(W[0]) == "-0.9999969"
+    assert "%.8f" % float(b[0]) == "0.99999082"           # the guide's 8-digit rendering of b
+    assert "%.5e" % float(loss) == "5.69997e-11"           # the guide's 6-digit rendering of the loss
+
+
 def test_simple_py_fixture():
     f = np.load(os.path.join(GOLDEN, "simple_py.npz"))
     W, b, loss, trace = oracle.simple_py()
