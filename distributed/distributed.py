@@ -43,6 +43,8 @@ flags.DEFINE_integer("train_rows", 55000, "synthetic pool: training rows (mnist.
 flags.DEFINE_integer("test_rows", 10000, "synthetic pool: test rows (mnist.test)")
 flags.DEFINE_boolean("shuffle", True, "reshuffle the training pool every epoch, as next_batch does (distributed.py:146)")
 flags.DEFINE_integer("shuffle_seed", 0, "seed of the per-epoch permutation (the reference's is unseeded)")
+flags.DEFINE_string("dump_perm", "", "write the per-epoch row permutations the shuffle drew to this .npy ([epochs, rows] "
+                    "int64), so that a run can be replayed elsewhere (next_batch's own shuffle is unseeded, distributed.py:146)")
 flags.DEFINE_string("logs_path", "", "TensorBoard event directory; the reference hard-codes /tmp/mnist/ (distributed.py:49). "
                     "Empty (default) writes no event files")
 flags.DEFINE_integer("async_period", 0, "k > 0: emulate the reference's asynchronous parameter-server updates -- every worker "
@@ -159,11 +161,14 @@ def main(argv):
     gen = torch.Generator(device=dev)
     gen.manual_seed(FLAGS.shuffle_seed)
     cost = float("nan")
+    perms = []
     start_time = time.time()
     for epoch in range(training_epochs):                                          # distributed.py:141
         if FLAGS.shuffle:
             # mnist.train.next_batch reshuffles every epoch; every worker draws the same permutation
             perm = torch.randperm(num_examples, device=dev, generator=gen)
+            if FLAGS.dump_perm:
+                perms.append(perm.cpu().numpy())
             pool_x, pool_y = train_x[perm].contiguous(), train_y[perm].contiguous()
         else:
             pool_x, pool_y = train_x, train_y
@@ -192,6 +197,8 @@ def main(argv):
     print(report.time_taken_line(time.time() - begin_time, FLAGS.strict_reference_bugs))   # distributed.py:165
     print(report.final_cost_line(cost))                                                    # distributed.py:166
     writer.close()
+    if FLAGS.dump_perm and role.rank == 0:
+        np.save(FLAGS.dump_perm, np.stack(perms) if perms else np.zeros((0, num_examples), np.int64))
     if FLAGS.save_path and role.rank == 0:
         model.save(FLAGS.save_path)
     cl.store_barrier(store, role, "b2_done")

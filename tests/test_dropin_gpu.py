@@ -79,10 +79,13 @@ def test_distributed_py_strict_bug_mode_raises_like_the_reference(cuda_device):
 
 
 def test_distributed_py_writes_tensorboard_scalars(cuda_device, tmp_path):
-    """distributed.py:121-125,138,151: cost and accuracy scalars, one event per step."""
+    """distributed.py:121-125,138,151: cost and accuracy scalars, one event per step -- and the VALUES are the step's
+    pre-update cost and training-batch accuracy, i.e. the oracle's trace."""
     pytest.importorskip("tensorboard")
-    r = _run_worker(["--ps_hosts=a:1", "--worker_hosts=127.0.0.1:2223", "--job_name=worker", "--train_rows=1000",
-                     "--test_rows=200", "--training_epochs=1", "--data_dir=/nonexistent", "--logs_path=%s" % tmp_path])
+    rows, bs = 1000, 100
+    r = _run_worker(["--ps_hosts=a:1", "--worker_hosts=127.0.0.1:2223", "--job_name=worker", "--train_rows=%d" % rows,
+                     "--test_rows=200", "--training_epochs=1", "--data_dir=/nonexistent", "--noshuffle",
+                     "--logs_path=%s" % tmp_path])
     assert r.returncode == 0, r.stderr[-2000:]
     from tensorboard.backend.event_processing.event_file_loader import EventFileLoader
     files = [f for f in os.listdir(tmp_path) if "tfevents" in f]
@@ -93,7 +96,85 @@ def test_distributed_py_writes_tensorboard_scalars(cuda_device, tmp_path):
             tags.setdefault(v.tag, []).append((ev.step, v.simple_value if v.HasField("simple_value") else float(v.tensor.float_val[0])))
     assert len(tags["cost"]) == 10 and len(tags["accuracy"]) == 10          # 1000 rows / batch 100
     assert [s for s, _ in tags["cost"]] == list(range(10))
-    assert all(0.0 <= a <= 1.0 for _, a in tags["accuracy"])
+    x, y = synthetic.make_pool(rows + 200)
+    Ws, bsz = synthetic.make_weights([784, 100, 10], False)
+    g = oracle.TF1Graph([784, 100, 10], oracle.ACT_SIGMOID, oracle.LOSS_SOFTMAX_CE, Ws, bsz)
+    for i in range(rows // bs):
+        lo, co = g.train_step(x[i * bs:(i + 1) * bs], y[i * bs:(i + 1) * bs], 0.001)
+        assert abs(tags["cost"][i][1] - float(lo)) <= 1e-5 * max(1.0, abs(float(lo))), (i, tags["cost"][i], float(lo))
+        assert abs(tags["accuracy"][i][1] - co / float(bs)) <= 1e-6, (i, tags["accuracy"][i], co)
+
+
+def _write_idx(path, arr):
+    import struct
+    arr = np.ascontiguousarray(arr, dtype=np.uint8)
+    with open(path, "wb") as f:
+        f.write(struct.pack(">I", 0x0800 | arr.ndim))
+        f.write(struct.pack(">" + "I" * arr.ndim, *arr.shape))
+        f.write(arr.tobytes())
+
+
+def test_distributed_py_from_idx_files_with_shuffling(cuda_device, tmp_path):
+    """SURVEY 8(f) row 1 (distributed.py:52-55,142,146,164): the drop-in reads the four MNIST IDX files, holds out the
+    first 5000 training rows, reshuffles every epoch like next_batch, and evaluates the test set.  Four small files are
+    written here; the permutations the run drew are exported (--dump_perm) and the oracle replays them."""
+    rng = np.random.default_rng(11)
+    n_train, n_val, n_test, bs, epochs = 1200, 5000, 700, 100, 3
+    tr_img = rng.integers(0, 256, (n_val + n_train, 28, 28), dtype=np.uint8)
+    tr_lab = rng.integers(0, 10, n_val + n_train).astype(np.uint8)
+    te_img = rng.integers(0, 256, (n_test, 28, 28), dtype=np.uint8)
+    te_lab = rng.integers(0, 10, n_test).astype(np.uint8)
+    d = tmp_path / "MNIST_data"
+    d.mkdir()
+    _write_idx(d / "train-images-idx3-ubyte", tr_img)
+    _write_idx(d / "train-labels-idx1-ubyte", tr_lab)
+    _write_idx(d / "t10k-images-idx3-ubyte", te_img)
+    _write_idx(d / "t10k-labels-idx1-ubyte", te_lab)
+    perm_path = str(tmp_path / "perm.npy")
+    r = _run_worker(["--ps_hosts=127.0.0.1:2222", "--worker_hosts=127.0.0.1:2223", "--job_name=worker", "--task_index=0",
+                     "--training_epochs=%d" % epochs, "--data_dir=%s" % d, "--shuffle_seed=3", "--dump_perm=" + perm_path])
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = r.stdout.strip().splitlines()
+    perms = np.load(perm_path)
+    assert perms.shape == (epochs, n_train)
+    for e in range(epochs):
+        assert sorted(perms[e].tolist()) == list(range(n_train))           # a permutation of the 1200 training rows
+    assert not np.array_equal(perms[0], perms[1])                           # reshuffled every epoch
+
+    # what input_data.read_data_sets(one_hot=True) hands the reference: float32 pixel / 255, one-hot labels, 5000 held out
+    def onehot(lab):
+        yy = np.zeros((len(lab), 10), np.float32)
+        yy[np.arange(len(lab)), lab] = 1.0
+        return yy
+    tx = tr_img[n_val:].reshape(n_train, 784).astype(np.float32) * np.float32(1.0 / 255.0)
+    ty = onehot(tr_lab[n_val:])
+    ex = te_img.reshape(n_test, 784).astype(np.float32) * np.float32(1.0 / 255.0)
+    ey = onehot(te_lab)
+    Ws, bsz = synthetic.make_weights([784, 100, 10], False)
+    g = oracle.TF1Graph([784, 100, 10], oracle.ACT_SIGMOID, oracle.LOSS_SOFTMAX_CE, Ws, bsz)
+    per_epoch = n_train // bs
+    want = []
+    for e in range(epochs):
+        px, py = tx[perms[e]], ty[perms[e]]
+        for i in range(per_epoch):
+            lo, _ = g.train_step(px[i * bs:(i + 1) * bs], py[i * bs:(i + 1) * bs], 0.001)
+        want.append(float(lo))                                              # the epoch's last batch is the printed one
+    prog = [ln for ln in out if ln.startswith("Step so far")]
+    assert len(prog) == epochs
+    for e, ln in enumerate(prog):
+        m = re.search(r"Step so far: (\d+),  Epoch so far: +(\d+),  Batch used: +(\d+) of +(\d+),  Cost now: ([0-9.]+),", ln)
+        assert m, ln
+        assert int(m[1]) == (e + 1) * per_epoch and int(m[2]) == e + 1 and int(m[3]) == int(m[4]) == per_epoch
+        assert abs(float(m[5]) - want[e]) <= 1e-4 + 1e-4 * want[e], (ln, want[e])
+    _, correct = g.evaluate(ex, ey)
+    g64 = oracle.TF1Graph([784, 100, 10], oracle.ACT_SIGMOID, oracle.LOSS_SOFTMAX_CE, g.W, g.b, dtype=np.float64)
+    _, z = g64.forward(ex)
+    top2 = np.sort(z, axis=1)[:, -2:]
+    amb = int(((top2[:, 1] - top2[:, 0]) < 1e-3).sum())
+    acc_line = [ln for ln in out if ln.startswith("Acc: ")][0]              # distributed.py:164 on the 700 test rows
+    got_acc = float(acc_line.split(": ")[1])
+    assert abs(got_acc - correct / float(n_test)) <= 0.005 + amb / float(n_test), (acc_line, correct)
+    assert out[-1] == "done with training"
 
 
 def test_distributed_py_tf_op_seeds_save_restore(cuda_device, tmp_path):

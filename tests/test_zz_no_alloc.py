@@ -17,6 +17,7 @@ import pytest
 import torch
 
 import tensorflow_examples_b200 as pkg
+from oracle import tf1_graph as oracle
 from tensorflow_examples_b200 import synthetic
 
 pytestmark = pytest.mark.gpu
@@ -40,6 +41,7 @@ def test_noalloc_step_matches_allocating_path_twice_in_a_row(cuda_device, batch)
     # the existing entry points: context-owned parameters and scratch
     ref = pkg.DenseTrainer(dims, pkg.ACT_IDENTITY, pkg.LOSS_SOFTMAX_CE, max_local_batch=batch)
     ref.set_params(Ws, bs)
+    cpu = oracle.TF1Graph(dims, oracle.ACT_IDENTITY, oracle.LOSS_SOFTMAX_CE, Ws, bs)     # and the CPU oracle beside both
 
     # the caller-owned buffers of the no-allocation path
     W = torch.from_numpy(Ws[0]).to(cuda_device).contiguous()
@@ -62,6 +64,10 @@ def test_noalloc_step_matches_allocating_path_twice_in_a_row(cuda_device, batch)
         tol = W_RTOL * max(1.0, float(np.abs(rW[0]).max()))
         assert np.abs(W.cpu().numpy() - rW[0]).max() <= tol, s
         assert np.abs(b.cpu().numpy() - rb[0]).max() <= tol, s
+        lo, co = cpu.train_step(x[s * batch:(s + 1) * batch], y[s * batch:(s + 1) * batch], lr)
+        assert abs(float(loss.item()) - float(lo)) <= LOSS_RTOL * max(1.0, abs(float(lo))), (s, loss.item(), float(lo))
+        assert abs(int(correct.item()) - co) <= 1, (s, int(correct.item()), co)
+        assert np.abs(W.cpu().numpy() - cpu.W[0]).max() <= tol and np.abs(b.cpu().numpy() - cpu.b[0]).max() <= tol, s
     ref.close()
 
 
@@ -74,4 +80,9 @@ def test_noalloc_rejects_sizes_beyond_its_fixed_scratch(cuda_device):
     assert b"exceeds the fixed-scratch limit" in lib.b2_last_error()
     rc = lib.b2_linear_step_noalloc(None, _ptr(t), 8, 8, 0.001, _ptr(t), _ptr(t), None, None, None)
     assert rc == 1 and b"NULL" in lib.b2_last_error()
+    # a view at an odd float offset: the rows are fetched with 16-byte bulk copies, so this is refused, not run
+    big = torch.zeros(8 * 784 + 8, device=cuda_device)
+    rc = lib.b2_linear_step_noalloc(ctypes.c_void_p(big.data_ptr() + 4), _ptr(t), 8, 8, 0.001, _ptr(t), _ptr(t), None,
+                                    None, None)
+    assert rc == 1 and b"16-byte aligned" in lib.b2_last_error()
     torch.cuda.synchronize(cuda_device)
