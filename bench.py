@@ -264,257 +264,112 @@ def sweep_main(args):
     return 0
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
-    ap.add_argument("--warmup", type=int, default=20)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
-    ap.add_argument("--batch", type=int, default=None, help="rows per GPU per step")
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--no-secondary", action="store_true",
-                    help="skip the second line (scaled-up MLP, c5) that a default 1-GPU run embeds as `secondary`")
-    ap.add_argument("--no-peer", action="store_true", help="multi-GPU: use the NCCL all-reduce instead of the peer-memory kernel")
-    ap.add_argument("--no-overlap", action="store_true",
-                    help="multi-GPU bf16 path: one all-reduce after the backward pass instead of overlapped per-layer buckets")
-    ap.add_argument("--sweep", action="store_true", help="batch-size sweep of c3 / c3 with the SSE head / 784-100-10 instead of the headline line")
-    ap.add_argument("--sweep-out", default=os.path.join(ROOT, "gpurun_out", "sweep.json"))
-    ap.add_argument("--sweep-points", default="c3,c3-sse,c2")
-    ap.add_argument("--sweep-batches", default="256,1024,4096,16384,65536")
-    ap.add_argument("--sweep-cpu", action="store_true", help="sweep: also time the CPU restatements on rank 0")
-    ap.add_argument("--strong", action="store_true", help="sweep: the batch is the GLOBAL batch, split over the ranks")
-    args = ap.parse_args()
-    if args.sweep:
-        return sweep_main(args)
-
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    dims, act, loss, scaled, dbatch, desc, precision = WORKLOADS[args.workload]
-    batch = args.batch or dbatch
+def make_config(workload, batch, world, no_peer=False, no_overlap=False):
+    """The `config` object of the JSON line -- built the same way by both arms, so the driver sees one config."""
+    dims, act, loss, scaled, dbatch, desc, precision = WORKLOADS[workload]
     global_batch = batch * world
-    warmup = max(3, args.warmup)
-    cfg = {"workload": "%s: %s" % (args.workload, desc), "dims": dims, "local_batch": batch,
-           "global_batch": global_batch, "lr": LR, "parallelism": "dp%d" % world}
-
-    # ------------------------------------------------------------------ reference arm (CPU)
-    if args.impl == "reference":
-        if rank != 0:
-            return 0
-        cbatch = min(batch, CPU_SAMPLE_BATCH.get(args.workload, batch))
-        r = cpu_reference_run(dims, act, loss, scaled, cbatch, args.steps, min(warmup, 5), budget_s=90.0)
-        batch = cbatch
-        line = {"impl": "reference", "metric": "training samples/sec", "value": r["value"], "unit": "samples/s",
-                "n_gpus": args.gpus, "steps": r["steps"], "warmup": min(warmup, 5), "ms_per_step": r["ms_per_step"],
-                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-                "data": "synthetic", "config": cfg,
-                "cpu_baseline": {"value": r["value"], "unit": "samples/s", "cores": r["threads"], "kind": r["kind"],
-                                 "sample": "%d steps of %d rows each (one GPU's batch), %s" % (r["steps"], batch, _CPU_KIND[r["kind"]])},
-                "e2e": {"value": r["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
-        return 0
-
-    # ------------------------------------------------------------------ B200 arm
-    import torch
-    import tensorflow_examples_b200 as pkg
-    from tensorflow_examples_b200 import synthetic
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU arm")
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=dev)
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-
-    def max_over_ranks(v):
-        if dist is None:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    # data: fixed-seed host pool, tiled on the device to >= 2 global batches and >= 1.6 GB (>> 126 MB L2)
-    hx, hy = synthetic.make_pool(HOST_POOL_ROWS)
     pool_rows = max(2 * global_batch, 1 << 19)
     pool_rows = ((pool_rows + global_batch - 1) // global_batch) * global_batch
-    reps = (pool_rows + HOST_POOL_ROWS - 1) // HOST_POOL_ROWS
-    x_pool = torch.from_numpy(hx).to(dev).repeat(reps, 1)[:pool_rows].contiguous()
-    y_pool = torch.from_numpy(hy).to(dev).repeat(reps, 1)[:pool_rows].contiguous()
-    cfg["pool_rows"] = pool_rows
-    cfg["l2"] = "inputs larger than L2: %.2f GB pool, consecutive batches" % (pool_rows * BYTES_PER_SAMPLE / 1e9)
+    exchange_floats = sum(((dims[i] * dims[i + 1] + 3) & ~3) + ((dims[i + 1] + 3) & ~3) for i in range(len(dims) - 1)) + 4
+    if world == 1:
+        gx = "none (one GPU)"
+    elif precision == "bf16":
+        gx = ("nccl all-reduce after the backward pass + apply" if no_overlap else
+              "nccl all-reduce per layer bucket on a second stream, overlapped with the backward pass, + apply")
+    elif no_peer or exchange_floats > (1 << 18):
+        gx = "nccl all-reduce + apply"
+    else:
+        gx = "pushed over NVLink peer memory inside the reduction step ({value, step} cells), fused with the SGD apply"
+    return {"workload": "%s: %s" % (workload, desc), "dims": dims, "local_batch": batch, "global_batch": global_batch,
+            "lr": LR, "parallelism": "dp%d" % world, "pool_rows": pool_rows,
+            "l2": "inputs larger than L2: %.2f GB pool, consecutive batches" % (pool_rows * BYTES_PER_SAMPLE / 1e9),
+            "gradient_exchange": gx}
 
-    tr = pkg.DenseTrainer(dims, act, loss, max_local_batch=batch, device=local_rank, precision=precision)
-    Ws, bs = synthetic.make_weights(dims, scaled)
-    tr.set_params(Ws, bs)
-    if world > 1:
-        uid = [pkg.DenseTrainer.new_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(uid, src=0)
-        tr.init_comm(rank, world, uid[0])
+
+class Dist:
+    """rank / world plumbing shared by every workload of one bench.py process."""
+
+    def __init__(self):
+        import torch
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local_rank)
+        self.dev = torch.device("cuda", self.local_rank)
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.init_process_group("nccl", device_id=self.dev)
+            self.dist = dist
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+
+    def max_over_ranks(self, v):
+        if self.dist is None:
+            return v
+        import torch
+        t = torch.tensor([v], dtype=torch.float64, device=self.dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def close(self):
+        if self.dist is not None:
+            self.dist.destroy_process_group()
+
+
+def make_trainer(D, workload, batch, args):
+    """Model on this rank's GPU with the shared initial weights; communicator + peer mapping when there are several ranks."""
+    import tensorflow_examples_b200 as pkg
+    from tensorflow_examples_b200 import synthetic
+    dims, act, loss, scaled, _, _, precision = WORKLOADS[workload]
+    tr = pkg.DenseTrainer(dims, act, loss, max_local_batch=batch, device=D.local_rank, precision=precision)
+    tr.set_params(*synthetic.make_weights(dims, scaled))
+    if args.no_persistent:
+        tr.persistent_steps(False)
+    if D.world > 1:
+        uid = [pkg.DenseTrainer.new_unique_id() if D.rank == 0 else None]
+        D.dist.broadcast_object_list(uid, src=0)
+        tr.init_comm(D.rank, D.world, uid[0])
         if not args.no_peer and tr.exchange_floats <= (1 << 18):
-            # map every rank's gradient buffer over NVLink: the exchange + SGD apply become one kernel
-            hs = [None] * world
-            dist.all_gather_object(hs, tr.peer_export())
+            # map every rank's gradient cells over NVLink: the exchange + SGD apply happen inside the step's own kernel
+            hs = [None] * D.world
+            D.dist.all_gather_object(hs, tr.peer_export())
             tr.peer_import(hs)
-        cfg["gradient_exchange"] = "nccl all-reduce + apply" if (args.no_peer or tr.exchange_floats > (1 << 18)) else "pushed over NVLink peer memory inside the reduction kernel ({value, step} cells), fused with the SGD apply"
         if precision == "bf16":
             tr.overlap_exchange(not args.no_overlap)
-            cfg["gradient_exchange"] = ("nccl all-reduce after the backward pass + apply" if args.no_overlap else
-                                        "nccl all-reduce per layer bucket on a second stream, overlapped with the backward pass, + apply")
+    return tr
 
-    # ---- value: device-resident pool -----------------------------------------------------
-    lt, ct = tr.train_steps(x_pool, y_pool, batch, warmup, first_row=0, lr=LR)
-    torch.cuda.synchronize(dev)
-    first_loss = float(lt[0].item())
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
-        time.sleep(0.3)
-    barrier()
-    torch.cuda.synchronize(dev)
-    l0 = tr.launch_count
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    lt, ct = tr.train_steps(x_pool, y_pool, batch, args.steps, first_row=(warmup * global_batch) % pool_rows, lr=LR)
-    ev1.record()
-    torch.cuda.synchronize(dev)
-    barrier()
-    ms = max_over_ranks(ev0.elapsed_time(ev1))
-    launches = tr.launch_count - l0
-    clocks = sampler.stop() if rank == 0 else None
-    last_loss = float(lt[args.steps - 1].item())
-    value = global_batch * args.steps / (ms / 1e3)
 
-    # ---- roofline: per-kernel device times over the same steps (events on the launch stream) ----
-    tr.kernel_timing(True)
-    tsteps = min(args.steps, 200 if precision == "fp32" else 20)
-    tr.train_steps(x_pool, y_pool, batch, tsteps, first_row=0, lr=LR)
-    kt = tr.kernel_times()
-    tr.kernel_timing(False)
-    total_ms = sum(v[0] for v in kt.values())
-    if precision == "bf16":
-        # tensor-core bound: flops of the three GEMM classes (2*in*out per layer and product)
-        hid = [(dims[i], dims[i + 1]) for i in range(len(dims) - 2)]
-        fl = {"gemm_fwd_tcgen05": sum(2.0 * a * b for a, b in hid) * batch,
-              "gemm_wgrad_tcgen05": sum(2.0 * a * b for a, b in hid) * batch,
-              "gemm_dgrad_tcgen05": sum(2.0 * a * b for a, b in hid[1:]) * batch}
-        gemm_ms = sum(kt[k][0] for k in fl if k in kt) / tsteps
-        gemm_flops = sum(fl.values())
-        peak_tf = 1406.5
-        src = "fallback"
-        try:
-            pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-            peak_tf, src = float(pk["bf16_tflops_sustained"]), "measured (MEASURED_PEAKS.json bf16_tflops_sustained, cuBLAS loop)"
-        except Exception:
-            pass
-        achieved = gemm_flops / (gemm_ms / 1e3) / 1e12
-        roofline = {"bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
-                    "traffic": _traffic_bytes(args.workload), "kernel": "gemm_bf16_kernel (tcgen05; fwd+dgrad+wgrad launches)",
-                    "kernel_ms": gemm_ms, "kernel_share_of_step": gemm_ms * tsteps / total_ms, "peak_source": "of " + src,
-                    "algorithmic_flops_per_step": gemm_flops,
-                    "per_class_tflops": {k: fl[k] / (kt[k][0] / tsteps / 1e3) / 1e12 for k in fl if k in kt},
-                    "kernel_ms_by_class": {k: v[0] / tsteps for k, v in kt.items()}}
+def parity_check(D, tr, workload, batch, x_host, y_host, loss0, correct0):
+    """Outside every timed region: step 0 of this run against the CPU oracle at the GLOBAL batch (rank 0), and -- with
+    several ranks -- a bit-level comparison of the replicas' parameters after all the steps run so far."""
+    import torch
+    dims, act, loss, scaled, _, _, precision = WORKLOADS[workload]
+    out = {}
+    gb = batch * D.world
+    if D.rank == 0 and precision == "bf16" and gb > 2 * HOST_POOL_ROWS:
+        out["oracle"] = "skipped: the 4096-wide forward of %d rows takes minutes in numpy" % gb
+    elif D.rank == 0:
+        from oracle.tf1_graph import TF1Graph
+        from tensorflow_examples_b200 import synthetic
+        Ws, bs = synthetic.make_weights(dims, scaled)
+        g = TF1Graph(dims, act, loss, Ws, bs, precision="bf16" if precision == "bf16" else "fp32")
+        idx = np.arange(gb) % len(x_host)                      # the device pool is the host pool tiled
+        lo, co = g.evaluate(x_host[idx], y_host[idx])          # forward + loss head: the pre-update loss of step 0
+        out["oracle"] = "numpy restatement of the TF1 graph, one process, global batch %d" % gb
+        out["loss_rel"] = abs(loss0 - float(lo)) / max(1.0, abs(float(lo)))
+        out["correct_diff"] = int(correct0) - int(co)
+    Ws, bs = tr.get_params()
+    flat = np.concatenate([w.ravel() for w in Ws] + [b.ravel() for b in bs]).view(np.uint32).astype(np.uint64)
+    chk = int((flat * (np.arange(flat.size, dtype=np.uint64) % np.uint64(65521) + np.uint64(1))).sum() % np.uint64(1 << 62))
+    if D.dist is not None:
+        t = torch.tensor([chk], dtype=torch.int64, device=D.dev)
+        all_t = [torch.zeros_like(t) for _ in range(D.world)]
+        D.dist.all_gather(all_t, t)
+        out["replicas_identical"] = bool(all(int(v.item()) == chk for v in all_t))
     else:
-        dom = max(kt.items(), key=lambda kv: kv[1][0])
-        dom_ms = dom[1][0] / dom[1][1]
-        peak, peak_src = _peaks()
-        achieved = batch * BYTES_PER_SAMPLE / (dom_ms / 1e3) / 1e9
-        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": _traffic_bytes(args.workload), "kernel": dom[0], "kernel_ms": dom_ms,
-                    "kernel_share_of_step": dom[1][0] / total_ms, "peak_source": "of " + peak_src,
-                    "algorithmic_bytes_per_launch": batch * BYTES_PER_SAMPLE,
-                    "kernel_ms_by_class": {k: v[0] / v[1] for k, v in kt.items()}}
-        if args.workload == "c2":
-            # 784-100-10 in fp32 is not HBM-bound: its work is the two 65536x784x100 products, run as six
-            # bf16 tensor-core products each; report the fp32-equivalent rate next to the HBM fraction
-            roofline["fp32_equivalent_tflops"] = value / world * 319600 / 1e12
-            roofline["cuda_core_fp32_peak_tflops_spec"] = FP32_PEAK_TFLOPS
-            roofline["note"] = ("compute-bound model: wide layer = 6 bf16 tcgen05 products per fp32 product (three-plane "
-                                "split, fp32-accurate); the HBM fraction is reported for completeness, it is not the bound")
-
-    # ---- e2e: host feeds through the sess.run-shaped call ------------------------------------
-    e2e = None
-    if not args.no_e2e:
-        in_b, out_b = batch * dims[0] * 4, batch * dims[-1] * 4
-        feeds = []
-        for i in range(2):
-            fx = torch.empty(batch, dims[0], dtype=torch.float32).pin_memory()
-            fy = torch.empty(batch, dims[-1], dtype=torch.float32).pin_memory()
-            src = slice((i * batch) % HOST_POOL_ROWS, (i * batch) % HOST_POOL_ROWS + batch)
-            n = min(batch, HOST_POOL_ROWS)
-            fx[:n].copy_(torch.from_numpy(hx[src][:n]) if batch <= HOST_POOL_ROWS else torch.from_numpy(hx[:n]))
-            fy[:n].copy_(torch.from_numpy(hy[src][:n]) if batch <= HOST_POOL_ROWS else torch.from_numpy(hy[:n]))
-            feeds.append((fx, fy))
-        esteps = max(5, min(args.steps, 50))
-        for i in range(3):
-            tr.run_train(feeds[i % 2][0], feeds[i % 2][1], LR)
-        barrier()
-        torch.cuda.synchronize(dev)
-        t0 = time.perf_counter()
-        for i in range(esteps):
-            tr.run_train(feeds[i % 2][0], feeds[i % 2][1], LR)
-        torch.cuda.synchronize(dev)
-        dt = max_over_ranks(time.perf_counter() - t0)
-        e2e = {"value": global_batch * esteps / dt, "unit": "samples/s", "h2d_bytes_per_step": in_b + out_b,
-               "d2h_bytes_per_step": 8, "steps": esteps, "ms_per_step": 1e3 * dt / esteps,
-               "api": "DenseTrainer.run_train -> b2_session_run_train (pinned host feeds, synchronous)"}
-
-    # ---- cpu_baseline: rank 0, N=1 only, bounded sample -----------------------------------------
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cbatch = min(batch, CPU_SAMPLE_BATCH.get(args.workload, batch))
-        r = cpu_reference_run(dims, act, loss, scaled, cbatch, 400, 2, budget_s=12.0)
-        cpu = {"value": r["value"], "unit": "samples/s", "cores": r["threads"], "kind": r["kind"],
-               "sample": "%d steps of %d rows in %.1f s, %s, all host threads"
-                         % (r["steps"], cbatch, r["seconds"], _CPU_KIND[r["kind"]]),
-               "first_loss_cpu": r["first_loss"], "first_loss_gpu": first_loss}
-
-    secondary, third = None, None
-    if rank == 0 and world == 1 and args.workload == "c3" and args.batch is None and not args.no_secondary:
-        # BASELINE.json quotes the metric on two models; the headline line is the simple.py-style 784->10 model
-        # (HBM-bound), the scaled-up 784-4096-4096-10 bf16 MLP (tensor-core-bound) rides along as `secondary`.
-        tr.close()
-        del x_pool, y_pool
-        torch.cuda.empty_cache()
-        try:
-            r = subprocess.run([sys.executable, os.path.abspath(__file__), "--workload", "c5", "--steps", "20", "--warmup", "3",
-                                "--no-cpu-baseline", "--no-e2e", "--no-secondary"], capture_output=True, text=True, timeout=600)
-            d = json.loads(r.stdout.strip().splitlines()[-1])
-            secondary = {k: d[k] for k in ("metric", "value", "unit", "ms_per_step", "steps", "warmup", "dtype", "config",
-                                           "roofline", "gpu_launches", "loss_first", "loss_last")}
-        except Exception as e:  # the headline line must not depend on the extra one
-            secondary = {"error": repr(e)[:300]}
-        # ... and distributed.py's own 784-100-10 model in fp32 (wide layer on the tensor cores as a three-plane bf16 split)
-        try:
-            r = subprocess.run([sys.executable, os.path.abspath(__file__), "--workload", "c2", "--steps", "100", "--warmup", "10",
-                                "--no-cpu-baseline", "--no-e2e", "--no-secondary"], capture_output=True, text=True, timeout=600)
-            d = json.loads(r.stdout.strip().splitlines()[-1])
-            third = {k: d[k] for k in ("metric", "value", "unit", "ms_per_step", "steps", "warmup", "dtype", "config",
-                                       "roofline", "gpu_launches", "loss_first", "loss_last")}
-        except Exception as e:
-            third = {"error": repr(e)[:300]}
-    if rank == 0:
-        line = {"metric": "training samples/sec", "value": value, "unit": "samples/s", "n_gpus": world,
-                "steps": args.steps, "warmup": warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if precision == "bf16" else "f32",
-                "data": "synthetic", "config": cfg, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
-                "gpu_launches": launches, "loss_first": first_loss, "loss_last": last_loss}
-        if secondary is not None:
-            line["secondary"] = secondary
-        if third is not None:
-            line["distributed_py_model"] = third
-        print(json.dumps(line))
-    tr.close()
-    if dist is not None:
-        dist.destroy_process_group()
-    return 0
-
-
-if __name__ == "__main__":
-    sys.exit(main())
+        out["replicas_identical"] = True
+    out["param_checksum"] = chk
+    return out
