@@ -373,3 +373,144 @@ def parity_check(D, tr, workload, batch, x_host, y_host, loss0, correct0):
         out["replicas_identical"] = True
     out["param_checksum"] = chk
     return out
+
+
+def run_b200(D, args, workload, batch, steps, warmup, hx, hy, with_e2e, with_cpu, with_parity=True):
+    """One workload on this process's GPU (all ranks call it together).  Returns the JSON line's fields (rank 0) or None."""
+    import torch
+    dims, act, loss, scaled, _, desc, precision = WORKLOADS[workload]
+    rank, world, dev = D.rank, D.world, D.dev
+    global_batch = batch * world
+    cfg = make_config(workload, batch, world, args.no_peer, args.no_overlap)
+    pool_rows = cfg["pool_rows"]
+    # data: fixed-seed host pool, tiled on the device to >= 2 global batches and >= 1.6 GB (>> 126 MB L2)
+    reps = (pool_rows + HOST_POOL_ROWS - 1) // HOST_POOL_ROWS
+    x_pool = torch.from_numpy(hx).to(dev).repeat(reps, 1)[:pool_rows].contiguous()
+    y_pool = torch.from_numpy(hy).to(dev).repeat(reps, 1)[:pool_rows].contiguous()
+    tr = make_trainer(D, workload, batch, args)
+
+    # ---- value: device-resident pool -----------------------------------------------------
+    lt, ct = tr.train_steps(x_pool, y_pool, batch, warmup, first_row=0, lr=LR)
+    torch.cuda.synchronize(dev)
+    first_loss, first_correct = float(lt[0].item()), int(ct[0].item())
+    sampler = ClockSampler(D.local_rank)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    D.barrier()
+    torch.cuda.synchronize(dev)
+    l0 = tr.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    lt, ct = tr.train_steps(x_pool, y_pool, batch, steps, first_row=(warmup * global_batch) % pool_rows, lr=LR)
+    ev1.record()
+    torch.cuda.synchronize(dev)
+    D.barrier()
+    ms = D.max_over_ranks(ev0.elapsed_time(ev1))
+    launches = tr.launch_count - l0
+    clocks = sampler.stop() if rank == 0 else None
+    last_loss = float(lt[steps - 1].item())
+    value = global_batch * steps / (ms / 1e3)
+
+    # ---- roofline: per-launch device times over the same steps (events on the launch stream) ----
+    tr.kernel_timing(True)
+    tsteps = min(steps, 200 if precision == "fp32" else 20)
+    tr.train_steps(x_pool, y_pool, batch, tsteps, first_row=0, lr=LR)
+    kt = tr.kernel_times()
+    tr.kernel_timing(False)
+    total_ms = sum(v[0] for v in kt.values())
+    if precision == "bf16":
+        # tensor-core bound: flops of the three GEMM classes (SURVEY.md section 8(a): 2*in*out per layer and product)
+        hid = [(dims[i], dims[i + 1]) for i in range(len(dims) - 2)]
+        fl = {"gemm_fwd_tcgen05": sum(2.0 * a * b for a, b in hid) * batch,
+              "gemm_wgrad_tcgen05": sum(2.0 * a * b for a, b in hid) * batch,
+              "gemm_dgrad_tcgen05": sum(2.0 * a * b for a, b in hid[1:]) * batch}
+        gemm_ms = sum(kt[k][0] for k in fl if k in kt) / tsteps
+        gemm_flops = sum(fl.values())
+        peak_tf, src = 1406.5, "fallback"
+        try:
+            pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            peak_tf, src = float(pk["bf16_tflops_sustained"]), "measured (MEASURED_PEAKS.json bf16_tflops_sustained, cuBLAS loop)"
+        except Exception:
+            pass
+        achieved = gemm_flops / (gemm_ms / 1e3) / 1e12
+        roofline = {"bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
+                    "traffic": _traffic_bytes(workload), "kernel": "gemm_bf16_kernel (tcgen05; fwd+dgrad+wgrad launches)",
+                    "kernel_ms": gemm_ms, "kernel_share_of_step": gemm_ms * tsteps / total_ms, "peak_source": "of " + src,
+                    "algorithmic_flops_per_step": gemm_flops,
+                    "per_class_tflops": {k: fl[k] / (kt[k][0] / tsteps / 1e3) / 1e12 for k in fl if k in kt},
+                    "kernel_ms_by_class": {k: v[0] / tsteps for k, v in kt.items()}}
+    else:
+        dom = max(kt.items(), key=lambda kv: kv[1][0])
+        # steps one launch of the dominant kernel covers: a persistent kernel runs the whole train_steps call
+        steps_per_launch = tsteps // dom[1][1] if dom[0] == "persistent_steps" else 1
+        dom_ms = dom[1][0] / dom[1][1]
+        peak, peak_src = _peaks()
+        bytes_per_launch = steps_per_launch * batch * BYTES_PER_SAMPLE
+        achieved = bytes_per_launch / (dom_ms / 1e3) / 1e9
+        traffic = _traffic_bytes(workload)
+        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": traffic * steps_per_launch if (traffic and steps_per_launch > 1) else traffic,
+                    "kernel": dom[0], "kernel_ms": dom_ms, "steps_per_launch": steps_per_launch,
+                    "kernel_share_of_step": dom[1][0] / total_ms, "peak_source": "of " + peak_src,
+                    "algorithmic_bytes_per_launch": bytes_per_launch,
+                    "kernel_ms_by_class": {k: v[0] / v[1] for k, v in kt.items()}}
+        if workload == "c2":
+            # 784-100-10 in fp32 is not HBM-bound (SURVEY 8(d)): its work is the two 65536x784x100 products, run as six
+            # bf16 tensor-core products each; report the fp32-equivalent rate next to the HBM fraction
+            roofline["fp32_equivalent_tflops"] = value / world * 319600 / 1e12
+            roofline["cuda_core_fp32_peak_tflops_spec"] = FP32_PEAK_TFLOPS
+            roofline["note"] = ("compute-bound model: wide layer = 6 bf16 tcgen05 products per fp32 product (three-plane "
+                                "split, fp32-accurate); the HBM fraction is reported for completeness, it is not the bound")
+
+    # ---- parity (outside the timed regions): oracle at the global batch, replicas bit-identical ------------------
+    parity = parity_check(D, tr, workload, batch, hx, hy, first_loss, first_correct) if with_parity else None
+
+    # ---- e2e: host feeds through the sess.run-shaped call ------------------------------------
+    e2e = None
+    if with_e2e:
+        in_b, out_b = batch * dims[0] * 4, batch * dims[-1] * 4
+        feeds = []
+        for i in range(2):
+            fx = torch.empty(batch, dims[0], dtype=torch.float32).pin_memory()
+            fy = torch.empty(batch, dims[-1], dtype=torch.float32).pin_memory()
+            idx = (np.arange(batch) + i * batch) % HOST_POOL_ROWS
+            fx.copy_(torch.from_numpy(hx[idx]))
+            fy.copy_(torch.from_numpy(hy[idx]))
+            feeds.append((fx, fy))
+        esteps = max(5, min(steps, 50))
+        for i in range(3):
+            tr.run_train(feeds[i % 2][0], feeds[i % 2][1], LR)
+        D.barrier()
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        for i in range(esteps):
+            tr.run_train(feeds[i % 2][0], feeds[i % 2][1], LR)
+        torch.cuda.synchronize(dev)
+        dt = D.max_over_ranks(time.perf_counter() - t0)
+        e2e = {"value": global_batch * esteps / dt, "unit": "samples/s", "h2d_bytes_per_step": in_b + out_b,
+               "d2h_bytes_per_step": 8, "steps": esteps, "ms_per_step": 1e3 * dt / esteps,
+               "api": "DenseTrainer.run_train -> b2_session_run_train (pinned host feeds, synchronous)"}
+
+    # ---- cpu_baseline: rank 0, N=1 only, bounded sample -----------------------------------------
+    cpu = None
+    if with_cpu and rank == 0 and world == 1:
+        cbatch = min(batch, CPU_SAMPLE_BATCH.get(workload, batch))
+        r = cpu_reference_run(dims, act, loss, scaled, cbatch, 400, 2, budget_s=12.0)
+        cpu = {"value": r["value"], "unit": "samples/s", "cores": r["threads"], "kind": r["kind"],
+               "sample": "%d steps of %d rows in %.1f s, %s, all host threads"
+                         % (r["steps"], cbatch, r["seconds"], _CPU_KIND[r["kind"]]),
+               "first_loss_cpu": r["first_loss"], "first_loss_gpu": first_loss}
+    tr.close()
+    del x_pool, y_pool
+    torch.cuda.empty_cache()
+    if rank != 0:
+        return None
+    line = {"metric": "training samples/sec", "value": value, "unit": "samples/s", "n_gpus": world,
+            "steps": steps, "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if precision == "bf16" else "f32",
+            "data": "synthetic", "config": cfg, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
+            "gpu_launches": launches, "loss_first": first_loss, "loss_last": last_loss}
+    if parity is not None:
+        line["parity"] = parity
+    return line
