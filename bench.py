@@ -514,3 +514,134 @@ def run_b200(D, args, workload, batch, steps, warmup, hx, hy, with_e2e, with_cpu
     if parity is not None:
         line["parity"] = parity
     return line
+
+
+def embedded_sweep(D, args, hx, hy, steps=100, warmup=10):
+    """BASELINE.json configs[2] asks for a batch sweep 256-65536: five points for 784->10 and for distributed.py's
+    784-100-10, device-resident pool, CUDA events around `steps` steps after `warmup`, one GPU.  Points below ~16384 rows
+    are latency-bound (their HBM fraction is printed for completeness only)."""
+    import torch
+    import tensorflow_examples_b200 as pkg
+    from tensorflow_examples_b200 import synthetic
+    peak_gbs, _ = _peaks()
+    pool_rows = 1 << 19
+    reps = pool_rows // HOST_POOL_ROWS
+    x_pool = torch.from_numpy(hx).to(D.dev).repeat(reps, 1).contiguous()
+    y_pool = torch.from_numpy(hy).to(D.dev).repeat(reps, 1).contiguous()
+    rows = []
+    for name in ("c3", "c2"):
+        dims, act, loss, scaled, prec, flops, lr = SWEEP_POINTS[name]
+        for B in (256, 1024, 4096, 16384, 65536):
+            tr = pkg.DenseTrainer(dims, act, loss, max_local_batch=B, device=D.local_rank, precision=prec)
+            tr.set_params(*synthetic.make_weights(dims, scaled))
+            if args.no_persistent:
+                tr.persistent_steps(False)
+            tr.train_steps(x_pool, y_pool, B, warmup, first_row=0, lr=lr)
+            torch.cuda.synchronize(D.dev)
+            l0 = tr.launch_count
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            tr.train_steps(x_pool, y_pool, B, steps, first_row=(warmup * B) % pool_rows, lr=lr)
+            e1.record()
+            torch.cuda.synchronize(D.dev)
+            ms = e0.elapsed_time(e1)
+            sps = B * steps / (ms / 1e3)
+            rows.append({"point": name, "dims": dims, "global_batch": B, "us_per_step": 1e3 * ms / steps,
+                         "samples_per_s": sps, "hbm_frac": sps * BYTES_PER_SAMPLE / (peak_gbs * 1e9),
+                         "launches_per_step": (tr.launch_count - l0) / steps})
+            tr.close()
+    del x_pool, y_pool
+    torch.cuda.empty_cache()
+    return rows
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=None, help="rows per GPU per step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true",
+                    help="skip the extra lines a default run embeds: `secondary` (scaled-up MLP, c5), `distributed_py_model` "
+                         "(784-100-10, c2) and, on one GPU, the batch `sweep`")
+    ap.add_argument("--no-peer", action="store_true", help="multi-GPU: use the NCCL all-reduce instead of the peer-memory kernel")
+    ap.add_argument("--no-overlap", action="store_true",
+                    help="multi-GPU bf16 path: one all-reduce after the backward pass instead of overlapped per-layer buckets")
+    ap.add_argument("--no-persistent", action="store_true", help="one launch sequence per step instead of the multi-step kernels")
+    ap.add_argument("--sweep", action="store_true", help="batch-size sweep of c3 / c3 with the SSE head / 784-100-10 instead of the headline line")
+    ap.add_argument("--sweep-out", default=os.path.join(ROOT, "gpurun_out", "sweep.json"))
+    ap.add_argument("--sweep-points", default="c3,c3-sse,c2")
+    ap.add_argument("--sweep-batches", default="256,1024,4096,16384,65536")
+    ap.add_argument("--sweep-cpu", action="store_true", help="sweep: also time the CPU restatements on rank 0")
+    ap.add_argument("--strong", action="store_true", help="sweep: the batch is the GLOBAL batch, split over the ranks")
+    args = ap.parse_args()
+    if args.sweep:
+        return sweep_main(args)
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    dims, act, loss, scaled, dbatch, desc, precision = WORKLOADS[args.workload]
+    batch = args.batch or dbatch
+    warmup = max(3, args.warmup)
+    cfg = make_config(args.workload, batch, world, args.no_peer, args.no_overlap)
+
+    # ------------------------------------------------------------------ reference arm (CPU)
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        cbatch = min(batch, CPU_SAMPLE_BATCH.get(args.workload, batch))
+        r = cpu_reference_run(dims, act, loss, scaled, cbatch, args.steps, min(warmup, 5), budget_s=90.0)
+        line = {"impl": "reference", "metric": "training samples/sec", "value": r["value"], "unit": "samples/s",
+                "n_gpus": args.gpus, "steps": r["steps"], "warmup": min(warmup, 5), "ms_per_step": r["ms_per_step"],
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic", "config": cfg,
+                "cpu_baseline": {"value": r["value"], "unit": "samples/s", "cores": r["threads"], "kind": r["kind"],
+                                 "sample": "%d steps of %d rows each (one GPU's batch), %s" % (r["steps"], cbatch, _CPU_KIND[r["kind"]])},
+                "e2e": {"value": r["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return 0
+
+    # ------------------------------------------------------------------ B200 arm
+    import torch
+    from tensorflow_examples_b200 import synthetic
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU arm")
+    D = Dist()
+    hx, hy = synthetic.make_pool(HOST_POOL_ROWS)
+    line = run_b200(D, args, args.workload, batch, args.steps, warmup, hx, hy, with_e2e=not args.no_e2e,
+                    with_cpu=not args.no_cpu_baseline)
+    if args.workload == "c3" and args.batch is None and not args.no_secondary:
+        # BASELINE.json quotes the metric on two models; the headline line is the simple.py-style 784->10 model
+        # (HBM-bound), the scaled-up 784-4096-4096-10 bf16 MLP (tensor-core-bound) rides along as `secondary`, and
+        # distributed.py's own 784-100-10 in fp32 as `distributed_py_model` -- at every N, so the scaling run has them.
+        keep = ("metric", "value", "unit", "n_gpus", "ms_per_step", "steps", "warmup", "dtype", "config", "roofline",
+                "gpu_launches", "loss_first", "loss_last", "parity", "scaling")
+        extra = {}
+        for key, wl, st, wu in (("secondary", "c5", 20, 3), ("distributed_py_model", "c2", 100, 10)):
+            try:
+                d = run_b200(D, args, wl, WORKLOADS[wl][4], st, wu, hx, hy, with_e2e=False, with_cpu=False)
+                if d is not None:
+                    extra[key] = {k: d[k] for k in keep if k in d}
+            except Exception as e:   # the headline line must not depend on the extra ones
+                if world > 1:
+                    raise            # ... but a rank that dropped out of a collective cannot be papered over
+                extra[key] = {"error": repr(e)[:300]}
+        if world == 1:
+            try:
+                extra["sweep"] = embedded_sweep(D, args, hx, hy)
+            except Exception as e:
+                extra["sweep"] = {"error": repr(e)[:300]}
+        if line is not None:
+            line.update(extra)
+    if rank == 0:
+        print(json.dumps(line))
+    D.close()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
