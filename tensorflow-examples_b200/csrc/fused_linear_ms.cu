@@ -12,6 +12,8 @@
 //   4. grid barrier b, every CTA reloads W (31 KB, from L2) and b
 // The producer warp does not take part in any of this: it keeps streaming the NEXT step's rows into the ring
 // (x and y do not depend on the parameters), so the data pipeline never drains between steps.
+#include <stdlib.h>
+
 #include "fused_linear.cuh"
 
 namespace fl {
@@ -36,8 +38,21 @@ struct ms_args {
   float* global_step;
   long P;
   int exchange;       // != 0: fx describes the peers (step1 / parity are those of step 0)
+  unsigned long long* stamps;   // diagnostics (B2_MS_STAMPS=1): %globaltimer of CTA 0's phases in steps stamp_step, +1
+  int stamp_step;
   b2_fx_args fx;
 };
+
+// ---- diagnostics: where the time of a step boundary goes (CTA 0 only, two consecutive steps) ----------------------------
+enum { ST_G_FIRST = 0, ST_G_LAST, ST_G_STAGED, ST_G_WRITTEN, ST_G_BAR_A, ST_SB_A, ST_SB_REDUCED, ST_SB_C0, ST_SB_BAR_B, ST_SB_C,
+       ST_SB_D, ST_F_FIRST_IN, ST_F_FIRST_DONE, ST_F_LAST_DONE, ST_H_FIRST_DONE, ST_H_LAST_DONE, ST_POINTS };
+__device__ __forceinline__ void stamp(const ms_args& a, int s, int point) {
+  if (a.stamps && blockIdx.x == 0 && (s == a.stamp_step || s == a.stamp_step + 1)) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    a.stamps[(s - a.stamp_step) * ST_POINTS + point] = t;
+  }
+}
 
 constexpr int NB_PART = 3, NB_ALL = 4;           // named barriers: G+H (256 threads), F+G+H (480 threads)
 constexpr int PART_THREADS = (G_WARPS + 1) * 32;  // 256
@@ -87,63 +102,111 @@ __device__ __forceinline__ void write_partial(const ms_args& a, const Smem& sm, 
   }
 }
 
+// Applies the reduced (and, with several ranks, exchanged) value of output i: gradient descent on the parameters,
+// the step's trace entries, global_step (distributed.py:107-108).  Called by the one thread that owns output i.
+__device__ __forceinline__ void apply_output(const ms_args& a, int s, int i, float g) {
+  const float sum = a.exchange ? b2_fx_exchange_at(a.fx, a.fx.step1 + (unsigned)s, (a.fx.parity + s) & 1, i, g) : g;
+  if (i < K * NC + NC) {
+    a.grads[i] = sum;
+    a.params[i] = fmaf(-a.lr, sum, __ldcg(a.params + i));
+  } else if (i == LOSS_IDX) {
+    a.grads[a.P] = sum;
+    if (a.loss_trace) a.loss_trace[s] = sum;
+  } else {
+    a.grads[a.P + 1] = sum;
+    if (a.correct_trace) a.correct_trace[s] = (int)(sum + 0.5f);
+    *a.global_step += 1.0f;
+  }
+}
+
+constexpr int RED_INFLIGHT = 20;   // partial values a thread requests from L2 before it starts adding (one round trip)
+
 // The part of the step boundary that F, G and H warps run together (480 threads, u = 0..479), after this CTA's partial
 // is in scratch and grid barrier a has been passed by the CTA's elected thread (which arrives at the first named
 // barrier below only then).  Returns with the updated W in shared memory (unless this was the last step).
+//
+// Every output is summed in the association of fused_linear_reduce_kernel: four quarter-sums over the CTAs
+// [q*qper, (q+1)*qper) in CTA order, combined ((s0+s1)+s2)+s3.  What differs is only who loads what, so that a thread
+// waits for ONE L2 round trip: all the values it needs are requested first, then added in order.
 __device__ __forceinline__ void step_boundary(const ms_args& a, Smem& sm, int s, int u) {
   const int grid = gridDim.x;
   named_sync(NB_ALL, ALL_THREADS);                                    // [A] every CTA's partial is visible
-  // ---- my slice of the outputs: element = 4 consecutive lanes (the four quarters of the grid), combined by shuffles
-  const int per = (RED_N + grid - 1) / grid;
+  if (u == 0) stamp(a, s, ST_SB_A);
+  const int per = (RED_N + grid - 1) / grid;                          // outputs this CTA owns
   const int e0 = blockIdx.x * per;
   const int qper = (grid + RED_Q - 1) / RED_Q;
-  const int q = u & 3;
-  const int c0 = q * qper, c1 = min(grid, c0 + qper);
-  constexpr int PER_ROUND = ALL_THREADS / RED_Q;                      // 120 elements per round
-  for (int base = 0; base < per; base += PER_ROUND) {
-    const int el = base + (u >> 2);
-    const int i = e0 + el;
-    const bool valid = el < per && i < RED_N;
-    float g = 0.f;
-    if (valid) {
-      const float* p = a.scratch + i;
-      int c = c0;
-      for (; c + 8 <= c1; c += 8) {
-        float v[8];
+  if (grid > RED_INFLIGHT) {
+    // large grids: output = 4 consecutive lanes, lane q adds quarter q (<= 37 CTAs), shuffles combine the quarters
+    const int q = u & 3;
+    const int c0 = q * qper, c1 = min(grid, c0 + qper);
+    constexpr int PER_ROUND = ALL_THREADS / RED_Q;                    // 120 outputs per round
+    for (int base = 0; base < per; base += PER_ROUND) {
+      const int el = base + (u >> 2);
+      const int i = e0 + el;
+      const bool valid = el < per && i < RED_N;
+      const float* p = a.scratch + (valid ? i : 0) + (size_t)c0 * SCRATCH_STRIDE;
+      float g = 0.f;
+      for (int k0 = 0; k0 < qper; k0 += RED_INFLIGHT) {               // <= 2 chunks: qper <= 37
+        float v[RED_INFLIGHT];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) v[k] = __ldcg(p + (size_t)(c + k) * SCRATCH_STRIDE);
+        for (int k = 0; k < RED_INFLIGHT; ++k)
+          v[k] = (valid && c0 + k0 + k < c1) ? __ldcg(p + (size_t)(k0 + k) * SCRATCH_STRIDE) : 0.f;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) g += v[k];
+        for (int k = 0; k < RED_INFLIGHT; ++k)
+          if (c0 + k0 + k < c1) g += v[k];
       }
-      for (; c < c1; ++c) g += __ldcg(p + (size_t)c * SCRATCH_STRIDE);
+      const float s1 = __shfl_down_sync(0xffffffffu, g, 1);
+      const float s2 = __shfl_down_sync(0xffffffffu, g, 2);
+      const float s3 = __shfl_down_sync(0xffffffffu, g, 3);
+      if (q == 0 && valid) apply_output(a, s, i, ((g + s1) + s2) + s3);
     }
-    const float s1 = __shfl_down_sync(0xffffffffu, g, 1);
-    const float s2 = __shfl_down_sync(0xffffffffu, g, 2);
-    const float s3 = __shfl_down_sync(0xffffffffu, g, 3);
-    if (q == 0 && valid) {
-      g = ((g + s1) + s2) + s3;                                       // this rank's value of output i
-      const float sum = a.exchange ? b2_fx_exchange_at(a.fx, a.fx.step1 + (unsigned)s, (a.fx.parity + s) & 1, i, g) : g;
-      if (i < K * NC + NC) {
-        a.grads[i] = sum;
-        a.params[i] = fmaf(-a.lr, sum, __ldcg(a.params + i));         // distributed.py:107-108
-      } else if (i == LOSS_IDX) {
-        a.grads[a.P] = sum;
-        if (a.loss_trace) a.loss_trace[s] = sum;
-      } else {
-        a.grads[a.P + 1] = sum;
-        if (a.correct_trace) a.correct_trace[s] = (int)(sum + 0.5f);
-        *a.global_step += 1.0f;
+  } else {
+    // small grids (<= 20 CTAs): one thread per output adds all four quarters itself; several outputs per batch so that
+    // about RED_INFLIGHT loads are in flight
+    const int epb = RED_INFLIGHT / grid;                              // outputs per thread and batch (>= 1)
+    for (int base = 0; base < per; base += ALL_THREADS * epb) {
+      float v[RED_INFLIGHT];
+#pragma unroll
+      for (int j = 0; j < RED_INFLIGHT; ++j) {
+        const int e = j / grid, c = j - e * grid;
+        const int el = base + e * ALL_THREADS + u;
+        const bool ok = e < epb && el < per && e0 + el < RED_N;
+        v[j] = ok ? __ldcg(a.scratch + (size_t)c * SCRATCH_STRIDE + e0 + el) : 0.f;
+      }
+      float tot = 0.f, acc = 0.f;
+#pragma unroll
+      for (int j = 0; j < RED_INFLIGHT; ++j) {
+        const int e = j / grid, c = j - e * grid;
+        if (e < epb) {
+          acc += v[j];
+          const bool q_end = (c + 1) % qper == 0 || c + 1 == grid;    // last CTA of its quarter
+          if (q_end) {
+            tot = (c < qper) ? acc : tot + acc;                       // quarter 0 starts the sum
+            acc = 0.f;
+          }
+          if (c + 1 == grid) {
+            for (int qq = (grid + qper - 1) / qper; qq < RED_Q; ++qq) tot += 0.f;   // empty quarters, as the reduction kernel adds them
+            const int el = base + e * ALL_THREADS + u;
+            if (el < per && e0 + el < RED_N) apply_output(a, s, e0 + el, tot);
+          }
+        }
       }
     }
   }
+  if (u == 0) stamp(a, s, ST_SB_REDUCED);
   if (s + 1 == a.n_steps) return;                                     // nothing reads the parameters after the last step
-  __threadfence();
-  named_sync(NB_ALL, ALL_THREADS);                                    // this CTA's slice is applied
-  if (u == 0) grid_arrive_wait(a.bar + 1, (unsigned)(s + 1) * (unsigned)grid);
+  named_sync(NB_ALL, ALL_THREADS);                                    // this CTA's slice is applied (CTA-scope order) ...
+  if (u == 0) {
+    stamp(a, s, ST_SB_C0);
+    grid_arrive_wait(a.bar + 1, (unsigned)(s + 1) * (unsigned)grid);  // ... and published by the fence in here
+    stamp(a, s, ST_SB_BAR_B);
+  }
   named_sync(NB_ALL, ALL_THREADS);                                    // [C] every CTA's slice is applied
+  if (u == 0) stamp(a, s, ST_SB_C);
   for (int i = u; i < K * NC / 4; i += ALL_THREADS)
     reinterpret_cast<float4*>(sm.W)[i] = __ldcg(reinterpret_cast<const float4*>(a.params) + i);
   named_sync(NB_ALL, ALL_THREADS);                                    // [D] W is in shared memory
+  if (u == 0) stamp(a, s, ST_SB_D);
 }
 
 __global__ void __launch_bounds__(THREADS, 1)
@@ -222,6 +285,7 @@ fused_linear_multistep_kernel(const ms_args a) {
         const int na = 2 * i_t, nb = na + 1, buf = i_t % NBUF;
         mbar_wait(&sm.full[na % NSTAGES], (uint32_t)(na / NSTAGES) & 1u);
         mbar_wait(&sm.full[nb % NSTAGES], (uint32_t)(nb / NSTAGES) & 1u);
+        if (tid == 0 && tile == blockIdx.x) stamp(a, s, ST_F_FIRST_IN);
         const float* xa = sm.x + ((na % NSTAGES) * STAGE_ROWS + rp) * XSTRIDE + slice * KW + 4 * ksub;
         const float* xb = sm.x + ((nb % NSTAGES) * STAGE_ROWS + rp) * XSTRIDE + slice * KW + 4 * ksub;
         const float* wp = sm.W + (slice * KW + 4 * ksub) * NC;
@@ -276,7 +340,9 @@ fused_linear_multistep_kernel(const ms_args a) {
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&sm.part_full[buf]);
+        if (tid == 0 && tile == blockIdx.x) stamp(a, s, ST_F_FIRST_DONE);
       }
+      if (tid == 0) stamp(a, s, ST_F_LAST_DONE);
       step_boundary(a, sm, s, u);
     }
   } else if (warp == H_WARP) {
@@ -377,15 +443,16 @@ fused_linear_multistep_kernel(const ms_args a) {
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&sm.dz_full[buf]);
+        if (lane == 0 && tile == blockIdx.x) stamp(a, s, ST_H_FIRST_DONE);
       }
       // ---- step boundary: my sums into shared memory, then the CTA partial goes to scratch together with G's
 #pragma unroll
       for (int cc = 0; cc < 5; ++cc) sm.red_db[lane * 5 + cc] = db[cc];
       if (half == 0) { sm.red_loss[row] = loss_acc; sm.red_corr[row] = corr_acc; }
       named_sync(NB_PART, PART_THREADS);                                   // staging complete (G's dW, my sums)
+      if (lane == 0) stamp(a, s, ST_H_LAST_DONE);
       write_partial(a, sm, G_WARPS * 32 + lane);
-      __threadfence();
-      named_sync(NB_PART, PART_THREADS);                                   // the CTA partial is written and fenced
+      named_sync(NB_PART, PART_THREADS);                                   // the CTA partial is written (published by G's fence)
       step_boundary(a, sm, s, u);
     }
   } else {
@@ -404,6 +471,7 @@ fused_linear_multistep_kernel(const ms_args a) {
         const int buf = i_t % NBUF;
         const int valid = min(TILE_ROWS, rows - tile * TILE_ROWS);
         mbar_wait(&sm.dz_full[buf], (uint32_t)(i_t / NBUF) & 1u);
+        if (gt == 0 && tile == blockIdx.x) stamp(a, s, ST_G_FIRST);
 #pragma unroll 1
         for (int q = 0; q < STAGES_PER_TILE; ++q) {
           const int n = 2 * i_t + q, slot = n % NSTAGES;
@@ -440,6 +508,7 @@ fused_linear_multistep_kernel(const ms_args a) {
         }
         if (lane == 0) mbar_arrive(&sm.dz_empty[buf]);
       }
+      if (gt == 0) stamp(a, s, ST_G_LAST);
       // ---- step boundary.  The forward team has finished with the weight tile (my last tile's dz needed its last
       // partial logits), so the per-CTA weight-gradient partial is staged there and then written out coalesced.
       if (active) {
@@ -457,10 +526,14 @@ fused_linear_multistep_kernel(const ms_args a) {
         }
       }
       named_sync(NB_PART, PART_THREADS);                                   // staging complete (my dW, H's sums)
+      if (gt == 0) stamp(a, s, ST_G_STAGED);
       write_partial(a, sm, gt);
-      __threadfence();
-      named_sync(NB_PART, PART_THREADS);                                   // the CTA partial is written and fenced
-      if (gt == 0) grid_arrive_wait(a.bar, (unsigned)(s + 1) * gridDim.x);  // grid barrier a
+      named_sync(NB_PART, PART_THREADS);                                   // the CTA partial is written ...
+      if (gt == 0) {
+        stamp(a, s, ST_G_WRITTEN);
+        grid_arrive_wait(a.bar, (unsigned)(s + 1) * gridDim.x);            // ... published (fence) + grid barrier a
+        stamp(a, s, ST_G_BAR_A);
+      }
       step_boundary(a, sm, s, u);
     }
   }
@@ -488,12 +561,37 @@ int b2_launch_fused_linear_multistep(const float* x_pool, const float* y_pool, l
   a.bar = bar; a.lr = lr; a.inv_B = 1.0f / (float)global_batch; a.loss_kind = loss; a.loss_trace = loss_trace;
   a.correct_trace = correct_trace; a.global_step = global_step; a.P = P;
   if (fx) { a.exchange = 1; a.fx = *fx; }
+  // diagnostics: B2_MS_STAMPS=1 prints CTA 0's timeline of two consecutive steps in the middle of the call (synchronises)
+  static unsigned long long* g_stamps = nullptr;
+  const char* env = getenv("B2_MS_STAMPS");
+  const bool stamps = env && *env == '1' && n_steps >= 4;
+  if (stamps) {
+    if (!g_stamps) B2_CUDA(cudaMallocManaged((void**)&g_stamps, 2 * fl::ST_POINTS * sizeof(unsigned long long)));
+    B2_CUDA(cudaStreamSynchronize(s));
+    memset(g_stamps, 0, 2 * fl::ST_POINTS * sizeof(unsigned long long));
+    a.stamps = g_stamps;
+    a.stamp_step = n_steps / 2;
+  }
   B2_CUDA(cudaMemsetAsync(bar, 0, 2 * sizeof(unsigned), s));
   fl::fused_linear_multistep_kernel<<<grid, fl::THREADS, (int)sizeof(fl::Smem), s>>>(a);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     b2_set_error("fused_linear_multistep launch failed: %s", cudaGetErrorString(e));
     return B2_ERR_CUDA;
+  }
+  if (stamps) {
+    B2_CUDA(cudaStreamSynchronize(s));
+    static const char* names[fl::ST_POINTS] = {"G first tile in", "G last tile done", "G staged", "partial written", "barrier a passed",
+                                               "[A] all partials visible", "slice reduced+applied", "slice barrier", "barrier b passed",
+                                               "[C] all slices applied", "[D] W reloaded", "F first tile in", "F first tile done",
+                                               "F last tile done", "H first tile done", "H last tile done"};
+    unsigned long long t0 = g_stamps[fl::ST_G_LAST];
+    fprintf(stderr, "B2_MS_STAMPS rows=%d grid=%d steps=%d: CTA 0, microseconds after 'G last tile done' of step %d\n", rows, grid,
+            n_steps, a.stamp_step);
+    for (int k = 0; k < 2; ++k)
+      for (int p = 0; p < fl::ST_POINTS; ++p)
+        if (g_stamps[k * fl::ST_POINTS + p])
+          fprintf(stderr, "  step+%d %-26s %9.3f\n", k, names[p], ((double)g_stamps[k * fl::ST_POINTS + p] - (double)t0) / 1e3);
   }
   return B2_OK;
 }

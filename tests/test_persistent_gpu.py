@@ -88,9 +88,9 @@ def test_simple_py_known_answer_in_one_launch(cuda_device, steps, line):
     assert oracle.simple_py_report(steps) == line
     _, _, _, trace = oracle.simple_py(steps)
     got, want = lt.cpu().numpy(), np.asarray(trace, dtype=np.float32)                       # every pre-update loss
-    big = want > 1e-6                                   # below that the loss is rounding noise of the residuals
-    np.testing.assert_allclose(got[big], want[big], rtol=1e-4)
-    assert got[~big].max() <= 2e-6
+    # numpy's BLAS dot and the kernel's fused multiply-adds round the 4-term sums differently: 1e-5 relative while the
+    # loss is a loss, 1e-8 absolute once it is the rounding noise of the residuals (it ends near 5e-11)
+    np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-8)
     assert tr.global_step == np.float32(steps)
     tr.close()
 
