@@ -144,13 +144,15 @@ __device__ __forceinline__ void step_boundary(const ms_args& a, Smem& sm, int s,
       const int el = base + (u >> 2);
       const int i = e0 + el;
       const bool valid = el < per && i < RED_N;
-      const float* p = a.scratch + (valid ? i : 0) + (size_t)c0 * SCRATCH_STRIDE;
+      // every load is issued unconditionally from a clamped (always valid) address, so that they all go out back to back;
+      // what lies outside this lane's quarter is simply not added
+      const float* p = a.scratch + (valid ? i : 0);
+      const int clast = max(c1 - 1, 0);
       float g = 0.f;
       for (int k0 = 0; k0 < qper; k0 += RED_INFLIGHT) {               // <= 2 chunks: qper <= 37
         float v[RED_INFLIGHT];
 #pragma unroll
-        for (int k = 0; k < RED_INFLIGHT; ++k)
-          v[k] = (valid && c0 + k0 + k < c1) ? __ldcg(p + (size_t)(k0 + k) * SCRATCH_STRIDE) : 0.f;
+        for (int k = 0; k < RED_INFLIGHT; ++k) v[k] = __ldcg(p + (size_t)min(c0 + k0 + k, clast) * SCRATCH_STRIDE);
 #pragma unroll
         for (int k = 0; k < RED_INFLIGHT; ++k)
           if (c0 + k0 + k < c1) g += v[k];
@@ -167,11 +169,10 @@ __device__ __forceinline__ void step_boundary(const ms_args& a, Smem& sm, int s,
     for (int base = 0; base < per; base += ALL_THREADS * epb) {
       float v[RED_INFLIGHT];
 #pragma unroll
-      for (int j = 0; j < RED_INFLIGHT; ++j) {
-        const int e = j / grid, c = j - e * grid;
-        const int el = base + e * ALL_THREADS + u;
-        const bool ok = e < epb && el < per && e0 + el < RED_N;
-        v[j] = ok ? __ldcg(a.scratch + (size_t)c * SCRATCH_STRIDE + e0 + el) : 0.f;
+      for (int j = 0; j < RED_INFLIGHT; ++j) {                        // unconditional loads from clamped addresses
+        const int e = min(j / grid, epb - 1), c = j % grid;
+        const int i = min(e0 + base + e * ALL_THREADS + u, RED_N - 1);
+        v[j] = __ldcg(a.scratch + (size_t)c * SCRATCH_STRIDE + i);
       }
       float tot = 0.f, acc = 0.f;
 #pragma unroll
@@ -566,9 +567,8 @@ int b2_launch_fused_linear_multistep(const float* x_pool, const float* y_pool, l
   const char* env = getenv("B2_MS_STAMPS");
   const bool stamps = env && *env == '1' && n_steps >= 4;
   if (stamps) {
-    if (!g_stamps) B2_CUDA(cudaMallocManaged((void**)&g_stamps, 2 * fl::ST_POINTS * sizeof(unsigned long long)));
-    B2_CUDA(cudaStreamSynchronize(s));
-    memset(g_stamps, 0, 2 * fl::ST_POINTS * sizeof(unsigned long long));
+    if (!g_stamps) B2_CUDA(cudaMalloc((void**)&g_stamps, 2 * fl::ST_POINTS * sizeof(unsigned long long)));
+    B2_CUDA(cudaMemsetAsync(g_stamps, 0, 2 * fl::ST_POINTS * sizeof(unsigned long long), s));
     a.stamps = g_stamps;
     a.stamp_step = n_steps / 2;
   }
@@ -580,18 +580,20 @@ int b2_launch_fused_linear_multistep(const float* x_pool, const float* y_pool, l
     return B2_ERR_CUDA;
   }
   if (stamps) {
+    unsigned long long h_stamps[2 * fl::ST_POINTS];
+    B2_CUDA(cudaMemcpyAsync(h_stamps, g_stamps, sizeof(h_stamps), cudaMemcpyDeviceToHost, s));
     B2_CUDA(cudaStreamSynchronize(s));
     static const char* names[fl::ST_POINTS] = {"G first tile in", "G last tile done", "G staged", "partial written", "barrier a passed",
                                                "[A] all partials visible", "slice reduced+applied", "slice barrier", "barrier b passed",
                                                "[C] all slices applied", "[D] W reloaded", "F first tile in", "F first tile done",
                                                "F last tile done", "H first tile done", "H last tile done"};
-    unsigned long long t0 = g_stamps[fl::ST_G_LAST];
+    unsigned long long t0 = h_stamps[fl::ST_G_LAST];
     fprintf(stderr, "B2_MS_STAMPS rows=%d grid=%d steps=%d: CTA 0, microseconds after 'G last tile done' of step %d\n", rows, grid,
             n_steps, a.stamp_step);
     for (int k = 0; k < 2; ++k)
       for (int p = 0; p < fl::ST_POINTS; ++p)
-        if (g_stamps[k * fl::ST_POINTS + p])
-          fprintf(stderr, "  step+%d %-26s %9.3f\n", k, names[p], ((double)g_stamps[k * fl::ST_POINTS + p] - (double)t0) / 1e3);
+        if (h_stamps[k * fl::ST_POINTS + p])
+          fprintf(stderr, "  step+%d %-26s %9.3f\n", k, names[p], ((double)h_stamps[k * fl::ST_POINTS + p] - (double)t0) / 1e3);
   }
   return B2_OK;
 }
