@@ -135,64 +135,47 @@ __device__ __forceinline__ void step_boundary(const ms_args& a, Smem& sm, int s,
   const int per = (RED_N + grid - 1) / grid;                          // outputs this CTA owns
   const int e0 = blockIdx.x * per;
   const int qper = (grid + RED_Q - 1) / RED_Q;
-  if (grid > RED_INFLIGHT) {
-    // large grids: output = 4 consecutive lanes, lane q adds quarter q (<= 37 CTAs), shuffles combine the quarters
-    const int q = u & 3;
-    const int c0 = q * qper, c1 = min(grid, c0 + qper);
-    constexpr int PER_ROUND = ALL_THREADS / RED_Q;                    // 120 outputs per round
-    for (int base = 0; base < per; base += PER_ROUND) {
-      const int el = base + (u >> 2);
-      const int i = e0 + el;
-      const bool valid = el < per && i < RED_N;
-      // every load is issued unconditionally from a clamped (always valid) address, so that they all go out back to back;
-      // what lies outside this lane's quarter is simply not added
-      const float* p = a.scratch + (valid ? i : 0);
-      const int clast = max(c1 - 1, 0);
-      float g = 0.f;
-      for (int k0 = 0; k0 < qper; k0 += RED_INFLIGHT) {               // <= 2 chunks: qper <= 37
-        float v[RED_INFLIGHT];
-#pragma unroll
-        for (int k = 0; k < RED_INFLIGHT; ++k) v[k] = __ldcg(p + (size_t)min(c0 + k0 + k, clast) * SCRATCH_STRIDE);
-#pragma unroll
-        for (int k = 0; k < RED_INFLIGHT; ++k)
-          if (c0 + k0 + k < c1) g += v[k];
-      }
-      const float s1 = __shfl_down_sync(0xffffffffu, g, 1);
-      const float s2 = __shfl_down_sync(0xffffffffu, g, 2);
-      const float s3 = __shfl_down_sync(0xffffffffu, g, 3);
-      if (q == 0 && valid) apply_output(a, s, i, ((g + s1) + s2) + s3);
-    }
-  } else {
-    // small grids (<= 20 CTAs): one thread per output adds all four quarters itself; several outputs per batch so that
-    // about RED_INFLIGHT loads are in flight
-    const int epb = RED_INFLIGHT / grid;                              // outputs per thread and batch (>= 1)
-    for (int base = 0; base < per; base += ALL_THREADS * epb) {
+  // Two ways to spread the loads, chosen by the grid size (uniform over the CTA); one place where the result is applied.
+  //   large grids : output = 4 consecutive lanes, lane q adds quarter q (<= 37 CTAs, two chunks of loads), the
+  //                 quarters are combined by shuffles; 120 outputs per round
+  //   <= 20 CTAs  : one thread per output adds all four quarters itself (<= 20 loads in flight); 480 outputs per round
+  // Every load is issued unconditionally from a clamped (always valid) address, so that they go out back to back.
+  const bool lanes4 = grid > RED_INFLIGHT;
+  const int q = lanes4 ? (u & 3) : 0;
+  const int c0 = lanes4 ? q * qper : 0, c1 = lanes4 ? min(grid, c0 + qper) : grid;
+  const int clast = max(c1 - 1, 0);
+  const int stride = lanes4 ? ALL_THREADS / RED_Q : ALL_THREADS;
+  for (int base = 0; base < per; base += stride) {
+    const int el = base + (lanes4 ? (u >> 2) : u);
+    const int i = e0 + el;
+    const bool valid = el < per && i < RED_N;
+    const float* p = a.scratch + (valid ? i : 0);
+    float tot = 0.f, acc = 0.f;
+    for (int k0 = c0; k0 < c1; k0 += RED_INFLIGHT) {
       float v[RED_INFLIGHT];
 #pragma unroll
-      for (int j = 0; j < RED_INFLIGHT; ++j) {                        // unconditional loads from clamped addresses
-        const int e = min(j / grid, epb - 1), c = j % grid;
-        const int i = min(e0 + base + e * ALL_THREADS + u, RED_N - 1);
-        v[j] = __ldcg(a.scratch + (size_t)c * SCRATCH_STRIDE + i);
-      }
-      float tot = 0.f, acc = 0.f;
+      for (int k = 0; k < RED_INFLIGHT; ++k) v[k] = __ldcg(p + (size_t)min(k0 + k, clast) * SCRATCH_STRIDE);
 #pragma unroll
-      for (int j = 0; j < RED_INFLIGHT; ++j) {
-        const int e = j / grid, c = j - e * grid;
-        if (e < epb) {
-          acc += v[j];
-          const bool q_end = (c + 1) % qper == 0 || c + 1 == grid;    // last CTA of its quarter
-          if (q_end) {
-            tot = (c < qper) ? acc : tot + acc;                       // quarter 0 starts the sum
+      for (int k = 0; k < RED_INFLIGHT; ++k) {
+        const int c = k0 + k;
+        if (c < c1) {
+          acc += v[k];
+          if (!lanes4 && ((c + 1) % qper == 0 || c + 1 == grid)) {    // last CTA of its quarter: fold the quarter in
+            tot = (c < qper) ? acc : tot + acc;
             acc = 0.f;
-          }
-          if (c + 1 == grid) {
-            for (int qq = (grid + qper - 1) / qper; qq < RED_Q; ++qq) tot += 0.f;   // empty quarters, as the reduction kernel adds them
-            const int el = base + e * ALL_THREADS + u;
-            if (el < per && e0 + el < RED_N) apply_output(a, s, e0 + el, tot);
           }
         }
       }
     }
+    if (lanes4) {
+      const float s1 = __shfl_down_sync(0xffffffffu, acc, 1);
+      const float s2 = __shfl_down_sync(0xffffffffu, acc, 2);
+      const float s3 = __shfl_down_sync(0xffffffffu, acc, 3);
+      tot = ((acc + s1) + s2) + s3;
+    } else {
+      for (int qq = (grid + qper - 1) / qper; qq < RED_Q; ++qq) tot += 0.f;   // empty quarters, as the reduction kernel adds them
+    }
+    if (valid && q == 0) apply_output(a, s, i, tot);
   }
   if (u == 0) stamp(a, s, ST_SB_REDUCED);
   if (s + 1 == a.n_steps) return;                                     // nothing reads the parameters after the last step
@@ -276,12 +259,13 @@ fused_linear_multistep_kernel(const ms_args a) {
     reinterpret_cast<float4*>(sm.W)[i] = __ldcg(reinterpret_cast<const float4*>(Wg) + i);
   named_sync(NB_ALL, ALL_THREADS);
 
+  // One loop over the steps for every role, so that the step boundary (a lot of code) exists once in the kernel.
+  int i_t = 0;                                  // tiles this CTA has processed so far: ring / buffer phases run on
+  for (int s = 0; s < a.n_steps; ++s) {
   if (warp < F_WARPS) {
     // =============================== F: forward ===============================
     const int slice = warp;                       // inputs 112*slice ..
     const int ksub = lane >> 3, rp = lane & 7;    // quads 4i+ksub; rows rp and rp+8
-    int i_t = 0;
-    for (int s = 0; s < a.n_steps; ++s) {
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++i_t) {
         const int na = 2 * i_t, nb = na + 1, buf = i_t % NBUF;
         mbar_wait(&sm.full[na % NSTAGES], (uint32_t)(na / NSTAGES) & 1u);
@@ -344,15 +328,11 @@ fused_linear_multistep_kernel(const ms_args a) {
         if (tid == 0 && tile == blockIdx.x) stamp(a, s, ST_F_FIRST_DONE);
       }
       if (tid == 0) stamp(a, s, ST_F_LAST_DONE);
-      step_boundary(a, sm, s, u);
-    }
   } else if (warp == H_WARP) {
     // =============================== H: loss head ===============================
     const int row = lane & 15, half = lane >> 4;          // classes 5*half .. 5*half+4
     const int loss_kind = a.loss_kind;
     const float inv_B = a.inv_B;
-    int i_t = 0;
-    for (int s = 0; s < a.n_steps; ++s) {
       float db[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
       float loss_acc = 0.f, corr_acc = 0.f;
       float bias5[5];
@@ -454,15 +434,11 @@ fused_linear_multistep_kernel(const ms_args a) {
       if (lane == 0) stamp(a, s, ST_H_LAST_DONE);
       write_partial(a, sm, G_WARPS * 32 + lane);
       named_sync(NB_PART, PART_THREADS);                                   // the CTA partial is written (published by G's fence)
-      step_boundary(a, sm, s, u);
-    }
   } else {
     // =============================== G: backward ===============================
     const int gt = tid - F_WARPS * 32;            // 0..223
     const int kg = gt >> 1, h = gt & 1;           // inputs 4kg..4kg+3 and 392+4kg..392+4kg+3, classes 5h..5h+4
     const bool active = kg < KGROUPS;
-    int i_t = 0;
-    for (int s = 0; s < a.n_steps; ++s) {
       u64 gacc[4][5];                               // [input pair][class]
 #pragma unroll
       for (int p = 0; p < 4; ++p)
@@ -535,8 +511,8 @@ fused_linear_multistep_kernel(const ms_args a) {
         grid_arrive_wait(a.bar, (unsigned)(s + 1) * gridDim.x);            // ... published (fence) + grid barrier a
         stamp(a, s, ST_G_BAR_A);
       }
-      step_boundary(a, sm, s, u);
-    }
+  }
+  step_boundary(a, sm, s, u);
   }
 }
 
