@@ -328,6 +328,8 @@ def make_trainer(D, workload, batch, args):
     tr.set_params(*synthetic.make_weights(dims, scaled))
     if args.no_persistent:
         tr.persistent_steps(False)
+    if args.multistep_fused:
+        tr.multistep_fused(True)
     if D.world > 1:
         uid = [pkg.DenseTrainer.new_unique_id() if D.rank == 0 else None]
         D.dist.broadcast_object_list(uid, src=0)
@@ -572,6 +574,7 @@ def main():
     ap.add_argument("--no-overlap", action="store_true",
                     help="multi-GPU bf16 path: one all-reduce after the backward pass instead of overlapped per-layer buckets")
     ap.add_argument("--no-persistent", action="store_true", help="one launch sequence per step instead of the multi-step kernels")
+    ap.add_argument("--multistep-fused", action="store_true", help="784->10: all steps in one launch of the fused kernel (optional path)")
     ap.add_argument("--sweep", action="store_true", help="batch-size sweep of c3 / c3 with the SSE head / 784-100-10 instead of the headline line")
     ap.add_argument("--sweep-out", default=os.path.join(ROOT, "gpurun_out", "sweep.json"))
     ap.add_argument("--sweep-points", default="c3,c3-sse,c2")

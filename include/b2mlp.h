@@ -60,7 +60,11 @@ enum {
   B2_OPT_NO_NARROW_HEAD = 7, /* value 1 (fp32, >= 2 layers): run the output layer as separate forward / loss-head / wgrad /
                                  dgrad kernels instead of the single narrow-head kernel (narrow_head.cu) */
   B2_OPT_NO_PERSISTENT = 8,  /* value 1: b2_train_steps enqueues every step as separate kernel launches instead of running
-                                 all n_steps inside one persistent kernel where such a kernel exists (784 -> 10; tiny models) */
+                                 all n_steps inside one persistent kernel where such a kernel exists */
+  B2_OPT_MULTISTEP_FUSED = 9, /* value 1: run the 784 -> 10 model's steps inside ONE launch of the fused step kernel with the
+                                 step boundary (reduction, exchange, apply) behind in-kernel grid barriers.  Bit-identical to
+                                 the default (one step kernel + one reduction kernel per step, chained by programmatic
+                                 dependent launch) and measured SLOWER than it at every batch size, so it is off by default */
   B2_OPT_ASYNC_PERIOD = 5     /* value k > 0: emulate the reference's ASYNCHRONOUS parameter-server training
                                  (distributed.py:107-113: plain GradientDescentOptimizer, SyncReplicas commented out):
                                  every worker applies its own gradients locally (mean over ITS batch) and the replicas'

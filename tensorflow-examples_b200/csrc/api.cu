@@ -790,6 +790,7 @@ extern "C" int b2_set_option(b2_ctx* ctx, int option, int value) {
     case B2_OPT_NO_SPLIT3: ctx->opt_no_split3 = value ? 1 : 0; return B2_OK;
     case B2_OPT_NO_BUCKET_OVERLAP: ctx->opt_no_overlap = value ? 1 : 0; return B2_OK;
     case B2_OPT_NO_PERSISTENT: ctx->opt_no_persistent = value ? 1 : 0; return B2_OK;
+    case B2_OPT_MULTISTEP_FUSED: ctx->opt_multistep_fused = value ? 1 : 0; return B2_OK;
     case B2_OPT_ASYNC_PERIOD:
       B2_CHECK_ARG(value >= 0, "b2_set_option: async period must be >= 0");
       ctx->async_period = value;
@@ -1000,7 +1001,7 @@ static int enqueue_persistent(b2_ctx* c, const float* xp, const float* yp, long 
     c->global_step_host += (float)n_steps;
     return B2_OK;
   }
-  if (use_fused_linear(c)) {
+  if (use_fused_linear(c) && c->opt_multistep_fused) {
     const bool use_peer = c->nranks > 1 && c->peer_ready && !c->opt_no_peer;
     if (c->nranks > 1 && !use_peer) return B2_NOT_PERSISTENT;       // NCCL exchange: one launch sequence per step
     b2_fx_args fx;

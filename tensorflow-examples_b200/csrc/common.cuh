@@ -104,6 +104,7 @@ struct b2_ctx {
   int opt_no_split3;               // B2_OPT_NO_SPLIT3
   int opt_no_narrow_head;          // B2_OPT_NO_NARROW_HEAD
   int opt_no_persistent;           // B2_OPT_NO_PERSISTENT
+  int opt_multistep_fused;         // B2_OPT_MULTISTEP_FUSED
   unsigned* grid_bar;              // [2] grid-barrier counters of the persistent multi-step kernels
   int head_used;                   // loss / correct partials written by the last forward (<= head_blocks)
   long head_db_off;                // scratch offset of the row-thread loss head's bias-gradient partials [head_blocks][16]

@@ -40,6 +40,7 @@ struct ms_args {
   int exchange;       // != 0: fx describes the peers (step1 / parity are those of step 0)
   unsigned long long* stamps;   // diagnostics (B2_MS_STAMPS=1): %globaltimer of CTA 0's phases in steps stamp_step, +1
   int stamp_step;
+  int debug;          // diagnostics (B2_MS_DEBUG bit mask): leave parts of the step boundary out to see what they cost
   b2_fx_args fx;
 };
 
@@ -154,7 +155,8 @@ __device__ __forceinline__ void step_boundary(const ms_args& a, Smem& sm, int s,
     for (int k0 = c0; k0 < c1; k0 += RED_INFLIGHT) {
       float v[RED_INFLIGHT];
 #pragma unroll
-      for (int k = 0; k < RED_INFLIGHT; ++k) v[k] = __ldcg(p + (size_t)min(k0 + k, clast) * SCRATCH_STRIDE);
+      for (int k = 0; k < RED_INFLIGHT; ++k)
+        v[k] = (a.debug & 1) ? 0.f : __ldcg(p + (size_t)min(k0 + k, clast) * SCRATCH_STRIDE);
 #pragma unroll
       for (int k = 0; k < RED_INFLIGHT; ++k) {
         const int c = k0 + k;
@@ -175,20 +177,21 @@ __device__ __forceinline__ void step_boundary(const ms_args& a, Smem& sm, int s,
     } else {
       for (int qq = (grid + qper - 1) / qper; qq < RED_Q; ++qq) tot += 0.f;   // empty quarters, as the reduction kernel adds them
     }
-    if (valid && q == 0) apply_output(a, s, i, tot);
+    if (valid && q == 0 && !(a.debug & 2)) apply_output(a, s, i, tot);
   }
   if (u == 0) stamp(a, s, ST_SB_REDUCED);
   if (s + 1 == a.n_steps) return;                                     // nothing reads the parameters after the last step
   named_sync(NB_ALL, ALL_THREADS);                                    // this CTA's slice is applied (CTA-scope order) ...
   if (u == 0) {
     stamp(a, s, ST_SB_C0);
-    grid_arrive_wait(a.bar + 1, (unsigned)(s + 1) * (unsigned)grid);  // ... and published by the fence in here
+    if (!(a.debug & 8)) grid_arrive_wait(a.bar + 1, (unsigned)(s + 1) * (unsigned)grid);  // ... and published by the fence in here
     stamp(a, s, ST_SB_BAR_B);
   }
   named_sync(NB_ALL, ALL_THREADS);                                    // [C] every CTA's slice is applied
   if (u == 0) stamp(a, s, ST_SB_C);
-  for (int i = u; i < K * NC / 4; i += ALL_THREADS)
-    reinterpret_cast<float4*>(sm.W)[i] = __ldcg(reinterpret_cast<const float4*>(a.params) + i);
+  if (!(a.debug & 4))
+    for (int i = u; i < K * NC / 4; i += ALL_THREADS)
+      reinterpret_cast<float4*>(sm.W)[i] = __ldcg(reinterpret_cast<const float4*>(a.params) + i);
   named_sync(NB_ALL, ALL_THREADS);                                    // [D] W is in shared memory
   if (u == 0) stamp(a, s, ST_SB_D);
 }
@@ -432,7 +435,7 @@ fused_linear_multistep_kernel(const ms_args a) {
       if (half == 0) { sm.red_loss[row] = loss_acc; sm.red_corr[row] = corr_acc; }
       named_sync(NB_PART, PART_THREADS);                                   // staging complete (G's dW, my sums)
       if (lane == 0) stamp(a, s, ST_H_LAST_DONE);
-      write_partial(a, sm, G_WARPS * 32 + lane);
+      if (!(a.debug & 16)) write_partial(a, sm, G_WARPS * 32 + lane);
       named_sync(NB_PART, PART_THREADS);                                   // the CTA partial is written (published by G's fence)
   } else {
     // =============================== G: backward ===============================
@@ -504,11 +507,11 @@ fused_linear_multistep_kernel(const ms_args a) {
       }
       named_sync(NB_PART, PART_THREADS);                                   // staging complete (my dW, H's sums)
       if (gt == 0) stamp(a, s, ST_G_STAGED);
-      write_partial(a, sm, gt);
+      if (!(a.debug & 16)) write_partial(a, sm, gt);
       named_sync(NB_PART, PART_THREADS);                                   // the CTA partial is written ...
       if (gt == 0) {
         stamp(a, s, ST_G_WRITTEN);
-        grid_arrive_wait(a.bar, (unsigned)(s + 1) * gridDim.x);            // ... published (fence) + grid barrier a
+        if (!(a.debug & 8)) grid_arrive_wait(a.bar, (unsigned)(s + 1) * gridDim.x);   // ... published (fence) + grid barrier a
         stamp(a, s, ST_G_BAR_A);
       }
   }
@@ -540,6 +543,8 @@ int b2_launch_fused_linear_multistep(const float* x_pool, const float* y_pool, l
   if (fx) { a.exchange = 1; a.fx = *fx; }
   // diagnostics: B2_MS_STAMPS=1 prints CTA 0's timeline of two consecutive steps in the middle of the call (synchronises)
   static unsigned long long* g_stamps = nullptr;
+  const char* dbg = getenv("B2_MS_DEBUG");
+  a.debug = dbg ? atoi(dbg) : 0;
   const char* env = getenv("B2_MS_STAMPS");
   const bool stamps = env && *env == '1' && n_steps >= 4;
   if (stamps) {

@@ -222,8 +222,14 @@ class DenseTrainer:
 
     def persistent_steps(self, on=True):
         """train_steps() runs all its steps inside ONE kernel launch where a persistent kernel exists for the model
-        (784 -> 10; tiny models such as simple.py's) -- the default -- or enqueues every step's kernels separately."""
+        (tiny models such as simple.py's; small batches of the 784-wide models) -- the default -- or enqueues every
+        step's kernels separately."""
         self.set_option(_ffi.OPT_NO_PERSISTENT, 0 if on else 1)
+
+    def multistep_fused(self, on=True):
+        """784 -> 10 only: all steps of train_steps() inside one launch of the fused step kernel (in-kernel grid barriers
+        around the reduction / apply).  Same bits as the default path, measured slower: an option, off by default."""
+        self.set_option(_ffi.OPT_MULTISTEP_FUSED, 1 if on else 0)
 
     def overlap_exchange(self, on=True):
         """bf16 path, several ranks: all-reduce each wide layer's weight gradient on a second stream while the backward

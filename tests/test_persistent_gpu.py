@@ -19,6 +19,7 @@ W_RTOL = 1e-5
 def _run(dev, dims, act, loss, Ws, bs, x, y, batch, steps, lr, persistent, first_row=0):
     tr = pkg.DenseTrainer(dims, act, loss, max_local_batch=batch, device=0)
     tr.persistent_steps(persistent)
+    tr.multistep_fused(persistent)        # 784 -> 10: the in-kernel step boundary is an option (off by default)
     tr.set_params(Ws, bs)
     xd, yd = torch.from_numpy(x).to(dev), torch.from_numpy(y).to(dev)
     l0 = tr.launch_count

@@ -20,7 +20,7 @@ for B in batches:
     for persistent in (True, False):
         tr = b2.DenseTrainer([784, 10], b2.ACT_IDENTITY, b2.LOSS_SOFTMAX_CE, max_local_batch=B)
         tr.set_params(*synthetic.make_weights([784, 10], True))
-        tr.persistent_steps(persistent)
+        tr.multistep_fused(persistent)
         os.environ["B2_MS_STAMPS"] = "0"
         tr.train_steps(x, y, B, 20)
         torch.cuda.synchronize()

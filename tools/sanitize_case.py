@@ -25,7 +25,7 @@ else:
     xh, yh = synthetic.make_pool(batch * steps)
     tr = b2.DenseTrainer([784, 10], b2.ACT_IDENTITY, b2.LOSS_SOFTMAX_CE, max_local_batch=batch)
     tr.set_params(*synthetic.make_weights([784, 10], True))
-    tr.persistent_steps(which == "multi")
+    tr.multistep_fused(which == "multi")
     lt, _ = tr.train_steps(torch.from_numpy(xh).to(dev), torch.from_numpy(yh).to(dev), batch, steps, lr=0.001)
 torch.cuda.synchronize()
 print(which, "losses", lt.cpu().numpy()[:3], "launches", tr.launch_count)
