@@ -5,7 +5,7 @@ import sys
 
 CSRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
 LIB = os.path.join(CSRC, "libb2mlp.so")
-SOURCES = ["api.cu", "kernels_layered.cu", "fused_linear.cu", "fused_linear_ms.cu", "tiny_steps.cu", "gemm_tcgen05.cu", "mixed_aux.cu", "sgemm_ffma2.cu", "gemm_split3.cu", "narrow_head.cu", "random_normal.cu"]
+SOURCES = ["api.cu", "kernels_layered.cu", "fused_linear.cu", "fused_linear_ms.cu", "tiny_steps.cu", "cluster_steps.cu", "gemm_tcgen05.cu", "mixed_aux.cu", "sgemm_ffma2.cu", "gemm_split3.cu", "narrow_head.cu", "random_normal.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
 

@@ -1025,6 +1025,17 @@ static int enqueue_persistent(b2_ctx* c, const float* xp, const float* yp, long 
     c->global_step_host += (float)n_steps;
     return B2_OK;
   }
+  if (c->nranks == 1 && b2_cluster_steps_applies(c->n_layers, c->dims, local_batch)) {
+    // small batches of the 784-wide models: one cluster of 14 CTAs runs the whole loop (cluster_steps.cu)
+    timed_scope t(c, B2_K_PERSISTENT_STEPS, s);
+    int rc = b2_launch_cluster_steps(c->n_layers, c->act, c->loss, c->w_off, c->b_off, c->P, xp, yp, span, first_row,
+                                     global_batch, local_batch, n_steps, lr, c->params, c->grads, loss_trace, correct_trace,
+                                     c->global_step_dev, s);
+    if (rc) return rc;
+    c->launches += 1;
+    c->global_step_host += (float)n_steps;
+    return B2_OK;
+  }
   return B2_NOT_PERSISTENT;
 }
 
@@ -1117,7 +1128,12 @@ extern "C" int b2_session_run_train(b2_ctx* ctx, const float* x_host, const floa
   cudaStream_t s = ctx->own_stream;
   B2_CUDA(cudaMemcpyAsync(ctx->feed_x, x_host, (size_t)rows * in * sizeof(float), cudaMemcpyHostToDevice, s));
   B2_CUDA(cudaMemcpyAsync(ctx->feed_y, y_host, (size_t)rows * outd * sizeof(float), cudaMemcpyHostToDevice, s));
-  int rc = enqueue_step_dp(ctx, ctx->feed_x, ctx->feed_y, rows, lr, ctx->fetch_dev, (int*)(ctx->fetch_dev + 1), s);
+  // the same kernels b2_train_steps would use for this model and batch size, so both entry points give the same bits
+  int rc = ctx->nranks > 1 ? B2_NOT_PERSISTENT
+                           : enqueue_persistent(ctx, ctx->feed_x, ctx->feed_y, rows, 0, rows, rows, 1, lr, ctx->fetch_dev,
+                                                (int*)(ctx->fetch_dev + 1), s);
+  if (rc == B2_NOT_PERSISTENT)
+    rc = enqueue_step_dp(ctx, ctx->feed_x, ctx->feed_y, rows, lr, ctx->fetch_dev, (int*)(ctx->fetch_dev + 1), s);
   if (rc) return rc;
   B2_CUDA(cudaMemcpyAsync(ctx->fetch_host, ctx->fetch_dev, 2 * sizeof(float), cudaMemcpyDeviceToHost, s));
   B2_CUDA(cudaStreamSynchronize(s));

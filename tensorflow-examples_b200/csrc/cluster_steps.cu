@@ -1,0 +1,517 @@
+// Small batches of the 784-wide models, all steps in ONE launch, on ONE thread-block cluster.
+//
+// The reference's shipped configuration is exactly this: distributed.py trains 784-100-10 with 100 rows per step
+// for 27 500 steps (distributed.py:46-48,141-150).  At that size a step is a few microseconds of arithmetic; run as
+// one launch sequence per step it costs 45-50 us, nearly all of it launch and grid-level synchronisation latency.
+// Here the loop runs inside one kernel on a cluster of 14 CTAs (14 SMs), which synchronise with the hardware cluster
+// barrier and exchange data through distributed shared memory instead of global memory:
+//
+//   CTA j owns inputs [56j, 56j+56) of the first layer for good: its slice of W1 lives in its shared memory for the whole
+//   call and is updated there (nothing of W1 moves between steps), and it streams only its 56 columns of x.
+//   per step:
+//     1. partial pre-activations  zpart_j = x[:, slice j] . W1[slice j, :]            [B, N1]   (FFMA2)
+//        -- cluster barrier --
+//     2. CTA j finishes rows [RO*j, RO*j+RO): z = b1 + sum_c zpart_c (CTA order, read from the peers' shared memory),
+//        sigmoid, output layer, softmax / loss / accuracy, dz3, dz2 = (dz3 W2^T) a(1-a); its rows of dz2 go into its
+//        own copy of the [B, N1] gradient matrix; partial sums of the small gradients (W2, b2, b1, loss, correct)
+//        -- cluster barrier --
+//     3. every CTA copies the other rows of dz2 from their owners; the small gradients are reduced slice-wise
+//        (-- cluster barrier --) and gathered, every CTA applies them to its replica of W2, b2, b1
+//     4. dW1[slice j] = x[:, slice j]^T . dz2, W1[slice j] -= lr dW1                  (FFMA2; local, no exchange)
+//   With one layer (784 -> 10, batch <= 256) step 2 is the loss head itself and step 3's small gradients are just the bias.
+// Every sum runs in a fixed order (CTA order, row order, ascending k), so a run is bit-reproducible.
+#include <cooperative_groups.h>
+#include <math.h>
+
+#include "common.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace cs {
+
+typedef unsigned long long u64;
+constexpr int C = 14;              // CTAs per cluster
+constexpr int K0 = 784;            // inputs
+constexpr int KS = K0 / C;         // 56 inputs per CTA
+constexpr int XS = 60;             // floats per staged x row (240 B: 16-byte aligned, rows spread over the banks)
+constexpr int THREADS = 512;
+constexpr int NC = 10;             // classes
+
+__device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c) {
+  u64 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ u64 pack2(float lo, float hi) {
+  u64 d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi));
+  return d;
+}
+__device__ __forceinline__ void unpack2(u64 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void* dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+struct args {
+  const float* x_pool;
+  const float* y_pool;
+  long span, first_row, global_batch;
+  int rows, n_steps;
+  int act, loss;
+  float lr, inv_B;
+  float* params;
+  long w1_off, b1_off, w2_off, b2_off;   // flat parameter layout (w2/b2 unused with one layer)
+  float* grads;                          // [P + 2]: loss and correct count of the last step at P, P+1
+  long P;
+  float* loss_trace;
+  int* correct_trace;
+  float* global_step;
+};
+
+// Shared-memory layout of one CTA (floats), the same in all CTAs of the cluster.
+template <int N1, int N2, int BMAX>
+struct Layout {
+  static constexpr int RO_MAX = (BMAX + C - 1) / C;                 // rows a CTA finishes per step
+  static constexpr int NS = N2 > 0 ? N1 * N2 + N2 + N1 + 2 : N1 + 2;   // small gradients: [W2][b2][b1][loss][correct] or [b][loss][correct]
+  static constexpr int SL = (NS + C - 1) / C;                       // slice of them a CTA reduces
+  static constexpr int P4_SLICES = N2 > 0 ? 1 : 16;                 // row slices of the weight-gradient pass
+  static constexpr int x = 0;                                       // [2][BMAX][XS]
+  static constexpr int w1 = x + 2 * BMAX * XS;                      // [KS][N1]
+  static constexpr int zpart = w1 + KS * N1;                        // [BMAX][N1]
+  static constexpr int dz = zpart + BMAX * N1;                      // [BMAX][N1]   gradient w.r.t. the first layer's pre-activations
+  static constexpr int small = dz + BMAX * N1;                      // replicated small parameters [W2][b2][b1] or [b]
+  static constexpr int spart = small + ((NS + 3) & ~3);             // this CTA's partial small gradients [NS]
+  static constexpr int sred = spart + ((NS + 3) & ~3);              // reduced slice [SL]
+  static constexpr int a2 = sred + ((SL + 3) & ~3);                 // [RO_MAX][N1]  activations of my rows
+  static constexpr int z3 = a2 + RO_MAX * N1;                       // [RO_MAX][16]  logits of my rows
+  static constexpr int dz3 = z3 + RO_MAX * 16;                      // [RO_MAX][16]
+  static constexpr int ys = dz3 + RO_MAX * 16;                      // [2][RO_MAX][NC] labels of my rows, double buffered
+  static constexpr int rowl = ys + 2 * RO_MAX * NC;                 // [RO_MAX] row loss, [RO_MAX] hit
+  static constexpr int p4 = (rowl + 2 * RO_MAX + 3) & ~3;           // [P4_SLICES][KS][N1] partial weight gradients (one layer only)
+  static constexpr int total = p4 + (P4_SLICES > 1 ? P4_SLICES * KS * N1 : 0);
+};
+
+// ---- step 1: zpart[r][n] = sum_k x[r][k] W1[k][n] over this CTA's 56 inputs.  Thread tile TR rows x TC columns, packed
+// FMAs over column pairs (the W pair is the vector operand, the x value the scalar one).
+template <int N1, int TR, int TC>
+__device__ __forceinline__ void forward_partial(const float* __restrict__ xs, const float* __restrict__ w1, float* __restrict__ zpart,
+                                                int rows, int t) {
+  constexpr int CG = N1 / TC;
+  static_assert(N1 % TC == 0 && TC % 2 == 0, "column tiling");
+  const int rg = t / CG, cgi = t - rg * CG;
+  const int r0 = rg * TR, n0 = cgi * TC;
+  if (r0 >= rows) return;
+  u64 acc[TR][TC / 2];
+#pragma unroll
+  for (int i = 0; i < TR; ++i)
+#pragma unroll
+    for (int p = 0; p < TC / 2; ++p) acc[i][p] = 0ull;
+#pragma unroll 2
+  for (int k = 0; k < KS; k += 4) {
+    float4 xv[TR];
+#pragma unroll
+    for (int i = 0; i < TR; ++i) xv[i] = *reinterpret_cast<const float4*>(xs + (r0 + i) * XS + k);   // rows >= `rows` hold zeros
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) {
+      u64 w[TC / 2];
+#pragma unroll
+      for (int p = 0; p < TC / 2; ++p) w[p] = *reinterpret_cast<const u64*>(w1 + (k + kk) * N1 + n0 + 2 * p);
+#pragma unroll
+      for (int i = 0; i < TR; ++i) {
+        const float xs_ = kk == 0 ? xv[i].x : (kk == 1 ? xv[i].y : (kk == 2 ? xv[i].z : xv[i].w));
+        const u64 xx = pack2(xs_, xs_);
+#pragma unroll
+        for (int p = 0; p < TC / 2; ++p) acc[i][p] = ffma2(xx, w[p], acc[i][p]);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < TR; ++i)
+#pragma unroll
+    for (int p = 0; p < TC / 2; ++p) *reinterpret_cast<u64*>(zpart + (r0 + i) * N1 + n0 + 2 * p) = acc[i][p];
+}
+
+// ---- step 4: dW1[k][n] = sum_r x[r][k] dz[r][n] for this CTA's 56 inputs, then W1 -= lr dW1.  Thread tile TK input
+// pairs x TCC columns over one of SLICES row slices; the x pair is the vector operand, dz the scalar one.
+template <int N1, int TK, int TCC, int SLICES>
+__device__ __forceinline__ void weight_gradient(const float* __restrict__ xs, const float* __restrict__ dz, float* __restrict__ w1,
+                                                float* __restrict__ p4, int rows, float lr, int t) {
+  constexpr int KG = KS / (2 * TK), CG = N1 / TCC;
+  static_assert(KS % (2 * TK) == 0 && N1 % TCC == 0 && TCC % 2 == 0, "tiling");
+  const int sl = t / (KG * CG);
+  const int rem = t - sl * (KG * CG);
+  const int kg = rem / CG, cgi = rem - kg * CG;      // consecutive lanes: consecutive column groups of one input group
+  const int k0 = kg * 2 * TK, n0 = cgi * TCC;
+  if (sl < SLICES) {
+    const int per = (rows + SLICES - 1) / SLICES;
+    const int ra = sl * per, rb = min(rows, ra + per);
+    u64 acc[TK][TCC];
+#pragma unroll
+    for (int a = 0; a < TK; ++a)
+#pragma unroll
+      for (int c = 0; c < TCC; ++c) acc[a][c] = 0ull;
+#pragma unroll 2
+    for (int r = ra; r < rb; ++r) {
+      u64 xp[TK];
+#pragma unroll
+      for (int a = 0; a < TK; ++a) xp[a] = *reinterpret_cast<const u64*>(xs + r * XS + k0 + 2 * a);
+#pragma unroll
+      for (int c2 = 0; c2 < TCC / 2; ++c2) {
+        const float2 d = *reinterpret_cast<const float2*>(dz + r * N1 + n0 + 2 * c2);
+        const u64 d0 = pack2(d.x, d.x), d1 = pack2(d.y, d.y);
+#pragma unroll
+        for (int a = 0; a < TK; ++a) {
+          acc[a][2 * c2] = ffma2(xp[a], d0, acc[a][2 * c2]);
+          acc[a][2 * c2 + 1] = ffma2(xp[a], d1, acc[a][2 * c2 + 1]);
+        }
+      }
+    }
+#pragma unroll
+    for (int a = 0; a < TK; ++a)
+#pragma unroll
+      for (int c = 0; c < TCC; ++c) {
+        float lo, hi;
+        unpack2(acc[a][c], lo, hi);
+        const int i0 = (k0 + 2 * a) * N1 + n0 + c;
+        if (SLICES == 1) {
+          w1[i0] = fmaf(-lr, lo, w1[i0]);
+          w1[i0 + N1] = fmaf(-lr, hi, w1[i0 + N1]);
+        } else {
+          p4[sl * KS * N1 + i0] = lo;
+          p4[sl * KS * N1 + i0 + N1] = hi;
+        }
+      }
+  }
+  if (SLICES > 1) {
+    __syncthreads();
+    for (int i = t; i < KS * N1; i += THREADS) {
+      float g = 0.f;
+#pragma unroll
+      for (int s2 = 0; s2 < SLICES; ++s2) g += p4[s2 * KS * N1 + i];    // row slices in order
+      w1[i] = fmaf(-lr, g, w1[i]);
+    }
+  }
+}
+
+template <int N1, int N2, int BMAX>
+__global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a) {
+  using L = Layout<N1, N2, BMAX>;
+  constexpr bool TWO = N2 > 0;
+  constexpr int NS = L::NS, SL = L::SL, RO_MAX = L::RO_MAX;
+  extern __shared__ __align__(16) float sm[];
+  cg::cluster_group cluster = cg::this_cluster();
+  const int j = (int)cluster.block_rank();
+  const int t = threadIdx.x;
+  const int B = a.rows;
+  const int RO = (B + C - 1) / C;                       // rows per owner CTA
+  const int rbeg = min(B, j * RO), rcnt = min(RO, B - rbeg);
+  float* xs = sm + L::x;
+  float* w1 = sm + L::w1;
+  float* zpart = sm + L::zpart;
+  float* dz = sm + L::dz;
+  float* small = sm + L::small;
+  float* spart = sm + L::spart;
+  float* sred = sm + L::sred;
+  float* a2 = sm + L::a2;
+  float* z3 = sm + L::z3;
+  float* dz3 = sm + L::dz3;
+  float* ys = sm + L::ys;
+  float* rowl = sm + L::rowl;
+  float* p4 = sm + L::p4;
+  // replicated small parameters: [W2][b2][b1] (two layers) or [b]
+  float* W2s = small;
+  float* b2s = small + N1 * N2;
+  float* b1s = TWO ? small + N1 * N2 + N2 : small;
+
+  // ---- prologue: parameters into shared memory, x buffers zeroed (rows past the batch must read as zeros)
+  for (int i = t; i < 2 * BMAX * XS; i += THREADS) xs[i] = 0.f;
+  for (int i = t; i < KS * N1; i += THREADS) w1[i] = a.params[a.w1_off + (long)(j * KS) * N1 + i];
+  for (int i = t; i < N1; i += THREADS) b1s[i] = a.params[a.b1_off + i];
+  if (TWO) {
+    for (int i = t; i < N1 * N2; i += THREADS) W2s[i] = a.params[a.w2_off + i];
+    for (int i = t; i < N2; i += THREADS) b2s[i] = a.params[a.b2_off + i];
+  }
+  __syncthreads();                                      // the zero fill is complete before any async copy lands
+  auto prefetch = [&](int s) {
+    const long start = (a.first_row + (long)s * a.global_batch) % a.span;
+    float* xb = xs + (s & 1) * BMAX * XS;
+    const float* src = a.x_pool + start * K0 + j * KS;
+    for (int i = t; i < B * (KS / 4); i += THREADS) {
+      const int r = i / (KS / 4), q = i - r * (KS / 4);
+      cp_async16(xb + r * XS + 4 * q, src + (long)r * K0 + 4 * q);
+    }
+    float* yb = ys + (s & 1) * RO_MAX * NC;
+    const float* ysrc = a.y_pool + (start + rbeg) * NC;
+    for (int i = t; i < rcnt * NC; i += THREADS) cp_async4(yb + i, ysrc + i);
+    cp_async_commit();
+  };
+  prefetch(0);
+  float gs = 0.f;
+  if (j == 0 && t == 0) gs = *a.global_step;
+
+  for (int s = 0; s < a.n_steps; ++s) {
+    if (s + 1 < a.n_steps) { prefetch(s + 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
+    __syncthreads();
+    const float* xb = xs + (s & 1) * BMAX * XS;
+    const float* yb = ys + (s & 1) * RO_MAX * NC;
+    // ---- 1. partial pre-activations over my 56 inputs
+    if constexpr (TWO) forward_partial<N1, 5, 4>(xb, w1, zpart, B, t);
+    else forward_partial<N1, 2, N1>(xb, w1, zpart, B, t);
+    cluster.sync();
+    // ---- 2. my rows: sum the partials of all CTAs in CTA order, finish the forward pass, loss head, backward to dz
+    {
+      constexpr int V = (N1 % 4 == 0) ? 4 : 2;          // floats per remote load
+      for (int i = t; i < rcnt * (N1 / V); i += THREADS) {
+        const int r = i / (N1 / V), n = (i - r * (N1 / V)) * V;
+        float acc[V];
+#pragma unroll
+        for (int v = 0; v < V; ++v) acc[v] = 0.f;
+        const int off = (rbeg + r) * N1 + n;
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          const float* rz = cluster.map_shared_rank(zpart, c) + off;
+          if (V == 4) {
+            const float4 p = *reinterpret_cast<const float4*>(rz);
+            acc[0] += p.x; acc[1] += p.y; acc[2 % V] += p.z; acc[3 % V] += p.w;
+          } else {
+            const float2 p = *reinterpret_cast<const float2*>(rz);
+            acc[0] += p.x; acc[1] += p.y;
+          }
+        }
+#pragma unroll
+        for (int v = 0; v < V; ++v) {
+          const float z = acc[v] + b1s[n + v];
+          if (TWO) a2[r * N1 + n + v] = a.act == B2_ACT_SIGMOID ? 1.0f / (1.0f + expf(-z)) : z;
+          else z3[r * 16 + n + v] = z;
+        }
+      }
+    }
+    __syncthreads();
+    if constexpr (TWO) {
+      // output layer z3 = a2 W2 + b2 (distributed.py:98)
+      for (int i = t; i < rcnt * N2; i += THREADS) {
+        const int r = i / N2, c = i - r * N2;
+        float z = 0.f;
+        for (int h = 0; h < N1; ++h) z = fmaf(a2[r * N1 + h], W2s[h * N2 + c], z);
+        z3[r * 16 + c] = z + b2s[c];
+      }
+      __syncthreads();
+    }
+    constexpr int NOUT = TWO ? N2 : N1;
+    if (t < rcnt) {
+      // loss head of one row (distributed.py:99-102,117-118 / simple.py:20)
+      const int r = t;
+      const float* z = z3 + r * 16;
+      const float* y = yb + r * NC;
+      float* d = dz3 + r * 16;
+      float l = 0.f, hit = 0.f;
+      if (a.loss == B2_LOSS_SSE_SUM) {
+        for (int c = 0; c < NOUT; ++c) {
+          const float e = z[c] - y[c];
+          l = fmaf(e, e, l);
+          d[c] = 2.0f * e;
+        }
+      } else {
+        float m = -INFINITY;
+        for (int c = 0; c < NOUT; ++c) m = fmaxf(m, z[c]);
+        float e[NOUT], ssum = 0.f;
+#pragma unroll
+        for (int c = 0; c < NOUT; ++c) { e[c] = expf(z[c] - m); ssum += e[c]; }
+        const float inv = 1.0f / ssum;
+        float sy = 0.f, bv = -INFINITY, lv = -INFINITY;
+        int bi = 0, li = 0;
+#pragma unroll
+        for (int c = 0; c < NOUT; ++c) {
+          const float p = e[c] * inv, tt = y[c];
+          l -= tt * logf(p);                           // un-fused log(softmax), as the reference writes it
+          sy += tt;
+          if (p > bv) { bv = p; bi = c; }              // first index wins ties (tf.argmax)
+          if (tt > lv) { lv = tt; li = c; }
+          e[c] = p;
+        }
+#pragma unroll
+        for (int c = 0; c < NOUT; ++c) d[c] = (e[c] * sy - y[c]) * a.inv_B;
+        hit = bi == li ? 1.0f : 0.0f;
+      }
+      rowl[r] = l;
+      rowl[RO_MAX + r] = hit;
+      if (!TWO) {
+#pragma unroll
+        for (int c = 0; c < NOUT; ++c) dz[(rbeg + r) * N1 + c] = d[c];     // one layer: this IS the first layer's dz
+      }
+    }
+    __syncthreads();
+    if constexpr (TWO) {
+      // dz2 = (dz3 W2^T) * a2 (1 - a2)   (MatMul grad transpose_b + SigmoidGrad), into my rows of the gradient matrix
+      for (int i = t; i < rcnt * N1; i += THREADS) {
+        const int r = i / N1, h = i - r * N1;
+        float d = 0.f;
+#pragma unroll
+        for (int c = 0; c < N2; ++c) d = fmaf(dz3[r * 16 + c], W2s[h * N2 + c], d);
+        const float av = a2[r * N1 + h];
+        dz[(rbeg + r) * N1 + h] = a.act == B2_ACT_SIGMOID ? d * av * (1.0f - av) : d;
+      }
+      __syncthreads();
+    }
+    // partial sums of the small gradients over my rows: [W2][b2][b1][loss][correct] or [b][loss][correct]
+    for (int i = t; i < NS; i += THREADS) {
+      float g = 0.f;
+      constexpr int N2D = TWO ? N2 : 1;                 // (keeps the index arithmetic of the two-layer branches legal)
+      if (TWO && i < N1 * N2) {
+        const int h = i / N2D, c = i - h * N2D;
+        for (int r = 0; r < rcnt; ++r) g = fmaf(a2[r * N1 + h], dz3[r * 16 + c], g);
+      } else if (TWO && i < N1 * N2 + N2) {
+        for (int r = 0; r < rcnt; ++r) g += dz3[r * 16 + (i - N1 * N2)];
+      } else if (i < NS - 2) {
+        const int h = TWO ? i - N1 * N2 - N2 : i;
+        for (int r = 0; r < rcnt; ++r) g += dz[(rbeg + r) * N1 + h];
+      } else {
+        const float* src = rowl + (i == NS - 2 ? 0 : RO_MAX);
+        for (int r = 0; r < rcnt; ++r) g += src[r];
+      }
+      spart[i] = g;
+    }
+    cluster.sync();
+    // ---- 3. gather: the other CTAs' rows of dz; the small gradients summed over the CTAs in CTA order
+    {
+      constexpr int V = (N1 % 4 == 0) ? 4 : 2;
+      for (int i = t; i < B * (N1 / V); i += THREADS) {
+        const int r = i / (N1 / V);
+        const int owner = r / RO;
+        if (owner != j) {
+          const float* src = cluster.map_shared_rank(dz, owner) + (size_t)i * V;
+          if (V == 4) *reinterpret_cast<float4*>(dz + (size_t)i * V) = *reinterpret_cast<const float4*>(src);
+          else *reinterpret_cast<float2*>(dz + (size_t)i * V) = *reinterpret_cast<const float2*>(src);
+        }
+      }
+    }
+    float step_loss = 0.f, step_correct = 0.f;
+    if (NS <= 64) {
+      // few of them (one layer: the bias): every CTA adds all partials itself
+      if (t < NS) {
+        float g = 0.f;
+#pragma unroll
+        for (int c = 0; c < C; ++c) g += cluster.map_shared_rank(spart, c)[t];
+        if (t < NS - 2) b1s[t] = fmaf(-a.lr, g, b1s[t]);
+        else if (t == NS - 2) step_loss = g;
+        else step_correct = g;
+      }
+    } else {
+      // reduce-scatter + all-gather: CTA j adds elements [SL*j, SL*j+SL) of all partials, then everybody reads all slices
+      if (t < SL) {
+        const int i = j * SL + t;
+        float g = 0.f;
+        if (i < NS) {
+#pragma unroll
+          for (int c = 0; c < C; ++c) g += cluster.map_shared_rank(spart, c)[i];
+        }
+        sred[t] = g;
+      }
+      cluster.sync();
+      for (int i = t; i < NS; i += THREADS) {
+        const int c = i / SL;
+        const float g = cluster.map_shared_rank(sred, c)[i - c * SL];
+        if (i < NS - 2) small[i] = fmaf(-a.lr, g, small[i]);       // [W2][b2][b1] in the order of the gradient vector
+        else if (i == NS - 2) step_loss = g;
+        else step_correct = g;
+      }
+    }
+    if (j == 0) {
+      // the thread that holds the step's loss / correct count writes the trace (distributed.py:148-151 fetches them every step)
+      const int tl = (NS - 2) % THREADS, tc = (NS - 1) % THREADS;
+      if (t == tl) {
+        const float l = a.loss == B2_LOSS_SSE_SUM ? step_loss : step_loss * a.inv_B;
+        if (a.loss_trace) a.loss_trace[s] = l;
+        if (s + 1 == a.n_steps) a.grads[a.P] = l;
+      }
+      if (t == tc) {
+        if (a.correct_trace) a.correct_trace[s] = (int)(step_correct + 0.5f);
+        if (s + 1 == a.n_steps) a.grads[a.P + 1] = step_correct;
+      }
+      if (t == 0) gs += 1.0f;                                       // global_step += 1 (distributed.py:108)
+    }
+    __syncthreads();                                                // dz is complete in my shared memory
+    // ---- 4. weight gradient of my 56 inputs and the update, all local
+    if constexpr (TWO) weight_gradient<N1, 2, 4, 1>(xb, dz, w1, p4, B, a.lr, t);
+    else weight_gradient<N1, 1, N1, L::P4_SLICES>(xb, dz, w1, p4, B, a.lr, t);
+    __syncthreads();
+  }
+  // ---- epilogue: parameters back to global memory; peers may still be reading my shared memory in their step 3
+  cluster.sync();
+  for (int i = t; i < KS * N1; i += THREADS) a.params[a.w1_off + (long)(j * KS) * N1 + i] = w1[i];
+  if (j == 0) {
+    for (int i = t; i < N1; i += THREADS) a.params[a.b1_off + i] = b1s[i];
+    if (TWO) {
+      for (int i = t; i < N1 * N2; i += THREADS) a.params[a.w2_off + i] = W2s[i];
+      for (int i = t; i < N2; i += THREADS) a.params[a.b2_off + i] = b2s[i];
+    }
+    if (t == 0) *a.global_step = gs;
+  }
+}
+
+template <int N1, int N2, int BMAX>
+static int launch(const args& a, cudaStream_t s) {
+  using L = Layout<N1, N2, BMAX>;
+  const int smem = L::total * (int)sizeof(float);
+  static bool prepared[64] = {};
+  int dev = 0;
+  B2_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && !prepared[dev]) {
+    B2_CUDA(cudaFuncSetAttribute(cluster_steps_kernel<N1, N2, BMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    B2_CUDA(cudaFuncSetAttribute(cluster_steps_kernel<N1, N2, BMAX>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    prepared[dev] = true;
+  }
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(C);
+  cfg.blockDim = dim3(THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = C;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, cluster_steps_kernel<N1, N2, BMAX>, a);
+  if (e != cudaSuccess) {
+    b2_set_error("cluster_steps launch failed: %s", cudaGetErrorString(e));
+    (void)cudaGetLastError();
+    return B2_ERR_CUDA;
+  }
+  return B2_OK;
+}
+
+}  // namespace cs
+
+// which models / batch sizes the cluster kernel takes: 784 -> 10 up to 256 rows, 784-100-10 up to 100 rows per step
+bool b2_cluster_steps_applies(int n_layers, const int* dims, int rows) {
+  if (n_layers == 1) return dims[0] == cs::K0 && dims[1] == 10 && rows >= 1 && rows <= 256;
+  if (n_layers == 2) return dims[0] == cs::K0 && dims[1] == 100 && dims[2] == 10 && rows >= 1 && rows <= 100;
+  return false;
+}
+
+int b2_launch_cluster_steps(int n_layers, int act, int loss, const long* w_off, const long* b_off, long P, const float* x_pool,
+                            const float* y_pool, long span, long first_row, long global_batch, int rows, int n_steps, float lr,
+                            float* params, float* grads, float* loss_trace, int* correct_trace, float* global_step,
+                            cudaStream_t s) {
+  if (n_steps <= 0) return B2_OK;
+  cs::args a;
+  memset(&a, 0, sizeof(a));
+  a.x_pool = x_pool; a.y_pool = y_pool; a.span = span; a.first_row = first_row; a.global_batch = global_batch;
+  a.rows = rows; a.n_steps = n_steps; a.act = act; a.loss = loss; a.lr = lr; a.inv_B = 1.0f / (float)global_batch;
+  a.params = params; a.grads = grads; a.P = P; a.loss_trace = loss_trace; a.correct_trace = correct_trace;
+  a.global_step = global_step;
+  a.w1_off = w_off[0]; a.b1_off = b_off[0];
+  if (n_layers == 2) { a.w2_off = w_off[1]; a.b2_off = b_off[1]; }
+  return n_layers == 2 ? cs::launch<100, 10, 100>(a, s) : cs::launch<10, 0, 256>(a, s);
+}

@@ -217,15 +217,15 @@ def test_argument_errors_surface_as_exceptions(cuda_device):
 
 
 # ---- distributed.py:99,102: the un-fused log(softmax) yields NaN when a probability underflows ---------------------
-@pytest.mark.parametrize("path", ["fused-784-10", "fused-multistep", "layered-784-10", "narrow-head-784-100-10", "tiny-4-3",
+@pytest.mark.parametrize("path", ["cluster-784-10", "fused-per-step", "fused-multistep", "layered-784-10", "cluster-784-100-10", "narrow-head-784-100-10", "tiny-4-3",
                                   "layered-20-3"])
 def test_softmax_underflow_gives_nan_like_the_reference(cuda_device, path):
     """The reference writes tf.log(tf.nn.softmax(z)) un-fused.  When one class's probability underflows to 0 the row's
     term is 0 * log(0) = 0 * -inf = NaN and so is the fetched cost; every GPU path keeps that, exactly like the oracle
     (tests/test_oracle.py::test_unfused_log_softmax_nan_is_reproduced)."""
-    if path in ("fused-784-10", "fused-multistep", "layered-784-10"):
+    if path in ("cluster-784-10", "fused-per-step", "fused-multistep", "layered-784-10"):
         dims, act = [784, 10], pkg.ACT_IDENTITY
-    elif path == "narrow-head-784-100-10":
+    elif path in ("narrow-head-784-100-10", "cluster-784-100-10"):
         dims, act = [784, 100, 10], pkg.ACT_SIGMOID
     elif path == "tiny-4-3":
         dims, act = [4, 3], pkg.ACT_IDENTITY
@@ -247,6 +247,8 @@ def test_softmax_underflow_gives_nan_like_the_reference(cuda_device, path):
         tr.force_layered(True)
     if path == "fused-multistep":
         tr.multistep_fused(True)
+    if path in ("fused-per-step", "narrow-head-784-100-10"):
+        tr.persistent_steps(False)
     tr.set_params(Ws, bs)
     xd, yd = torch.from_numpy(x).to(cuda_device), torch.from_numpy(y).to(cuda_device)
     loss_eval, _ = tr.evaluate(xd, yd)

@@ -122,3 +122,90 @@ def test_tiny_models_vs_oracle_and_vs_layer_kernels(cuda_device, dims, act, loss
         assert np.abs(one[2][l] - g.W[l]).max() <= tol and np.abs(one[3][l] - g.b[l]).max() <= tol
         assert np.abs(one[2][l] - per[2][l]).max() <= tol
     assert one[4] == np.float32(steps)
+
+
+# ---- small batches of the 784-wide models: one cluster of 14 CTAs runs the loop (cluster_steps.cu) ------------------
+def _ambiguous(g64, x, margin=1e-4):
+    _, z = g64.forward(x)
+    top2 = np.sort(z, axis=1)[:, -2:]
+    return int(((top2[:, 1] - top2[:, 0]) < margin).sum())
+
+
+@pytest.mark.parametrize("dims,act,scaled,loss,batch,steps", [
+    ([784, 10], oracle.ACT_IDENTITY, True, oracle.LOSS_SOFTMAX_CE, 256, 60),       # the sweep's smallest point
+    ([784, 10], oracle.ACT_IDENTITY, True, oracle.LOSS_SOFTMAX_CE, 1, 5),
+    ([784, 10], oracle.ACT_IDENTITY, True, oracle.LOSS_SOFTMAX_CE, 13, 9),         # fewer rows than CTAs
+    ([784, 10], oracle.ACT_IDENTITY, True, oracle.LOSS_SOFTMAX_CE, 255, 7),
+    ([784, 10], oracle.ACT_IDENTITY, True, oracle.LOSS_SSE, 100, 7),
+    ([784, 100, 10], oracle.ACT_SIGMOID, False, oracle.LOSS_SOFTMAX_CE, 100, 120),  # distributed.py as shipped (:46,85-86)
+    ([784, 100, 10], oracle.ACT_SIGMOID, False, oracle.LOSS_SOFTMAX_CE, 1, 5),
+    ([784, 100, 10], oracle.ACT_SIGMOID, False, oracle.LOSS_SOFTMAX_CE, 37, 11),
+    ([784, 100, 10], oracle.ACT_SIGMOID, False, oracle.LOSS_SOFTMAX_CE, 99, 6),
+    ([784, 100, 10], oracle.ACT_IDENTITY, True, oracle.LOSS_SOFTMAX_CE, 64, 6),
+    ([784, 100, 10], oracle.ACT_SIGMOID, True, oracle.LOSS_SSE, 50, 6),
+])
+def test_cluster_kernel_vs_oracle_and_vs_per_step_kernels(cuda_device, dims, act, scaled, loss, batch, steps):
+    lr = 1e-4 if loss == oracle.LOSS_SSE else 0.001
+    nb = min(steps, 9)
+    x, y = synthetic.make_pool(batch * nb)
+    Ws, bs = synthetic.make_weights(dims, scaled)
+    one = _run(cuda_device, dims, act, loss, Ws, bs, x, y, batch, steps, lr, True)
+    # (persistent=True also switches the optional fused multi-step path on; it only applies to 784 -> 10, where it would
+    #  take precedence -- so ask for the cluster kernel explicitly)
+    tr = pkg.DenseTrainer(dims, act, loss, max_local_batch=batch, device=0)
+    tr.set_params(Ws, bs)
+    xd, yd = torch.from_numpy(x).to(cuda_device), torch.from_numpy(y).to(cuda_device)
+    l0 = tr.launch_count
+    lt, ct = tr.train_steps(xd, yd, batch, steps, lr=lr)
+    torch.cuda.synchronize()
+    assert tr.launch_count - l0 == 1                     # the whole loop is one launch
+    gW, gb = tr.get_params()
+    gs = tr.global_step
+    tr.close()
+    lt, ct = lt.cpu().numpy(), ct.cpu().numpy()
+    per = _run(cuda_device, dims, act, loss, Ws, bs, x, y, batch, steps, lr, False)
+    g = oracle.TF1Graph(dims, act, loss, Ws, bs)
+    g64 = oracle.TF1Graph(dims, act, loss, Ws, bs, dtype=np.float64)
+    for s in range(steps):
+        sl = slice((s % nb) * batch, (s % nb) * batch + batch)
+        amb = _ambiguous(g64, x[sl]) if loss == oracle.LOSS_SOFTMAX_CE else 0
+        lo, co = g.train_step(x[sl], y[sl], lr)
+        g64.train_step(x[sl], y[sl], lr)
+        assert abs(float(lt[s]) - float(lo)) <= LOSS_RTOL * max(1.0, abs(float(lo))), (s, float(lt[s]), float(lo))
+        assert abs(float(per[0][s]) - float(lo)) <= LOSS_RTOL * max(1.0, abs(float(lo))), s
+        if loss == oracle.LOSS_SOFTMAX_CE:
+            assert abs(int(ct[s]) - co) <= amb, (s, int(ct[s]), co, amb)
+    for l in range(len(dims) - 1):
+        tol = W_RTOL * max(1.0, float(np.abs(g.W[l]).max()))
+        assert np.abs(gW[l] - g.W[l]).max() <= tol, ("W", l, float(np.abs(gW[l] - g.W[l]).max()), tol)
+        assert np.abs(gb[l] - g.b[l]).max() <= tol, ("b", l)
+        assert np.abs(gW[l] - per[2][l]).max() <= tol
+    assert gs == np.float32(steps)
+    del one
+
+
+def test_cluster_kernel_is_bit_reproducible_and_matches_session_run(cuda_device):
+    """Two runs give the same bits (fixed-order sums, no atomics), and the sess.run-shaped entry point, which runs the same
+    kernel one step at a time, gives the same bits as the one-launch loop."""
+    dims, batch, steps, lr = [784, 100, 10], 100, 12, 0.001
+    x, y = synthetic.make_pool(batch * steps)
+    Ws, bs = synthetic.make_weights(dims, False)
+    runs = []
+    for _ in range(2):
+        tr = pkg.DenseTrainer(dims, pkg.ACT_SIGMOID, pkg.LOSS_SOFTMAX_CE, max_local_batch=batch, device=0)
+        tr.set_params(Ws, bs)
+        lt, ct = tr.train_steps(torch.from_numpy(x).to(cuda_device), torch.from_numpy(y).to(cuda_device), batch, steps, lr=lr)
+        torch.cuda.synchronize()
+        runs.append((lt.cpu().numpy(), ct.cpu().numpy(), tr.get_params()))
+        tr.close()
+    np.testing.assert_array_equal(runs[0][0], runs[1][0])
+    np.testing.assert_array_equal(runs[0][2][0][0], runs[1][2][0][0])
+    tr = pkg.DenseTrainer(dims, pkg.ACT_SIGMOID, pkg.LOSS_SOFTMAX_CE, max_local_batch=batch, device=0)
+    tr.set_params(Ws, bs)
+    for s in range(steps):
+        lo, co = tr.run_train(x[s * batch:(s + 1) * batch], y[s * batch:(s + 1) * batch], lr)
+        assert np.float32(lo) == runs[0][0][s] and co == int(runs[0][1][s])
+    W, b = tr.get_params()
+    np.testing.assert_array_equal(W[0], runs[0][2][0][0])
+    np.testing.assert_array_equal(W[1], runs[0][2][0][1])
+    tr.close()
