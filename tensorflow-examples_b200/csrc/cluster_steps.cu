@@ -22,6 +22,7 @@
 // Every sum runs in a fixed order (CTA order, row order, ascending k), so a run is bit-reproducible.
 #include <cooperative_groups.h>
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -74,7 +75,17 @@ struct args {
   float* loss_trace;
   int* correct_trace;
   float* global_step;
+  long long* prof;                       // diagnostics (B2_CS_PROF=1): SM clocks CTA 0 / thread 0 spent per phase, summed over steps
 };
+constexpr int NPROF = 12;
+#define CS_TICK(slot)                                     \
+  do {                                                    \
+    if (a.prof && j == 0 && t == 0) {                     \
+      const long long now_ = clock64();                   \
+      prof_acc[slot] += now_ - prof_t;                    \
+      prof_t = now_;                                      \
+    }                                                     \
+  } while (0)
 
 // Shared-memory layout of one CTA (floats), the same in all CTAs of the cluster.
 template <int N1, int N2, int BMAX>
@@ -256,16 +267,21 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
   prefetch(0);
   float gs = 0.f;
   if (j == 0 && t == 0) gs = *a.global_step;
+  long long prof_acc[NPROF] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  long long prof_t = clock64();
 
   for (int s = 0; s < a.n_steps; ++s) {
     if (s + 1 < a.n_steps) { prefetch(s + 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
     __syncthreads();
+    CS_TICK(0);
     const float* xb = xs + (s & 1) * BMAX * XS;
     const float* yb = ys + (s & 1) * RO_MAX * NC;
     // ---- 1. partial pre-activations over my 56 inputs
     if constexpr (TWO) forward_partial<N1, 5, 4>(xb, w1, zpart, B, t);
     else forward_partial<N1, 2, N1>(xb, w1, zpart, B, t);
+    CS_TICK(1);
     cluster.sync();
+    CS_TICK(2);
     // ---- 2. my rows: sum the partials of all CTAs in CTA order, finish the forward pass, loss head, backward to dz
     {
       constexpr int V = (N1 % 4 == 0) ? 4 : 2;          // floats per remote load
@@ -295,6 +311,7 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
       }
     }
     __syncthreads();
+    CS_TICK(3);
     if constexpr (TWO) {
       // output layer z3 = a2 W2 + b2 (distributed.py:98)
       for (int i = t; i < rcnt * N2; i += THREADS) {
@@ -305,6 +322,7 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
       }
       __syncthreads();
     }
+    CS_TICK(4);
     constexpr int NOUT = TWO ? N2 : N1;
     if (t < rcnt) {
       // loss head of one row (distributed.py:99-102,117-118 / simple.py:20)
@@ -349,6 +367,7 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
       }
     }
     __syncthreads();
+    CS_TICK(5);
     if constexpr (TWO) {
       // dz2 = (dz3 W2^T) * a2 (1 - a2)   (MatMul grad transpose_b + SigmoidGrad), into my rows of the gradient matrix
       for (int i = t; i < rcnt * N1; i += THREADS) {
@@ -379,7 +398,9 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
       }
       spart[i] = g;
     }
+    CS_TICK(6);
     cluster.sync();
+    CS_TICK(7);
     // ---- 3. gather: the other CTAs' rows of dz; the small gradients summed over the CTAs in CTA order
     {
       constexpr int V = (N1 % 4 == 0) ? 4 : 2;
@@ -438,12 +459,17 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
       }
       if (t == 0) gs += 1.0f;                                       // global_step += 1 (distributed.py:108)
     }
+    CS_TICK(8);
     __syncthreads();                                                // dz is complete in my shared memory
+    CS_TICK(9);
     // ---- 4. weight gradient of my 56 inputs and the update, all local
     if constexpr (TWO) weight_gradient<N1, 2, 4, 1>(xb, dz, w1, p4, B, a.lr, t);
     else weight_gradient<N1, 1, N1, L::P4_SLICES>(xb, dz, w1, p4, B, a.lr, t);
     __syncthreads();
+    CS_TICK(10);
   }
+  if (a.prof && j == 0 && t == 0)
+    for (int i = 0; i < NPROF; ++i) a.prof[i] = prof_acc[i];
   // ---- epilogue: parameters back to global memory; peers may still be reading my shared memory in their step 3
   cluster.sync();
   for (int i = t; i < KS * N1; i += THREADS) a.params[a.w1_off + (long)(j * KS) * N1 + i] = w1[i];
@@ -482,11 +508,29 @@ static int launch(const args& a, cudaStream_t s) {
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, cluster_steps_kernel<N1, N2, BMAX>, a);
+  // diagnostics: B2_CS_PROF=1 prints where CTA 0 spends its clocks (synchronises the stream)
+  static long long* g_prof = nullptr;
+  const char* env = getenv("B2_CS_PROF");
+  args b = a;
+  if (env && *env == '1') {
+    if (!g_prof) B2_CUDA(cudaMalloc((void**)&g_prof, NPROF * sizeof(long long)));
+    b.prof = g_prof;
+  }
+  cudaError_t e = cudaLaunchKernelEx(&cfg, cluster_steps_kernel<N1, N2, BMAX>, b);
   if (e != cudaSuccess) {
     b2_set_error("cluster_steps launch failed: %s", cudaGetErrorString(e));
     (void)cudaGetLastError();
     return B2_ERR_CUDA;
+  }
+  if (b.prof) {
+    long long h[NPROF];
+    B2_CUDA(cudaMemcpyAsync(h, g_prof, sizeof(h), cudaMemcpyDeviceToHost, s));
+    B2_CUDA(cudaStreamSynchronize(s));
+    static const char* names[NPROF] = {"wait x + sync", "1 forward partial", "cluster barrier 1", "2a sum partials (DSMEM)",
+                                       "2b output layer", "2c loss head", "2d dz2 + 2e small partials", "cluster barrier 2",
+                                       "3 gather dz + small grads", "sync", "4 weight gradient + apply", ""};
+    fprintf(stderr, "B2_CS_PROF N1=%d N2=%d rows=%d steps=%d: CTA 0 thread 0, SM clocks per step\n", N1, N2, a.rows, a.n_steps);
+    for (int i = 0; i < 11; ++i) fprintf(stderr, "  %-30s %9.0f\n", names[i], (double)h[i] / a.n_steps);
   }
   return B2_OK;
 }
