@@ -591,6 +591,7 @@ void free_ctx(b2_ctx* c) {
   cudaFree(c->feed_y);
   cudaFree(c->fetch_dev);
   cudaFree(c->grid_bar);
+  cudaFree(c->cs_scratch);
   if (c->fetch_host) cudaFreeHost(c->fetch_host);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   if (c->timed) {
@@ -752,6 +753,8 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
   B2_ALLOC(c->eval_acc_dev, 2);
   B2_ALLOC(c->fetch_dev, 2);
   B2_ALLOC(c->grid_bar, 2);
+  if (precision == B2_PREC_FP32 && b2_cluster_steps_applies(n_layers, dims, 1))
+    B2_ALLOC(c->cs_scratch, b2_cluster_steps_scratch_floats(n_layers));
   if (b2_fused_linear_supported(dims[0], dims[1], loss) && n_layers == 1) {
     c->fused_grid = b2_fused_linear_grid(c->sm_count);
     c->fused_stride = b2_fused_linear_stride();
@@ -1025,12 +1028,12 @@ static int enqueue_persistent(b2_ctx* c, const float* xp, const float* yp, long 
     c->global_step_host += (float)n_steps;
     return B2_OK;
   }
-  if (c->nranks == 1 && b2_cluster_steps_applies(c->n_layers, c->dims, local_batch)) {
+  if (c->nranks == 1 && c->cs_scratch && b2_cluster_steps_applies(c->n_layers, c->dims, local_batch)) {
     // small batches of the 784-wide models: one cluster of 14 CTAs runs the whole loop (cluster_steps.cu)
     timed_scope t(c, B2_K_PERSISTENT_STEPS, s);
     int rc = b2_launch_cluster_steps(c->n_layers, c->act, c->loss, c->w_off, c->b_off, c->P, xp, yp, span, first_row,
                                      global_batch, local_batch, n_steps, lr, c->params, c->grads, loss_trace, correct_trace,
-                                     c->global_step_dev, s);
+                                     c->global_step_dev, c->cs_scratch, s);
     if (rc) return rc;
     c->launches += 1;
     c->global_step_host += (float)n_steps;

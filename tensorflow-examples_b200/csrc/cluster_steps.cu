@@ -9,16 +9,21 @@
 //   CTA j owns inputs [56j, 56j+56) of the first layer for good: its slice of W1 lives in its shared memory for the whole
 //   call and is updated there (nothing of W1 moves between steps), and it streams only its 56 columns of x.
 //   per step:
-//     1. partial pre-activations  zpart_j = x[:, slice j] . W1[slice j, :]            [B, N1]   (FFMA2)
+//     1. partial pre-activations  zpart_j = x[:, slice j] . W1[slice j, :]   [B, N1]   (FFMA2), stored to an L2-resident
+//        scratch buffer, one slot per CTA
 //        -- cluster barrier --
-//     2. CTA j finishes rows [RO*j, RO*j+RO): z = b1 + sum_c zpart_c (CTA order, read from the peers' shared memory),
-//        sigmoid, output layer, softmax / loss / accuracy, dz3, dz2 = (dz3 W2^T) a(1-a); its rows of dz2 go into its
-//        own copy of the [B, N1] gradient matrix; partial sums of the small gradients (W2, b2, b1, loss, correct)
+//     2. CTA j finishes rows [RO*j, RO*j+RO): z = b1 + sum_c zpart_c (CTA order), sigmoid, output layer, softmax / loss /
+//        accuracy (16 lanes per row), dz3, dz2 = (dz3 W2^T) a(1-a); its rows of dz2 go to the scratch buffer; partial
+//        sums of the small gradients (W2, b2, b1, loss, correct) stay in shared memory
 //        -- cluster barrier --
-//     3. every CTA copies the other rows of dz2 from their owners; the small gradients are reduced slice-wise
-//        (-- cluster barrier --) and gathered, every CTA applies them to its replica of W2, b2, b1
-//     4. dW1[slice j] = x[:, slice j]^T . dz2, W1[slice j] -= lr dW1                  (FFMA2; local, no exchange)
+//     3. every CTA copies the whole dz2 [B, N1] into its shared memory (cp.async from L2) while the small gradients are
+//        reduced slice-wise through distributed shared memory (-- cluster barrier --), gathered and applied to every
+//        CTA's replica of W2, b2, b1
+//     4. dW1[slice j] = x[:, slice j]^T . dz2, W1[slice j] -= lr dW1            (FFMA2; local, no exchange)
 //   With one layer (784 -> 10, batch <= 256) step 2 is the loss head itself and step 3's small gradients are just the bias.
+// The two bulk exchanges go through L2 and not through distributed shared memory: a CTA has to take in ~40 KB in each, and
+// DSMEM delivers ~20 B/clk per SM where L2 delivers several times that (measured: 3.5 us -> 0.8 us for the dz2 gather).
+// The cluster is what makes the barriers cheap (hardware cluster barrier, ~0.3 us) and the CTAs co-scheduled.
 // Every sum runs in a fixed order (CTA order, row order, ascending k), so a run is bit-reproducible.
 #include <cooperative_groups.h>
 #include <math.h>
@@ -75,6 +80,7 @@ struct args {
   float* loss_trace;
   int* correct_trace;
   float* global_step;
+  float* scratch;                        // [C][rows][N1] partial pre-activations, then [rows][N1] dz (L2-resident exchange buffers)
   long long* prof;                       // diagnostics (B2_CS_PROF=1): SM clocks CTA 0 / thread 0 spent per phase, summed over steps
 };
 constexpr int NPROF = 12;
@@ -93,27 +99,34 @@ struct Layout {
   static constexpr int RO_MAX = (BMAX + C - 1) / C;                 // rows a CTA finishes per step
   static constexpr int NS = N2 > 0 ? N1 * N2 + N2 + N1 + 2 : N1 + 2;   // small gradients: [W2][b2][b1][loss][correct] or [b][loss][correct]
   static constexpr int SL = (NS + C - 1) / C;                       // slice of them a CTA reduces
-  static constexpr int P4_SLICES = N2 > 0 ? 1 : 16;                 // row slices of the weight-gradient pass
+  static constexpr int P4_SLICES = N2 > 0 ? 2 : 16;                 // row slices of the weight-gradient pass
   static constexpr int x = 0;                                       // [2][BMAX][XS]
   static constexpr int w1 = x + 2 * BMAX * XS;                      // [KS][N1]
-  static constexpr int zpart = w1 + KS * N1;                        // [BMAX][N1]
-  static constexpr int dz = zpart + BMAX * N1;                      // [BMAX][N1]   gradient w.r.t. the first layer's pre-activations
+  static constexpr int dz = w1 + KS * N1;                           // [BMAX][N1]   gradient w.r.t. the first layer's pre-activations
   static constexpr int small = dz + BMAX * N1;                      // replicated small parameters [W2][b2][b1] or [b]
   static constexpr int spart = small + ((NS + 3) & ~3);             // this CTA's partial small gradients [NS]
   static constexpr int sred = spart + ((NS + 3) & ~3);              // reduced slice [SL]
   static constexpr int a2 = sred + ((SL + 3) & ~3);                 // [RO_MAX][N1]  activations of my rows
-  static constexpr int z3 = a2 + RO_MAX * N1;                       // [RO_MAX][16]  logits of my rows
+  static constexpr int dzown = a2 + RO_MAX * N1;                    // [RO_MAX][N1]  my rows of dz
+  static constexpr int z3 = dzown + RO_MAX * N1;                    // [RO_MAX][16]  logits of my rows
   static constexpr int dz3 = z3 + RO_MAX * 16;                      // [RO_MAX][16]
   static constexpr int ys = dz3 + RO_MAX * 16;                      // [2][RO_MAX][NC] labels of my rows, double buffered
   static constexpr int rowl = ys + 2 * RO_MAX * NC;                 // [RO_MAX] row loss, [RO_MAX] hit
-  static constexpr int p4 = (rowl + 2 * RO_MAX + 3) & ~3;           // [P4_SLICES][KS][N1] partial weight gradients (one layer only)
-  static constexpr int total = p4 + (P4_SLICES > 1 ? P4_SLICES * KS * N1 : 0);
+  static constexpr int p4 = (rowl + 2 * RO_MAX + 3) & ~3;           // [P4_SLICES][KS][N1] partial weight gradients
+  static constexpr int total = p4 + P4_SLICES * KS * N1;
 };
 
-// ---- step 1: zpart[r][n] = sum_k x[r][k] W1[k][n] over this CTA's 56 inputs.  Thread tile TR rows x TC columns, packed
-// FMAs over column pairs (the W pair is the vector operand, the x value the scalar one).
+__device__ __forceinline__ void cp_async8(void* dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+
+// ---- step 1: zpart[r][n] = sum_k x[r][k] W1[k][n] over this CTA's 56 inputs, written to this CTA's slot of the exchange
+// buffer in global memory.  Thread tile TR rows x TC columns, packed FMAs over column pairs (the W pair is the vector
+// operand, the x value the scalar one).  Consecutive lanes take consecutive column groups of one row group: the x loads
+// are broadcasts and the W loads contiguous.  The tile is tall (TR = 10 for N1 = 100) because every warp reads whole rows
+// of W: with short tiles the pass is bound by shared-memory wavefronts, not by the FMA pipe.
 template <int N1, int TR, int TC>
-__device__ __forceinline__ void forward_partial(const float* __restrict__ xs, const float* __restrict__ w1, float* __restrict__ zpart,
+__device__ __forceinline__ void forward_partial(const float* __restrict__ xs, const float* __restrict__ w1, float* __restrict__ zout,
                                                 int rows, int t) {
   constexpr int CG = N1 / TC;
   static_assert(N1 % TC == 0 && TC % 2 == 0, "column tiling");
@@ -125,7 +138,7 @@ __device__ __forceinline__ void forward_partial(const float* __restrict__ xs, co
   for (int i = 0; i < TR; ++i)
 #pragma unroll
     for (int p = 0; p < TC / 2; ++p) acc[i][p] = 0ull;
-#pragma unroll 2
+#pragma unroll 1
   for (int k = 0; k < KS; k += 4) {
     float4 xv[TR];
 #pragma unroll
@@ -133,8 +146,17 @@ __device__ __forceinline__ void forward_partial(const float* __restrict__ xs, co
 #pragma unroll
     for (int kk = 0; kk < 4; ++kk) {
       u64 w[TC / 2];
+      if (TC % 4 == 0) {
 #pragma unroll
-      for (int p = 0; p < TC / 2; ++p) w[p] = *reinterpret_cast<const u64*>(w1 + (k + kk) * N1 + n0 + 2 * p);
+        for (int p = 0; p < TC / 4; ++p) {
+          const ulonglong2 ww = *reinterpret_cast<const ulonglong2*>(w1 + (k + kk) * N1 + n0 + 4 * p);
+          w[2 * p] = ww.x;
+          w[(2 * p + 1) % (TC / 2)] = ww.y;
+        }
+      } else {
+#pragma unroll
+        for (int p = 0; p < TC / 2; ++p) w[p] = *reinterpret_cast<const u64*>(w1 + (k + kk) * N1 + n0 + 2 * p);
+      }
 #pragma unroll
       for (int i = 0; i < TR; ++i) {
         const float xs_ = kk == 0 ? xv[i].x : (kk == 1 ? xv[i].y : (kk == 2 ? xv[i].z : xv[i].w));
@@ -145,13 +167,28 @@ __device__ __forceinline__ void forward_partial(const float* __restrict__ xs, co
     }
   }
 #pragma unroll
-  for (int i = 0; i < TR; ++i)
+  for (int i = 0; i < TR; ++i) {
+    if (r0 + i < rows) {
+      float* o = zout + (size_t)(r0 + i) * N1 + n0;
+      if (TC % 4 == 0) {
 #pragma unroll
-    for (int p = 0; p < TC / 2; ++p) *reinterpret_cast<u64*>(zpart + (r0 + i) * N1 + n0 + 2 * p) = acc[i][p];
+        for (int p = 0; p < TC / 4; ++p) {
+          ulonglong2 v;
+          v.x = acc[i][2 * p];
+          v.y = acc[i][(2 * p + 1) % (TC / 2)];
+          *reinterpret_cast<ulonglong2*>(o + 4 * p) = v;
+        }
+      } else {
+#pragma unroll
+        for (int p = 0; p < TC / 2; ++p) *reinterpret_cast<u64*>(o + 2 * p) = acc[i][p];
+      }
+    }
+  }
 }
 
 // ---- step 4: dW1[k][n] = sum_r x[r][k] dz[r][n] for this CTA's 56 inputs, then W1 -= lr dW1.  Thread tile TK input
-// pairs x TCC columns over one of SLICES row slices; the x pair is the vector operand, dz the scalar one.
+// pairs x TCC columns over one of SLICES row slices (summed in slice order afterwards); the x pair is the vector operand,
+// dz the scalar one.  Consecutive lanes: consecutive column groups of one input group (x broadcast, dz contiguous).
 template <int N1, int TK, int TCC, int SLICES>
 __device__ __forceinline__ void weight_gradient(const float* __restrict__ xs, const float* __restrict__ dz, float* __restrict__ w1,
                                                 float* __restrict__ p4, int rows, float lr, int t) {
@@ -159,7 +196,7 @@ __device__ __forceinline__ void weight_gradient(const float* __restrict__ xs, co
   static_assert(KS % (2 * TK) == 0 && N1 % TCC == 0 && TCC % 2 == 0, "tiling");
   const int sl = t / (KG * CG);
   const int rem = t - sl * (KG * CG);
-  const int kg = rem / CG, cgi = rem - kg * CG;      // consecutive lanes: consecutive column groups of one input group
+  const int kg = rem / CG, cgi = rem - kg * CG;
   const int k0 = kg * 2 * TK, n0 = cgi * TCC;
   if (sl < SLICES) {
     const int per = (rows + SLICES - 1) / SLICES;
@@ -172,17 +209,36 @@ __device__ __forceinline__ void weight_gradient(const float* __restrict__ xs, co
 #pragma unroll 2
     for (int r = ra; r < rb; ++r) {
       u64 xp[TK];
+      if (TK % 2 == 0) {
 #pragma unroll
-      for (int a = 0; a < TK; ++a) xp[a] = *reinterpret_cast<const u64*>(xs + r * XS + k0 + 2 * a);
-#pragma unroll
-      for (int c2 = 0; c2 < TCC / 2; ++c2) {
-        const float2 d = *reinterpret_cast<const float2*>(dz + r * N1 + n0 + 2 * c2);
-        const u64 d0 = pack2(d.x, d.x), d1 = pack2(d.y, d.y);
-#pragma unroll
-        for (int a = 0; a < TK; ++a) {
-          acc[a][2 * c2] = ffma2(xp[a], d0, acc[a][2 * c2]);
-          acc[a][2 * c2 + 1] = ffma2(xp[a], d1, acc[a][2 * c2 + 1]);
+        for (int a = 0; a < TK / 2; ++a) {
+          const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(xs + r * XS + k0 + 4 * a);
+          xp[2 * a] = v.x;
+          xp[(2 * a + 1) % TK] = v.y;
         }
+      } else {
+#pragma unroll
+        for (int a = 0; a < TK; ++a) xp[a] = *reinterpret_cast<const u64*>(xs + r * XS + k0 + 2 * a);
+      }
+      float d[TCC];
+      if (TCC % 4 == 0) {
+#pragma unroll
+        for (int c4 = 0; c4 < TCC / 4; ++c4) {
+          const float4 v = *reinterpret_cast<const float4*>(dz + r * N1 + n0 + 4 * c4);
+          d[4 * c4] = v.x; d[(4 * c4 + 1) % TCC] = v.y; d[(4 * c4 + 2) % TCC] = v.z; d[(4 * c4 + 3) % TCC] = v.w;
+        }
+      } else {
+#pragma unroll
+        for (int c2 = 0; c2 < TCC / 2; ++c2) {
+          const float2 v = *reinterpret_cast<const float2*>(dz + r * N1 + n0 + 2 * c2);
+          d[2 * c2] = v.x; d[2 * c2 + 1] = v.y;
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < TCC; ++c) {
+        const u64 dd = pack2(d[c], d[c]);
+#pragma unroll
+        for (int a = 0; a < TK; ++a) acc[a][c] = ffma2(xp[a], dd, acc[a][c]);
       }
     }
 #pragma unroll
@@ -192,23 +248,16 @@ __device__ __forceinline__ void weight_gradient(const float* __restrict__ xs, co
         float lo, hi;
         unpack2(acc[a][c], lo, hi);
         const int i0 = (k0 + 2 * a) * N1 + n0 + c;
-        if (SLICES == 1) {
-          w1[i0] = fmaf(-lr, lo, w1[i0]);
-          w1[i0 + N1] = fmaf(-lr, hi, w1[i0 + N1]);
-        } else {
-          p4[sl * KS * N1 + i0] = lo;
-          p4[sl * KS * N1 + i0 + N1] = hi;
-        }
+        p4[sl * KS * N1 + i0] = lo;
+        p4[sl * KS * N1 + i0 + N1] = hi;
       }
   }
-  if (SLICES > 1) {
-    __syncthreads();
-    for (int i = t; i < KS * N1; i += THREADS) {
-      float g = 0.f;
+  __syncthreads();
+  for (int i = t; i < KS * N1; i += THREADS) {
+    float g = 0.f;
 #pragma unroll
-      for (int s2 = 0; s2 < SLICES; ++s2) g += p4[s2 * KS * N1 + i];    // row slices in order
-      w1[i] = fmaf(-lr, g, w1[i]);
-    }
+    for (int s2 = 0; s2 < SLICES; ++s2) g += p4[s2 * KS * N1 + i];      // row slices in order
+    w1[i] = fmaf(-lr, g, w1[i]);
   }
 }
 
@@ -217,21 +266,23 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
   using L = Layout<N1, N2, BMAX>;
   constexpr bool TWO = N2 > 0;
   constexpr int NS = L::NS, SL = L::SL, RO_MAX = L::RO_MAX;
+  constexpr int NOUT = TWO ? N2 : N1;                   // classes
+  constexpr int V = (N1 % 4 == 0) ? 4 : 2;              // floats per exchange load (rows of N1 floats)
   extern __shared__ __align__(16) float sm[];
   cg::cluster_group cluster = cg::this_cluster();
   const int j = (int)cluster.block_rank();
-  const int t = threadIdx.x;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int B = a.rows;
   const int RO = (B + C - 1) / C;                       // rows per owner CTA
   const int rbeg = min(B, j * RO), rcnt = min(RO, B - rbeg);
   float* xs = sm + L::x;
   float* w1 = sm + L::w1;
-  float* zpart = sm + L::zpart;
   float* dz = sm + L::dz;
   float* small = sm + L::small;
   float* spart = sm + L::spart;
   float* sred = sm + L::sred;
   float* a2 = sm + L::a2;
+  float* dzown = sm + L::dzown;
   float* z3 = sm + L::z3;
   float* dz3 = sm + L::dz3;
   float* ys = sm + L::ys;
@@ -241,6 +292,10 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
   float* W2s = small;
   float* b2s = small + N1 * N2;
   float* b1s = TWO ? small + N1 * N2 + N2 : small;
+  // exchange buffers in global memory (they stay in L2): one slot of partial pre-activations per CTA, then dz
+  float* zp_all = a.scratch;
+  float* zp_mine = zp_all + (size_t)j * B * N1;
+  float* dzg = zp_all + (size_t)C * B * N1;
 
   // ---- prologue: parameters into shared memory, x buffers zeroed (rows past the batch must read as zeros)
   for (int i = t; i < 2 * BMAX * XS; i += THREADS) xs[i] = 0.f;
@@ -265,49 +320,51 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
     cp_async_commit();
   };
   prefetch(0);
+  cp_async_wait<0>();
+  __syncthreads();
   float gs = 0.f;
   if (j == 0 && t == 0) gs = *a.global_step;
   long long prof_acc[NPROF] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
   long long prof_t = clock64();
 
   for (int s = 0; s < a.n_steps; ++s) {
-    if (s + 1 < a.n_steps) { prefetch(s + 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
-    __syncthreads();
+    // step s's rows are in shared memory (the previous step waited for them); request the next step's now
+    if (s + 1 < a.n_steps) prefetch(s + 1);
     CS_TICK(0);
     const float* xb = xs + (s & 1) * BMAX * XS;
     const float* yb = ys + (s & 1) * RO_MAX * NC;
-    // ---- 1. partial pre-activations over my 56 inputs
-    if constexpr (TWO) forward_partial<N1, 5, 4>(xb, w1, zpart, B, t);
-    else forward_partial<N1, 2, N1>(xb, w1, zpart, B, t);
+    // ---- 1. partial pre-activations over my 56 inputs -> my slot of the exchange buffer
+    if constexpr (TWO) forward_partial<N1, 10, 4>(xb, w1, zp_mine, B, t);
+    else forward_partial<N1, 2, N1>(xb, w1, zp_mine, B, t);
     CS_TICK(1);
+    __threadfence();
     cluster.sync();
     CS_TICK(2);
     // ---- 2. my rows: sum the partials of all CTAs in CTA order, finish the forward pass, loss head, backward to dz
-    {
-      constexpr int V = (N1 % 4 == 0) ? 4 : 2;          // floats per remote load
-      for (int i = t; i < rcnt * (N1 / V); i += THREADS) {
-        const int r = i / (N1 / V), n = (i - r * (N1 / V)) * V;
-        float acc[V];
+    for (int i = t; i < rcnt * (N1 / V); i += THREADS) {
+      const int r = i / (N1 / V), n = (i - r * (N1 / V)) * V;
+      const float* src = zp_all + (size_t)(rbeg + r) * N1 + n;
+      float acc[V];
 #pragma unroll
-        for (int v = 0; v < V; ++v) acc[v] = 0.f;
-        const int off = (rbeg + r) * N1 + n;
+      for (int v = 0; v < V; ++v) acc[v] = 0.f;
+      if (V == 4) {
+        float4 p[C];
 #pragma unroll
-        for (int c = 0; c < C; ++c) {
-          const float* rz = cluster.map_shared_rank(zpart, c) + off;
-          if (V == 4) {
-            const float4 p = *reinterpret_cast<const float4*>(rz);
-            acc[0] += p.x; acc[1] += p.y; acc[2 % V] += p.z; acc[3 % V] += p.w;
-          } else {
-            const float2 p = *reinterpret_cast<const float2*>(rz);
-            acc[0] += p.x; acc[1] += p.y;
-          }
-        }
+        for (int c = 0; c < C; ++c) p[c] = __ldcg(reinterpret_cast<const float4*>(src + (size_t)c * B * N1));
 #pragma unroll
-        for (int v = 0; v < V; ++v) {
-          const float z = acc[v] + b1s[n + v];
-          if (TWO) a2[r * N1 + n + v] = a.act == B2_ACT_SIGMOID ? 1.0f / (1.0f + expf(-z)) : z;
-          else z3[r * 16 + n + v] = z;
-        }
+        for (int c = 0; c < C; ++c) { acc[0] += p[c].x; acc[1] += p[c].y; acc[2 % V] += p[c].z; acc[3 % V] += p[c].w; }
+      } else {
+        float2 p[C];
+#pragma unroll
+        for (int c = 0; c < C; ++c) p[c] = __ldcg(reinterpret_cast<const float2*>(src + (size_t)c * B * N1));
+#pragma unroll
+        for (int c = 0; c < C; ++c) { acc[0] += p[c].x; acc[1] += p[c].y; }
+      }
+#pragma unroll
+      for (int v = 0; v < V; ++v) {
+        const float z = acc[v] + b1s[n + v];
+        if (TWO) a2[r * N1 + n + v] = a.act == B2_ACT_SIGMOID ? 1.0f / (1.0f + expf(-z)) : z;
+        else z3[r * 16 + n + v] = z;
       }
     }
     __syncthreads();
@@ -323,60 +380,69 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
       __syncthreads();
     }
     CS_TICK(4);
-    constexpr int NOUT = TWO ? N2 : N1;
-    if (t < rcnt) {
-      // loss head of one row (distributed.py:99-102,117-118 / simple.py:20)
-      const int r = t;
-      const float* z = z3 + r * 16;
-      const float* y = yb + r * NC;
-      float* d = dz3 + r * 16;
-      float l = 0.f, hit = 0.f;
+    {
+      // loss head (distributed.py:99-102,117-118 / simple.py:20): 16 lanes per row, lane = class; two rows per warp
+      const int r = 2 * warp + (lane >> 4), c = lane & 15;
+      const bool act_lane = r < rcnt && c < NOUT;
+      const float z = act_lane ? z3[r * 16 + c] : -INFINITY;
+      const float tt = act_lane ? yb[r * NC + c] : 0.f;
+      float l, d, hit = 0.f;
       if (a.loss == B2_LOSS_SSE_SUM) {
-        for (int c = 0; c < NOUT; ++c) {
-          const float e = z[c] - y[c];
-          l = fmaf(e, e, l);
-          d[c] = 2.0f * e;
-        }
+        const float e = act_lane ? z - tt : 0.f;
+        l = e * e;
+        d = 2.0f * e;
       } else {
-        float m = -INFINITY;
-        for (int c = 0; c < NOUT; ++c) m = fmaxf(m, z[c]);
-        float e[NOUT], ssum = 0.f;
+        float m = z;
 #pragma unroll
-        for (int c = 0; c < NOUT; ++c) { e[c] = expf(z[c] - m); ssum += e[c]; }
-        const float inv = 1.0f / ssum;
-        float sy = 0.f, bv = -INFINITY, lv = -INFINITY;
-        int bi = 0, li = 0;
+        for (int o = 8; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        const float e = act_lane ? expf(z - m) : 0.f;
+        float ssum = e;
 #pragma unroll
-        for (int c = 0; c < NOUT; ++c) {
-          const float p = e[c] * inv, tt = y[c];
-          l -= tt * logf(p);                           // un-fused log(softmax), as the reference writes it
-          sy += tt;
-          if (p > bv) { bv = p; bi = c; }              // first index wins ties (tf.argmax)
-          if (tt > lv) { lv = tt; li = c; }
-          e[c] = p;
+        for (int o = 8; o >= 1; o >>= 1) ssum += __shfl_xor_sync(0xffffffffu, ssum, o);
+        const float p = e * (1.0f / ssum);
+        l = act_lane ? -(tt * logf(p)) : 0.f;          // un-fused log(softmax): 0 * log(0) = NaN, as in the reference
+        float sy = tt;
+#pragma unroll
+        for (int o = 8; o >= 1; o >>= 1) sy += __shfl_xor_sync(0xffffffffu, sy, o);
+        // arg max of the prediction and of the label, first index wins ties (tf.argmax)
+        float bv = act_lane ? p : -INFINITY, lv = act_lane ? tt : -INFINITY;
+        int bi = c, li = c;
+#pragma unroll
+        for (int o = 8; o >= 1; o >>= 1) {
+          const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+          const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+          if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+          const float ov2 = __shfl_xor_sync(0xffffffffu, lv, o);
+          const int oi2 = __shfl_xor_sync(0xffffffffu, li, o);
+          if (ov2 > lv || (ov2 == lv && oi2 < li)) { lv = ov2; li = oi2; }
         }
-#pragma unroll
-        for (int c = 0; c < NOUT; ++c) d[c] = (e[c] * sy - y[c]) * a.inv_B;
         hit = bi == li ? 1.0f : 0.0f;
+        d = (p * sy - tt) * a.inv_B;
       }
-      rowl[r] = l;
-      rowl[RO_MAX + r] = hit;
-      if (!TWO) {
 #pragma unroll
-        for (int c = 0; c < NOUT; ++c) dz[(rbeg + r) * N1 + c] = d[c];     // one layer: this IS the first layer's dz
+      for (int o = 8; o >= 1; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
+      if (act_lane) {
+        dz3[r * 16 + c] = d;
+        if (!TWO) {                                     // one layer: this IS the first layer's dz
+          dzown[r * N1 + c] = d;
+          dzg[(size_t)(rbeg + r) * N1 + c] = d;
+        }
       }
+      if (r < rcnt && c == 0) { rowl[r] = l; rowl[RO_MAX + r] = hit; }
     }
     __syncthreads();
     CS_TICK(5);
     if constexpr (TWO) {
-      // dz2 = (dz3 W2^T) * a2 (1 - a2)   (MatMul grad transpose_b + SigmoidGrad), into my rows of the gradient matrix
+      // dz2 = (dz3 W2^T) * a2 (1 - a2)   (MatMul grad transpose_b + SigmoidGrad): my rows, also to the exchange buffer
       for (int i = t; i < rcnt * N1; i += THREADS) {
         const int r = i / N1, h = i - r * N1;
         float d = 0.f;
 #pragma unroll
         for (int c = 0; c < N2; ++c) d = fmaf(dz3[r * 16 + c], W2s[h * N2 + c], d);
         const float av = a2[r * N1 + h];
-        dz[(rbeg + r) * N1 + h] = a.act == B2_ACT_SIGMOID ? d * av * (1.0f - av) : d;
+        d = a.act == B2_ACT_SIGMOID ? d * av * (1.0f - av) : d;
+        dzown[r * N1 + h] = d;
+        dzg[(size_t)(rbeg + r) * N1 + h] = d;
       }
       __syncthreads();
     }
@@ -391,7 +457,7 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
         for (int r = 0; r < rcnt; ++r) g += dz3[r * 16 + (i - N1 * N2)];
       } else if (i < NS - 2) {
         const int h = TWO ? i - N1 * N2 - N2 : i;
-        for (int r = 0; r < rcnt; ++r) g += dz[(rbeg + r) * N1 + h];
+        for (int r = 0; r < rcnt; ++r) g += dzown[r * N1 + h];
       } else {
         const float* src = rowl + (i == NS - 2 ? 0 : RO_MAX);
         for (int r = 0; r < rcnt; ++r) g += src[r];
@@ -399,21 +465,16 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
       spart[i] = g;
     }
     CS_TICK(6);
+    __threadfence();
     cluster.sync();
     CS_TICK(7);
-    // ---- 3. gather: the other CTAs' rows of dz; the small gradients summed over the CTAs in CTA order
-    {
-      constexpr int V = (N1 % 4 == 0) ? 4 : 2;
-      for (int i = t; i < B * (N1 / V); i += THREADS) {
-        const int r = i / (N1 / V);
-        const int owner = r / RO;
-        if (owner != j) {
-          const float* src = cluster.map_shared_rank(dz, owner) + (size_t)i * V;
-          if (V == 4) *reinterpret_cast<float4*>(dz + (size_t)i * V) = *reinterpret_cast<const float4*>(src);
-          else *reinterpret_cast<float2*>(dz + (size_t)i * V) = *reinterpret_cast<const float2*>(src);
-        }
-      }
+    // ---- 3. the whole dz into my shared memory (asynchronous copy from L2); meanwhile the small gradients
+    if (V == 4) {
+      for (int i = t; i < B * N1 / 4; i += THREADS) cp_async16(dz + 4 * i, dzg + 4 * i);
+    } else {
+      for (int i = t; i < B * N1 / 2; i += THREADS) cp_async8(dz + 2 * i, dzg + 2 * i);
     }
+    cp_async_commit();
     float step_loss = 0.f, step_correct = 0.f;
     if (NS <= 64) {
       // few of them (one layer: the bias): every CTA adds all partials itself
@@ -460,10 +521,11 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
       if (t == 0) gs += 1.0f;                                       // global_step += 1 (distributed.py:108)
     }
     CS_TICK(8);
-    __syncthreads();                                                // dz is complete in my shared memory
+    cp_async_wait<0>();                                             // dz (and the next step's rows) have landed
+    __syncthreads();
     CS_TICK(9);
     // ---- 4. weight gradient of my 56 inputs and the update, all local
-    if constexpr (TWO) weight_gradient<N1, 2, 4, 1>(xb, dz, w1, p4, B, a.lr, t);
+    if constexpr (TWO) weight_gradient<N1, 4, 4, L::P4_SLICES>(xb, dz, w1, p4, B, a.lr, t);
     else weight_gradient<N1, 1, N1, L::P4_SLICES>(xb, dz, w1, p4, B, a.lr, t);
     __syncthreads();
     CS_TICK(10);
@@ -526,9 +588,9 @@ static int launch(const args& a, cudaStream_t s) {
     long long h[NPROF];
     B2_CUDA(cudaMemcpyAsync(h, g_prof, sizeof(h), cudaMemcpyDeviceToHost, s));
     B2_CUDA(cudaStreamSynchronize(s));
-    static const char* names[NPROF] = {"wait x + sync", "1 forward partial", "cluster barrier 1", "2a sum partials (DSMEM)",
-                                       "2b output layer", "2c loss head", "2d dz2 + 2e small partials", "cluster barrier 2",
-                                       "3 gather dz + small grads", "sync", "4 weight gradient + apply", ""};
+    static const char* names[NPROF] = {"issue next step's loads", "1 forward partial", "fence + cluster barrier 1", "2a sum partials (L2)",
+                                       "2b output layer", "2c loss head", "2d dz2 + 2e small partials", "fence + cluster barrier 2",
+                                       "3 small grads (dz copy in flight)", "wait dz + sync", "4 weight gradient + apply", ""};
     fprintf(stderr, "B2_CS_PROF N1=%d N2=%d rows=%d steps=%d: CTA 0 thread 0, SM clocks per step\n", N1, N2, a.rows, a.n_steps);
     for (int i = 0; i < 11; ++i) fprintf(stderr, "  %-30s %9.0f\n", names[i], (double)h[i] / a.n_steps);
   }
@@ -536,6 +598,12 @@ static int launch(const args& a, cudaStream_t s) {
 }
 
 }  // namespace cs
+
+// floats of global scratch the kernel exchanges through for a model whose first layer has n1 outputs: 14 slots of partial
+// pre-activations + dz, at the largest batch the kernel takes
+long b2_cluster_steps_scratch_floats(int n_layers) {
+  return n_layers == 2 ? (long)(cs::C + 1) * 100 * 100 : (long)(cs::C + 1) * 256 * 10;
+}
 
 // which models / batch sizes the cluster kernel takes: 784 -> 10 up to 256 rows, 784-100-10 up to 100 rows per step
 bool b2_cluster_steps_applies(int n_layers, const int* dims, int rows) {
@@ -547,7 +615,7 @@ bool b2_cluster_steps_applies(int n_layers, const int* dims, int rows) {
 int b2_launch_cluster_steps(int n_layers, int act, int loss, const long* w_off, const long* b_off, long P, const float* x_pool,
                             const float* y_pool, long span, long first_row, long global_batch, int rows, int n_steps, float lr,
                             float* params, float* grads, float* loss_trace, int* correct_trace, float* global_step,
-                            cudaStream_t s) {
+                            float* scratch, cudaStream_t s) {
   if (n_steps <= 0) return B2_OK;
   cs::args a;
   memset(&a, 0, sizeof(a));
@@ -555,6 +623,7 @@ int b2_launch_cluster_steps(int n_layers, int act, int loss, const long* w_off, 
   a.rows = rows; a.n_steps = n_steps; a.act = act; a.loss = loss; a.lr = lr; a.inv_B = 1.0f / (float)global_batch;
   a.params = params; a.grads = grads; a.P = P; a.loss_trace = loss_trace; a.correct_trace = correct_trace;
   a.global_step = global_step;
+  a.scratch = scratch;
   a.w1_off = w_off[0]; a.b1_off = b_off[0];
   if (n_layers == 2) { a.w2_off = w_off[1]; a.b2_off = b_off[1]; }
   return n_layers == 2 ? cs::launch<100, 10, 100>(a, s) : cs::launch<10, 0, 256>(a, s);

@@ -106,6 +106,7 @@ struct b2_ctx {
   int opt_no_persistent;           // B2_OPT_NO_PERSISTENT
   int opt_multistep_fused;         // B2_OPT_MULTISTEP_FUSED
   unsigned* grid_bar;              // [2] grid-barrier counters of the persistent multi-step kernels
+  float* cs_scratch;               // exchange buffers of the cluster kernel (cluster_steps.cu), when the model qualifies
   int head_used;                   // loss / correct partials written by the last forward (<= head_blocks)
   long head_db_off;                // scratch offset of the row-thread loss head's bias-gradient partials [head_blocks][16]
   long nh_db_off;                  // scratch offset of the narrow-head kernel's bias-gradient partials for layer L-1, or -1
@@ -240,7 +241,8 @@ bool b2_cluster_steps_applies(int n_layers, const int* dims, int rows);
 int b2_launch_cluster_steps(int n_layers, int act, int loss, const long* w_off, const long* b_off, long P, const float* x_pool,
                             const float* y_pool, long span, long first_row, long global_batch, int rows, int n_steps, float lr,
                             float* params, float* grads, float* loss_trace, int* correct_trace, float* global_step,
-                            cudaStream_t s);
+                            float* scratch, cudaStream_t s);
+long b2_cluster_steps_scratch_floats(int n_layers);
 // tiny_steps.cu: whole runs of tiny models (<= 4 layers, widths <= 16, <= 32 rows per step) by one warp
 bool b2_tiny_steps_applies(int n_layers, const int* dims, int rows);
 int b2_launch_tiny_steps(int n_layers, const int* dims, int act, int loss, const long* w_off, const long* b_off, long P,
