@@ -80,7 +80,7 @@ struct args {
   float* loss_trace;
   int* correct_trace;
   float* global_step;
-  float* scratch;                        // [C][rows][N1] partial pre-activations, then [rows][N1] dz (L2-resident exchange buffers)
+  float* scratch;                        // [slots][rows][N1] partial pre-activations, then [rows][N1] dz (L2-resident exchange buffers)
   long long* prof;                       // diagnostics (B2_CS_PROF=1): SM clocks CTA 0 / thread 0 spent per phase, summed over steps
 };
 constexpr int NPROF = 12;
@@ -127,7 +127,7 @@ __device__ __forceinline__ void cp_async8(void* dst, const void* src) {
 // of W: with short tiles the pass is bound by shared-memory wavefronts, not by the FMA pipe.
 template <int N1, int TR, int TC>
 __device__ __forceinline__ void forward_partial(const float* __restrict__ xs, const float* __restrict__ w1, float* __restrict__ zout,
-                                                int rows, int t) {
+                                                int rows, int t, int kbeg, int kend) {
   constexpr int CG = N1 / TC;
   static_assert(N1 % TC == 0 && TC % 2 == 0, "column tiling");
   const int rg = t / CG, cgi = t - rg * CG;
@@ -139,7 +139,7 @@ __device__ __forceinline__ void forward_partial(const float* __restrict__ xs, co
 #pragma unroll
     for (int p = 0; p < TC / 2; ++p) acc[i][p] = 0ull;
 #pragma unroll 1
-  for (int k = 0; k < KS; k += 4) {
+  for (int k = kbeg; k < kend; k += 4) {
     float4 xv[TR];
 #pragma unroll
     for (int i = 0; i < TR; ++i) xv[i] = *reinterpret_cast<const float4*>(xs + (r0 + i) * XS + k);   // rows >= `rows` hold zeros
@@ -206,7 +206,7 @@ __device__ __forceinline__ void weight_gradient(const float* __restrict__ xs, co
     for (int a = 0; a < TK; ++a)
 #pragma unroll
       for (int c = 0; c < TCC; ++c) acc[a][c] = 0ull;
-#pragma unroll 2
+#pragma unroll 4
     for (int r = ra; r < rb; ++r) {
       u64 xp[TK];
       if (TK % 2 == 0) {
@@ -268,6 +268,8 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
   constexpr int NS = L::NS, SL = L::SL, RO_MAX = L::RO_MAX;
   constexpr int NOUT = TWO ? N2 : N1;                   // classes
   constexpr int V = (N1 % 4 == 0) ? 4 : 2;              // floats per exchange load (rows of N1 floats)
+  constexpr int KSPLIT = TWO ? 2 : 1;                   // slots of partial pre-activations per CTA
+  constexpr int NSLOT = C * KSPLIT;
   extern __shared__ __align__(16) float sm[];
   cg::cluster_group cluster = cg::this_cluster();
   const int j = (int)cluster.block_rank();
@@ -294,8 +296,8 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
   float* b1s = TWO ? small + N1 * N2 + N2 : small;
   // exchange buffers in global memory (they stay in L2): one slot of partial pre-activations per CTA, then dz
   float* zp_all = a.scratch;
-  float* zp_mine = zp_all + (size_t)j * B * N1;
-  float* dzg = zp_all + (size_t)C * B * N1;
+  float* zp_mine = zp_all + (size_t)j * KSPLIT * B * N1;
+  float* dzg = zp_all + (size_t)NSLOT * B * N1;
 
   // ---- prologue: parameters into shared memory, x buffers zeroed (rows past the batch must read as zeros)
   for (int i = t; i < 2 * BMAX * XS; i += THREADS) xs[i] = 0.f;
@@ -334,11 +336,16 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
     const float* xb = xs + (s & 1) * BMAX * XS;
     const float* yb = ys + (s & 1) * RO_MAX * NC;
     // ---- 1. partial pre-activations over my 56 inputs -> my slot of the exchange buffer
-    if constexpr (TWO) forward_partial<N1, 10, 4>(xb, w1, zp_mine, B, t);
-    else forward_partial<N1, 2, N1>(xb, w1, zp_mine, B, t);
+    // (N1 = 100: the 56 inputs are cut once more, 28 for each half of the CTA's warps -- more warps in flight hide the
+    //  shared-memory latency of the operand loads; each half writes its own slot, KSPLIT * C slots in all)
+    if constexpr (TWO) {
+      const int half = t >> 8;
+      forward_partial<N1, 10, 4>(xb, w1, zp_all + (size_t)(j * KSPLIT + half) * B * N1, B, t & 255, half * (KS / 2), (half + 1) * (KS / 2));
+    } else {
+      forward_partial<N1, 2, N1>(xb, w1, zp_mine, B, t, 0, KS);
+    }
     CS_TICK(1);
-    __threadfence();
-    cluster.sync();
+    cluster.sync();          // release / acquire at cluster scope: the partials are visible to every CTA of the cluster
     CS_TICK(2);
     // ---- 2. my rows: sum the partials of all CTAs in CTA order, finish the forward pass, loss head, backward to dz
     for (int i = t; i < rcnt * (N1 / V); i += THREADS) {
@@ -348,17 +355,20 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
 #pragma unroll
       for (int v = 0; v < V; ++v) acc[v] = 0.f;
       if (V == 4) {
-        float4 p[C];
 #pragma unroll
-        for (int c = 0; c < C; ++c) p[c] = __ldcg(reinterpret_cast<const float4*>(src + (size_t)c * B * N1));
+        for (int c0 = 0; c0 < NSLOT; c0 += C) {         // C loads in flight at a time, added in slot order
+          float4 p[C];
 #pragma unroll
-        for (int c = 0; c < C; ++c) { acc[0] += p[c].x; acc[1] += p[c].y; acc[2 % V] += p[c].z; acc[3 % V] += p[c].w; }
+          for (int c = 0; c < C; ++c) p[c] = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(c0 + c) * B * N1));
+#pragma unroll
+          for (int c = 0; c < C; ++c) { acc[0] += p[c].x; acc[1] += p[c].y; acc[2 % V] += p[c].z; acc[3 % V] += p[c].w; }
+        }
       } else {
-        float2 p[C];
+        float2 p[NSLOT];
 #pragma unroll
-        for (int c = 0; c < C; ++c) p[c] = __ldcg(reinterpret_cast<const float2*>(src + (size_t)c * B * N1));
+        for (int c = 0; c < NSLOT; ++c) p[c] = __ldcg(reinterpret_cast<const float2*>(src + (size_t)c * B * N1));
 #pragma unroll
-        for (int c = 0; c < C; ++c) { acc[0] += p[c].x; acc[1] += p[c].y; }
+        for (int c = 0; c < NSLOT; ++c) { acc[0] += p[c].x; acc[1] += p[c].y; }
       }
 #pragma unroll
       for (int v = 0; v < V; ++v) {
@@ -465,7 +475,6 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
       spart[i] = g;
     }
     CS_TICK(6);
-    __threadfence();
     cluster.sync();
     CS_TICK(7);
     // ---- 3. the whole dz into my shared memory (asynchronous copy from L2); meanwhile the small gradients
@@ -602,7 +611,7 @@ static int launch(const args& a, cudaStream_t s) {
 // floats of global scratch the kernel exchanges through for a model whose first layer has n1 outputs: 14 slots of partial
 // pre-activations + dz, at the largest batch the kernel takes
 long b2_cluster_steps_scratch_floats(int n_layers) {
-  return n_layers == 2 ? (long)(cs::C + 1) * 100 * 100 : (long)(cs::C + 1) * 256 * 10;
+  return n_layers == 2 ? (long)(2 * cs::C + 1) * 100 * 100 : (long)(cs::C + 1) * 256 * 10;
 }
 
 // which models / batch sizes the cluster kernel takes: 784 -> 10 up to 256 rows, 784-100-10 up to 100 rows per step
