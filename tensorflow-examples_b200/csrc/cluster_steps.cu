@@ -16,9 +16,8 @@
 //        accuracy (16 lanes per row), dz3, dz2 = (dz3 W2^T) a(1-a); its rows of dz2 go to the scratch buffer; partial
 //        sums of the small gradients (W2, b2, b1, loss, correct) stay in shared memory
 //        -- cluster barrier --
-//     3. every CTA copies the whole dz2 [B, N1] into its shared memory (cp.async from L2) while the small gradients are
-//        reduced slice-wise through distributed shared memory (-- cluster barrier --), gathered and applied to every
-//        CTA's replica of W2, b2, b1
+//     3. every CTA copies the whole dz2 [B, N1] into its shared memory (cp.async from L2); meanwhile it adds the partial
+//        small gradients of all CTAs (from L2, CTA order) and applies them to its replica of W2, b2, b1
 //     4. dW1[slice j] = x[:, slice j]^T . dz2, W1[slice j] -= lr dW1            (FFMA2; local, no exchange)
 //   With one layer (784 -> 10, batch <= 256) step 2 is the loss head itself and step 3's small gradients are just the bias.
 // The two bulk exchanges go through L2 and not through distributed shared memory: a CTA has to take in ~40 KB in each, and
@@ -308,7 +307,7 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
   constexpr int NS = L::NS, SL = L::SL, RO_MAX = L::RO_MAX;
   constexpr int NOUT = TWO ? N2 : N1;                   // classes
   constexpr int V = (N1 % 4 == 0) ? 4 : 2;              // floats per exchange load (rows of N1 floats)
-  constexpr int KSPLIT = TWO ? 2 : 1;                   // slots of partial pre-activations per CTA
+  constexpr int KSPLIT = 1;                             // slots of partial pre-activations per CTA
   constexpr int NSLOT = C * KSPLIT;
   extern __shared__ __align__(16) float sm[];
   cg::cluster_group cluster = cg::this_cluster();
@@ -338,6 +337,7 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
   float* zp_all = a.scratch;
   float* zp_mine = zp_all + (size_t)j * KSPLIT * B * N1;
   float* dzg = zp_all + (size_t)NSLOT * B * N1;
+  float* sp_all = dzg + (size_t)B * N1;                  // [C][NS] partial small gradients (two-layer model)
 
   // ---- prologue: parameters into shared memory, x buffers zeroed (rows past the batch must read as zeros)
   for (int i = t; i < 2 * BMAX * XS; i += THREADS) xs[i] = 0.f;
@@ -348,20 +348,24 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
     for (int i = t; i < N2; i += THREADS) b2s[i] = a.params[a.b2_off + i];
   }
   __syncthreads();                                      // the zero fill is complete before any async copy lands
-  auto prefetch = [&](int s) {
+  // the rows of step s into their buffer: issued by `nthr` threads starting at thread `t0` (in the two-layer model the
+  // upper half of the CTA requests the next step's rows while the lower half already runs the forward pass)
+  auto prefetch = [&](int s, int t0, int nthr) {
+    const int tt = t - t0;
+    if (tt < 0 || tt >= nthr) return;
     const long start = (a.first_row + (long)s * a.global_batch) % a.span;
     float* xb = xs + (s & 1) * BMAX * XS;
     const float* src = a.x_pool + start * K0 + j * KS;
-    for (int i = t; i < B * (KS / 4); i += THREADS) {
+    for (int i = tt; i < B * (KS / 4); i += nthr) {
       const int r = i / (KS / 4), q = i - r * (KS / 4);
       cp_async16(xb + r * XS + 4 * q, src + (long)r * K0 + 4 * q);
     }
     float* yb = ys + (s & 1) * RO_MAX * NC;
     const float* ysrc = a.y_pool + (start + rbeg) * NC;
-    for (int i = t; i < rcnt * NC; i += THREADS) cp_async4(yb + i, ysrc + i);
+    for (int i = tt; i < rcnt * NC; i += nthr) cp_async4(yb + i, ysrc + i);
     cp_async_commit();
   };
-  prefetch(0);
+  prefetch(0, 0, THREADS);
   cp_async_wait<0>();
   __syncthreads();
   float gs = 0.f;
@@ -371,19 +375,13 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
 
   for (int s = 0; s < a.n_steps; ++s) {
     // step s's rows are in shared memory (the previous step waited for them); request the next step's now
-    if (s + 1 < a.n_steps) prefetch(s + 1);
+    if (s + 1 < a.n_steps) prefetch(s + 1, TWO ? THREADS / 2 : 0, TWO ? THREADS / 2 : THREADS);
     CS_TICK(0);
     const float* xb = xs + (s & 1) * BMAX * XS;
     const float* yb = ys + (s & 1) * RO_MAX * NC;
     // ---- 1. partial pre-activations over my 56 inputs -> my slot of the exchange buffer
-    // (N1 = 100: the 56 inputs are cut once more, 28 for each half of the CTA's warps -- more warps in flight hide the
-    //  shared-memory latency of the operand loads; each half writes its own slot, KSPLIT * C slots in all)
-    if constexpr (TWO) {
-      const int half = t >> 8;
-      forward_partial<N1, 10, 4>(xb, w1, zp_all + (size_t)(j * KSPLIT + half) * B * N1, B, t & 255, half * (KS / 2), (half + 1) * (KS / 2));
-    } else {
-      forward_partial<N1, 2, N1>(xb, w1, zp_mine, B, t, 0, KS);
-    }
+    if constexpr (TWO) forward_partial<N1, 10, 4>(xb, w1, zp_mine, B, t, 0, KS);      // warps 0-7
+    else forward_partial<N1, 2, N1>(xb, w1, zp_mine, B, t, 0, KS);
     CS_TICK(1);
     cluster.sync();          // release / acquire at cluster scope: the partials are visible to every CTA of the cluster
     CS_TICK(2);
@@ -513,6 +511,7 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
         for (int r = 0; r < rcnt; ++r) g += src[r];
       }
       spart[i] = g;
+      if (NS > 64) sp_all[(size_t)j * NS + i] = g;       // many of them: exchanged through L2 like the bulk data
     }
     CS_TICK(6);
     cluster.sync();
@@ -536,20 +535,15 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
         else step_correct = g;
       }
     } else {
-      // reduce-scatter + all-gather: CTA j adds elements [SL*j, SL*j+SL) of all partials, then everybody reads all slices
-      if (t < SL) {
-        const int i = j * SL + t;
-        float g = 0.f;
-        if (i < NS) {
-#pragma unroll
-          for (int c = 0; c < C; ++c) g += cluster.map_shared_rank(spart, c)[i];
-        }
-        sred[t] = g;
-      }
-      cluster.sync();
+      // every CTA adds all C partials of every element itself (C loads from L2 in flight per element, CTA order): no
+      // reduce-scatter, no third barrier
       for (int i = t; i < NS; i += THREADS) {
-        const int c = i / SL;
-        const float g = cluster.map_shared_rank(sred, c)[i - c * SL];
+        float p[C];
+#pragma unroll
+        for (int c = 0; c < C; ++c) p[c] = __ldcg(sp_all + (size_t)c * NS + i);
+        float g = 0.f;
+#pragma unroll
+        for (int c = 0; c < C; ++c) g += p[c];
         if (i < NS - 2) small[i] = fmaf(-a.lr, g, small[i]);       // [W2][b2][b1] in the order of the gradient vector
         else if (i == NS - 2) step_loss = g;
         else step_correct = g;
@@ -651,7 +645,7 @@ static int launch(const args& a, cudaStream_t s) {
 // floats of global scratch the kernel exchanges through for a model whose first layer has n1 outputs: 14 slots of partial
 // pre-activations + dz, at the largest batch the kernel takes
 long b2_cluster_steps_scratch_floats(int n_layers) {
-  return n_layers == 2 ? (long)(2 * cs::C + 1) * 100 * 100 : (long)(cs::C + 1) * 256 * 10;
+  return n_layers == 2 ? (long)(cs::C + 1) * 100 * 100 + (long)cs::C * (100 * 10 + 10 + 100 + 2) : (long)(cs::C + 1) * 256 * 10 + 64;
 }
 
 // which models / batch sizes the cluster kernel takes: 784 -> 10 up to 256 rows, 784-100-10 up to 100 rows per step
