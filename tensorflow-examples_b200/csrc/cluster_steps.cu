@@ -221,82 +221,104 @@ __device__ __forceinline__ void forward_partial(const float* __restrict__ xs, co
 template <int N1, int TK, int TCC, int SLICES>
 __device__ __forceinline__ void weight_gradient(const float* __restrict__ xs, const float* __restrict__ dz, float* __restrict__ w1,
                                                 float* __restrict__ p4, int rows, float lr, int t) {
-  constexpr int KG = KS / (2 * TK), CG = N1 / TCC;
+  constexpr int KG = KS / (2 * TK), CG = N1 / TCC, TILES = KG * CG;
   static_assert(KS % (2 * TK) == 0 && N1 % TCC == 0 && TCC % 2 == 0, "tiling");
-  const int sl = t / (KG * CG);
-  const int rem = t - sl * (KG * CG);
+  // SLICES == 2: the two row slices of a tile sit on the two halves of a warp (lanes l and l ^ 16) and are added with
+  // shuffles -- no trip through shared memory.  More slices: one thread group per slice, partials summed through p4.
+  constexpr bool LANE_SLICES = SLICES == 2;
+  const int lane = t & 31;
+  const int tile = LANE_SLICES ? (t >> 5) * 16 + (lane & 15) : t % TILES;
+  const int sl = LANE_SLICES ? (lane >> 4) : t / TILES;
+  const bool has_tile = tile < TILES && sl < SLICES;
+  const int rem = has_tile ? tile : 0;
   const int kg = rem / CG, cgi = rem - kg * CG;
   const int k0 = kg * 2 * TK, n0 = cgi * TCC;
-  if (sl < SLICES) {
-    const int per = (rows + SLICES - 1) / SLICES;
-    const int ra = sl * per, rb = min(rows, ra + per);
-    u64 acc[TK][TCC];
+  const int per = (rows + SLICES - 1) / SLICES;
+  const int ra = has_tile ? min(rows, sl * per) : 0, rb = has_tile ? min(rows, ra + per) : 0;   // no tile: no rows
+  u64 acc[TK][TCC];
 #pragma unroll
-    for (int a = 0; a < TK; ++a)
+  for (int a = 0; a < TK; ++a)
 #pragma unroll
-      for (int c = 0; c < TCC; ++c) acc[a][c] = 0ull;
-    constexpr int RB = 4;                                             // rows per step: their loads first, then the FMAs
+    for (int c = 0; c < TCC; ++c) acc[a][c] = 0ull;
+  constexpr int RB = 4;                                             // rows per step: their loads first, then the FMAs
 #pragma unroll 1
-    for (int r = ra; r < rb; r += RB) {
-      u64 xp[RB][TK];
-      float d[RB][TCC];
+  for (int r = ra; r < rb; r += RB) {
+    u64 xp[RB][TK];
+    float d[RB][TCC];
 #pragma unroll
-      for (int q = 0; q < RB; ++q) {
-        const int rr = min(r + q, rb - 1);                            // rows past the slice: a valid address, masked below
-        if (TK % 2 == 0) {
+    for (int q = 0; q < RB; ++q) {
+      const int rr = min(r + q, rb - 1);                            // rows past the slice: a valid address, masked below
+      if (TK % 2 == 0) {
 #pragma unroll
-          for (int a = 0; a < TK / 2; ++a) {
-            const ulonglong2 v = lds_u64x2(xs + rr * XS + k0 + 4 * a);
-            xp[q][2 * a] = v.x;
-            xp[q][(2 * a + 1) % TK] = v.y;
-          }
-        } else {
-#pragma unroll
-          for (int a = 0; a < TK; ++a) xp[q][a] = lds_u64(xs + rr * XS + k0 + 2 * a);
+        for (int a = 0; a < TK / 2; ++a) {
+          const ulonglong2 v = lds_u64x2(xs + rr * XS + k0 + 4 * a);
+          xp[q][2 * a] = v.x;
+          xp[q][(2 * a + 1) % TK] = v.y;
         }
-        if (TCC % 4 == 0) {
+      } else {
 #pragma unroll
-          for (int c4 = 0; c4 < TCC / 4; ++c4) {
-            const float4 v = lds_f4(dz + rr * N1 + n0 + 4 * c4);
-            d[q][4 * c4] = v.x; d[q][(4 * c4 + 1) % TCC] = v.y; d[q][(4 * c4 + 2) % TCC] = v.z; d[q][(4 * c4 + 3) % TCC] = v.w;
-          }
-        } else {
-#pragma unroll
-          for (int c2 = 0; c2 < TCC / 2; ++c2) {
-            const float2 v = lds_f2(dz + rr * N1 + n0 + 2 * c2);
-            d[q][2 * c2] = v.x; d[q][2 * c2 + 1] = v.y;
-          }
-        }
+        for (int a = 0; a < TK; ++a) xp[q][a] = lds_u64(xs + rr * XS + k0 + 2 * a);
       }
+      if (TCC % 4 == 0) {
 #pragma unroll
-      for (int q = 0; q < RB; ++q) {
-        const bool on = r + q < rb;
+        for (int c4 = 0; c4 < TCC / 4; ++c4) {
+          const float4 v = lds_f4(dz + rr * N1 + n0 + 4 * c4);
+          d[q][4 * c4] = v.x; d[q][(4 * c4 + 1) % TCC] = v.y; d[q][(4 * c4 + 2) % TCC] = v.z; d[q][(4 * c4 + 3) % TCC] = v.w;
+        }
+      } else {
 #pragma unroll
-        for (int c = 0; c < TCC; ++c) {
-          const float dv = on ? d[q][c] : 0.f;                        // a masked row adds exact zeros
-          const u64 dd = pack2(dv, dv);
-#pragma unroll
-          for (int a = 0; a < TK; ++a) acc[a][c] = ffma2(xp[q][a], dd, acc[a][c]);
+        for (int c2 = 0; c2 < TCC / 2; ++c2) {
+          const float2 v = lds_f2(dz + rr * N1 + n0 + 2 * c2);
+          d[q][2 * c2] = v.x; d[q][2 * c2 + 1] = v.y;
         }
       }
     }
+#pragma unroll
+    for (int q = 0; q < RB; ++q) {
+      const bool on = r + q < rb;
+#pragma unroll
+      for (int c = 0; c < TCC; ++c) {
+        const float dv = on ? d[q][c] : 0.f;                        // a masked row adds exact zeros
+        const u64 dd = pack2(dv, dv);
+#pragma unroll
+        for (int a = 0; a < TK; ++a) acc[a][c] = ffma2(xp[q][a], dd, acc[a][c]);
+      }
+    }
+  }
+  if (LANE_SLICES) {
 #pragma unroll
     for (int a = 0; a < TK; ++a)
 #pragma unroll
       for (int c = 0; c < TCC; ++c) {
         float lo, hi;
         unpack2(acc[a][c], lo, hi);
-        const int i0 = (k0 + 2 * a) * N1 + n0 + c;
-        p4[sl * KS * N1 + i0] = lo;
-        p4[sl * KS * N1 + i0 + N1] = hi;
+        const float lo1 = __shfl_xor_sync(0xffffffffu, lo, 16), hi1 = __shfl_xor_sync(0xffffffffu, hi, 16);
+        if (has_tile && sl == 0) {                                    // slice 0 + slice 1, then the update
+          const int i0 = (k0 + 2 * a) * N1 + n0 + c;
+          w1[i0] = fmaf(-lr, lo + lo1, w1[i0]);
+          w1[i0 + N1] = fmaf(-lr, hi + hi1, w1[i0 + N1]);
+        }
       }
-  }
-  __syncthreads();
-  for (int i = t; i < KS * N1; i += THREADS) {
-    float g = 0.f;
+  } else {
+    if (has_tile) {
 #pragma unroll
-    for (int s2 = 0; s2 < SLICES; ++s2) g += p4[s2 * KS * N1 + i];      // row slices in order
-    w1[i] = fmaf(-lr, g, w1[i]);
+      for (int a = 0; a < TK; ++a)
+#pragma unroll
+        for (int c = 0; c < TCC; ++c) {
+          float lo, hi;
+          unpack2(acc[a][c], lo, hi);
+          const int i0 = (k0 + 2 * a) * N1 + n0 + c;
+          p4[sl * KS * N1 + i0] = lo;
+          p4[sl * KS * N1 + i0 + N1] = hi;
+        }
+    }
+    __syncthreads();
+    for (int i = t; i < KS * N1; i += THREADS) {
+      float g = 0.f;
+#pragma unroll
+      for (int s2 = 0; s2 < SLICES; ++s2) g += p4[s2 * KS * N1 + i];    // row slices in order
+      w1[i] = fmaf(-lr, g, w1[i]);
+    }
   }
 }
 
