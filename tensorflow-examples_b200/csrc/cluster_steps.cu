@@ -162,38 +162,48 @@ __device__ __forceinline__ void forward_partial(const float* __restrict__ xs, co
   for (int i = 0; i < TR; ++i)
 #pragma unroll
     for (int p = 0; p < TC / 2; ++p) acc[i][p] = 0ull;
-#pragma unroll 1
-  for (int k = kbeg; k < kend; k += 4) {
-    // all operand loads of this step of four inputs first ...
-    float4 xv[TR];
+  // Software pipeline over steps of two inputs, two register buffers: the loads of the next step are issued before the
+  // FMAs of the current one, so the shared-memory pipe and the FMA pipe work at the same time inside one warp (with 2-4
+  // warps per sub-partition there are not enough other warps to do that overlapping for us).
+  struct Ops { float2 x[TR]; u64 w[2][TC / 2]; };
+  auto load = [&](Ops& o, int k) {
+    k = min(k, kend - 2);                                               // past the end: a valid address, result unused
 #pragma unroll
-    for (int i = 0; i < TR; ++i) xv[i] = lds_f4(xs + (r0 + i) * XS + k);   // rows >= `rows` hold zeros
-    u64 w[4][TC / 2];
+    for (int i = 0; i < TR; ++i) o.x[i] = lds_f2(xs + (r0 + i) * XS + k);   // rows >= `rows` hold zeros
 #pragma unroll
-    for (int kk = 0; kk < 4; ++kk) {
+    for (int kk = 0; kk < 2; ++kk) {
       if (TC % 4 == 0) {
 #pragma unroll
         for (int p = 0; p < TC / 4; ++p) {
           const ulonglong2 ww = lds_u64x2(w1 + (k + kk) * N1 + n0 + 4 * p);
-          w[kk][2 * p] = ww.x;
-          w[kk][(2 * p + 1) % (TC / 2)] = ww.y;
+          o.w[kk][2 * p] = ww.x;
+          o.w[kk][(2 * p + 1) % (TC / 2)] = ww.y;
         }
       } else {
 #pragma unroll
-        for (int p = 0; p < TC / 2; ++p) w[kk][p] = lds_u64(w1 + (k + kk) * N1 + n0 + 2 * p);
+        for (int p = 0; p < TC / 2; ++p) o.w[kk][p] = lds_u64(w1 + (k + kk) * N1 + n0 + 2 * p);
       }
     }
-    // ... then the FMAs, input by input: TR * TC/2 independent accumulators per input
+  };
+  auto fmas = [&](const Ops& o) {
 #pragma unroll
-    for (int kk = 0; kk < 4; ++kk) {
+    for (int kk = 0; kk < 2; ++kk)
 #pragma unroll
       for (int i = 0; i < TR; ++i) {
-        const float xs_ = kk == 0 ? xv[i].x : (kk == 1 ? xv[i].y : (kk == 2 ? xv[i].z : xv[i].w));
+        const float xs_ = kk == 0 ? o.x[i].x : o.x[i].y;
         const u64 xx = pack2(xs_, xs_);
 #pragma unroll
-        for (int p = 0; p < TC / 2; ++p) acc[i][p] = ffma2(xx, w[kk][p], acc[i][p]);
+        for (int p = 0; p < TC / 2; ++p) acc[i][p] = ffma2(xx, o.w[kk][p], acc[i][p]);
       }
-    }
+  };
+  Ops A, Bf;
+  load(A, kbeg);
+#pragma unroll 1
+  for (int k = kbeg; k < kend; k += 4) {
+    load(Bf, k + 2);
+    fmas(A);
+    load(A, k + 4);
+    fmas(Bf);
   }
 #pragma unroll
   for (int i = 0; i < TR; ++i) {
@@ -240,50 +250,60 @@ __device__ __forceinline__ void weight_gradient(const float* __restrict__ xs, co
   for (int a = 0; a < TK; ++a)
 #pragma unroll
     for (int c = 0; c < TCC; ++c) acc[a][c] = 0ull;
-  constexpr int RB = 4;                                             // rows per step: their loads first, then the FMAs
-#pragma unroll 1
-  for (int r = ra; r < rb; r += RB) {
-    u64 xp[RB][TK];
-    float d[RB][TCC];
+  // Software pipeline over pairs of rows, two register buffers (see forward_partial).
+  constexpr int RB = 2;
+  struct Ops { u64 xp[RB][TK]; float d[RB][TCC]; };
+  auto load = [&](Ops& o, int r) {
 #pragma unroll
     for (int q = 0; q < RB; ++q) {
-      const int rr = min(r + q, rb - 1);                            // rows past the slice: a valid address, masked below
+      const int rr = max(min(r + q, rb - 1), 0);                      // rows past the slice: a valid address, masked in fmas()
       if (TK % 2 == 0) {
 #pragma unroll
         for (int a = 0; a < TK / 2; ++a) {
           const ulonglong2 v = lds_u64x2(xs + rr * XS + k0 + 4 * a);
-          xp[q][2 * a] = v.x;
-          xp[q][(2 * a + 1) % TK] = v.y;
+          o.xp[q][2 * a] = v.x;
+          o.xp[q][(2 * a + 1) % TK] = v.y;
         }
       } else {
 #pragma unroll
-        for (int a = 0; a < TK; ++a) xp[q][a] = lds_u64(xs + rr * XS + k0 + 2 * a);
+        for (int a = 0; a < TK; ++a) o.xp[q][a] = lds_u64(xs + rr * XS + k0 + 2 * a);
       }
       if (TCC % 4 == 0) {
 #pragma unroll
         for (int c4 = 0; c4 < TCC / 4; ++c4) {
           const float4 v = lds_f4(dz + rr * N1 + n0 + 4 * c4);
-          d[q][4 * c4] = v.x; d[q][(4 * c4 + 1) % TCC] = v.y; d[q][(4 * c4 + 2) % TCC] = v.z; d[q][(4 * c4 + 3) % TCC] = v.w;
+          o.d[q][4 * c4] = v.x; o.d[q][(4 * c4 + 1) % TCC] = v.y; o.d[q][(4 * c4 + 2) % TCC] = v.z; o.d[q][(4 * c4 + 3) % TCC] = v.w;
         }
       } else {
 #pragma unroll
         for (int c2 = 0; c2 < TCC / 2; ++c2) {
           const float2 v = lds_f2(dz + rr * N1 + n0 + 2 * c2);
-          d[q][2 * c2] = v.x; d[q][2 * c2 + 1] = v.y;
+          o.d[q][2 * c2] = v.x; o.d[q][2 * c2 + 1] = v.y;
         }
       }
     }
+  };
+  auto fmas = [&](const Ops& o, int r) {
 #pragma unroll
     for (int q = 0; q < RB; ++q) {
       const bool on = r + q < rb;
 #pragma unroll
       for (int c = 0; c < TCC; ++c) {
-        const float dv = on ? d[q][c] : 0.f;                        // a masked row adds exact zeros
+        const float dv = on ? o.d[q][c] : 0.f;                        // a masked row adds exact zeros
         const u64 dd = pack2(dv, dv);
 #pragma unroll
-        for (int a = 0; a < TK; ++a) acc[a][c] = ffma2(xp[q][a], dd, acc[a][c]);
+        for (int a = 0; a < TK; ++a) acc[a][c] = ffma2(o.xp[q][a], dd, acc[a][c]);
       }
     }
+  };
+  Ops A, Bf;
+  load(A, ra);
+#pragma unroll 1
+  for (int r = ra; r < rb; r += 2 * RB) {
+    load(Bf, r + RB);
+    fmas(A, r);
+    load(A, r + 2 * RB);
+    fmas(Bf, r + RB);
   }
   if (LANE_SLICES) {
 #pragma unroll
