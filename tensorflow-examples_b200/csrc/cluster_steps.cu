@@ -346,7 +346,7 @@ template <int N1, int N2, int BMAX>
 __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a) {
   using L = Layout<N1, N2, BMAX>;
   constexpr bool TWO = N2 > 0;
-  constexpr int NS = L::NS, SL = L::SL, RO_MAX = L::RO_MAX;
+  constexpr int NS = L::NS, RO_MAX = L::RO_MAX;
   constexpr int NOUT = TWO ? N2 : N1;                   // classes
   constexpr int V = (N1 % 4 == 0) ? 4 : 2;              // floats per exchange load (rows of N1 floats)
   constexpr int KSPLIT = 1;                             // slots of partial pre-activations per CTA
@@ -690,9 +690,11 @@ long b2_cluster_steps_scratch_floats(int n_layers) {
   return n_layers == 2 ? (long)(cs::C + 1) * 100 * 100 + (long)cs::C * (100 * 10 + 10 + 100 + 2) : (long)(cs::C + 1) * 256 * 10 + 64;
 }
 
-// which models / batch sizes the cluster kernel takes: 784 -> 10 up to 256 rows, 784-100-10 up to 100 rows per step
+// which models / batch sizes the cluster kernel takes: 784-100-10 up to 100 rows per step (distributed.py's shipped batch),
+// 784 -> 10 up to 128 rows (measured: 5.6 / 6.4 us per step at 16 / 100 rows against 7.7 for the per-step kernels; at 256
+// rows the per-step kernels win, 7.8 against 9.1 us, although the kernel itself handles up to 256)
 bool b2_cluster_steps_applies(int n_layers, const int* dims, int rows) {
-  if (n_layers == 1) return dims[0] == cs::K0 && dims[1] == 10 && rows >= 1 && rows <= 256;
+  if (n_layers == 1) return dims[0] == cs::K0 && dims[1] == 10 && rows >= 1 && rows <= 128;
   if (n_layers == 2) return dims[0] == cs::K0 && dims[1] == 100 && dims[2] == 10 && rows >= 1 && rows <= 100;
   return false;
 }
