@@ -378,16 +378,18 @@ fused_linear_reduce_kernel(const float* __restrict__ scratch, int grid, float* _
   const int c0 = q * per, c1 = min(grid, c0 + per);
   float g = 0.f;
   if (i < RED_N) {
+    // all of this quarter's partials are requested before the first add (one L2 round trip instead of five): the loads go
+    // out unconditionally from clamped addresses, the adds run in CTA order over the valid ones -- same sum as before
     const float* p = scratch + i;
-    int c = c0;
-    for (; c + 8 <= c1; c += 8) {
-      float v[8];
+    const int clast = max(c1 - 1, 0);
+    for (int k0 = c0; k0 < c1; k0 += RED_CHUNK) {
+      float v[RED_CHUNK];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = p[(size_t)(c + u) * SCRATCH_STRIDE];
+      for (int u = 0; u < RED_CHUNK; ++u) v[u] = p[(size_t)min(k0 + u, clast) * SCRATCH_STRIDE];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) g += v[u];
+      for (int u = 0; u < RED_CHUNK; ++u)
+        if (k0 + u < c1) g += v[u];
     }
-    for (; c < c1; ++c) g += p[(size_t)c * SCRATCH_STRIDE];
   }
   sh[q][o] = g;
   __syncthreads();
@@ -428,16 +430,18 @@ fused_linear_reduce_exchange_kernel(const float* __restrict__ scratch, int grid,
   const int c0 = q * per, c1 = min(grid, c0 + per);
   float g = 0.f;
   if (i < RED_N) {
+    // all of this quarter's partials are requested before the first add (one L2 round trip instead of five): the loads go
+    // out unconditionally from clamped addresses, the adds run in CTA order over the valid ones -- same sum as before
     const float* p = scratch + i;
-    int c = c0;
-    for (; c + 8 <= c1; c += 8) {
-      float v[8];
+    const int clast = max(c1 - 1, 0);
+    for (int k0 = c0; k0 < c1; k0 += RED_CHUNK) {
+      float v[RED_CHUNK];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = p[(size_t)(c + u) * SCRATCH_STRIDE];
+      for (int u = 0; u < RED_CHUNK; ++u) v[u] = p[(size_t)min(k0 + u, clast) * SCRATCH_STRIDE];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) g += v[u];
+      for (int u = 0; u < RED_CHUNK; ++u)
+        if (k0 + u < c1) g += v[u];
     }
-    for (; c < c1; ++c) g += p[(size_t)c * SCRATCH_STRIDE];
   }
   sh[q][o] = g;
   __syncthreads();

@@ -28,6 +28,7 @@ constexpr int LOSS_IDX = 7850, CORRECT_IDX = 7851;
 // reduction over the per-CTA partials: 7852 outputs, each the sum of four quarter-sums of the grid (CTA order inside a
 // quarter, quarters combined 0,1,2,3) -- the same association in every kernel that reduces them
 constexpr int RED_OUT = 32, RED_Q = 4, RED_N = 7852;
+constexpr int RED_CHUNK = 40;   // partials a reducing thread keeps in flight (a quarter of a 148-CTA grid is 37)
 
 struct __align__(16) Smem {
   float W[K * NC];                             // 31360 B   [784][10], as in global memory
