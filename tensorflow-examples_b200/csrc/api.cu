@@ -475,6 +475,7 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
     fx.step1 = c->peer_step + 1;
     fx.parity = (int)(c->peer_step & 1u);
     for (int p = 0; p < c->nranks; ++p) fx.region[p] = (unsigned long long*)c->peer_base[p];
+    fx.prof = c->fx_prof;
   }
   int rc;
   if (use_fused_linear(c)) {
@@ -780,6 +781,14 @@ extern "C" void b2_destroy(b2_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
+  if (ctx->fx_prof) {
+    unsigned long long h[4] = {0, 0, 0, 0};
+    if (cudaMemcpy(h, ctx->fx_prof, sizeof(h), cudaMemcpyDeviceToHost) == cudaSuccess && h[2])
+      fprintf(stderr, "B2_FX_PROF rank %d of %d: %llu exchanges of element 0: %.2f us issuing the pushes, %.2f us waiting for the "
+              "last peer's cell (NVLink latency + rank skew)\n", ctx->rank, ctx->nranks, h[2], h[0] / 1e3 / h[2], h[1] / 1e3 / h[2]);
+    cudaFree(ctx->fx_prof);
+    ctx->fx_prof = nullptr;
+  }
   free_ctx(ctx);
 }
 
@@ -961,6 +970,11 @@ extern "C" int b2_peer_import(b2_ctx* ctx, const void* handles) {
     ctx->peer_base[p] = ptr;
   }
   ctx->peer_ready = 1;
+  const char* env = getenv("B2_FX_PROF");
+  if (env && *env == '1' && !ctx->fx_prof) {
+    B2_CUDA(cudaMalloc((void**)&ctx->fx_prof, 4 * sizeof(unsigned long long)));
+    B2_CUDA(cudaMemset(ctx->fx_prof, 0, 4 * sizeof(unsigned long long)));
+  }
   return B2_OK;
 }
 
@@ -1014,6 +1028,7 @@ static int enqueue_persistent(b2_ctx* c, const float* xp, const float* yp, long 
       fx.step1 = c->peer_step + 1;
       fx.parity = (int)(c->peer_step & 1u);
       for (int p = 0; p < c->nranks; ++p) fx.region[p] = (unsigned long long*)c->peer_base[p];
+      fx.prof = c->fx_prof;
     }
     const int tr = b2_fused_linear_tile_rows();
     int grid = (local_batch + tr - 1) / tr;

@@ -83,6 +83,7 @@ struct b2_ctx {
   int async_period;                // B2_OPT_ASYNC_PERIOD (0 = synchronous)
   long async_count;                // local steps since the context was created
   unsigned peer_step;              // exchanges enqueued so far
+  unsigned long long* fx_prof;     // device [4]: exchange timeline sums (B2_FX_PROF=1), printed by b2_destroy
   // bucketed all-reduce of the wide layers' weight gradients, overlapped with the rest of the backward pass
   cudaStream_t comm_stream;        // created by b2_comm_init when nranks > 1
   cudaEvent_t ev_bucket, ev_comm_done;
@@ -187,6 +188,7 @@ struct b2_fx_args {
   unsigned step1;                             // stamp of this step (exchanges so far + 1)
   int parity;
   unsigned long long* region[B2_MAX_PEERS];   // every rank's region (own entry = local memory, the others = peer mappings)
+  unsigned long long* prof;                   // diagnostics (B2_FX_PROF=1): [ns issuing pushes, ns waiting, exchanges] of element 0
 };
 #ifdef __CUDACC__
 // device side of the exchange: push my value of element i, wait for the peers' values of the same element, return the
@@ -197,25 +199,44 @@ __device__ __forceinline__ float b2_fx_exchange_at(const b2_fx_args& a, unsigned
   // one 64-bit access per cell: {value (low word), stamp (high word)}.  A .b64 access is single-copy atomic by the PTX
   // memory model, so a reader can never pair a new stamp with an old value (a .v2.u32 access gives no such guarantee)
   const unsigned long long cell = ((unsigned long long)step1 << 32) | (unsigned long long)__float_as_uint(mine);
+  const bool prof = a.prof != nullptr && i == 0;
+  unsigned long long t0 = 0, t1 = 0;
+  if (prof) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
   for (int p = 0; p < a.nranks; ++p)
     if (p != a.rank)
       asm volatile("st.relaxed.sys.global.b64 [%0], %1;" ::"l"(a.region[p] + slot + (size_t)a.rank * a.stride + i), "l"(cell)
                    : "memory");
+  if (prof) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+  // poll ALL outstanding peers' cells in each round (independent loads, issued back to back): the wait costs one round
+  // trip to local memory after the last peer's store has landed, not one per peer
   const unsigned long long* cells = a.region[a.rank] + slot + i;
-  float sum = 0.f;
-  for (int p = 0; p < a.nranks; ++p) {
-    float v = mine;
-    if (p != a.rank) {
-      unsigned long long got;
-      unsigned spins = 0;
-      for (;;) {
-        asm volatile("ld.relaxed.sys.global.b64 %0, [%1];" : "=l"(got) : "l"(cells + (size_t)p * a.stride) : "memory");
-        if ((unsigned)(got >> 32) == step1) break;
-        if (++spins > (1u << 26)) __trap();   // a dead peer must not hang this GPU for ever
+  unsigned pending = ((a.nranks >= 32 ? 0u : (1u << a.nranks)) - 1u) & ~(1u << a.rank);
+  float vals[B2_MAX_PEERS];
+  unsigned spins = 0;
+  while (pending) {
+    unsigned long long got[B2_MAX_PEERS];
+#pragma unroll
+    for (int p = 0; p < B2_MAX_PEERS; ++p)
+      if ((pending >> p) & 1u)
+        asm volatile("ld.relaxed.sys.global.b64 %0, [%1];" : "=l"(got[p]) : "l"(cells + (size_t)p * a.stride) : "memory");
+#pragma unroll
+    for (int p = 0; p < B2_MAX_PEERS; ++p)
+      if (((pending >> p) & 1u) && (unsigned)(got[p] >> 32) == step1) {
+        vals[p] = __uint_as_float((unsigned)got[p]);
+        pending &= ~(1u << p);
       }
-      v = __uint_as_float((unsigned)got);
-    }
-    sum += v;
+    if (++spins > (1u << 26)) __trap();   // a dead peer must not hang this GPU for ever
+  }
+  float sum = 0.f;
+#pragma unroll
+  for (int p = 0; p < B2_MAX_PEERS; ++p)
+    if (p < a.nranks) sum += (p == a.rank) ? mine : vals[p];        // rank order: the same sum on every rank
+  if (prof) {
+    unsigned long long t2;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t2));
+    a.prof[0] += t1 - t0;      // issuing the pushes
+    a.prof[1] += t2 - t1;      // waiting for the last peer (NVLink latency + rank skew)
+    a.prof[2] += 1;
   }
   return sum;
 }
