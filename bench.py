@@ -341,6 +341,8 @@ def make_trainer(D, workload, batch, args):
             tr.peer_import(hs)
         if precision == "bf16":
             tr.overlap_exchange(not args.no_overlap)
+        if args.sharded_apply:
+            tr.sharded_apply(True)
     return tr
 
 
@@ -574,6 +576,8 @@ def main():
     ap.add_argument("--no-overlap", action="store_true",
                     help="multi-GPU bf16 path: one all-reduce after the backward pass instead of overlapped per-layer buckets")
     ap.add_argument("--no-persistent", action="store_true", help="one launch sequence per step instead of the multi-step kernels")
+    ap.add_argument("--sharded-apply", action="store_true",
+                    help="multi-GPU, NCCL exchange: reduce-scatter + apply on the own slice + all-gather instead of all-reduce + full apply")
     ap.add_argument("--multistep-fused", action="store_true", help="784->10: all steps in one launch of the fused kernel (optional path)")
     ap.add_argument("--sweep", action="store_true", help="batch-size sweep of c3 / c3 with the SSE head / 784-100-10 instead of the headline line")
     ap.add_argument("--sweep-out", default=os.path.join(ROOT, "gpurun_out", "sweep.json"))

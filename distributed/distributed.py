@@ -49,6 +49,8 @@ flags.DEFINE_string("logs_path", "", "TensorBoard event directory; the reference
                     "Empty (default) writes no event files")
 flags.DEFINE_integer("async_period", 0, "k > 0: emulate the reference's asynchronous parameter-server updates -- every worker "
                      "applies its own gradients, replicas are averaged every k steps; 0 (default): synchronous all-reduce")
+flags.DEFINE_boolean("sharded_apply", False, "several workers, NCCL exchange: every worker owns one slice of the variables (reduce-"
+                     "scatter, apply on the slice, all-gather) -- what several ps tasks are in the reference (distributed.py:63-65)")
 flags.DEFINE_boolean("peer_exchange", True, "workers on one NVLink box sum gradients through peer memory instead of NCCL")
 flags.DEFINE_string("tf_op_seeds", "", "two integers 'a,b': draw W1 and W2 with TensorFlow 1.x's own generator for "
                     "tf.set_random_seed(2) (distributed.py:83) and these op seeds (the graph's op counter at "
@@ -146,6 +148,9 @@ def main(argv):
         store.set("b2_peer_ok_%d" % role.rank, b"1" if ok else b"0")
         if not all(bytes(store.get("b2_peer_ok_%d" % r)) == b"1" for r in range(role.world)):
             model.use_peer_exchange(False)      # somebody could not map a peer: everyone stays on NCCL
+    if role.world > 1 and FLAGS.sharded_apply:
+        model.use_peer_exchange(False)
+        model.sharded_apply(True)
     if role.world > 1 and FLAGS.async_period > 0:
         model.set_async_period(FLAGS.async_period)
     cl.store_barrier(store, role, "b2_comm_ready")

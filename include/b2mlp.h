@@ -65,6 +65,11 @@ enum {
                                  step boundary (reduction, exchange, apply) behind in-kernel grid barriers.  Bit-identical to
                                  the default (one step kernel + one reduction kernel per step, chained by programmatic
                                  dependent launch) and measured SLOWER than it at every batch size, so it is off by default */
+  B2_OPT_SHARDED_APPLY = 10, /* value 1 (nranks > 1, NCCL exchange): the B200 analogue of SEVERAL parameter servers
+                                 (distributed.py:63-65: replica_device_setter spreads the variables over the ps tasks):
+                                 rank r owns slice r of the flat parameter vector -- reduce-scatter of the gradients, SGD apply
+                                 on the own slice only, all-gather of the updated parameters -- instead of an all-reduce and
+                                 a full apply on every rank.  Same update, replicas stay bit-identical */
   B2_OPT_ASYNC_PERIOD = 5     /* value k > 0: emulate the reference's ASYNCHRONOUS parameter-server training
                                  (distributed.py:107-113: plain GradientDescentOptimizer, SyncReplicas commented out):
                                  every worker applies its own gradients locally (mean over ITS batch) and the replicas'

@@ -24,6 +24,7 @@ OPT_NO_SPLIT3 = 6
 OPT_NO_NARROW_HEAD = 7
 OPT_NO_PERSISTENT = 8
 OPT_MULTISTEP_FUSED = 9
+OPT_SHARDED_APPLY = 10
 OPT_ASYNC_PERIOD = 5
 PEER_HANDLE_BYTES = 64
 

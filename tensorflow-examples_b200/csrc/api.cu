@@ -33,6 +33,8 @@ typedef int (*pfn_ncclGetUniqueId)(nccl_uid*);
 typedef int (*pfn_ncclCommInitRank)(void**, int, nccl_uid, int);
 typedef int (*pfn_ncclCommDestroy)(void*);
 typedef int (*pfn_ncclAllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*pfn_ncclReduceScatter)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*pfn_ncclAllGather)(const void*, void*, size_t, int, void*, cudaStream_t);
 typedef const char* (*pfn_ncclGetErrorString)(int);
 typedef int (*pfn_ncclGroup)(void);
 struct nccl_api {
@@ -41,10 +43,12 @@ struct nccl_api {
   pfn_ncclCommInitRank CommInitRank;
   pfn_ncclCommDestroy CommDestroy;
   pfn_ncclAllReduce AllReduce;
+  pfn_ncclReduceScatter ReduceScatter;
+  pfn_ncclAllGather AllGather;
   pfn_ncclGetErrorString GetErrorString;
   pfn_ncclGroup GroupStart, GroupEnd;
 };
-nccl_api g_nccl = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+nccl_api g_nccl = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 constexpr int kNcclFloat = 7;  // ncclFloat32
 constexpr int kNcclSum = 0;    // ncclSum
 
@@ -65,10 +69,13 @@ int load_nccl() {
   g_nccl.CommInitRank = (pfn_ncclCommInitRank)dlsym(h, "ncclCommInitRank");
   g_nccl.CommDestroy = (pfn_ncclCommDestroy)dlsym(h, "ncclCommDestroy");
   g_nccl.AllReduce = (pfn_ncclAllReduce)dlsym(h, "ncclAllReduce");
+  g_nccl.ReduceScatter = (pfn_ncclReduceScatter)dlsym(h, "ncclReduceScatter");
+  g_nccl.AllGather = (pfn_ncclAllGather)dlsym(h, "ncclAllGather");
   g_nccl.GetErrorString = (pfn_ncclGetErrorString)dlsym(h, "ncclGetErrorString");
   g_nccl.GroupStart = (pfn_ncclGroup)dlsym(h, "ncclGroupStart");
   g_nccl.GroupEnd = (pfn_ncclGroup)dlsym(h, "ncclGroupEnd");
-  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.CommDestroy || !g_nccl.AllReduce ||
+  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.CommDestroy || !g_nccl.AllReduce || !g_nccl.ReduceScatter ||
+      !g_nccl.AllGather ||
       !g_nccl.GetErrorString || !g_nccl.GroupStart || !g_nccl.GroupEnd) {
     b2_set_error("NCCL library lacks a required symbol");
     return B2_ERR_NCCL;
@@ -244,6 +251,30 @@ int enqueue_layered(b2_ctx* c, const float* x, const float* y, int rows, float i
   return B2_OK;
 }
 
+// Sharded update -- the analogue of k parameter servers (distributed.py:63-65).  Rank r owns elements [r*S, (r+1)*S) of
+// the flat parameter vector: reduce-scatter of the gradients (in place), SGD apply on the own slice, all-gather of the
+// updated parameters (in place).  loss / correct sit in one rank's slice of the gradient vector, so they are summed on
+// the side.  Both buffers are allocated with room for nranks * S elements.
+inline long shard_size(const b2_ctx* c) { return round4((c->P + 4 + c->nranks - 1) / c->nranks); }
+
+int exchange_sharded(b2_ctx* c, float lr, float* loss_trace, int* correct_trace, cudaStream_t s) {
+  const long S = shard_size(c);
+  B2_CUDA(cudaMemcpyAsync(c->lc_dev, c->grads + c->P, 4 * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  B2_NCCL(g_nccl.GroupStart());
+  B2_NCCL(g_nccl.AllReduce(c->lc_dev, c->lc_dev, 4, kNcclFloat, kNcclSum, c->nccl_comm, s));
+  B2_NCCL(g_nccl.ReduceScatter(c->grads, c->grads + (long)c->rank * S, (size_t)S, kNcclFloat, kNcclSum, c->nccl_comm, s));
+  B2_NCCL(g_nccl.GroupEnd());
+  long n = c->P - (long)c->rank * S;                       // my slice may reach past the parameters (padding, loss, correct)
+  n = n < 0 ? 0 : (n > S ? S : n);
+  int rc = b2_launch_sharded_apply(c->params + (long)c->rank * S, c->grads + (long)c->rank * S, n, lr, c->lc_dev, loss_trace,
+                                   correct_trace, c->global_step_dev, c->sm_count, s);
+  if (rc) return rc;
+  c->launches++;
+  B2_NCCL(g_nccl.AllGather(c->params + (long)c->rank * S, c->params, (size_t)S, kNcclFloat, c->nccl_comm, s));
+  c->wb_stale = 1;                                         // bf16 path: the weight copies are refreshed before the next forward
+  return B2_OK;
+}
+
 // ---- bf16-operand path: tensor-core GEMMs for the hidden layers, CUDA cores for the narrow output layer ----
 inline bool is_mixed(const b2_ctx* c) { return c->precision == B2_PREC_BF16_FP32ACC; }
 
@@ -352,7 +383,8 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
   if (rc) return rc;
   c->launches++;
   const bool exchange = c->nranks > 1 && c->async_period == 0;
-  const bool overlap = exchange && !c->opt_no_overlap && !c->opt_timing && c->comm_stream != nullptr;
+  const bool sharded = exchange && c->opt_sharded;
+  const bool overlap = exchange && !sharded && !c->opt_no_overlap && !c->opt_timing && c->comm_stream != nullptr;
   bool bucketed[B2_MAX_LAYERS] = {};
   int cur = 0;
   for (int l = L - 1; l >= 0; --l) {
@@ -428,6 +460,13 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
   }
   if (rc) return rc;
   c->launches++;
+  if (sharded) {
+    timed_scope t(c, B2_K_ALLREDUCE_APPLY, s);
+    rc = exchange_sharded(c, lr, loss_trace, correct_trace, s);
+    if (rc) return rc;
+    c->global_step_host += 1.0f;
+    return B2_OK;
+  }
   if (exchange) {
     // everything that was not sent as a bucket: the first layer's weights, all biases, the output layer, loss and correct
     timed_scope t(c, B2_K_ALLREDUCE_APPLY, s);
@@ -551,11 +590,16 @@ int enqueue_step(b2_ctx* c, const float* x, const float* y, int rows, long globa
     // the parameter-server push/pull of the reference (distributed.py:63-65) becomes one
     // all-reduce of [gradients..., loss, correct]; every rank then applies the same update.
     timed_scope t(c, B2_K_ALLREDUCE_APPLY, s);
-    B2_NCCL(g_nccl.AllReduce(c->grads, c->grads, (size_t)(c->P + 4), kNcclFloat, kNcclSum, c->nccl_comm, s));
-    rc = b2_launch_sgd_apply(c->params, c->grads, c->P, lr, loss_trace, correct_trace,
-                             c->global_step_dev, c->sm_count, s);
-    if (rc) return rc;
-    c->launches++;
+    if (c->opt_sharded) {
+      rc = exchange_sharded(c, lr, loss_trace, correct_trace, s);
+      if (rc) return rc;
+    } else {
+      B2_NCCL(g_nccl.AllReduce(c->grads, c->grads, (size_t)(c->P + 4), kNcclFloat, kNcclSum, c->nccl_comm, s));
+      rc = b2_launch_sgd_apply(c->params, c->grads, c->P, lr, loss_trace, correct_trace,
+                               c->global_step_dev, c->sm_count, s);
+      if (rc) return rc;
+      c->launches++;
+    }
   }
   c->global_step_host += 1.0f;
   return B2_OK;
@@ -580,6 +624,7 @@ void free_ctx(b2_ctx* c) {
   cudaFree(c->dzn);
   cudaFree(c->params);
   cudaFree(c->grads);
+  cudaFree(c->lc_dev);
   for (int l = 0; l < B2_MAX_LAYERS; ++l) cudaFree(c->act_buf[l]);
   cudaFree(c->z_last);
   cudaFree(c->dz[0]);
@@ -710,8 +755,10 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
     }                                                                                  \
   } while (0)
 
-  B2_ALLOC(c->params, c->P);
-  B2_ALLOC(c->grads, c->P + 4);
+  // (+ 4 * B2_MAX_PEERS: a sharded update cuts both vectors into nranks slices of round4(ceil((P+4)/nranks)) elements)
+  B2_ALLOC(c->params, c->P + 4 + 4 * B2_MAX_PEERS);
+  B2_ALLOC(c->grads, c->P + 4 + 4 * B2_MAX_PEERS);
+  B2_ALLOC(c->lc_dev, 4);
   B2_ALLOC(c->z_last, (long)max_local_batch * dims[n_layers]);
   if (precision == B2_PREC_BF16_FP32ACC) {
     // bf16 buffers are sized in floats / 2 (dims are multiples of 8)
@@ -763,8 +810,8 @@ extern "C" int b2_create(b2_ctx** out, int device, int n_layers, const int* dims
     if (b2_fused_linear_prepare() != B2_OK || b2_fused_linear_ms_prepare() != B2_OK) { free_ctx(c); return B2_ERR_CUDA; }
   }
 #undef B2_ALLOC
-  cudaError_t e = cudaMemset(c->params, 0, (size_t)c->P * sizeof(float));
-  if (e == cudaSuccess) e = cudaMemset(c->grads, 0, (size_t)(c->P + 4) * sizeof(float));
+  cudaError_t e = cudaMemset(c->params, 0, (size_t)(c->P + 4 + 4 * B2_MAX_PEERS) * sizeof(float));
+  if (e == cudaSuccess) e = cudaMemset(c->grads, 0, (size_t)(c->P + 4 + 4 * B2_MAX_PEERS) * sizeof(float));
   if (e == cudaSuccess) e = cudaMemset(c->global_step_dev, 0, sizeof(float));
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaMallocHost((void**)&c->fetch_host, 2 * sizeof(float));
@@ -803,6 +850,7 @@ extern "C" int b2_set_option(b2_ctx* ctx, int option, int value) {
     case B2_OPT_NO_BUCKET_OVERLAP: ctx->opt_no_overlap = value ? 1 : 0; return B2_OK;
     case B2_OPT_NO_PERSISTENT: ctx->opt_no_persistent = value ? 1 : 0; return B2_OK;
     case B2_OPT_MULTISTEP_FUSED: ctx->opt_multistep_fused = value ? 1 : 0; return B2_OK;
+    case B2_OPT_SHARDED_APPLY: ctx->opt_sharded = value ? 1 : 0; return B2_OK;
     case B2_OPT_ASYNC_PERIOD:
       B2_CHECK_ARG(value >= 0, "b2_set_option: async period must be >= 0");
       ctx->async_period = value;

@@ -106,6 +106,8 @@ struct b2_ctx {
   int opt_no_narrow_head;          // B2_OPT_NO_NARROW_HEAD
   int opt_no_persistent;           // B2_OPT_NO_PERSISTENT
   int opt_multistep_fused;         // B2_OPT_MULTISTEP_FUSED
+  int opt_sharded;                 // B2_OPT_SHARDED_APPLY
+  float* lc_dev;                   // [4] loss / correct on the side of a sharded update
   unsigned* grid_bar;              // [2] grid-barrier counters of the persistent multi-step kernels
   float* cs_scratch;               // exchange buffers of the cluster kernel (cluster_steps.cu), when the model qualifies
   int head_used;                   // loss / correct partials written by the last forward (<= head_blocks)
@@ -151,6 +153,9 @@ int b2_launch_reduce(const b2_reduce_args& a, const float* scratch, float* grads
 // params -= lr * grads after the all-reduce; trace writes; global_step += 1
 int b2_launch_sgd_apply(float* params, const float* grads, long P, float lr, float* loss_trace,
                         int* correct_trace, float* global_step, int sm_count, cudaStream_t s);
+// sharded update of the parameters one rank owns (after a reduce-scatter of the gradients); lc = {loss, correct} over all ranks
+int b2_launch_sharded_apply(float* params_shard, const float* grads_shard, long n, float lr, const float* lc, float* loss_trace,
+                            int* correct_trace, float* global_step, int sm_count, cudaStream_t s);
 // eval accumulation: acc[0] += loss partials, acc[1] += correct partials (fixed order)
 int b2_launch_eval_accumulate(const float* loss_part, const float* correct_part, int blocks,
                               float* acc, cudaStream_t s);

@@ -302,6 +302,21 @@ sgd_apply_kernel(float* __restrict__ params, const float* __restrict__ grads, lo
   }
 }
 
+// Sharded update: this rank owns n consecutive parameters; `lc` = {loss, correct} summed over the ranks (all-reduced on
+// the side, since they live in one rank's shard of the gradient vector only).
+__global__ void __launch_bounds__(256)
+sharded_apply_kernel(float* __restrict__ params_shard, const float* __restrict__ grads_shard, long n, float lr,
+                     const float* __restrict__ lc, float* __restrict__ loss_trace, int* __restrict__ correct_trace,
+                     float* __restrict__ global_step) {
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
+    params_shard[i] -= lr * grads_shard[i];
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    if (loss_trace) *loss_trace = lc[0];
+    if (correct_trace) *correct_trace = (int)(lc[1] + 0.5f);
+    *global_step += 1.0f;
+  }
+}
+
 __global__ void __launch_bounds__(256) scale_kernel(float* __restrict__ p, long n, float a) {
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) p[i] *= a;
 }
@@ -381,6 +396,17 @@ int b2_launch_sgd_apply(float* params, const float* grads, long P, float lr, flo
   if (blocks < 1) blocks = 1;
   sgd_apply_kernel<<<(int)blocks, 256, 0, s>>>(params, grads, P, lr, loss_trace, correct_trace,
                                                global_step);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_launch_sharded_apply(float* params_shard, const float* grads_shard, long n, float lr, const float* lc, float* loss_trace,
+                            int* correct_trace, float* global_step, int sm_count, cudaStream_t s) {
+  long blocks = (n + 255) / 256;
+  const long cap = (long)sm_count * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  sharded_apply_kernel<<<(int)blocks, 256, 0, s>>>(params_shard, grads_shard, n, lr, lc, loss_trace, correct_trace, global_step);
   B2_LAUNCH_CHECK();
   return B2_OK;
 }

@@ -207,6 +207,12 @@ class DenseTrainer:
         every k steps; distributed.py:107-113).  0: synchronous all-reduce (default)."""
         self.set_option(_ffi.OPT_ASYNC_PERIOD, int(k))
 
+    def sharded_apply(self, on=True):
+        """Several ranks, NCCL exchange: every rank owns one slice of the parameter vector (reduce-scatter of the gradients,
+        SGD apply on the own slice, all-gather of the parameters) -- what k parameter servers are in the reference
+        (distributed.py:63-65) -- instead of an all-reduce and a full apply on every rank."""
+        self.set_option(_ffi.OPT_SHARDED_APPLY, 1 if on else 0)
+
     def use_peer_exchange(self, on=True):
         self.set_option(_ffi.OPT_NO_PEER_EXCHANGE, 0 if on else 1)
 

@@ -37,6 +37,8 @@ dist.broadcast_object_list(uid, src=0)
 tr.init_comm(rank, world, uid[0])
 if %(async_k)d:
     tr.set_async_period(%(async_k)d)
+if %(sharded)d:
+    tr.sharded_apply(True)
 if %(peer)d:
     hs = [None] * world
     dist.all_gather_object(hs, tr.peer_export())
@@ -61,7 +63,7 @@ def test_n_rank_trace_equals_single_process_oracle(cuda_device, tmp_path, dims, 
         pytest.skip("needs at least 2 GPUs")
     lb, steps = 96, 12
     script = tmp_path / "worker.py"
-    script.write_text(WORKER % dict(root=ROOT, dims=dims, act=act, scaled=scaled, lb=lb, steps=steps, out=str(tmp_path), peer=peer, prec=prec, async_k=0))
+    script.write_text(WORKER % dict(root=ROOT, dims=dims, act=act, scaled=scaled, lb=lb, steps=steps, out=str(tmp_path), peer=peer, prec=prec, async_k=0, sharded=0))
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % world,
                         "--master-addr", "127.0.0.1", "--master-port", "29611", str(script)],
                        capture_output=True, text=True, timeout=900)
@@ -125,7 +127,7 @@ def test_async_emulation_mode(cuda_device, tmp_path, period):
     dims, act, scaled, lb, steps = [784, 100, 10], 1, False, 64, 8
     script = tmp_path / "worker.py"
     script.write_text(WORKER % dict(root=ROOT, dims=dims, act=act, scaled=scaled, lb=lb, steps=steps, out=str(tmp_path),
-                                    peer=0, prec="fp32", async_k=period))
+                                    peer=0, prec="fp32", async_k=period, sharded=0))
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % world,
                         "--master-addr", "127.0.0.1", "--master-port", "29613", str(script)],
                        capture_output=True, text=True, timeout=900)
@@ -144,3 +146,38 @@ def test_async_emulation_mode(cuda_device, tmp_path, period):
         assert diff <= 1e-5 * max(1.0, float(np.abs(g.W[0]).max()))    # same update as synchronous data parallelism
     else:
         assert 0 < diff < 1e-2                                          # drifted, but still the same training run
+
+
+@pytest.mark.parametrize("dims,act,scaled,prec", [([784, 100, 10], 1, False, "fp32"), ([784, 256, 128, 10], 1, True, "bf16")])
+def test_sharded_apply_equals_single_process_oracle(cuda_device, tmp_path, dims, act, scaled, prec):
+    """SURVEY 8(f) row 3, second half (distributed.py:63-65: replica_device_setter spreads the variables over k parameter
+    servers): every rank owns one slice of the parameter vector -- reduce-scatter of the gradients, SGD apply on the own
+    slice, all-gather of the parameters.  The N-rank trace must equal the single-process oracle at the global batch, and
+    the replicas must stay bit-identical."""
+    world = min(torch.cuda.device_count(), 4)
+    if world < 2:
+        pytest.skip("needs at least 2 GPUs")
+    lb, steps = 96, 12
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER % dict(root=ROOT, dims=dims, act=act, scaled=scaled, lb=lb, steps=steps, out=str(tmp_path), peer=0,
+                                    prec=prec, async_k=0, sharded=1))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % world,
+                        "--master-addr", "127.0.0.1", "--master-port", "29615", str(script)],
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-3000:]
+    gb = lb * world
+    x, y = synthetic.make_pool(gb * steps)
+    Ws, bs = synthetic.make_weights(dims, scaled)
+    g = oracle.TF1Graph(dims, act, oracle.LOSS_SOFTMAX_CE, Ws, bs, precision=prec)
+    want = [g.train_step(x[s * gb:(s + 1) * gb], y[s * gb:(s + 1) * gb], 0.001) for s in range(steps)]
+    outs = [np.load(tmp_path / ("rank%d.npz" % r_)) for r_ in range(world)]
+    ltol, wtol, ctol = (1e-5, 1e-5, 1) if prec == "fp32" else (2e-3, 2e-3, 4)
+    for o in outs:
+        for s in range(steps):
+            assert abs(float(o["loss"][s]) - float(want[s][0])) <= ltol * max(1.0, abs(float(want[s][0])))
+            assert abs(int(o["correct"][s]) - want[s][1]) <= ctol
+        assert np.abs(o["W0"] - g.W[0]).max() <= wtol * max(1.0, float(np.abs(g.W[0]).max()))
+        assert np.abs(o["b0"] - g.b[0]).max() <= wtol * max(1.0, float(np.abs(g.W[0]).max()))
+        assert o["gs"] == np.float32(steps)
+        np.testing.assert_array_equal(o["W0"], outs[0]["W0"])      # replicas stay bit-identical
+        np.testing.assert_array_equal(o["loss"], outs[0]["loss"])
