@@ -35,3 +35,19 @@ def test_reference_arm_line_has_the_contract_keys():
 def test_reference_arm_other_ranks_print_nothing():
     # under torchrun only rank 0 runs the CPU arm; the other ranks exit 0 without work
     assert _ref_line(["--gpus", "2"], env={"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"}) == []
+
+
+def test_both_arms_build_the_same_config_object():
+    """The driver compares the two arms' `config` objects (`same_config`): both come from bench.make_config, and every key
+    is a function of (workload, batch, world, exchange flags) only -- nothing an arm could fill in differently."""
+    sys.path.insert(0, ROOT)
+    import bench
+    d = json.loads(_ref_line([])[0])
+    assert d["config"] == bench.make_config("c3", 256, 1)
+    for world in (1, 2, 8):
+        cfg = bench.make_config("c3", 65536, world)
+        assert cfg["global_batch"] == 65536 * world and cfg["parallelism"] == "dp%d" % world
+        assert cfg["pool_rows"] % cfg["global_batch"] == 0 and cfg["pool_rows"] >= 2 * cfg["global_batch"]
+        assert ("NVLink" in cfg["gradient_exchange"]) == (world > 1)
+    assert "nccl" in bench.make_config("c5", 65536, 8)["gradient_exchange"]
+    assert "nccl" in bench.make_config("c3", 65536, 8, no_peer=True)["gradient_exchange"]
