@@ -97,22 +97,20 @@ template <int N1, int N2, int BMAX>
 struct Layout {
   static constexpr int RO_MAX = (BMAX + C - 1) / C;                 // rows a CTA finishes per step
   static constexpr int NS = N2 > 0 ? N1 * N2 + N2 + N1 + 2 : N1 + 2;   // small gradients: [W2][b2][b1][loss][correct] or [b][loss][correct]
-  static constexpr int SL = (NS + C - 1) / C;                       // slice of them a CTA reduces
   static constexpr int P4_SLICES = N2 > 0 ? 2 : 16;                 // row slices of the weight-gradient pass
   static constexpr int x = 0;                                       // [2][BMAX][XS]
   static constexpr int w1 = x + 2 * BMAX * XS;                      // [KS][N1]
   static constexpr int dz = w1 + KS * N1;                           // [BMAX][N1]   gradient w.r.t. the first layer's pre-activations
   static constexpr int small = dz + BMAX * N1;                      // replicated small parameters [W2][b2][b1] or [b]
   static constexpr int spart = small + ((NS + 3) & ~3);             // this CTA's partial small gradients [NS]
-  static constexpr int sred = spart + ((NS + 3) & ~3);              // reduced slice [SL]
-  static constexpr int a2 = sred + ((SL + 3) & ~3);                 // [RO_MAX][N1]  activations of my rows
+  static constexpr int a2 = spart + ((NS + 3) & ~3);                // [RO_MAX][N1]  activations of my rows
   static constexpr int dzown = a2 + RO_MAX * N1;                    // [RO_MAX][N1]  my rows of dz
   static constexpr int z3 = dzown + RO_MAX * N1;                    // [RO_MAX][16]  logits of my rows
   static constexpr int dz3 = z3 + RO_MAX * 16;                      // [RO_MAX][16]
   static constexpr int ys = dz3 + RO_MAX * 16;                      // [2][RO_MAX][NC] labels of my rows, double buffered
   static constexpr int rowl = ys + 2 * RO_MAX * NC;                 // [RO_MAX] row loss, [RO_MAX] hit
-  static constexpr int p4 = (rowl + 2 * RO_MAX + 3) & ~3;           // [P4_SLICES][KS][N1] partial weight gradients
-  static constexpr int total = p4 + P4_SLICES * KS * N1;
+  static constexpr int p4 = (rowl + 2 * RO_MAX + 3) & ~3;           // [P4_SLICES][KS][N1] partial weight gradients (none when
+  static constexpr int total = p4 + (P4_SLICES > 2 ? P4_SLICES * KS * N1 : 0);   // the two slices sit on the halves of a warp)
 };
 
 // Shared-memory loads as volatile asm: they stay where the source puts them -- all operand loads of a tile step first,
@@ -363,7 +361,6 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
   float* dz = sm + L::dz;
   float* small = sm + L::small;
   float* spart = sm + L::spart;
-  float* sred = sm + L::sred;
   float* a2 = sm + L::a2;
   float* dzown = sm + L::dzown;
   float* z3 = sm + L::z3;
@@ -462,8 +459,8 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
     if constexpr (TWO) {
       // output layer z3 = a2 W2 + b2 (distributed.py:98)
       // four lanes per output: lane q adds hidden units q, q+4, ...; the four parts are combined ((p0+p1)+(p2+p3))
-      {
-        const int i = t >> 2, q = t & 3;                             // RO_MAX * N2 <= 128 outputs: one pass
+      for (int base = 0; base < rcnt * N2; base += THREADS / 4) {     // (uniform over the CTA: whole warps shuffle)
+        const int i = base + (t >> 2), q = t & 3;
         const bool on = i < rcnt * N2;
         const int r = on ? i / N2 : 0, c = on ? i - r * N2 : 0;
         float z = 0.f;
@@ -701,15 +698,16 @@ static int launch(const args& a, cudaStream_t s) {
 // floats of global scratch the kernel exchanges through for a model whose first layer has n1 outputs: 14 slots of partial
 // pre-activations + dz, at the largest batch the kernel takes
 long b2_cluster_steps_scratch_floats(int n_layers) {
-  return n_layers == 2 ? (long)(cs::C + 1) * 100 * 100 + (long)cs::C * (100 * 10 + 10 + 100 + 2) : (long)(cs::C + 1) * 256 * 10 + 64;
+  return n_layers == 2 ? (long)(cs::C + 1) * 200 * 100 + (long)cs::C * (100 * 10 + 10 + 100 + 2) : (long)(cs::C + 1) * 256 * 10 + 64;
 }
 
-// which models / batch sizes the cluster kernel takes: 784-100-10 up to 100 rows per step (distributed.py's shipped batch),
+// which models / batch sizes the cluster kernel takes: 784-100-10 up to 200 rows per step (distributed.py ships 100; 200 is
+// what fits the shared memory with x double-buffered),
 // 784 -> 10 up to 128 rows (measured: 5.6 / 6.4 us per step at 16 / 100 rows against 7.7 for the per-step kernels; at 256
 // rows the per-step kernels win, 7.8 against 9.1 us, although the kernel itself handles up to 256)
 bool b2_cluster_steps_applies(int n_layers, const int* dims, int rows) {
   if (n_layers == 1) return dims[0] == cs::K0 && dims[1] == 10 && rows >= 1 && rows <= 128;
-  if (n_layers == 2) return dims[0] == cs::K0 && dims[1] == 100 && dims[2] == 10 && rows >= 1 && rows <= 100;
+  if (n_layers == 2) return dims[0] == cs::K0 && dims[1] == 100 && dims[2] == 10 && rows >= 1 && rows <= 200;
   return false;
 }
 
@@ -727,5 +725,5 @@ int b2_launch_cluster_steps(int n_layers, int act, int loss, const long* w_off, 
   a.scratch = scratch;
   a.w1_off = w_off[0]; a.b1_off = b_off[0];
   if (n_layers == 2) { a.w2_off = w_off[1]; a.b2_off = b_off[1]; }
-  return n_layers == 2 ? cs::launch<100, 10, 100>(a, s) : cs::launch<10, 0, 256>(a, s);
+  return n_layers == 2 ? cs::launch<100, 10, 200>(a, s) : cs::launch<10, 0, 256>(a, s);
 }

@@ -141,6 +141,8 @@ def _ambiguous(g64, x, margin=1e-4):
     ([784, 100, 10], oracle.ACT_SIGMOID, False, oracle.LOSS_SOFTMAX_CE, 1, 5),
     ([784, 100, 10], oracle.ACT_SIGMOID, False, oracle.LOSS_SOFTMAX_CE, 37, 11),
     ([784, 100, 10], oracle.ACT_SIGMOID, False, oracle.LOSS_SOFTMAX_CE, 99, 6),
+    ([784, 100, 10], oracle.ACT_SIGMOID, False, oracle.LOSS_SOFTMAX_CE, 200, 8),   # the largest batch it takes
+    ([784, 100, 10], oracle.ACT_SIGMOID, False, oracle.LOSS_SOFTMAX_CE, 173, 5),
     ([784, 100, 10], oracle.ACT_IDENTITY, True, oracle.LOSS_SOFTMAX_CE, 64, 6),
     ([784, 100, 10], oracle.ACT_SIGMOID, True, oracle.LOSS_SSE, 50, 6),
 ])

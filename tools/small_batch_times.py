@@ -13,7 +13,7 @@ from tensorflow_examples_b200 import synthetic  # noqa: E402
 dev = torch.device("cuda", 0)
 hx, hy = synthetic.make_pool(55000)
 x, y = torch.from_numpy(hx).to(dev), torch.from_numpy(hy).to(dev)
-cases = [([784, 10], 0, True, [16, 64, 100, 256]), ([784, 100, 10], 1, False, [16, 32, 64, 100])]
+cases = [([784, 10], 0, True, [16, 64, 100, 256]), ([784, 100, 10], 1, False, [16, 32, 64, 100, 128, 200])]
 for dims, act, scaled, batches in cases:
     for B in batches:
         for persistent in (True, False):
