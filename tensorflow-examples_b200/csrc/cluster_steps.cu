@@ -458,16 +458,11 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
     CS_TICK(3);
     if constexpr (TWO) {
       // output layer z3 = a2 W2 + b2 (distributed.py:98)
-      // four lanes per output: lane q adds hidden units q, q+4, ...; the four parts are combined ((p0+p1)+(p2+p3))
-      for (int base = 0; base < rcnt * N2; base += THREADS / 4) {     // (uniform over the CTA: whole warps shuffle)
-        const int i = base + (t >> 2), q = t & 3;
-        const bool on = i < rcnt * N2;
-        const int r = on ? i / N2 : 0, c = on ? i - r * N2 : 0;
+      for (int i = t; i < rcnt * N2; i += THREADS) {
+        const int r = i / N2, c = i - r * N2;
         float z = 0.f;
-        for (int h = q; h < N1; h += 4) z = fmaf(a2[r * N1 + h], W2s[h * N2 + c], z);
-        z += __shfl_xor_sync(0xffffffffu, z, 1);
-        z += __shfl_xor_sync(0xffffffffu, z, 2);
-        if (on && q == 0) z3[r * 16 + c] = z + b2s[c];
+        for (int h = 0; h < N1; ++h) z = fmaf(a2[r * N1 + h], W2s[h * N2 + c], z);
+        z3[r * 16 + c] = z + b2s[c];
       }
       __syncthreads();
     }
@@ -581,25 +576,16 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
     } else {
       // every CTA adds all C partials of every element itself (C loads from L2 in flight per element, CTA order): no
       // reduce-scatter, no third barrier
-      constexpr int ROUNDS = (NS + THREADS - 1) / THREADS;          // elements per thread (3 for the two-layer model)
-      float p[ROUNDS][C];
+      for (int i = t; i < NS; i += THREADS) {
+        float p[C];
 #pragma unroll
-      for (int rd = 0; rd < ROUNDS; ++rd) {                         // every load is requested before the first add
-        const int i = min(t + rd * THREADS, NS - 1);
+        for (int c = 0; c < C; ++c) p[c] = __ldcg(sp_all + (size_t)c * NS + i);
+        float g = 0.f;
 #pragma unroll
-        for (int c = 0; c < C; ++c) p[rd][c] = __ldcg(sp_all + (size_t)c * NS + i);
-      }
-#pragma unroll
-      for (int rd = 0; rd < ROUNDS; ++rd) {
-        const int i = t + rd * THREADS;
-        if (i < NS) {
-          float g = 0.f;
-#pragma unroll
-          for (int c = 0; c < C; ++c) g += p[rd][c];
-          if (i < NS - 2) small[i] = fmaf(-a.lr, g, small[i]);     // [W2][b2][b1] in the order of the gradient vector
-          else if (i == NS - 2) step_loss = g;
-          else step_correct = g;
-        }
+        for (int c = 0; c < C; ++c) g += p[c];
+        if (i < NS - 2) small[i] = fmaf(-a.lr, g, small[i]);       // [W2][b2][b1] in the order of the gradient vector
+        else if (i == NS - 2) step_loss = g;
+        else step_correct = g;
       }
     }
     if (j == 0) {
