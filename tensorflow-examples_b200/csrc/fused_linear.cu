@@ -7,11 +7,10 @@
 // Persistent grid, one CTA per SM, 16 warps working as a pipeline over 16-row tiles; the stages
 // hand tiles to each other through mbarriers, so nobody waits on a CTA-wide barrier:
 //   warp 14     P  producer: cp.async.bulk of rows + labels into a 7-stage ring of 8-row stages
-//   warps 0-6   F  forward of tile t+1: warp = 112-wide slice of the 784 inputs, lane = (8 input
-//                  sub-slices) x (4 row quads): 4 rows x 10 classes per thread, packed fp32x2 FMAs
+//   warps 0-6   F  forward of tile t+1: warp = 112-wide slice of the 784 inputs, lane = (4 input
+//                  sub-slices) x (8 row pairs): 2 rows x 10 classes per thread, packed fp32x2 FMAs
 //                  (FFMA2) over class pairs: the W pair comes straight from the [784][10] tile in
-//                  shared memory (one bulk copy), the x value is the scalar-broadcast operand;
-//                  reduce-scatter over the sub-slices by shuffles (forward_tile, fused_linear.cuh)
+//                  shared memory (one bulk copy), the x value is the scalar-broadcast operand
 //   warp 15     H  head of tile t+1: sums the 7 partial logits, softmax / loss / accuracy / dz
 //                  (lane = row x class-half, one shuffle per reduction), dz stored as (d,d) pairs
 //   warps 7-13  G  backward of tile t: thread = 8 inputs x 5 classes, 20 packed accumulators (input
@@ -102,13 +101,69 @@ fused_linear_step_kernel(const float* __restrict__ x, const float* __restrict__ 
     if (warp < F_WARPS) {
       // =============================== F: forward ===============================
       const int slice = warp;                       // inputs 112*slice ..
+      const int ksub = lane >> 3, rp = lane & 7;    // quads 4i+ksub; rows rp and rp+8
       mbar_wait(&sm.w_full, 0u);
       int i_t = 0;
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++i_t) {
         const int na = 2 * i_t, nb = na + 1, buf = i_t % NBUF;
         mbar_wait(&sm.full[na % NSTAGES], (uint32_t)(na / NSTAGES) & 1u);
         mbar_wait(&sm.full[nb % NSTAGES], (uint32_t)(nb / NSTAGES) & 1u);
-        forward_tile(sm, slice, lane, na, nb, buf, i_t);
+        const float* xa = sm.x + ((na % NSTAGES) * STAGE_ROWS + rp) * XSTRIDE + slice * KW + 4 * ksub;
+        const float* xb = sm.x + ((nb % NSTAGES) * STAGE_ROWS + rp) * XSTRIDE + slice * KW + 4 * ksub;
+        const float* wp = sm.W + (slice * KW + 4 * ksub) * NC;
+        u64 acc_a[5], acc_b[5];                       // class pairs (2p, 2p+1) of rows a and b
+#pragma unroll
+        for (int p = 0; p < 5; ++p) { acc_a[p] = 0ull; acc_b[p] = 0ull; }
+#pragma unroll
+        for (int i = 0; i < 7; ++i) {
+          const float4 va = *reinterpret_cast<const float4*>(xa + 16 * i);
+          const float4 vb = *reinterpret_cast<const float4*>(xb + 16 * i);
+          const ulonglong2* w0 = reinterpret_cast<const ulonglong2*>(wp + i * 16 * NC);   // 4 inputs x 10 classes = 10 x 16 B
+          const float xsa[4] = {va.x, va.y, va.z, va.w};
+          const float xsb[4] = {vb.x, vb.y, vb.z, vb.w};
+#pragma unroll
+          for (int kp = 0; kp < 2; ++kp) {            // inputs 2kp and 2kp+1 of the quad: 20 floats = 5 x 16 B
+            const ulonglong2 w01 = w0[5 * kp + 0], w23 = w0[5 * kp + 1], w45 = w0[5 * kp + 2],
+                             w67 = w0[5 * kp + 3], w89 = w0[5 * kp + 4];
+            // first input: class pairs (0,1)(2,3)(4,5)(6,7)(8,9) = w01.x w01.y w23.x w23.y w45.x
+            const u64 xa0 = pack2(xsa[2 * kp], xsa[2 * kp]), xb0 = pack2(xsb[2 * kp], xsb[2 * kp]);
+            acc_a[0] = ffma2(xa0, w01.x, acc_a[0]); acc_b[0] = ffma2(xb0, w01.x, acc_b[0]);
+            acc_a[1] = ffma2(xa0, w01.y, acc_a[1]); acc_b[1] = ffma2(xb0, w01.y, acc_b[1]);
+            acc_a[2] = ffma2(xa0, w23.x, acc_a[2]); acc_b[2] = ffma2(xb0, w23.x, acc_b[2]);
+            acc_a[3] = ffma2(xa0, w23.y, acc_a[3]); acc_b[3] = ffma2(xb0, w23.y, acc_b[3]);
+            acc_a[4] = ffma2(xa0, w45.x, acc_a[4]); acc_b[4] = ffma2(xb0, w45.x, acc_b[4]);
+            // second input: w45.y w67.x w67.y w89.x w89.y
+            const u64 xa1 = pack2(xsa[2 * kp + 1], xsa[2 * kp + 1]), xb1 = pack2(xsb[2 * kp + 1], xsb[2 * kp + 1]);
+            acc_a[0] = ffma2(xa1, w45.y, acc_a[0]); acc_b[0] = ffma2(xb1, w45.y, acc_b[0]);
+            acc_a[1] = ffma2(xa1, w67.x, acc_a[1]); acc_b[1] = ffma2(xb1, w67.x, acc_b[1]);
+            acc_a[2] = ffma2(xa1, w67.y, acc_a[2]); acc_b[2] = ffma2(xb1, w67.y, acc_b[2]);
+            acc_a[3] = ffma2(xa1, w89.x, acc_a[3]); acc_b[3] = ffma2(xb1, w89.x, acc_b[3]);
+            acc_a[4] = ffma2(xa1, w89.y, acc_a[4]); acc_b[4] = ffma2(xb1, w89.y, acc_b[4]);
+          }
+        }
+        // the four input sub-slices (lanes xor 8, 16)
+        float fa[NC], fb[NC];
+#pragma unroll
+        for (int p = 0; p < 5; ++p) {
+          unpack2(acc_a[p], fa[2 * p], fa[2 * p + 1]);
+          unpack2(acc_b[p], fb[2 * p], fb[2 * p + 1]);
+        }
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+          fa[c] += __shfl_xor_sync(0xffffffffu, fa[c], 8);
+          fb[c] += __shfl_xor_sync(0xffffffffu, fb[c], 8);
+          fa[c] += __shfl_xor_sync(0xffffffffu, fa[c], 16);
+          fb[c] += __shfl_xor_sync(0xffffffffu, fb[c], 16);
+        }
+        mbar_wait(&sm.part_empty[buf], ((uint32_t)(i_t / NBUF) & 1u) ^ 1u);   // H is done with this buffer
+        if (ksub == 0) {
+          float* pa = sm.part + buf * PART_BUF + slice * PART_SET + rp * PART_ROW;
+          float* pb = pa + 8 * PART_ROW;
+#pragma unroll
+          for (int c = 0; c < NC; ++c) { pa[c] = fa[c]; pb[c] = fb[c]; }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.part_full[buf]);
       }
     } else if (warp == H_WARP) {
       // =============================== H: loss head ===============================

@@ -268,12 +268,66 @@ fused_linear_multistep_kernel(const ms_args a) {
   if (warp < F_WARPS) {
     // =============================== F: forward ===============================
     const int slice = warp;                       // inputs 112*slice ..
+    const int ksub = lane >> 3, rp = lane & 7;    // quads 4i+ksub; rows rp and rp+8
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++i_t) {
         const int na = 2 * i_t, nb = na + 1, buf = i_t % NBUF;
         mbar_wait(&sm.full[na % NSTAGES], (uint32_t)(na / NSTAGES) & 1u);
         mbar_wait(&sm.full[nb % NSTAGES], (uint32_t)(nb / NSTAGES) & 1u);
         if (tid == 0 && tile == blockIdx.x) stamp(a, s, ST_F_FIRST_IN);
-        forward_tile(sm, slice, lane, na, nb, buf, i_t);
+        const float* xa = sm.x + ((na % NSTAGES) * STAGE_ROWS + rp) * XSTRIDE + slice * KW + 4 * ksub;
+        const float* xb = sm.x + ((nb % NSTAGES) * STAGE_ROWS + rp) * XSTRIDE + slice * KW + 4 * ksub;
+        const float* wp = sm.W + (slice * KW + 4 * ksub) * NC;
+        u64 acc_a[5], acc_b[5];                       // class pairs (2p, 2p+1) of rows a and b
+#pragma unroll
+        for (int p = 0; p < 5; ++p) { acc_a[p] = 0ull; acc_b[p] = 0ull; }
+#pragma unroll
+        for (int i = 0; i < 7; ++i) {
+          const float4 va = *reinterpret_cast<const float4*>(xa + 16 * i);
+          const float4 vb = *reinterpret_cast<const float4*>(xb + 16 * i);
+          const ulonglong2* w0 = reinterpret_cast<const ulonglong2*>(wp + i * 16 * NC);   // 4 inputs x 10 classes = 10 x 16 B
+          const float xsa[4] = {va.x, va.y, va.z, va.w};
+          const float xsb[4] = {vb.x, vb.y, vb.z, vb.w};
+#pragma unroll
+          for (int kp = 0; kp < 2; ++kp) {            // inputs 2kp and 2kp+1 of the quad: 20 floats = 5 x 16 B
+            const ulonglong2 w01 = w0[5 * kp + 0], w23 = w0[5 * kp + 1], w45 = w0[5 * kp + 2],
+                             w67 = w0[5 * kp + 3], w89 = w0[5 * kp + 4];
+            const u64 xa0 = pack2(xsa[2 * kp], xsa[2 * kp]), xb0 = pack2(xsb[2 * kp], xsb[2 * kp]);
+            acc_a[0] = ffma2(xa0, w01.x, acc_a[0]); acc_b[0] = ffma2(xb0, w01.x, acc_b[0]);
+            acc_a[1] = ffma2(xa0, w01.y, acc_a[1]); acc_b[1] = ffma2(xb0, w01.y, acc_b[1]);
+            acc_a[2] = ffma2(xa0, w23.x, acc_a[2]); acc_b[2] = ffma2(xb0, w23.x, acc_b[2]);
+            acc_a[3] = ffma2(xa0, w23.y, acc_a[3]); acc_b[3] = ffma2(xb0, w23.y, acc_b[3]);
+            acc_a[4] = ffma2(xa0, w45.x, acc_a[4]); acc_b[4] = ffma2(xb0, w45.x, acc_b[4]);
+            const u64 xa1 = pack2(xsa[2 * kp + 1], xsa[2 * kp + 1]), xb1 = pack2(xsb[2 * kp + 1], xsb[2 * kp + 1]);
+            acc_a[0] = ffma2(xa1, w45.y, acc_a[0]); acc_b[0] = ffma2(xb1, w45.y, acc_b[0]);
+            acc_a[1] = ffma2(xa1, w67.x, acc_a[1]); acc_b[1] = ffma2(xb1, w67.x, acc_b[1]);
+            acc_a[2] = ffma2(xa1, w67.y, acc_a[2]); acc_b[2] = ffma2(xb1, w67.y, acc_b[2]);
+            acc_a[3] = ffma2(xa1, w89.x, acc_a[3]); acc_b[3] = ffma2(xb1, w89.x, acc_b[3]);
+            acc_a[4] = ffma2(xa1, w89.y, acc_a[4]); acc_b[4] = ffma2(xb1, w89.y, acc_b[4]);
+          }
+        }
+        // the four input sub-slices (lanes xor 8, 16)
+        float fa[NC], fb[NC];
+#pragma unroll
+        for (int p = 0; p < 5; ++p) {
+          unpack2(acc_a[p], fa[2 * p], fa[2 * p + 1]);
+          unpack2(acc_b[p], fb[2 * p], fb[2 * p + 1]);
+        }
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+          fa[c] += __shfl_xor_sync(0xffffffffu, fa[c], 8);
+          fb[c] += __shfl_xor_sync(0xffffffffu, fb[c], 8);
+          fa[c] += __shfl_xor_sync(0xffffffffu, fa[c], 16);
+          fb[c] += __shfl_xor_sync(0xffffffffu, fb[c], 16);
+        }
+        mbar_wait(&sm.part_empty[buf], ((uint32_t)(i_t / NBUF) & 1u) ^ 1u);   // H is done with this buffer
+        if (ksub == 0) {
+          float* pa = sm.part + buf * PART_BUF + slice * PART_SET + rp * PART_ROW;
+          float* pb = pa + 8 * PART_ROW;
+#pragma unroll
+          for (int c = 0; c < NC; ++c) { pa[c] = fa[c]; pb[c] = fb[c]; }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.part_full[buf]);
         if (tid == 0 && tile == blockIdx.x) stamp(a, s, ST_F_FIRST_DONE);
       }
       if (tid == 0) stamp(a, s, ST_F_LAST_DONE);
