@@ -11,11 +11,11 @@ namespace fl {
 constexpr int K = 784, NC = 10;
 constexpr int TILE_ROWS = 16, STAGE_ROWS = 8, STAGES_PER_TILE = 2, NSTAGES = 7;
 constexpr int XSTRIDE = 788;  // floats per staged row: 3152 B, keeps 16 B alignment, conflict-free LDS.128
-constexpr int F_WARPS = 7, G_WARPS = 13;
-constexpr int P_WARP = F_WARPS + G_WARPS, H_WARP = P_WARP + 1;
-constexpr int THREADS = (H_WARP + 1) * 32;    // 22 warps
+constexpr int F_WARPS = 7, G_WARPS = 7;
+constexpr int P_WARP = 14, H_WARP = 15;
+constexpr int THREADS = 16 * 32;
 constexpr int KSLICES = 7, KW = K / KSLICES;    // forward: 7 slices of 112 inputs (28 quads, 7 per lane sub-slice)
-constexpr int KPAIRS = K / 2;                   // backward: one thread per input pair (392 of the 13 warps' 416 threads)
+constexpr int KGROUPS = K / 8;                  // backward: 98 groups of 8 inputs (quads kg and kg+98)
 constexpr int ROW_BYTES = K * 4;                // 3136
 constexpr int PART_ROW = 11;                    // floats per row of a partial-logit set (odd: conflict-free)
 constexpr int PART_SET = TILE_ROWS * PART_ROW;  // 176

@@ -439,12 +439,14 @@ fused_linear_multistep_kernel(const ms_args a) {
       named_sync(NB_PART, PART_THREADS);                                   // the CTA partial is written (published by G's fence)
   } else {
     // =============================== G: backward ===============================
-    const int gt = tid - F_WARPS * 32;            // 0..415
-    const int kp = gt;                           // input pair (2kp, 2kp+1), all ten classes
-    const bool active = kp < KPAIRS;
-      u64 gacc[NC];                                 // [class], lanes of the u64 = the two inputs of the pair
+    const int gt = tid - F_WARPS * 32;            // 0..223
+    const int kg = gt >> 1, h = gt & 1;           // inputs 4kg..4kg+3 and 392+4kg..392+4kg+3, classes 5h..5h+4
+    const bool active = kg < KGROUPS;
+      u64 gacc[4][5];                               // [input pair][class]
 #pragma unroll
-      for (int c = 0; c < NC; ++c) gacc[c] = 0ull;
+      for (int p = 0; p < 4; ++p)
+#pragma unroll
+        for (int c = 0; c < 5; ++c) gacc[p][c] = 0ull;
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++i_t) {
         const int buf = i_t % NBUF;
         const int valid = min(TILE_ROWS, rows - tile * TILE_ROWS);
@@ -457,17 +459,22 @@ fused_linear_multistep_kernel(const ms_args a) {
           int nrows = valid - q * STAGE_ROWS;
           nrows = nrows < 0 ? 0 : (nrows > STAGE_ROWS ? STAGE_ROWS : nrows);
           if (active) {
-            const float* xp = sm.x + (slot * STAGE_ROWS) * XSTRIDE + 2 * kp;
-            const float* dp = sm.dz + buf * DZ_BUF + (q * STAGE_ROWS) * DZ_ROW;
+            const float* xp = sm.x + (slot * STAGE_ROWS) * XSTRIDE + 4 * kg;
+            const float* dp = sm.dz + buf * DZ_BUF + (q * STAGE_ROWS) * DZ_ROW + 8 * h;
             auto bwd_row = [&](int rr) {
-              const u64 xv = *reinterpret_cast<const u64*>(xp + rr * XSTRIDE);
+              const ulonglong2 x0 = *reinterpret_cast<const ulonglong2*>(xp + rr * XSTRIDE);
+              const ulonglong2 x1 = *reinterpret_cast<const ulonglong2*>(xp + rr * XSTRIDE + K / 2);
               const float4 d03 = *reinterpret_cast<const float4*>(dp + rr * DZ_ROW);
               const float d4 = dp[rr * DZ_ROW + 4];
-              const float4 d58 = *reinterpret_cast<const float4*>(dp + rr * DZ_ROW + 8);
-              const float d9 = dp[rr * DZ_ROW + 12];
-              const float ds[NC] = {d03.x, d03.y, d03.z, d03.w, d4, d58.x, d58.y, d58.z, d58.w, d9};
+              const float ds[5] = {d03.x, d03.y, d03.z, d03.w, d4};
 #pragma unroll
-              for (int c = 0; c < NC; ++c) gacc[c] = ffma2(xv, pack2(ds[c], ds[c]), gacc[c]);
+              for (int c = 0; c < 5; ++c) {
+                const u64 dd = pack2(ds[c], ds[c]);
+                gacc[0][c] = ffma2(x0.x, dd, gacc[0][c]);
+                gacc[1][c] = ffma2(x0.y, dd, gacc[1][c]);
+                gacc[2][c] = ffma2(x1.x, dd, gacc[2][c]);
+                gacc[3][c] = ffma2(x1.y, dd, gacc[3][c]);
+              }
             };
             if (nrows == STAGE_ROWS) {
 #pragma unroll
@@ -485,13 +492,17 @@ fused_linear_multistep_kernel(const ms_args a) {
       // ---- step boundary.  The forward team has finished with the weight tile (my last tile's dz needed its last
       // partial logits), so the per-CTA weight-gradient partial is staged there and then written out coalesced.
       if (active) {
-        float* out = sm.W + 2 * kp * NC;
+        float* out = sm.W + 5 * h;
 #pragma unroll
-        for (int c = 0; c < NC; ++c) {
-          float lo, hi;
-          unpack2(gacc[c], lo, hi);
-          out[c] = lo;
-          out[NC + c] = hi;
+        for (int p = 0; p < 4; ++p) {
+          const int k0 = (p < 2 ? 4 * kg : K / 2 + 4 * kg) + 2 * (p & 1);
+#pragma unroll
+          for (int c = 0; c < 5; ++c) {
+            float lo, hi;
+            unpack2(gacc[p][c], lo, hi);
+            out[k0 * NC + c] = lo;
+            out[(k0 + 1) * NC + c] = hi;
+          }
         }
       }
       named_sync(NB_PART, PART_THREADS);                                   // staging complete (my dW, H's sums)
