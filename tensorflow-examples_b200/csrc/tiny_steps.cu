@@ -40,8 +40,7 @@ __global__ void __launch_bounds__(32) tiny_steps_kernel(const tiny_args a) {
   __shared__ float sP[MAX_P];                       // parameters, flat layout
   __shared__ float sA[MAX_L + 1][MAX_B][MAX_W];     // sA[l] = input of layer l (sA[0] = x), sA[L] = logits / predictions
   __shared__ float sD[2][MAX_B][MAX_W];             // dz ping-pong
-  __shared__ float sX[2][MAX_B * MAX_W];            // the step's rows, flat [row][in0], double buffered
-  __shared__ float sY[2][MAX_B * MAX_W];            // the step's labels, flat [row][C]
+  __shared__ float sY[MAX_B][MAX_W];
   __shared__ float sRow[2][MAX_B];                  // per-row loss, hit
   const int lane = threadIdx.x;
   const int L = a.n_layers, B = a.rows;
@@ -50,39 +49,29 @@ __global__ void __launch_bounds__(32) tiny_steps_kernel(const tiny_args a) {
   float gs = *a.global_step;
   __syncwarp();
 
-  // The step's rows travel global -> registers -> shared memory, one step ahead: the loads of step s+1 are issued at the
-  // top of step s and stored into the other buffer at its end, so no step waits for a global-memory round trip (that
-  // wait was most of a 1->1 step).  nu = values per lane actually needed (1 for simple.py's four points).
-  constexpr int XR = MAX_B * MAX_W / 32;
-  const int nx = B * in0, ny = B * C;
-  const int nu = (max(nx, ny) + 31) / 32;
+  // The step's rows travel global -> registers -> shared memory, one step ahead: the loads of step s+1 are in flight
+  // while step s computes, so no step waits for a global-memory round trip (that wait was most of a 1->1 step).
+  constexpr int XR = MAX_B * MAX_W / 32;                // values per lane
   float xr[XR], yr[XR];
   auto fetch = [&](int s) {
     const long start = (a.first_row + (long)s * a.global_batch) % a.span;
 #pragma unroll
-    for (int u = 0; u < XR; ++u)
-      if (u < nu) {
-        const int i = lane + 32 * u;
-        xr[u] = i < nx ? a.x_pool[start * in0 + i] : 0.f;
-        yr[u] = i < ny ? a.y_pool[start * C + i] : 0.f;
-      }
-  };
-  auto stash = [&](int buf) {
-#pragma unroll
-    for (int u = 0; u < XR; ++u)
-      if (u < nu) {
-        const int i = lane + 32 * u;
-        if (i < nx) sX[buf][i] = xr[u];
-        if (i < ny) sY[buf][i] = yr[u];
-      }
+    for (int u = 0; u < XR; ++u) {
+      const int i = lane + 32 * u;
+      xr[u] = i < B * in0 ? a.x_pool[start * in0 + i] : 0.f;
+      yr[u] = i < B * C ? a.y_pool[start * C + i] : 0.f;
+    }
   };
   fetch(0);
-  stash(0);
-  __syncwarp();
   for (int s = 0; s < a.n_steps; ++s) {
-    const float* X = sX[s & 1];
-    const float* Y = sY[s & 1];
+#pragma unroll
+    for (int u = 0; u < XR; ++u) {
+      const int i = lane + 32 * u;
+      if (i < B * in0) sA[0][i / in0][i % in0] = xr[u];
+      if (i < B * C) sY[i / C][i % C] = yr[u];
+    }
     if (s + 1 < a.n_steps) fetch(s + 1);
+    __syncwarp();
     // ---- forward
     for (int l = 0; l < L; ++l) {
       const int Kin = a.dims[l], N = a.dims[l + 1];
@@ -92,8 +81,7 @@ __global__ void __launch_bounds__(32) tiny_steps_kernel(const tiny_args a) {
       for (int i = lane; i < B * N; i += 32) {
         const int r = i / N, n = i % N;
         float z = 0.f;
-        if (l == 0) { for (int k = 0; k < Kin; ++k) z = fmaf(X[r * in0 + k], W[k * N + n], z); }
-        else { for (int k = 0; k < Kin; ++k) z = fmaf(sA[l][r][k], W[k * N + n], z); }
+        for (int k = 0; k < Kin; ++k) z = fmaf(sA[l][r][k], W[k * N + n], z);
         z += b[n];
         sA[l + 1][r][n] = sig ? 1.0f / (1.0f + expf(-z)) : z;
       }
@@ -105,7 +93,7 @@ __global__ void __launch_bounds__(32) tiny_steps_kernel(const tiny_args a) {
       float l = 0.f, hit = 0.f;
       if (a.loss == B2_LOSS_SSE_SUM) {
         for (int c = 0; c < C; ++c) {
-          const float d = sA[L][r][c] - Y[r * C + c];
+          const float d = sA[L][r][c] - sY[r][c];
           l = fmaf(d, d, l);
           sD[0][r][c] = 2.0f * d;
         }
@@ -118,7 +106,7 @@ __global__ void __launch_bounds__(32) tiny_steps_kernel(const tiny_args a) {
         float sy = 0.f, bv = -INFINITY, lv = -INFINITY;
         int bi = 0, li = 0;
         for (int c = 0; c < C; ++c) {
-          const float y = expf(sA[L][r][c] - m) * inv, t = Y[r * C + c];
+          const float y = expf(sA[L][r][c] - m) * inv, t = sY[r][c];
           l -= t * logf(y);                          // un-fused log(softmax), distributed.py:102
           sy += t;
           if (y > bv) { bv = y; bi = c; }            // first index wins ties (tf.argmax)
@@ -126,7 +114,7 @@ __global__ void __launch_bounds__(32) tiny_steps_kernel(const tiny_args a) {
         }
         for (int c = 0; c < C; ++c) {
           const float y = expf(sA[L][r][c] - m) * inv;
-          sD[0][r][c] = (y * sy - Y[r * C + c]) * a.inv_B;
+          sD[0][r][c] = (y * sy - sY[r][c]) * a.inv_B;
         }
         hit = bi == li ? 1.0f : 0.0f;
       }
@@ -165,8 +153,7 @@ __global__ void __launch_bounds__(32) tiny_steps_kernel(const tiny_args a) {
         float g = 0.f;
         if (i < Kin * N) {
           const int k = i / N, n = i % N;
-          if (l == 0) { for (int r = 0; r < B; ++r) g = fmaf(X[r * in0 + k], sD[cur][r][n], g); }
-          else { for (int r = 0; r < B; ++r) g = fmaf(sA[l][r][k], sD[cur][r][n], g); }
+          for (int r = 0; r < B; ++r) g = fmaf(sA[l][r][k], sD[cur][r][n], g);
           W[i] = fmaf(-a.lr, g, W[i]);
           if (last) a.grads[a.w_off[l] + i] = g;
         } else {
@@ -179,8 +166,6 @@ __global__ void __launch_bounds__(32) tiny_steps_kernel(const tiny_args a) {
       __syncwarp();
       cur ^= 1;
     }
-    if (s + 1 < a.n_steps) stash((s + 1) & 1);
-    __syncwarp();
   }
   for (int i = lane; i < a.P; i += 32) a.params[i] = sP[i];
   if (lane == 0) *a.global_step = gs;
