@@ -49,28 +49,10 @@ __global__ void __launch_bounds__(32) tiny_steps_kernel(const tiny_args a) {
   float gs = *a.global_step;
   __syncwarp();
 
-  // The step's rows travel global -> registers -> shared memory, one step ahead: the loads of step s+1 are in flight
-  // while step s computes, so no step waits for a global-memory round trip (that wait was most of a 1->1 step).
-  constexpr int XR = MAX_B * MAX_W / 32;                // values per lane
-  float xr[XR], yr[XR];
-  auto fetch = [&](int s) {
-    const long start = (a.first_row + (long)s * a.global_batch) % a.span;
-#pragma unroll
-    for (int u = 0; u < XR; ++u) {
-      const int i = lane + 32 * u;
-      xr[u] = i < B * in0 ? a.x_pool[start * in0 + i] : 0.f;
-      yr[u] = i < B * C ? a.y_pool[start * C + i] : 0.f;
-    }
-  };
-  fetch(0);
   for (int s = 0; s < a.n_steps; ++s) {
-#pragma unroll
-    for (int u = 0; u < XR; ++u) {
-      const int i = lane + 32 * u;
-      if (i < B * in0) sA[0][i / in0][i % in0] = xr[u];
-      if (i < B * C) sY[i / C][i % C] = yr[u];
-    }
-    if (s + 1 < a.n_steps) fetch(s + 1);
+    const long start = (a.first_row + (long)s * a.global_batch) % a.span;
+    for (int i = lane; i < B * in0; i += 32) sA[0][i / in0][i % in0] = a.x_pool[start * in0 + i];
+    for (int i = lane; i < B * C; i += 32) sY[i / C][i % C] = a.y_pool[start * C + i];
     __syncwarp();
     // ---- forward
     for (int l = 0; l < L; ++l) {
