@@ -49,8 +49,8 @@ __global__ void __launch_bounds__(32) tiny_steps_kernel(const tiny_args a) {
   float gs = *a.global_step;
   __syncwarp();
 
-  for (int s = 0; s < a.n_steps; ++s) {
-    const long start = (a.first_row + (long)s * a.global_batch) % a.span;
+  long start = a.first_row % a.span;                  // batches wrap inside the pool; kept incrementally (no 64-bit modulo per step)
+  for (int s = 0; s < a.n_steps; ++s, start = start + a.global_batch >= a.span ? start + a.global_batch - a.span : start + a.global_batch) {
     for (int i = lane; i < B * in0; i += 32) sA[0][i / in0][i % in0] = a.x_pool[start * in0 + i];
     for (int i = lane; i < B * C; i += 32) sY[i / C][i % C] = a.y_pool[start * C + i];
     __syncwarp();
