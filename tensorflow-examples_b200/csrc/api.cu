@@ -1091,16 +1091,29 @@ static int enqueue_persistent(b2_ctx* c, const float* xp, const float* yp, long 
     c->global_step_host += (float)n_steps;
     return B2_OK;
   }
-  if (c->nranks == 1 && c->cs_scratch && b2_cluster_steps_applies(c->n_layers, c->dims, local_batch)) {
-    // small batches of the 784-wide models: one cluster of 14 CTAs runs the whole loop (cluster_steps.cu)
-    timed_scope t(c, B2_K_PERSISTENT_STEPS, s);
-    int rc = b2_launch_cluster_steps(c->n_layers, c->act, c->loss, c->w_off, c->b_off, c->P, xp, yp, span, first_row,
-                                     global_batch, local_batch, n_steps, lr, c->params, c->grads, loss_trace, correct_trace,
-                                     c->global_step_dev, c->cs_scratch, s);
-    if (rc) return rc;
-    c->launches += 1;
-    c->global_step_host += (float)n_steps;
-    return B2_OK;
+  {
+    // small batches of the 784-wide models: one cluster of 14 CTAs runs the whole loop (cluster_steps.cu); with several
+    // workers the ranks' gradients are exchanged inside the kernel through the NVLink peer cells
+    const bool use_peer = c->nranks > 1 && c->peer_ready && !c->opt_no_peer;
+    if ((c->nranks == 1 || use_peer) && c->cs_scratch && b2_cluster_steps_applies(c->n_layers, c->dims, local_batch)) {
+      b2_fx_args fx;
+      memset(&fx, 0, sizeof(fx));
+      if (use_peer) {
+        fx.rank = c->rank; fx.nranks = c->nranks; fx.stride = c->peer_stride;
+        fx.step1 = c->peer_step + 1;
+        fx.parity = (int)(c->peer_step & 1u);
+        for (int p = 0; p < c->nranks; ++p) fx.region[p] = (unsigned long long*)c->peer_base[p];
+      }
+      timed_scope t(c, B2_K_PERSISTENT_STEPS, s);
+      int rc = b2_launch_cluster_steps(c->n_layers, c->act, c->loss, c->w_off, c->b_off, c->P, xp, yp, span, first_row,
+                                       global_batch, local_batch, n_steps, lr, c->params, c->grads, loss_trace, correct_trace,
+                                       c->global_step_dev, c->cs_scratch, (long)c->rank * local_batch, use_peer ? &fx : nullptr, s);
+      if (rc) return rc;
+      if (use_peer) c->peer_step += (unsigned)n_steps;
+      c->launches += 1;
+      c->global_step_host += (float)n_steps;
+      return B2_OK;
+    }
   }
   return B2_NOT_PERSISTENT;
 }

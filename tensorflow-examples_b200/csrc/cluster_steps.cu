@@ -79,6 +79,9 @@ struct args {
   float* loss_trace;
   int* correct_trace;
   float* global_step;
+  long rank_off;                         // rank * rows: this rank's slice of every global batch
+  int exchange;                          // != 0: several ranks, fx describes the peers (step1 / parity are those of step 0)
+  b2_fx_args fx;
   float* scratch;                        // [slots][rows][N1] partial pre-activations, then [rows][N1] dz (L2-resident exchange buffers)
   long long* prof;                       // diagnostics (B2_CS_PROF=1): SM clocks CTA 0 / thread 0 spent per phase, summed over steps
 };
@@ -226,9 +229,18 @@ __device__ __forceinline__ void forward_partial(const float* __restrict__ xs, co
 // ---- step 4: dW1[k][n] = sum_r x[r][k] dz[r][n] for this CTA's 56 inputs, then W1 -= lr dW1.  Thread tile TK input
 // pairs x TCC columns over one of SLICES row slices (summed in slice order afterwards); the x pair is the vector operand,
 // dz the scalar one.  Consecutive lanes: consecutive column groups of one input group (x broadcast, dz contiguous).
+// Exchange of one gradient element with the other ranks (several workers): cell index = element of the first layer's
+// weight matrix, or w1_elems + index of a small gradient.
+struct Xchg {
+  const b2_fx_args* fx;       // NULL: one rank
+  unsigned step1;
+  int parity;
+  long base;                  // cell index of this CTA's first weight-gradient element
+};
+
 template <int N1, int TK, int TCC, int SLICES>
 __device__ __forceinline__ void weight_gradient(const float* __restrict__ xs, const float* __restrict__ dz, float* __restrict__ w1,
-                                                float* __restrict__ p4, int rows, float lr, int t) {
+                                                float* __restrict__ p4, int rows, float lr, int t, const Xchg& xc) {
   constexpr int KG = KS / (2 * TK), CG = N1 / TCC, TILES = KG * CG;
   static_assert(KS % (2 * TK) == 0 && N1 % TCC == 0 && TCC % 2 == 0, "tiling");
   // SLICES == 2: the two row slices of a tile sit on the two halves of a warp (lanes l and l ^ 16) and are added with
@@ -304,19 +316,43 @@ __device__ __forceinline__ void weight_gradient(const float* __restrict__ xs, co
     fmas(Bf, r + RB);
   }
   if (LANE_SLICES) {
+    float g[TK][TCC][2];                                              // slice 0 + slice 1 of my tile's 2*TK x TCC elements
 #pragma unroll
     for (int a = 0; a < TK; ++a)
 #pragma unroll
       for (int c = 0; c < TCC; ++c) {
         float lo, hi;
         unpack2(acc[a][c], lo, hi);
-        const float lo1 = __shfl_xor_sync(0xffffffffu, lo, 16), hi1 = __shfl_xor_sync(0xffffffffu, hi, 16);
-        if (has_tile && sl == 0) {                                    // slice 0 + slice 1, then the update
-          const int i0 = (k0 + 2 * a) * N1 + n0 + c;
-          w1[i0] = fmaf(-lr, lo + lo1, w1[i0]);
-          w1[i0 + N1] = fmaf(-lr, hi + hi1, w1[i0 + N1]);
-        }
+        g[a][c][0] = lo + __shfl_xor_sync(0xffffffffu, lo, 16);
+        g[a][c][1] = hi + __shfl_xor_sync(0xffffffffu, hi, 16);
       }
+    if (has_tile && sl == 0) {
+      if (xc.fx) {
+        // several ranks: push all my elements to the peers, then collect theirs (the NVLink trips overlap)
+#pragma unroll
+        for (int a = 0; a < TK; ++a)
+#pragma unroll
+          for (int c = 0; c < TCC; ++c)
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+              b2_fx_push(*xc.fx, xc.step1, xc.parity, xc.base + (k0 + 2 * a + h) * N1 + n0 + c, g[a][c][h]);
+#pragma unroll
+        for (int a = 0; a < TK; ++a)
+#pragma unroll
+          for (int c = 0; c < TCC; ++c)
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+              g[a][c][h] = b2_fx_collect(*xc.fx, xc.step1, xc.parity, xc.base + (k0 + 2 * a + h) * N1 + n0 + c, g[a][c][h]);
+      }
+#pragma unroll
+      for (int a = 0; a < TK; ++a)
+#pragma unroll
+        for (int c = 0; c < TCC; ++c) {
+          const int i0 = (k0 + 2 * a) * N1 + n0 + c;
+          w1[i0] = fmaf(-lr, g[a][c][0], w1[i0]);
+          w1[i0 + N1] = fmaf(-lr, g[a][c][1], w1[i0 + N1]);
+        }
+    }
   } else {
     if (has_tile) {
 #pragma unroll
@@ -335,6 +371,10 @@ __device__ __forceinline__ void weight_gradient(const float* __restrict__ xs, co
       float g = 0.f;
 #pragma unroll
       for (int s2 = 0; s2 < SLICES; ++s2) g += p4[s2 * KS * N1 + i];    // row slices in order
+      if (xc.fx) {
+        b2_fx_push(*xc.fx, xc.step1, xc.parity, xc.base + i, g);
+        g = b2_fx_collect(*xc.fx, xc.step1, xc.parity, xc.base + i, g);
+      }
       w1[i] = fmaf(-lr, g, w1[i]);
     }
   }
@@ -392,7 +432,7 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
   auto prefetch = [&](int s, int t0, int nthr) {
     const int tt = t - t0;
     if (tt < 0 || tt >= nthr) return;
-    const long start = (a.first_row + (long)s * a.global_batch) % a.span;
+    const long start = (a.first_row + (long)s * a.global_batch) % a.span + a.rank_off;
     float* xb = xs + (s & 1) * BMAX * XS;
     const float* src = a.x_pool + start * K0 + j * KS;
     for (int i = tt; i < B * (KS / 4); i += nthr) {
@@ -418,6 +458,8 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
     CS_TICK(0);
     const float* xb = xs + (s & 1) * BMAX * XS;
     const float* yb = ys + (s & 1) * RO_MAX * NC;
+    const unsigned xstep1 = a.fx.step1 + (unsigned)s;               // this step's stamp / cell parity of the rank exchange
+    const int xparity = (a.fx.parity + s) & 1;
     // ---- 1. partial pre-activations over my 56 inputs -> my slot of the exchange buffer
     if constexpr (TWO) forward_partial<N1, 10, 4>(xb, w1, zp_mine, B, t, 0, KS);      // warps 0-7
     else forward_partial<N1, 2, N1>(xb, w1, zp_mine, B, t, 0, KS);
@@ -569,6 +611,10 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
         float g = 0.f;
 #pragma unroll
         for (int c = 0; c < C; ++c) g += cluster.map_shared_rank(spart, c)[t];
+        if (a.exchange) {                         // several ranks: CTA 0 publishes this rank's sums, every CTA collects
+          if (j == 0) b2_fx_push(a.fx, xstep1, xparity, (long)K0 * N1 + t, g);
+          g = b2_fx_collect(a.fx, xstep1, xparity, (long)K0 * N1 + t, g);
+        }
         if (t < NS - 2) b1s[t] = fmaf(-a.lr, g, b1s[t]);
         else if (t == NS - 2) step_loss = g;
         else step_correct = g;
@@ -583,6 +629,10 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
         float g = 0.f;
 #pragma unroll
         for (int c = 0; c < C; ++c) g += p[c];
+        if (a.exchange) {                         // several ranks: CTA 0 publishes this rank's sums, every CTA collects
+          if (j == 0) b2_fx_push(a.fx, xstep1, xparity, (long)K0 * N1 + i, g);
+          g = b2_fx_collect(a.fx, xstep1, xparity, (long)K0 * N1 + i, g);
+        }
         if (i < NS - 2) small[i] = fmaf(-a.lr, g, small[i]);       // [W2][b2][b1] in the order of the gradient vector
         else if (i == NS - 2) step_loss = g;
         else step_correct = g;
@@ -607,8 +657,13 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
     __syncthreads();
     CS_TICK(9);
     // ---- 4. weight gradient of my 56 inputs and the update, all local
-    if constexpr (TWO) weight_gradient<N1, 4, 4, L::P4_SLICES>(xb, dz, w1, p4, B, a.lr, t);
-    else weight_gradient<N1, 1, N1, L::P4_SLICES>(xb, dz, w1, p4, B, a.lr, t);
+    Xchg xc;
+    xc.fx = a.exchange ? &a.fx : nullptr;
+    xc.step1 = xstep1;
+    xc.parity = xparity;
+    xc.base = (long)(j * KS) * N1;
+    if constexpr (TWO) weight_gradient<N1, 4, 4, L::P4_SLICES>(xb, dz, w1, p4, B, a.lr, t, xc);
+    else weight_gradient<N1, 1, N1, L::P4_SLICES>(xb, dz, w1, p4, B, a.lr, t, xc);
     __syncthreads();
     CS_TICK(10);
   }
@@ -700,7 +755,7 @@ bool b2_cluster_steps_applies(int n_layers, const int* dims, int rows) {
 int b2_launch_cluster_steps(int n_layers, int act, int loss, const long* w_off, const long* b_off, long P, const float* x_pool,
                             const float* y_pool, long span, long first_row, long global_batch, int rows, int n_steps, float lr,
                             float* params, float* grads, float* loss_trace, int* correct_trace, float* global_step,
-                            float* scratch, cudaStream_t s) {
+                            float* scratch, long rank_off, const b2_fx_args* fx, cudaStream_t s) {
   if (n_steps <= 0) return B2_OK;
   cs::args a;
   memset(&a, 0, sizeof(a));
@@ -709,6 +764,8 @@ int b2_launch_cluster_steps(int n_layers, int act, int loss, const long* w_off, 
   a.params = params; a.grads = grads; a.P = P; a.loss_trace = loss_trace; a.correct_trace = correct_trace;
   a.global_step = global_step;
   a.scratch = scratch;
+  a.rank_off = rank_off;
+  if (fx) { a.exchange = 1; a.fx = *fx; }
   a.w1_off = w_off[0]; a.b1_off = b_off[0];
   if (n_layers == 2) { a.w2_off = w_off[1]; a.b2_off = b_off[1]; }
   return n_layers == 2 ? cs::launch<100, 10, 200>(a, s) : cs::launch<10, 0, 256>(a, s);

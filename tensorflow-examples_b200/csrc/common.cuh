@@ -198,20 +198,22 @@ struct b2_fx_args {
 #ifdef __CUDACC__
 // device side of the exchange: push my value of element i, wait for the peers' values of the same element, return the
 // sum in rank order.  Called by exactly one thread per element.
-// (step1, parity) are passed separately so that a kernel that runs several steps can advance them itself
-__device__ __forceinline__ float b2_fx_exchange_at(const b2_fx_args& a, unsigned step1, int parity, long i, float mine) {
+// (step1, parity) are passed separately so that a kernel that runs several steps can advance them itself.  The two halves
+// are also available on their own (b2_fx_push / b2_fx_collect), for a thread that owns several elements: push them all,
+// then collect them all -- the NVLink trips of the elements overlap.
+__device__ __forceinline__ void b2_fx_push(const b2_fx_args& a, unsigned step1, int parity, long i, float mine) {
   const size_t slot = ((size_t)parity * B2_MAX_PEERS) * (size_t)a.stride;
   // one 64-bit access per cell: {value (low word), stamp (high word)}.  A .b64 access is single-copy atomic by the PTX
   // memory model, so a reader can never pair a new stamp with an old value (a .v2.u32 access gives no such guarantee)
   const unsigned long long cell = ((unsigned long long)step1 << 32) | (unsigned long long)__float_as_uint(mine);
-  const bool prof = a.prof != nullptr && i == 0;
-  unsigned long long t0 = 0, t1 = 0;
-  if (prof) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
   for (int p = 0; p < a.nranks; ++p)
     if (p != a.rank)
       asm volatile("st.relaxed.sys.global.b64 [%0], %1;" ::"l"(a.region[p] + slot + (size_t)a.rank * a.stride + i), "l"(cell)
                    : "memory");
-  if (prof) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+}
+// waits for the peers' values of element i and returns the sum over all ranks in rank order (the same sum on every rank)
+__device__ __forceinline__ float b2_fx_collect(const b2_fx_args& a, unsigned step1, int parity, long i, float mine) {
+  const size_t slot = ((size_t)parity * B2_MAX_PEERS) * (size_t)a.stride;
   // poll ALL outstanding peers' cells in each round (independent loads, issued back to back): the wait costs one round
   // trip to local memory after the last peer's store has landed, not one per peer
   const unsigned long long* cells = a.region[a.rank] + slot + i;
@@ -236,6 +238,15 @@ __device__ __forceinline__ float b2_fx_exchange_at(const b2_fx_args& a, unsigned
 #pragma unroll
   for (int p = 0; p < B2_MAX_PEERS; ++p)
     if (p < a.nranks) sum += (p == a.rank) ? mine : vals[p];        // rank order: the same sum on every rank
+  return sum;
+}
+__device__ __forceinline__ float b2_fx_exchange_at(const b2_fx_args& a, unsigned step1, int parity, long i, float mine) {
+  const bool prof = a.prof != nullptr && i == 0;
+  unsigned long long t0 = 0, t1 = 0;
+  if (prof) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+  b2_fx_push(a, step1, parity, i, mine);
+  if (prof) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+  const float sum = b2_fx_collect(a, step1, parity, i, mine);
   if (prof) {
     unsigned long long t2;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t2));
@@ -267,7 +278,7 @@ bool b2_cluster_steps_applies(int n_layers, const int* dims, int rows);
 int b2_launch_cluster_steps(int n_layers, int act, int loss, const long* w_off, const long* b_off, long P, const float* x_pool,
                             const float* y_pool, long span, long first_row, long global_batch, int rows, int n_steps, float lr,
                             float* params, float* grads, float* loss_trace, int* correct_trace, float* global_step,
-                            float* scratch, cudaStream_t s);
+                            float* scratch, long rank_off, const b2_fx_args* fx, cudaStream_t s);
 long b2_cluster_steps_scratch_floats(int n_layers);
 // tiny_steps.cu: whole runs of tiny models (<= 4 layers, widths <= 16, <= 32 rows per step) by one warp
 bool b2_tiny_steps_applies(int n_layers, const int* dims, int rows);
