@@ -106,7 +106,8 @@ struct Layout {
   static constexpr int dz = w1 + KS * N1;                           // [BMAX][N1]   gradient w.r.t. the first layer's pre-activations
   static constexpr int small = dz + BMAX * N1;                      // replicated small parameters [W2][b2][b1] or [b]
   static constexpr int spart = small + ((NS + 3) & ~3);             // this CTA's partial small gradients [NS]
-  static constexpr int a2 = spart + ((NS + 3) & ~3);                // [RO_MAX][N1]  activations of my rows
+  static constexpr int ssum = spart + ((NS + 3) & ~3);              // this rank's small gradients, kept until the rank exchange
+  static constexpr int a2 = ssum + ((NS + 3) & ~3);                 // [RO_MAX][N1]  activations of my rows
   static constexpr int dzown = a2 + RO_MAX * N1;                    // [RO_MAX][N1]  my rows of dz
   static constexpr int z3 = dzown + RO_MAX * N1;                    // [RO_MAX][16]  logits of my rows
   static constexpr int dz3 = z3 + RO_MAX * 16;                      // [RO_MAX][16]
@@ -229,18 +230,9 @@ __device__ __forceinline__ void forward_partial(const float* __restrict__ xs, co
 // ---- step 4: dW1[k][n] = sum_r x[r][k] dz[r][n] for this CTA's 56 inputs, then W1 -= lr dW1.  Thread tile TK input
 // pairs x TCC columns over one of SLICES row slices (summed in slice order afterwards); the x pair is the vector operand,
 // dz the scalar one.  Consecutive lanes: consecutive column groups of one input group (x broadcast, dz contiguous).
-// Exchange of one gradient element with the other ranks (several workers): cell index = element of the first layer's
-// weight matrix, or w1_elems + index of a small gradient.
-struct Xchg {
-  const b2_fx_args* fx;       // NULL: one rank
-  unsigned step1;
-  int parity;
-  long base;                  // cell index of this CTA's first weight-gradient element
-};
-
 template <int N1, int TK, int TCC, int SLICES>
 __device__ __forceinline__ void weight_gradient(const float* __restrict__ xs, const float* __restrict__ dz, float* __restrict__ w1,
-                                                float* __restrict__ p4, int rows, float lr, int t, const Xchg& xc) {
+                                                float* __restrict__ p4, int rows, float lr, int t, float* gout) {
   constexpr int KG = KS / (2 * TK), CG = N1 / TCC, TILES = KG * CG;
   static_assert(KS % (2 * TK) == 0 && N1 % TCC == 0 && TCC % 2 == 0, "tiling");
   // SLICES == 2: the two row slices of a tile sit on the two halves of a warp (lanes l and l ^ 16) and are added with
@@ -326,31 +318,20 @@ __device__ __forceinline__ void weight_gradient(const float* __restrict__ xs, co
         g[a][c][0] = lo + __shfl_xor_sync(0xffffffffu, lo, 16);
         g[a][c][1] = hi + __shfl_xor_sync(0xffffffffu, hi, 16);
       }
+    if (gout) __syncthreads();                                        // several ranks: every warp is done reading dz, gout may alias it
     if (has_tile && sl == 0) {
-      if (xc.fx) {
-        // several ranks: push all my elements to the peers, then collect theirs (the NVLink trips overlap)
-#pragma unroll
-        for (int a = 0; a < TK; ++a)
-#pragma unroll
-          for (int c = 0; c < TCC; ++c)
-#pragma unroll
-            for (int h = 0; h < 2; ++h)
-              b2_fx_push(*xc.fx, xc.step1, xc.parity, xc.base + (k0 + 2 * a + h) * N1 + n0 + c, g[a][c][h]);
-#pragma unroll
-        for (int a = 0; a < TK; ++a)
-#pragma unroll
-          for (int c = 0; c < TCC; ++c)
-#pragma unroll
-            for (int h = 0; h < 2; ++h)
-              g[a][c][h] = b2_fx_collect(*xc.fx, xc.step1, xc.parity, xc.base + (k0 + 2 * a + h) * N1 + n0 + c, g[a][c][h]);
-      }
 #pragma unroll
       for (int a = 0; a < TK; ++a)
 #pragma unroll
         for (int c = 0; c < TCC; ++c) {
           const int i0 = (k0 + 2 * a) * N1 + n0 + c;
-          w1[i0] = fmaf(-lr, g[a][c][0], w1[i0]);
-          w1[i0 + N1] = fmaf(-lr, g[a][c][1], w1[i0 + N1]);
+          if (gout) {                                                 // handed to the rank exchange instead of applied here
+            gout[i0] = g[a][c][0];
+            gout[i0 + N1] = g[a][c][1];
+          } else {
+            w1[i0] = fmaf(-lr, g[a][c][0], w1[i0]);
+            w1[i0 + N1] = fmaf(-lr, g[a][c][1], w1[i0 + N1]);
+          }
         }
     }
   } else {
@@ -371,12 +352,65 @@ __device__ __forceinline__ void weight_gradient(const float* __restrict__ xs, co
       float g = 0.f;
 #pragma unroll
       for (int s2 = 0; s2 < SLICES; ++s2) g += p4[s2 * KS * N1 + i];    // row slices in order
-      if (xc.fx) {
-        b2_fx_push(*xc.fx, xc.step1, xc.parity, xc.base + i, g);
-        g = b2_fx_collect(*xc.fx, xc.step1, xc.parity, xc.base + i, g);
-      }
-      w1[i] = fmaf(-lr, g, w1[i]);
+      if (gout) gout[i] = g;                                         // (gout aliases dz: all reads of dz ended before the barrier above)
+      else w1[i] = fmaf(-lr, g, w1[i]);
     }
+  }
+}
+
+// Several workers: every element of buf[0..n) (this rank's gradient) is replaced by the sum over all ranks, in rank order.
+// All `nthr` threads take part, EPT elements each: push them all to the peers' cells, then collect peer by peer, all of a
+// peer's cells polled together -- the NVLink trips of the elements overlap.  Cell index of element i = cell0 + i; elements
+// [npush_all, n) are pushed by CTAs with `push_tail` set only (values every CTA of the rank holds identically).
+template <int EPT>
+__device__ __forceinline__ void exchange_block(const b2_fx_args& fx, unsigned step1, int parity, long cell0, long tail_cell0,
+                                               float* __restrict__ buf, int n, int npush_all, bool push_tail, int t, int nthr) {
+  const size_t slot = ((size_t)parity * B2_MAX_PEERS) * (size_t)fx.stride;
+  float mine[EPT], acc[EPT];
+#pragma unroll
+  for (int e = 0; e < EPT; ++e) {
+    const int i = t + e * nthr;
+    mine[e] = i < n ? buf[i] : 0.f;
+    acc[e] = 0.f;
+    if (i < n && (i < npush_all || push_tail)) {
+      const long ci = i < npush_all ? cell0 + i : tail_cell0 + (i - npush_all);
+      b2_fx_push(fx, step1, parity, ci, mine[e]);
+    }
+  }
+  for (int p = 0; p < fx.nranks; ++p) {
+    if (p == fx.rank) {
+#pragma unroll
+      for (int e = 0; e < EPT; ++e) acc[e] += mine[e];
+      continue;
+    }
+    const unsigned long long* cells = fx.region[fx.rank] + slot + (size_t)p * fx.stride;
+    unsigned pending = 0;
+#pragma unroll
+    for (int e = 0; e < EPT; ++e)
+      if (t + e * nthr < n) pending |= 1u << e;
+    unsigned spins = 0;
+    while (pending) {
+      unsigned long long got[EPT];
+#pragma unroll
+      for (int e = 0; e < EPT; ++e)
+        if ((pending >> e) & 1u) {
+          const int i = t + e * nthr;
+          const long ci = i < npush_all ? cell0 + i : tail_cell0 + (i - npush_all);
+          asm volatile("ld.relaxed.sys.global.b64 %0, [%1];" : "=l"(got[e]) : "l"(cells + ci) : "memory");
+        }
+#pragma unroll
+      for (int e = 0; e < EPT; ++e)
+        if (((pending >> e) & 1u) && (unsigned)(got[e] >> 32) == step1) {
+          acc[e] += __uint_as_float((unsigned)got[e]);
+          pending &= ~(1u << e);
+        }
+      if (++spins > (1u << 26)) __trap();   // a dead peer must not hang this GPU for ever
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < EPT; ++e) {
+    const int i = t + e * nthr;
+    if (i < n) buf[i] = acc[e];
   }
 }
 
@@ -401,6 +435,7 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
   float* dz = sm + L::dz;
   float* small = sm + L::small;
   float* spart = sm + L::spart;
+  float* ssum = sm + L::ssum;
   float* a2 = sm + L::a2;
   float* dzown = sm + L::dzown;
   float* z3 = sm + L::z3;
@@ -611,11 +646,8 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
         float g = 0.f;
 #pragma unroll
         for (int c = 0; c < C; ++c) g += cluster.map_shared_rank(spart, c)[t];
-        if (a.exchange) {                         // several ranks: CTA 0 publishes this rank's sums, every CTA collects
-          if (j == 0) b2_fx_push(a.fx, xstep1, xparity, (long)K0 * N1 + t, g);
-          g = b2_fx_collect(a.fx, xstep1, xparity, (long)K0 * N1 + t, g);
-        }
-        if (t < NS - 2) b1s[t] = fmaf(-a.lr, g, b1s[t]);
+        if (a.exchange) ssum[t] = g;              // several ranks: summed over the ranks and applied after step 4
+        else if (t < NS - 2) b1s[t] = fmaf(-a.lr, g, b1s[t]);
         else if (t == NS - 2) step_loss = g;
         else step_correct = g;
       }
@@ -629,16 +661,13 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
         float g = 0.f;
 #pragma unroll
         for (int c = 0; c < C; ++c) g += p[c];
-        if (a.exchange) {                         // several ranks: CTA 0 publishes this rank's sums, every CTA collects
-          if (j == 0) b2_fx_push(a.fx, xstep1, xparity, (long)K0 * N1 + i, g);
-          g = b2_fx_collect(a.fx, xstep1, xparity, (long)K0 * N1 + i, g);
-        }
-        if (i < NS - 2) small[i] = fmaf(-a.lr, g, small[i]);       // [W2][b2][b1] in the order of the gradient vector
+        if (a.exchange) ssum[i] = g;              // several ranks: summed over the ranks and applied after step 4
+        else if (i < NS - 2) small[i] = fmaf(-a.lr, g, small[i]); // [W2][b2][b1] in the order of the gradient vector
         else if (i == NS - 2) step_loss = g;
         else step_correct = g;
       }
     }
-    if (j == 0) {
+    if (j == 0 && !a.exchange) {
       // the thread that holds the step's loss / correct count writes the trace (distributed.py:148-151 fetches them every step)
       const int tl = (NS - 2) % THREADS, tc = (NS - 1) % THREADS;
       if (t == tl) {
@@ -650,20 +679,40 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
         if (a.correct_trace) a.correct_trace[s] = (int)(step_correct + 0.5f);
         if (s + 1 == a.n_steps) a.grads[a.P + 1] = step_correct;
       }
-      if (t == 0) gs += 1.0f;                                       // global_step += 1 (distributed.py:108)
     }
+    if (j == 0 && t == 0) gs += 1.0f;                               // global_step += 1 (distributed.py:108)
     CS_TICK(8);
     cp_async_wait<0>();                                             // dz (and the next step's rows) have landed
     __syncthreads();
     CS_TICK(9);
     // ---- 4. weight gradient of my 56 inputs and the update, all local
-    Xchg xc;
-    xc.fx = a.exchange ? &a.fx : nullptr;
-    xc.step1 = xstep1;
-    xc.parity = xparity;
-    xc.base = (long)(j * KS) * N1;
-    if constexpr (TWO) weight_gradient<N1, 4, 4, L::P4_SLICES>(xb, dz, w1, p4, B, a.lr, t, xc);
-    else weight_gradient<N1, 1, N1, L::P4_SLICES>(xb, dz, w1, p4, B, a.lr, t, xc);
+    float* gout = a.exchange ? dz : nullptr;                        // several ranks: the local gradient goes to shared memory
+    if constexpr (TWO) weight_gradient<N1, 4, 4, L::P4_SLICES>(xb, dz, w1, p4, B, a.lr, t, gout);
+    else weight_gradient<N1, 1, N1, L::P4_SLICES>(xb, dz, w1, p4, B, a.lr, t, gout);
+    if (a.exchange) {
+      // ---- 5. several workers: this rank's gradients (my slice of dW1, then the small ones) summed over the ranks through
+      // the NVLink peer cells, then the update.  Cell index: element of W1 in [0, 784*N1), small gradients behind it.
+      __syncthreads();
+      constexpr int NW = KS * N1;
+      for (int i = t; i < NS; i += THREADS) dz[NW + i] = ssum[i];   // one buffer for both
+      __syncthreads();
+      constexpr int EPT = (NW + NS + THREADS - 1) / THREADS;
+      exchange_block<EPT>(a.fx, xstep1, xparity, (long)(j * KS) * N1, (long)K0 * N1, dz, NW + NS, NW, j == 0, t, THREADS);
+      __syncthreads();
+      for (int i = t; i < NW; i += THREADS) w1[i] = fmaf(-a.lr, dz[i], w1[i]);
+      for (int i = t; i < NS; i += THREADS) {
+        const float g = dz[NW + i];
+        if (i < NS - 2) small[i] = fmaf(-a.lr, g, small[i]);       // [W2][b2][b1] or [b], the order of the gradient vector
+        else if (j == 0 && i == NS - 2) {
+          const float l = a.loss == B2_LOSS_SSE_SUM ? g : g * a.inv_B;
+          if (a.loss_trace) a.loss_trace[s] = l;
+          if (s + 1 == a.n_steps) a.grads[a.P] = l;
+        } else if (j == 0 && i == NS - 1) {
+          if (a.correct_trace) a.correct_trace[s] = (int)(g + 0.5f);
+          if (s + 1 == a.n_steps) a.grads[a.P + 1] = g;
+        }
+      }
+    }
     __syncthreads();
     CS_TICK(10);
   }
