@@ -23,7 +23,10 @@
 // The two bulk exchanges go through L2 and not through distributed shared memory: a CTA has to take in ~40 KB in each, and
 // DSMEM delivers ~20 B/clk per SM where L2 delivers several times that (measured: 3.5 us -> 0.8 us for the dz2 gather).
 // The cluster is what makes the barriers cheap (hardware cluster barrier, ~0.3 us) and the CTAs co-scheduled.
-// Every sum runs in a fixed order (CTA order, row order, ascending k), so a run is bit-reproducible.
+// Several workers (distributed.py:11-13: 1 ps + 2 workers): one cluster per GPU; at the end of a step the rank's gradients
+// (every CTA's slice of dW1, the small ones once) are summed over the ranks through the NVLink peer cells of common.cuh
+// (exchange_block: push all, collect peer by peer in rank order) and only then applied -- still one launch for all steps.
+// Every sum runs in a fixed order (CTA order, row order, ascending k, rank order), so a run is bit-reproducible.
 #include <cooperative_groups.h>
 #include <math.h>
 #include <stdlib.h>
