@@ -1108,6 +1108,7 @@ static int enqueue_persistent(b2_ctx* c, const float* xp, const float* yp, long 
       int rc = b2_launch_cluster_steps(c->n_layers, c->act, c->loss, c->w_off, c->b_off, c->P, xp, yp, span, first_row,
                                        global_batch, local_batch, n_steps, lr, c->params, c->grads, loss_trace, correct_trace,
                                        c->global_step_dev, c->cs_scratch, (long)c->rank * local_batch, use_peer ? &fx : nullptr, s);
+      if (rc == -2) return B2_NOT_PERSISTENT;      // this device cannot co-schedule the 14-CTA cluster: per-step kernels
       if (rc) return rc;
       if (use_peer) c->peer_step += (unsigned)n_steps;
       c->launches += 1;

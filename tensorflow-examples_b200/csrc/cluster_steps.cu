@@ -734,18 +734,38 @@ __global__ void __launch_bounds__(THREADS, 1) cluster_steps_kernel(const args a)
   }
 }
 
+constexpr int B2_CLUSTER_UNAVAILABLE = -2;
+
 template <int N1, int N2, int BMAX>
 static int launch(const args& a, cudaStream_t s) {
   using L = Layout<N1, N2, BMAX>;
   const int smem = L::total * (int)sizeof(float);
-  static bool prepared[64] = {};
+  static int prepared[64] = {};                    // 0 = not yet, 1 = usable, -1 = this device cannot co-schedule the cluster
   int dev = 0;
   B2_CUDA(cudaGetDevice(&dev));
-  if (dev >= 0 && dev < 64 && !prepared[dev]) {
+  if (dev < 0 || dev >= 64) return B2_CLUSTER_UNAVAILABLE;
+  if (!prepared[dev]) {
     B2_CUDA(cudaFuncSetAttribute(cluster_steps_kernel<N1, N2, BMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     B2_CUDA(cudaFuncSetAttribute(cluster_steps_kernel<N1, N2, BMAX>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-    prepared[dev] = true;
+    // can 14 CTAs of this size be resident in one cluster at all (a MIG slice or a partitioned GPU may not have them)?
+    cudaLaunchConfig_t q;
+    memset(&q, 0, sizeof(q));
+    q.gridDim = dim3(C);
+    q.blockDim = dim3(THREADS);
+    q.dynamicSmemBytes = smem;
+    cudaLaunchAttribute qa[1];
+    qa[0].id = cudaLaunchAttributeClusterDimension;
+    qa[0].val.clusterDim.x = C;
+    qa[0].val.clusterDim.y = 1;
+    qa[0].val.clusterDim.z = 1;
+    q.attrs = qa;
+    q.numAttrs = 1;
+    int clusters = 0;
+    cudaError_t qe = cudaOccupancyMaxActiveClusters(&clusters, cluster_steps_kernel<N1, N2, BMAX>, &q);
+    if (qe != cudaSuccess) (void)cudaGetLastError();
+    prepared[dev] = (qe == cudaSuccess && clusters >= 1) ? 1 : -1;
   }
+  if (prepared[dev] < 0) return B2_CLUSTER_UNAVAILABLE;      // the caller uses the per-step kernels instead
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(C);
