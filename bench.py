@@ -394,13 +394,15 @@ def run_b200(D, args, workload, batch, steps, warmup, hx, hy, with_e2e, with_cpu
     tr = make_trainer(D, workload, batch, args)
 
     # ---- value: device-resident pool -----------------------------------------------------
-    lt, ct = tr.train_steps(x_pool, y_pool, batch, warmup, first_row=0, lr=LR)
-    torch.cuda.synchronize(dev)
-    first_loss, first_correct = float(lt[0].item()), int(ct[0].item())
+    # the clock sampler is started BEFORE the warm-up steps, so that nothing idles between warm-up and the timed region
     sampler = ClockSampler(D.local_rank)
     if rank == 0:
         sampler.start()
         time.sleep(0.3)
+    D.barrier()
+    lt, ct = tr.train_steps(x_pool, y_pool, batch, warmup, first_row=0, lr=LR)
+    torch.cuda.synchronize(dev)
+    first = torch.stack([lt[0], ct[0].float()]).cpu()               # one small read; the values are used after the timing
     D.barrier()
     torch.cuda.synchronize(dev)
     l0 = tr.launch_count
@@ -414,6 +416,7 @@ def run_b200(D, args, workload, batch, steps, warmup, hx, hy, with_e2e, with_cpu
     launches = tr.launch_count - l0
     clocks = sampler.stop() if rank == 0 else None
     last_loss = float(lt[steps - 1].item())
+    first_loss, first_correct = float(first[0].item()), int(first[1].item())
     value = global_batch * steps / (ms / 1e3)
 
     # ---- roofline: per-launch device times over the same steps (events on the launch stream) ----
