@@ -400,23 +400,27 @@ def run_b200(D, args, workload, batch, steps, warmup, hx, hy, with_e2e, with_cpu
         sampler.start()
         time.sleep(0.3)
     D.barrier()
-    t_w = time.perf_counter()
     lt, ct = tr.train_steps(x_pool, y_pool, batch, warmup, first_row=0, lr=LR)
     torch.cuda.synchronize(dev)
     first = torch.stack([lt[0], ct[0].float()]).cpu()               # one small read; the values are used after the timing
     # W warm-up steps of a 60 us step are 0.3 ms: not enough for the GPU to reach its steady clocks.  Keep warming up (untimed,
-    # same steps) until the warm-up has lasted >= 20 ms; the line reports the number of warm-up steps actually run.
-    warm_s = time.perf_counter() - t_w
-    extra = 0
-    if warm_s < 0.020:
-        extra = int(min(2000, max(0.0, 0.020 - warm_s) / max(warm_s / warmup, 1e-6)))
+    # same steps) until >= 20 ms of steps have run; the line reports the number of warm-up steps actually run.  The step
+    # time is estimated from a second, already warm round of W steps (the first one pays module loading).
+    t_w = time.perf_counter()
+    tr.train_steps(x_pool, y_pool, batch, warmup, first_row=(warmup * global_batch) % pool_rows, lr=LR)
+    torch.cuda.synchronize(dev)
+    round_s = time.perf_counter() - t_w
+    extra = warmup
+    if round_s < 0.020:
+        more = int(min(4000, (0.020 - round_s) / max(round_s / warmup, 1e-6)))
         if D.dist is not None:                                     # the same count on every rank
-            tt = torch.tensor([extra], dtype=torch.int64, device=dev)
+            tt = torch.tensor([more], dtype=torch.int64, device=dev)
             D.dist.all_reduce(tt, op=D.dist.ReduceOp.MAX)
-            extra = int(tt.item())
-        if extra > 0:
-            tr.train_steps(x_pool, y_pool, batch, extra, first_row=(warmup * global_batch) % pool_rows, lr=LR)
+            more = int(tt.item())
+        if more > 0:
+            tr.train_steps(x_pool, y_pool, batch, more, first_row=(2 * warmup * global_batch) % pool_rows, lr=LR)
             torch.cuda.synchronize(dev)
+        extra += more
     warm_total = warmup + extra
     D.barrier()
     torch.cuda.synchronize(dev)
