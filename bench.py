@@ -440,7 +440,7 @@ def run_b200(D, args, workload, batch, steps, warmup, hx, hy, with_e2e, with_cpu
 
     # ---- roofline: per-launch device times over the same steps (events on the launch stream) ----
     tr.kernel_timing(True)
-    tsteps = min(steps, 200 if precision == "fp32" else 20)
+    tsteps = 200 if precision == "fp32" else min(max(steps, 3), 20)   # enough launches for a stable mean (13 ms of fp32 steps)
     tr.train_steps(x_pool, y_pool, batch, tsteps, first_row=0, lr=LR)
     kt = tr.kernel_times()
     tr.kernel_timing(False)
