@@ -165,3 +165,30 @@ def test_two_worker_data_parallel_equals_single_process():
             assert abs(out[r][2][s][0] - float(lo)) < 1e-12 and int(round(out[r][2][s][1])) == co
     np.testing.assert_allclose(out[0][3], ref.W[0], rtol=1e-12, atol=1e-15)
     np.testing.assert_array_equal(out[0][3], out[1][3])           # replicas stay identical
+
+
+def test_peer_exchange_only_when_all_workers_share_the_node():
+    """The NVLink peer-memory exchange maps the other workers' buffers with CUDA IPC: it is only tried when every worker
+    address names this node (distributed.py:11-13 uses 127.0.0.1 throughout); otherwise all workers stay on NCCL."""
+    assert cluster.single_node(cluster.parse_cluster("127.0.0.1:2222", "127.0.0.1:2223,127.0.0.1:2224"))
+    assert cluster.single_node(cluster.parse_cluster("a:1", "localhost:2223,127.0.0.1:2224"))
+    assert cluster.single_node(cluster.parse_cluster("a:1", "node7:2223,node7:2224"))
+    assert not cluster.single_node(cluster.parse_cluster("a:1", "node7:2223,node8:2223"))
+    assert not cluster.single_node(cluster.parse_cluster("a:1", "10.0.0.1:2223,127.0.0.1:2224"))
+
+
+def test_run_train_keeps_converted_feeds_alive():
+    """sess.run takes Python lists (simple.py:25-26) and float64 arrays: both feeds are converted to float32 copies, and BOTH
+    copies must stay alive until the C call has read them (the first used to be dropped when the second was converted)."""
+    from tensorflow_examples_b200 import session
+    x = [[1.0], [2.0], [3.0], [4.0]]                       # a list, as in simple.py
+    y = np.array([[0.0], [-1.0], [-2.0], [-3.0]])          # float64
+    px, rows_x, keep_x = session._host_ptr(x, 1)
+    py, rows_y, keep_y = session._host_ptr(y, 1)
+    assert rows_x == rows_y == 4 and keep_x.dtype == np.float32 and keep_y.dtype == np.float32
+    assert px.value == keep_x.ctypes.data and py.value == keep_y.ctypes.data and px.value != py.value
+    np.testing.assert_array_equal(keep_x.ravel(), [1, 2, 3, 4])      # x's copy is intact after y was converted
+    np.testing.assert_array_equal(keep_y.ravel(), [0, -1, -2, -3])
+    t = torch.arange(6, dtype=torch.float64).reshape(3, 2)[:, :1]    # non-contiguous float64 tensor
+    pt, rows_t, keep_t = session._host_ptr(t, 1)
+    assert rows_t == 3 and keep_t.dtype == torch.float32 and keep_t.is_contiguous() and pt.value == keep_t.data_ptr()
