@@ -36,11 +36,16 @@ struct tiny_args {
   float* global_step;
 };
 
+__device__ __forceinline__ void cp_async4(float* dst, const float* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+
 __global__ void __launch_bounds__(32) tiny_steps_kernel(const tiny_args a) {
   __shared__ float sP[MAX_P];                       // parameters, flat layout
-  __shared__ float sA[MAX_L + 1][MAX_B][MAX_W];     // sA[l] = input of layer l (sA[0] = x), sA[L] = logits / predictions
+  __shared__ float sA[MAX_L + 1][MAX_B][MAX_W];     // sA[l] = input of layer l (l >= 1), sA[L] = logits / predictions
   __shared__ float sD[2][MAX_B][MAX_W];             // dz ping-pong
-  __shared__ float sY[MAX_B][MAX_W];
+  __shared__ float sX[2][MAX_B * MAX_W];            // this step's / the next step's rows, compact ([rows][in0]), filled by cp.async
+  __shared__ float sYb[2][MAX_B * MAX_W];           // likewise the targets ([rows][C])
   __shared__ float sRow[2][MAX_B];                  // per-row loss, hit
   const int lane = threadIdx.x;
   const int L = a.n_layers, B = a.rows;
@@ -50,10 +55,19 @@ __global__ void __launch_bounds__(32) tiny_steps_kernel(const tiny_args a) {
   __syncwarp();
 
   long start = a.first_row % a.span;                  // batches wrap inside the pool; kept incrementally (no 64-bit modulo per step)
-  for (int s = 0; s < a.n_steps; ++s, start = start + a.global_batch >= a.span ? start + a.global_batch - a.span : start + a.global_batch) {
-    for (int i = lane; i < B * in0; i += 32) sA[0][i / in0][i % in0] = a.x_pool[start * in0 + i];
-    for (int i = lane; i < B * C; i += 32) sY[i / C][i % C] = a.y_pool[start * C + i];
+  auto fetch = [&](int buf, long row0) {              // asynchronous copy of one step's rows: lands while the previous step computes
+    for (int i = lane; i < B * in0; i += 32) cp_async4(&sX[buf][i], a.x_pool + row0 * in0 + i);
+    for (int i = lane; i < B * C; i += 32) cp_async4(&sYb[buf][i], a.y_pool + row0 * C + i);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  fetch(0, start);
+  for (int s = 0; s < a.n_steps; ++s) {
+    const float* X = sX[s & 1];
+    const float* Y = sYb[s & 1];
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncwarp();
+    start = start + a.global_batch >= a.span ? start + a.global_batch - a.span : start + a.global_batch;
+    if (s + 1 < a.n_steps) fetch((s + 1) & 1, start);   // the other buffer was last read in step s-1
     // ---- forward
     for (int l = 0; l < L; ++l) {
       const int Kin = a.dims[l], N = a.dims[l + 1];
@@ -63,7 +77,11 @@ __global__ void __launch_bounds__(32) tiny_steps_kernel(const tiny_args a) {
       for (int i = lane; i < B * N; i += 32) {
         const int r = i / N, n = i % N;
         float z = 0.f;
-        for (int k = 0; k < Kin; ++k) z = fmaf(sA[l][r][k], W[k * N + n], z);
+        if (l == 0) {
+          for (int k = 0; k < Kin; ++k) z = fmaf(X[r * Kin + k], W[k * N + n], z);
+        } else {
+          for (int k = 0; k < Kin; ++k) z = fmaf(sA[l][r][k], W[k * N + n], z);
+        }
         z += b[n];
         sA[l + 1][r][n] = sig ? 1.0f / (1.0f + expf(-z)) : z;
       }
@@ -75,7 +93,7 @@ __global__ void __launch_bounds__(32) tiny_steps_kernel(const tiny_args a) {
       float l = 0.f, hit = 0.f;
       if (a.loss == B2_LOSS_SSE_SUM) {
         for (int c = 0; c < C; ++c) {
-          const float d = sA[L][r][c] - sY[r][c];
+          const float d = sA[L][r][c] - Y[r * C + c];
           l = fmaf(d, d, l);
           sD[0][r][c] = 2.0f * d;
         }
@@ -88,7 +106,7 @@ __global__ void __launch_bounds__(32) tiny_steps_kernel(const tiny_args a) {
         float sy = 0.f, bv = -INFINITY, lv = -INFINITY;
         int bi = 0, li = 0;
         for (int c = 0; c < C; ++c) {
-          const float y = expf(sA[L][r][c] - m) * inv, t = sY[r][c];
+          const float y = expf(sA[L][r][c] - m) * inv, t = Y[r * C + c];
           l -= t * logf(y);                          // un-fused log(softmax), distributed.py:102
           sy += t;
           if (y > bv) { bv = y; bi = c; }            // first index wins ties (tf.argmax)
@@ -96,7 +114,7 @@ __global__ void __launch_bounds__(32) tiny_steps_kernel(const tiny_args a) {
         }
         for (int c = 0; c < C; ++c) {
           const float y = expf(sA[L][r][c] - m) * inv;
-          sD[0][r][c] = (y * sy - sY[r][c]) * a.inv_B;
+          sD[0][r][c] = (y * sy - Y[r * C + c]) * a.inv_B;
         }
         hit = bi == li ? 1.0f : 0.0f;
       }
@@ -135,7 +153,11 @@ __global__ void __launch_bounds__(32) tiny_steps_kernel(const tiny_args a) {
         float g = 0.f;
         if (i < Kin * N) {
           const int k = i / N, n = i % N;
-          for (int r = 0; r < B; ++r) g = fmaf(sA[l][r][k], sD[cur][r][n], g);
+          if (l == 0) {
+            for (int r = 0; r < B; ++r) g = fmaf(X[r * Kin + k], sD[cur][r][n], g);
+          } else {
+            for (int r = 0; r < B; ++r) g = fmaf(sA[l][r][k], sD[cur][r][n], g);
+          }
           W[i] = fmaf(-a.lr, g, W[i]);
           if (last) a.grads[a.w_off[l] + i] = g;
         } else {
