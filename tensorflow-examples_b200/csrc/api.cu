@@ -373,7 +373,7 @@ int enqueue_step_mixed(b2_ctx* c, const float* x, const float* y, int rows, long
   c->launches++;
   // dz_prev = (dz . W_out^T) * a(1-a)   (MatMul grad transpose_b + SigmoidGrad)
   // ten classes in the reduction: an element-wise pass on the CUDA cores, not a GEMM; it also leaves the column sums of
-  // its output (bias gradient of layer L-1) as one partial row per 128-row block
+  // its output (bias gradient of layer L-1) as one partial row per 64-row block
   int colsum_slices = b2_narrow_dgrad_slices(rows);
   bool colsum_pending = true;
   {

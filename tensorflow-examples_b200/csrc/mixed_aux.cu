@@ -261,18 +261,21 @@ loss_head_rows_kernel(const float* __restrict__ z, const float* __restrict__ y_,
 // with K = 10 in the reduction this is an element-wise pass over two 512 MB matrices, not a GEMM: run through the
 // tensor-core kernel (K padded to 64) it was epilogue-bound (398 us at 65536 x 4096); here every thread owns 8 columns
 // (their 8 x C weights live in registers), streams rows, and also produces the column sums of the ROUNDED outputs (the
-// bias gradient of the layer below) as one partial row per 128-row block.
-// grid = (K / 512, ceil(rows / 128)), 256 threads = 64 column groups x 4 row lanes.
+// bias gradient of the layer below) as one partial row per 64-row block.
+// grid = (ceil(K / (8 CG)), ceil(rows / 64)), CG column groups x RL row lanes per CTA.  Two shapes: 64 x 4 (a 512-column
+// strip: narrow layers) and 512 x 1 (rows of up to 4096 columns, walked one after the other: every CTA streams whole
+// 8 KB rows instead of 1 KB pieces 8 KB apart, which is what HBM likes).
 // ---------------------------------------------------------------------------------------------
-constexpr int ND_COLS = 512, ND_ROWS = 128;
+constexpr int ND_ROWS = 64;
 
-template <int CT>   // classes rounded up to an even number: the weights of a thread's 8 columns live in 8 x CT registers
-__global__ void __launch_bounds__(256, 2)
+template <int CT, int CG, int RL>   // classes rounded up to an even number: the weights of a thread's 8 columns live in 8 x CT registers
+__global__ void __launch_bounds__(CG * RL, CG * RL >= 512 ? 1 : 2)
 narrow_dgrad_bf16_kernel(const __nv_bfloat16* __restrict__ dzn, const __nv_bfloat16* __restrict__ wpad,
                          const __nv_bfloat16* __restrict__ act, __nv_bfloat16* __restrict__ out,
                          float* __restrict__ colsum_part, int rows, int K) {
-  __shared__ float sh[4][ND_COLS + 8];
-  const int cg = threadIdx.x & 63, rl = threadIdx.x >> 6;
+  constexpr int ND_COLS = 8 * CG;
+  __shared__ float sh[RL > 1 ? RL : 1][RL > 1 ? ND_COLS + 8 : 1];
+  const int cg = threadIdx.x % CG, rl = threadIdx.x / CG;
   const int j0 = blockIdx.x * ND_COLS + cg * 8;
   const bool col_ok = j0 < K;                                   // K is a multiple of 8
   float w[8][CT];
@@ -292,7 +295,7 @@ narrow_dgrad_bf16_kernel(const __nv_bfloat16* __restrict__ dzn, const __nv_bfloa
   for (int u = 0; u < 8; ++u) cs[u] = 0.f;
   const int r_begin = blockIdx.y * ND_ROWS, r_end = min(rows, r_begin + ND_ROWS);
 #pragma unroll 2
-  for (int r = r_begin + rl; r < r_end; r += 4) {
+  for (int r = r_begin + rl; r < r_end; r += RL) {
     const uint4* dp = reinterpret_cast<const uint4*>(dzn + (size_t)r * NARROW);
     const uint4 d0 = dp[0], d1 = dp[1];
     uint4 av = make_uint4(0u, 0u, 0u, 0u);
@@ -317,12 +320,23 @@ narrow_dgrad_bf16_kernel(const __nv_bfloat16* __restrict__ dzn, const __nv_bfloa
     if (col_ok) *reinterpret_cast<uint4*>(out + (size_t)r * K + j0) = make_uint4(o[0], o[1], o[2], o[3]);
   }
   if (colsum_part == nullptr) return;
+  if (RL == 1) {                                                  // one row lane: the thread's sums are the block's
+    if (col_ok) {
+      float4* o4 = reinterpret_cast<float4*>(colsum_part + (size_t)blockIdx.y * K + j0);
+      o4[0] = make_float4(cs[0], cs[1], cs[2], cs[3]);
+      o4[1] = make_float4(cs[4], cs[5], cs[6], cs[7]);
+    }
+    return;
+  }
 #pragma unroll
   for (int u = 0; u < 8; ++u) sh[rl][cg * 8 + u] = cs[u];
   __syncthreads();
-  for (int j = threadIdx.x; j < ND_COLS; j += 256) {
+  for (int j = threadIdx.x; j < ND_COLS; j += CG * RL) {
     const int col = blockIdx.x * ND_COLS + j;
-    if (col < K) colsum_part[(size_t)blockIdx.y * K + col] = ((sh[0][j] + sh[1][j]) + sh[2][j]) + sh[3][j];
+    float t = sh[0][j];
+#pragma unroll
+    for (int q = 1; q < RL; ++q) t += sh[q][j];                   // row lanes in a fixed order
+    if (col < K) colsum_part[(size_t)blockIdx.y * K + col] = t;
   }
 }
 
@@ -366,26 +380,33 @@ int b2_launch_loss_head_rows(const float* z, const float* y, void* dzn, float* l
 }
 
 // dz_prev = (dzn . wpad^T) * act * (1 - act) for the narrow output layer; colsum_part (may be NULL) gets one partial row of
-// column sums per 128-row block: finish with b2_launch_colsum_finish(part, out, K, b2_narrow_dgrad_slices(rows))
+// column sums per 64-row block: finish with b2_launch_colsum_finish(part, out, K, b2_narrow_dgrad_slices(rows))
 int b2_narrow_dgrad_slices(int rows) { return (rows + mx::ND_ROWS - 1) / mx::ND_ROWS; }
 int b2_launch_narrow_dgrad_bf16(const void* dzn, const void* wpad, const void* act, void* out, float* colsum_part, int rows,
                                 int K, int C, cudaStream_t s) {
   if (K % 8 || C > 16) { b2_set_error("narrow_dgrad_bf16: K must be a multiple of 8 and C <= 16"); return B2_ERR_ARG; }
-  const dim3 grid((K + mx::ND_COLS - 1) / mx::ND_COLS, (rows + mx::ND_ROWS - 1) / mx::ND_ROWS);
+  const bool wide = K >= 2048;                                     // whole rows per CTA once a row is a few KB
+  const int cols = wide ? 4096 : 512;
+  const dim3 grid((K + cols - 1) / cols, (rows + mx::ND_ROWS - 1) / mx::ND_ROWS);
   const __nv_bfloat16* d = reinterpret_cast<const __nv_bfloat16*>(dzn);
   const __nv_bfloat16* w = reinterpret_cast<const __nv_bfloat16*>(wpad);
   const __nv_bfloat16* a = reinterpret_cast<const __nv_bfloat16*>(act);
   __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+#define ND_CASE(CT)                                                                                              \
+  if (wide) mx::narrow_dgrad_bf16_kernel<CT, 512, 1><<<grid, 512, 0, s>>>(d, w, a, o, colsum_part, rows, K);     \
+  else mx::narrow_dgrad_bf16_kernel<CT, 64, 4><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K);           \
+  break;
   switch ((C + 1) / 2) {
-    case 1: mx::narrow_dgrad_bf16_kernel<2><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
-    case 2: mx::narrow_dgrad_bf16_kernel<4><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
-    case 3: mx::narrow_dgrad_bf16_kernel<6><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
-    case 4: mx::narrow_dgrad_bf16_kernel<8><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
-    case 5: mx::narrow_dgrad_bf16_kernel<10><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
-    case 6: mx::narrow_dgrad_bf16_kernel<12><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
-    case 7: mx::narrow_dgrad_bf16_kernel<14><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
-    default: mx::narrow_dgrad_bf16_kernel<16><<<grid, 256, 0, s>>>(d, w, a, o, colsum_part, rows, K); break;
+    case 1: ND_CASE(2)
+    case 2: ND_CASE(4)
+    case 3: ND_CASE(6)
+    case 4: ND_CASE(8)
+    case 5: ND_CASE(10)
+    case 6: ND_CASE(12)
+    case 7: ND_CASE(14)
+    default: ND_CASE(16)
   }
+#undef ND_CASE
   MX_CHECK();
   return B2_OK;
 }
