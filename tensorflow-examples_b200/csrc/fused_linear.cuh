@@ -90,6 +90,21 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
       "l"(src), "r"(bytes), "r"(smem_u32(bar))
       : "memory");
 }
+// the same with an L2 eviction policy (createpolicy): the x rows are read once per step and should not push the
+// per-CTA partials and the weights, which the reduction kernel re-reads a few microseconds later, out of L2
+__device__ __forceinline__ unsigned long long l2_evict_first_policy() {
+  unsigned long long pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void bulk_g2s_hint(void* dst, const void* src, uint32_t bytes, unsigned long long* bar,
+                                              unsigned long long policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+          smem_u32(dst)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+      : "memory");
+}
 // Programmatic dependent launch: the kernel may start while its predecessor on the stream is still running
 // (launch latency and prologue overlap); pdl_wait() blocks until the predecessor's writes are visible.  Both
 // are no-ops when the kernel was launched without the attribute.

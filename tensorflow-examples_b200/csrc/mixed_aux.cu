@@ -320,23 +320,23 @@ narrow_dgrad_bf16_kernel(const __nv_bfloat16* __restrict__ dzn, const __nv_bfloa
     if (col_ok) *reinterpret_cast<uint4*>(out + (size_t)r * K + j0) = make_uint4(o[0], o[1], o[2], o[3]);
   }
   if (colsum_part == nullptr) return;
-  if (RL == 1) {                                                  // one row lane: the thread's sums are the block's
+  if constexpr (RL == 1) {                                        // one row lane: the thread's sums are the block's
     if (col_ok) {
       float4* o4 = reinterpret_cast<float4*>(colsum_part + (size_t)blockIdx.y * K + j0);
       o4[0] = make_float4(cs[0], cs[1], cs[2], cs[3]);
       o4[1] = make_float4(cs[4], cs[5], cs[6], cs[7]);
     }
-    return;
-  }
+  } else {
 #pragma unroll
-  for (int u = 0; u < 8; ++u) sh[rl][cg * 8 + u] = cs[u];
-  __syncthreads();
-  for (int j = threadIdx.x; j < ND_COLS; j += CG * RL) {
-    const int col = blockIdx.x * ND_COLS + j;
-    float t = sh[0][j];
+    for (int u = 0; u < 8; ++u) sh[rl][cg * 8 + u] = cs[u];
+    __syncthreads();
+    for (int j = threadIdx.x; j < ND_COLS; j += CG * RL) {
+      const int col = blockIdx.x * ND_COLS + j;
+      float t = sh[0][j];
 #pragma unroll
-    for (int q = 1; q < RL; ++q) t += sh[q][j];                   // row lanes in a fixed order
-    if (col < K) colsum_part[(size_t)blockIdx.y * K + col] = t;
+      for (int q = 1; q < RL; ++q) t += sh[q][j];                 // row lanes in a fixed order
+      if (col < K) colsum_part[(size_t)blockIdx.y * K + col] = t;
+    }
   }
 }
 
