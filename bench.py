@@ -411,16 +411,19 @@ def run_b200(D, args, workload, batch, steps, warmup, hx, hy, with_e2e, with_cpu
     torch.cuda.synchronize(dev)
     round_s = time.perf_counter() - t_w
     extra = warmup
+    more = 0
     if round_s < 0.020:
         more = int(min(4000, (0.020 - round_s) / max(round_s / warmup, 1e-6)))
-        if D.dist is not None:                                     # the same count on every rank
-            tt = torch.tensor([more], dtype=torch.int64, device=dev)
-            D.dist.all_reduce(tt, op=D.dist.ReduceOp.MAX)
-            more = int(tt.item())
-        if more > 0:
-            tr.train_steps(x_pool, y_pool, batch, more, first_row=(2 * warmup * global_batch) % pool_rows, lr=LR)
-            torch.cuda.synchronize(dev)
-        extra += more
+    if D.dist is not None:
+        # the same count on every rank, and EVERY rank takes part whatever its own clock said: a round that takes 20 ms on
+        # one rank and 19.9 ms on another must not leave one of them alone in the collective
+        tt = torch.tensor([more], dtype=torch.int64, device=dev)
+        D.dist.all_reduce(tt, op=D.dist.ReduceOp.MAX)
+        more = int(tt.item())
+    if more > 0:
+        tr.train_steps(x_pool, y_pool, batch, more, first_row=(2 * warmup * global_batch) % pool_rows, lr=LR)
+        torch.cuda.synchronize(dev)
+    extra += more
     warm_total = warmup + extra
     D.barrier()
     torch.cuda.synchronize(dev)
