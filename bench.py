@@ -12,6 +12,7 @@ accuracy, backward, [all-reduce], SGD apply) over one batch of synthetic MNIST-s
 Multi-GPU: launched by torchrun, one rank per GPU; weak scaling (per-GPU batch fixed).
 """
 import argparse
+import datetime
 import json
 import os
 import statistics
@@ -202,7 +203,7 @@ def sweep_main(args):
     dist = None
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=dev)
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=600))   # a lost rank ends the run, not hangs it
     peak_gbs, _ = _peaks()
     batches = [int(b) for b in args.sweep_batches.split(",")]
     hx, hy = synthetic.make_pool(HOST_POOL_ROWS)
@@ -299,7 +300,8 @@ class Dist:
         self.dist = None
         if self.world > 1:
             import torch.distributed as dist
-            dist.init_process_group("nccl", device_id=self.dev)
+            # a rank that died leaves the others in a collective: bound that wait so the run ends with an error
+            dist.init_process_group("nccl", device_id=self.dev, timeout=datetime.timedelta(seconds=600))
             self.dist = dist
 
     def barrier(self):
