@@ -257,3 +257,27 @@ def test_softmax_underflow_gives_nan_like_the_reference(cuda_device, path):
     assert np.isnan(float(loss_eval)), (path, loss_eval)
     assert np.isnan(float(lt[0].item())), (path, float(lt[0].item()))
     tr.close()
+
+
+def test_misaligned_rows_are_refused_not_trapped(cuda_device):
+    """The fused step loads x rows with cp.async.bulk, which needs a 16-byte aligned source: a pool that starts at an odd
+    float offset (a view into a larger buffer) must come back as B2_ERR_ARG with a message, from every entry point that
+    takes device rows -- not as a misaligned-address fault that kills the context."""
+    dims, rows = [784, 10], 64
+    x, y = synthetic.make_pool(rows, dims[0], dims[-1])
+    flat = torch.zeros(rows * dims[0] + 8, dtype=torch.float32, device=cuda_device)
+    xd = flat[1:1 + rows * dims[0]].view(rows, dims[0])             # contiguous, 4 bytes off a 16-byte boundary
+    xd.copy_(torch.from_numpy(x))
+    yd = torch.from_numpy(y).to(cuda_device)
+    assert xd.is_contiguous() and xd.data_ptr() % 16 == 4
+    tr = pkg.DenseTrainer(dims, pkg.ACT_IDENTITY, pkg.LOSS_SOFTMAX_CE, max_local_batch=rows)
+    tr.set_params(*synthetic.make_weights(dims, True))
+    with pytest.raises(pkg.B2Error, match="16-byte aligned"):
+        tr.train_steps(xd, yd, rows, 1, lr=0.001)
+    with pytest.raises(pkg.B2Error, match="16-byte aligned"):
+        tr.evaluate(xd, yd)
+    good = torch.from_numpy(x).to(cuda_device)                      # the context is alive and the aligned pool works
+    lt, _ = tr.train_steps(good, yd, rows, 1, lr=0.001)
+    torch.cuda.synchronize()
+    assert np.isfinite(float(lt[0]))
+    tr.close()
