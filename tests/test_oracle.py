@@ -54,6 +54,23 @@ def test_simple_py_1000_steps_equals_the_line_tensorflow_publishes():
     assert "%.5e" % float(loss) == "5.69997e-11"           # the guide's 6-digit rendering of the loss
 
 
+def test_simple_py_forward_and_loss_lines_of_the_guide():
+    """The same guide evaluates the untrained model first (W = .3, b = -.3, the initial values of simple.py:11-12) and prints
+        [ 0.          0.30000001  0.60000002  0.90000004]      sess.run(linear_model, {x: [1, 2, 3, 4]})
+        23.66                                                  sess.run(loss, {x: [1, 2, 3, 4], y: [0, -1, -2, -3]})
+        0.0                                                    the loss after assigning W = -1, b = 1
+    (float32 values at numpy 1.x's 8 significant digits).  The restatement's forward pass gives those float32 values."""
+    x, y = np.array([1, 2, 3, 4], np.float32), np.array([0, -1, -2, -3], np.float32)
+    g = oracle.TF1Graph([1, 1], oracle.ACT_IDENTITY, oracle.LOSS_SSE, [[0.3]], [[-0.3]])
+    _, pred = g.forward(x.reshape(-1, 1))
+    assert ["%.8g" % v for v in np.asarray(pred, np.float32).ravel()] == ["0", "0.30000001", "0.60000002", "0.90000004"]
+    loss, _ = g.evaluate(x, y)
+    assert "%.4g" % float(loss) == "23.66"
+    g = oracle.TF1Graph([1, 1], oracle.ACT_IDENTITY, oracle.LOSS_SSE, [[-1.0]], [[1.0]])
+    loss, _ = g.evaluate(x, y)
+    assert float(loss) == 0.0
+
+
 def test_simple_py_fixture():
     f = np.load(os.path.join(GOLDEN, "simple_py.npz"))
     W, b, loss, trace = oracle.simple_py()
