@@ -527,7 +527,7 @@ def run_b200(D, args, workload, batch, steps, warmup, hx, hy, with_e2e, with_cpu
     cpu = None
     if with_cpu and rank == 0 and world == 1:
         cbatch = min(batch, CPU_SAMPLE_BATCH.get(workload, batch))
-        r = cpu_reference_run(dims, act, loss, scaled, cbatch, 400, 2, budget_s=12.0)
+        r = cpu_reference_run(dims, act, loss, scaled, cbatch, 1200, 2, budget_s=15.0)   # ~10 s of CPU work at 8-9 ms per 65536-row step
         cpu = {"value": r["value"], "unit": "samples/s", "cores": r["threads"], "kind": r["kind"],
                "sample": "%d steps of %d rows in %.1f s, %s, all host threads"
                          % (r["steps"], cbatch, r["seconds"], _CPU_KIND[r["kind"]]),
