@@ -192,3 +192,43 @@ def test_run_train_keeps_converted_feeds_alive():
     t = torch.arange(6, dtype=torch.float64).reshape(3, 2)[:, :1]    # non-contiguous float64 tensor
     pt, rows_t, keep_t = session._host_ptr(t, 1)
     assert rows_t == 3 and keep_t.dtype == torch.float32 and keep_t.is_contiguous() and pt.value == keep_t.data_ptr()
+
+
+def test_native_event_writer_is_read_by_tensorboard(tmp_path, monkeypatch):
+    """distributed.py:121-125,138,151 without the tensorboard package: the native writer's file -- TFRecord framing, masked
+    CRC-32C, hand-encoded Event / Summary messages -- is what tensorboard's own loader (which verifies both checksums of
+    every record) reads back: the file-version event first, then one event per step with the two scalars."""
+    from tensorflow_examples_b200 import summaries
+    assert summaries.crc32c(b"123456789") == 0xE3069283                      # the CRC-32C check value
+    assert summaries.crc32c(b"") == 0
+    monkeypatch.setenv("B2_NATIVE_SUMMARIES", "1")
+    w = summaries.SummaryWriter(str(tmp_path))
+    assert w.enabled and w._native is not None
+    vals = [(0, 2.3025851, 0.09), (1, 1.5, 0.25), (300, 1e-9, 1.0), (2 ** 40, -3.75, 0.0)]
+    for step, cost, acc in vals:
+        w.add_scalars(step, cost, acc)
+    w.close()
+    files = [f for f in os.listdir(tmp_path) if "tfevents" in f]
+    assert len(files) == 1
+    path = os.path.join(tmp_path, files[0])
+    # (1) a parser of our own: framing and checksums
+    import struct
+    raw = open(path, "rb").read()
+    pos, records = 0, []
+    while pos < len(raw):
+        (n,) = struct.unpack_from("<Q", raw, pos)
+        assert struct.unpack_from("<I", raw, pos + 8)[0] == summaries.masked_crc32c(raw[pos:pos + 8])
+        data = raw[pos + 12:pos + 12 + n]
+        assert struct.unpack_from("<I", raw, pos + 12 + n)[0] == summaries.masked_crc32c(data)
+        records.append(data)
+        pos += 16 + n
+    assert pos == len(raw) and len(records) == 1 + len(vals)
+    # (2) tensorboard's loader, when the package is there
+    tb = pytest.importorskip("tensorboard.backend.event_processing.event_file_loader")
+    events = list(tb.EventFileLoader(path).Load())
+    assert events[0].file_version == "brain.Event:2"
+    got = [(ev.step, {v.tag: (v.simple_value if v.HasField("simple_value") else float(v.tensor.float_val[0]))
+                      for v in ev.summary.value}) for ev in events[1:]]
+    assert [s for s, _ in got] == [s for s, _, _ in vals]
+    for (_, d), (_, cost, acc) in zip(got, vals):
+        assert d["cost"] == np.float32(cost) and d["accuracy"] == np.float32(acc)
