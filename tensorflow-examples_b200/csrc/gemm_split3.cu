@@ -413,16 +413,13 @@ colsum_f32_kernel(const float* __restrict__ dz, float* __restrict__ partB, long 
 // 128B swizzle.
 static int make_map3(CUtensorMap* m, const void* base, long rows, long cols, long ld, long plane_stride, int box_rows,
                      bool mn_major) {
-  pfn_encode enc = b2_tensor_map_encoder();
-  if (!enc) return B2_ERR_CUDA;
+  if (!b2_tensor_map_encoder()) return B2_ERR_CUDA;
   const cuuint64_t gdim[3] = {(cuuint64_t)cols, (cuuint64_t)rows, 3};
   const cuuint64_t gstr[2] = {(cuuint64_t)ld * 2, (cuuint64_t)plane_stride * 2};
   const cuuint32_t box[3] = {mn_major ? 64u : (cuuint32_t)BLOCK_K, (cuuint32_t)box_rows, 1u};
-  const cuuint32_t estr[3] = {1u, 1u, 1u};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), gdim, gstr, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, mn_major ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
-                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
+  const int r = b2_tensor_map_cached(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, base, gdim, gstr, box,
+                                     mn_major ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B);
+  if (r != (int)CUDA_SUCCESS) {
     b2_set_error("cuTensorMapEncodeTiled failed (%d) for the planes of a [%ld, %ld] matrix (pitch %ld)", (int)r, rows, cols, ld);
     return B2_ERR_CUDA;
   }
@@ -431,16 +428,12 @@ static int make_map3(CUtensorMap* m, const void* base, long rows, long cols, lon
 
 // 2-D map over a row-major fp32 matrix [rows, cols] (row pitch ld floats), dense box {box_cols, box_rows}, no swizzle
 static int make_map_f32(CUtensorMap* m, const float* base, long rows, long cols, long ld, int box_cols, int box_rows) {
-  pfn_encode enc = b2_tensor_map_encoder();
-  if (!enc) return B2_ERR_CUDA;
+  if (!b2_tensor_map_encoder()) return B2_ERR_CUDA;
   const cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   const cuuint64_t gstr[1] = {(cuuint64_t)ld * 4};
   const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
-  const cuuint32_t estr[2] = {1u, 1u};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstr, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
+  const int r = b2_tensor_map_cached(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, base, gdim, gstr, box, CU_TENSOR_MAP_SWIZZLE_NONE);
+  if (r != (int)CUDA_SUCCESS) {
     b2_set_error("cuTensorMapEncodeTiled failed (%d) for a [%ld, %ld] fp32 matrix (pitch %ld)", (int)r, rows, cols, ld);
     return B2_ERR_CUDA;
   }

@@ -19,6 +19,9 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include <mutex>
+#include <string.h>
+
 #include "tc_common.cuh"
 
 namespace tg {
@@ -353,11 +356,8 @@ static int make_map(CUtensorMap* m, const void* base, long rows, long cols, int 
   const cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   const cuuint64_t gstr[1] = {(cuuint64_t)cols * 2};
   const cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
-  const cuuint32_t estr[2] = {1u, 1u};
-  CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
+  const int r = tcx::b2_tensor_map_cached(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, gdim, gstr, box, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (r != (int)CUDA_SUCCESS) {
     b2_set_error("cuTensorMapEncodeTiled failed (%d) for a [%ld, %ld] bf16 matrix", (int)r, rows, cols);
     return B2_ERR_CUDA;
   }
@@ -379,6 +379,52 @@ pfn_encode b2_tensor_map_encoder() {
   }
   fn_cached = (pfn_encode)fn;
   return fn_cached;
+}
+
+namespace {
+struct map_key {
+  int type, rank, swizzle, pad;
+  const void* base;
+  unsigned long long gdim[3], gstr[2];
+  unsigned box[3], pad2;
+};
+struct map_slot {
+  bool used;
+  map_key key;
+  CUtensorMap map;
+};
+constexpr int MAP_SLOTS = 128;          // direct-mapped; a collision just re-encodes
+map_slot g_maps[MAP_SLOTS];
+std::mutex g_maps_mu;
+}  // namespace
+
+int b2_tensor_map_cached(CUtensorMap* out, CUtensorMapDataType type, unsigned rank, const void* base, const cuuint64_t* gdim,
+                         const cuuint64_t* gstr, const cuuint32_t* box, CUtensorMapSwizzle swizzle) {
+  pfn_encode enc = b2_tensor_map_encoder();
+  if (!enc) return (int)CUDA_ERROR_NOT_SUPPORTED;
+  map_key k;
+  memset(&k, 0, sizeof(k));
+  k.type = (int)type; k.rank = (int)rank; k.swizzle = (int)swizzle; k.base = base;
+  for (unsigned i = 0; i < rank; ++i) { k.gdim[i] = gdim[i]; k.box[i] = box[i]; }
+  for (unsigned i = 0; i + 1 < rank; ++i) k.gstr[i] = gstr[i];
+  unsigned long long h = 1469598103934665603ull;      // FNV-1a over the key
+  const unsigned char* kb = reinterpret_cast<const unsigned char*>(&k);
+  for (size_t i = 0; i < sizeof(k); ++i) h = (h ^ kb[i]) * 1099511628211ull;
+  map_slot& slot = g_maps[h % MAP_SLOTS];
+  std::lock_guard<std::mutex> lock(g_maps_mu);
+  if (slot.used && memcmp(&slot.key, &k, sizeof(k)) == 0) {
+    *out = slot.map;
+    return (int)CUDA_SUCCESS;
+  }
+  const cuuint32_t estr[3] = {1u, 1u, 1u};
+  CUresult r = enc(out, type, rank, const_cast<void*>(base), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r == CUDA_SUCCESS) {
+    slot.used = true;
+    slot.key = k;
+    slot.map = *out;
+  }
+  return (int)r;
 }
 }  // namespace tcx
 

@@ -111,5 +111,10 @@ typedef CUresult (*pfn_encode)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, vo
                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 // cuTensorMapEncodeTiled resolved through the runtime (no link against libcuda); NULL + error text when unavailable
 pfn_encode b2_tensor_map_encoder();
+// The same encode, memoised: a tensor map is a pure function of (type, base address, dims, strides, box, swizzle), and a
+// training loop asks for the same few maps every step (its buffers live as long as the context), so they are encoded once
+// per shape instead of once per launch.  Interleave NONE, element strides 1, L2 promotion 256 B, zero fill.  CUresult.
+int b2_tensor_map_cached(CUtensorMap* out, CUtensorMapDataType type, unsigned rank, const void* base, const cuuint64_t* gdim,
+                         const cuuint64_t* gstr, const cuuint32_t* box, CUtensorMapSwizzle swizzle);
 
 }  // namespace tcx
