@@ -4,7 +4,8 @@
 // for 27 500 steps (distributed.py:46-48,141-150).  At that size a step is a few microseconds of arithmetic; run as
 // one launch sequence per step it costs 45-50 us, nearly all of it launch and grid-level synchronisation latency.
 // Here the loop runs inside one kernel on a cluster of 14 CTAs (14 SMs), which synchronise with the hardware cluster
-// barrier and exchange data through distributed shared memory instead of global memory:
+// barrier and exchange their per-step data through a small L2-resident scratch buffer (why not through distributed shared
+// memory: see below):
 //
 //   CTA j owns inputs [56j, 56j+56) of the first layer for good: its slice of W1 lives in its shared memory for the whole
 //   call and is updated there (nothing of W1 moves between steps), and it streams only its 56 columns of x.

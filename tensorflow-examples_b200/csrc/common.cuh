@@ -272,8 +272,9 @@ int b2_launch_fused_linear_multistep(const float* x_pool, const float* y_pool, l
                                      long rank_off, int rows, int n_steps, float* params, float* grads, float* scratch,
                                      unsigned* bar, int grid, float lr, int loss, float* loss_trace, int* correct_trace,
                                      float* global_step, long P, const b2_fx_args* fx, cudaStream_t s);
-// cluster_steps.cu: small batches of the 784-wide models (784 -> 10 up to 256 rows, 784-100-10 up to 100 rows) on one
-// cluster of 14 CTAs: W1 sliced over the CTAs' shared memory, exchanges through distributed shared memory
+// cluster_steps.cu: small batches of the 784-wide models (784 -> 10 up to 128 rows, 784-100-10 up to 200 rows) on one
+// cluster of 14 CTAs: W1 sliced over the CTAs' shared memory, the per-step exchanges through an L2-resident scratch
+// buffer between two cluster barriers
 bool b2_cluster_steps_applies(int n_layers, const int* dims, int rows);
 int b2_launch_cluster_steps(int n_layers, int act, int loss, const long* w_off, const long* b_off, long P, const float* x_pool,
                             const float* y_pool, long span, long first_row, long global_batch, int rows, int n_steps, float lr,
